@@ -1,0 +1,729 @@
+"""Host-side mirror of the reference's operator interface over the C-ABI (no compute here).
+
+Reference surface mirrored (file:line in gher-uliege/DINCAE.jl):
+  interpnd / interp_adjn                     src/points.jl:29-34, :73-77
+  NCData + getxy! + DataBatches              src/data.jl:250-369, :391-517, :771-868
+  genmodel / StepModel / loss_function       src/model.jl:286-363, :151-222
+  train_init / train_epoch!                  src/flux.jl:7-40
+  reconstruct / reconstruct_points           src/model.jl:446-679, src/points.jl:509-696
+Arrays are numpy, indexed like Julia ([i,j,...] = [lon,lat,...]) and Fortran-ordered, so the
+pointer handed to the library is the memory a Julia caller would hand over.
+"""
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import lib as L
+
+
+def _f32(a, order="F"):
+    return np.asarray(a, dtype=np.float32, order=order)
+
+
+class Context:
+    """One GPU (replaces `_to_device(Atype)`, src/flux.jl:47-49)."""
+
+    def __init__(self, device: int = 0, torch_stream=None):
+        self._lib = L.load()
+        h = C.c_void_p()
+        L.check(self._lib.dincae_ctx_create(device, C.byref(h)))
+        self.handle = h
+        self.device = device
+        self._stream = None
+        if torch_stream is not None:
+            self.set_stream(torch_stream)
+
+    def set_stream(self, torch_stream):
+        """Run on a torch.cuda.Stream so torch events / NCCL collectives order with the kernels."""
+        self._stream = torch_stream
+        L.check(self._lib.dincae_ctx_set_stream(self.handle, C.c_void_p(torch_stream.cuda_stream)))
+
+    def sync(self):
+        L.check(self._lib.dincae_sync(self.handle))
+
+    @property
+    def launches(self) -> int:
+        return int(self._lib.dincae_launch_count(self.handle))
+
+    def close(self):
+        if self.handle:
+            self._lib.dincae_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default_ctx = None
+
+
+def default_context() -> Context:
+    global _default_ctx
+    if _default_ctx is None:
+        _default_ctx = Context(0)
+    return _default_ctx
+
+
+# ---- K4 ------------------------------------------------------------------------------------
+def interpnd(pos, A, ctx: Optional[Context] = None):
+    """interpnd(pos, A) (src/points.jl:29-34): pos (P,2) 1-based, A (W,H) -> (P,)"""
+    ctx = ctx or default_context()
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 2)
+    A = _f32(A)
+    out = np.zeros(len(pos), np.float32)
+    L.check(ctx._lib.dincae_interp(ctx.handle, L.ptr(pos), len(pos), L.ptr(A), A.shape[0], A.shape[1], L.ptr(out), L.HOST))
+    return out
+
+
+def interp_adjn(pos, values, sz, ctx: Optional[Context] = None):
+    """interp_adjn(pos, values, sz) (src/points.jl:73-77) -> (W,H)"""
+    ctx = ctx or default_context()
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 2)
+    values = np.ascontiguousarray(values, np.float32)
+    if len(values) != len(pos):
+        raise ValueError("interp_adjn: %d positions but %d values" % (len(pos), len(values)))
+    out = np.zeros(sz, np.float32, order="F")
+    L.check(ctx._lib.dincae_interp_adjoint(ctx.handle, L.ptr(pos), L.ptr(values), len(pos), sz[0], sz[1], L.ptr(out), L.HOST))
+    return out
+
+
+def interp_cells(pos, ctx: Optional[Context] = None):
+    ctx = ctx or default_context()
+    pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 2)
+    out = np.zeros((len(pos), 2), np.int32)
+    L.check(ctx._lib.dincae_interp_cells(ctx.handle, L.ptr(pos), len(pos), L.ptr(out), L.HOST))
+    return out
+
+
+def posindices(grid, lon, lat, ctx: Optional[Context] = None):
+    """posindices! for one time step (src/points.jl:98-134): returns (pos (P,2), inside (P,) bool)."""
+    ctx = ctx or default_context()
+    lon = np.ascontiguousarray(lon, np.float32); lat = np.ascontiguousarray(lat, np.float32)
+    P = len(lon)
+    pos = np.zeros((P, 2), np.float32); inside = np.zeros(P, np.uint8)
+    gx, gy = np.asarray(grid[0], np.float64), np.asarray(grid[1], np.float64)
+    L.check(ctx._lib.dincae_posindices(ctx.handle, L.ptr(lon), L.ptr(lat), P, gx[0], gx[-1], len(gx), gy[0], gy[-1], len(gy),
+                                       L.ptr(pos), L.ptr(inside), L.HOST))
+    return pos, inside.astype(bool)
+
+
+# ---- model ------------------------------------------------------------------------------------
+@dataclass
+class ModelConfig:
+    """Keyword surface of genmodel / reconstruct that shapes the model (src/model.jl:286-299)."""
+    W: int
+    H: int
+    ninput: int
+    noutput: int = 1
+    enc_nfilter_internal: Sequence[int] = (16, 24, 36, 54)
+    skipconnections: Optional[Sequence[int]] = None           # 1-based levels, default 2:(L+1)
+    upsampling_method: str = "nearest"
+    loss_weights_refine: Tuple[float, ...] = (1.0,)
+    min_std_err: float = 0.006737946999085467
+    truth_uncertain: bool = False
+    regularization_L1_beta: float = 0.0
+    regularization_L2_beta: float = 0.0
+    laplacian_penalty: float = 0.0
+    laplacian_error_penalty: Optional[float] = None
+    clip_grad: Optional[float] = 5.0
+    adam_beta: Tuple[float, float] = (0.9, 0.999)
+    adam_eps: float = 1e-8
+    leaky_slope: float = 0.0
+    precision: str = "tf32"
+    max_batch: int = 50
+
+    def to_struct(self) -> L.Config:
+        nf = list(self.enc_nfilter_internal)
+        nl = len(nf)
+        if nl > L.MAX_LEVELS:
+            raise ValueError("at most %d levels" % L.MAX_LEVELS)
+        if len(self.loss_weights_refine) > L.MAX_CHAINS:
+            raise ValueError("at most %d refinement chains" % L.MAX_CHAINS)
+        skips = range(2, nl + 2) if self.skipconnections is None else self.skipconnections
+        mask = 0
+        for s in skips:
+            if 1 <= s <= nl:            # level L+1 is the identity (src/model.jl:263-264): no effect
+                mask |= 1 << (s - 1)
+        if self.upsampling_method not in ("nearest", "bilinear"):
+            raise ValueError("upsampling_method must be :nearest or :bilinear")
+        c = L.Config()
+        c.W, c.H, c.ninput, c.noutput, c.nlevels = self.W, self.H, self.ninput, self.noutput, nl
+        for i, f in enumerate(nf):
+            c.nfilter[i] = int(f)
+        c.skip_mask = mask
+        c.upsampling = L.UP_NEAREST if self.upsampling_method == "nearest" else L.UP_BILINEAR
+        c.nchains = len(self.loss_weights_refine)
+        for i, w in enumerate(self.loss_weights_refine):
+            c.loss_weights[i] = float(w)
+        c.gamma = math.log(self.min_std_err ** (-2))                 # src/model.jl:318
+        c.truth_uncertain = int(bool(self.truth_uncertain))
+        c.l1_beta = float(self.regularization_L1_beta)
+        c.l2_beta = float(self.regularization_L2_beta)
+        c.laplacian_penalty = float(self.laplacian_penalty)
+        lep = self.laplacian_penalty if self.laplacian_error_penalty is None else self.laplacian_error_penalty
+        c.laplacian_error_penalty = float(lep)
+        c.clip_grad = float(self.clip_grad) if self.clip_grad is not None else 0.0
+        c.adam_beta1, c.adam_beta2, c.adam_eps = self.adam_beta[0], self.adam_beta[1], self.adam_eps
+        c.leaky_slope = float(self.leaky_slope)
+        c.precision = {"fp32": L.PREC_FP32, "tf32": L.PREC_TF32}[self.precision]
+        c.max_batch = int(self.max_batch)
+        return c
+
+
+class Model:
+    """genmodel(...) |> device + train_init (src/model.jl:546-559, src/flux.jl:7-21)."""
+
+    def __init__(self, ctx: Context, cfg: ModelConfig, seed: Optional[int] = 0):
+        self.ctx, self.cfg, self._lib = ctx, cfg, ctx._lib
+        self._cstruct = cfg.to_struct()
+        h = C.c_void_p()
+        L.check(self._lib.dincae_model_create(ctx.handle, C.byref(self._cstruct), C.byref(h)))
+        self.handle = h
+        n = C.c_int64()
+        L.check(self._lib.dincae_model_num_params(h, C.byref(n)))
+        self.num_params = n.value
+        if seed is not None:
+            L.check(self._lib.dincae_model_init_glorot(h, seed))
+
+    # -- parameters in Flux.trainables order
+    def get_params(self):
+        out = np.zeros(self.num_params, np.float32)
+        L.check(self._lib.dincae_model_get_params(self.handle, L.ptr(out), out.size))
+        return out
+
+    def set_params(self, flat):
+        flat = np.ascontiguousarray(flat, np.float32)
+        L.check(self._lib.dincae_model_set_params(self.handle, L.ptr(flat), flat.size))
+
+    def get_opt_state(self):
+        m = np.zeros(self.num_params, np.float32); v = np.zeros_like(m); t = C.c_int64()
+        L.check(self._lib.dincae_model_get_opt_state(self.handle, L.ptr(m), L.ptr(v), m.size, C.byref(t)))
+        return m, v, t.value
+
+    def set_opt_state(self, m, v, t):
+        m = np.ascontiguousarray(m, np.float32); v = np.ascontiguousarray(v, np.float32)
+        L.check(self._lib.dincae_model_set_opt_state(self.handle, L.ptr(m), L.ptr(v), m.size, int(t)))
+
+    # -- calls; x may be numpy (host) or an int / torch tensor (device)
+    @staticmethod
+    def _loc(a):
+        return L.HOST if isinstance(a, np.ndarray) else L.DEVICE
+
+    def _batch(self, xin, B):
+        if isinstance(xin, np.ndarray):
+            xin = _f32(xin)
+            return xin, xin.shape[3]
+        if B is None:
+            raise ValueError("B is required with device pointers")
+        return xin, B
+
+    def __call__(self, xin, B=None, out=None):
+        """model(xin) -> (W,H,2*noutput,B) = (mean, sigma^2) (src/model.jl:182-189)."""
+        xin, B = self._batch(xin, B)
+        loc = self._loc(xin)
+        if out is None:
+            if loc != L.HOST:
+                raise ValueError("pass `out` (device) with device inputs")
+            out = np.zeros((self.cfg.W, self.cfg.H, 2 * self.cfg.noutput, B), np.float32, order="F")
+        L.check(self._lib.dincae_forward(self.handle, L.ptr(xin), B, L.ptr(out), loc))
+        return out
+
+    def loss(self, xin, xtrue, B=None):
+        xin, B = self._batch(xin, B)
+        if isinstance(xtrue, np.ndarray):
+            xtrue = _f32(xtrue)
+        out = C.c_double()
+        L.check(self._lib.dincae_loss(self.handle, L.ptr(xin), L.ptr(xtrue), B, self._loc(xin), C.byref(out)))
+        return out.value
+
+    def train_step(self, xin, xtrue, lr, B=None, want_loss=True):
+        xin, B = self._batch(xin, B)
+        if isinstance(xtrue, np.ndarray):
+            xtrue = _f32(xtrue)
+        out = C.c_float()
+        L.check(self._lib.dincae_train_step(self.handle, L.ptr(xin), L.ptr(xtrue), B, lr, self._loc(xin),
+                                            C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
+
+    def grad_step(self, xin, xtrue, B=None, n_valid_global=None):
+        xin, B = self._batch(xin, B)
+        if isinstance(xtrue, np.ndarray):
+            xtrue = _f32(xtrue)
+        nv = None if n_valid_global is None else np.ascontiguousarray(n_valid_global, np.int64)
+        L.check(self._lib.dincae_grad_step(self.handle, L.ptr(xin), L.ptr(xtrue), B, L.ptr(nv), self._loc(xin)))
+
+    def grad_buffer(self):
+        p = C.c_void_p(); n = C.c_int64()
+        L.check(self._lib.dincae_grad_buffer(self.handle, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def grad_tensor(self):
+        """Zero-copy torch view of the flat gradient buffer (for torch.distributed.all_reduce)."""
+        import torch
+        p, n = self.grad_buffer()
+
+        class _View:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (p, False), "version": 2}
+        return torch.as_tensor(_View(), device=torch.device("cuda", self.ctx.device))
+
+    def apply_step(self, lr, want_loss=True):
+        out = C.c_float()
+        L.check(self._lib.dincae_apply_step(self.handle, lr, C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
+
+    def count_valid(self, xtrue, B=None):
+        if isinstance(xtrue, np.ndarray):
+            xtrue = _f32(xtrue); B = xtrue.shape[3]
+        out = np.zeros(self.cfg.noutput, np.int64)
+        L.check(self._lib.dincae_count_valid(self.handle, L.ptr(xtrue), B, self._loc(xtrue), L.ptr(out)))
+        return out
+
+    # -- point-cloud truth: list of (pos (P,2), x (P,2)) per sample (src/points.jl:310)
+    @staticmethod
+    def _pack_points(point_truth):
+        offs = np.zeros(len(point_truth) + 1, np.int64)
+        for b, (p, _) in enumerate(point_truth):
+            offs[b + 1] = offs[b] + len(p)
+        pos = np.concatenate([np.asarray(p, np.float32).reshape(-1, 2) for p, _ in point_truth]) if offs[-1] else np.zeros((0, 2), np.float32)
+        x = np.concatenate([np.asarray(xx, np.float32).reshape(-1, 2) for _, xx in point_truth]) if offs[-1] else np.zeros((0, 2), np.float32)
+        return np.ascontiguousarray(pos), np.asfortranarray(x), offs
+
+    def loss_points(self, xin, point_truth):
+        xin, B = self._batch(xin, None)
+        pos, x, offs = self._pack_points(point_truth)
+        out = C.c_double()
+        L.check(self._lib.dincae_loss_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, L.HOST, C.byref(out)))
+        return out.value
+
+    def train_step_points(self, xin, point_truth, lr):
+        xin, B = self._batch(xin, None)
+        pos, x, offs = self._pack_points(point_truth)
+        out = C.c_float()
+        L.check(self._lib.dincae_train_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, lr, L.HOST, C.byref(out)))
+        return out.value
+
+    def grad_step_points(self, xin, point_truth, n_valid_global=-1):
+        xin, B = self._batch(xin, None)
+        pos, x, offs = self._pack_points(point_truth)
+        L.check(self._lib.dincae_grad_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, int(n_valid_global), L.HOST))
+
+    def close(self):
+        if self.handle:
+            self._lib.dincae_model_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---- gridded data -------------------------------------------------------------------------------
+def time_cos_sin(days_since_1970, cycle_period=365.25):
+    """time_cos/time_sin of NCData (src/data.jl:289-297): the reference's `t` is in HOURS."""
+    t = np.asarray(days_since_1970, np.float64) * 24.0
+    return (np.cos(2 * np.pi * t / cycle_period).astype(np.float32), np.sin(2 * np.pi * t / cycle_period).astype(np.float32))
+
+
+def scale_pm1(v):
+    v = np.asarray(v, np.float64)
+    return (2 * (v - v.min()) / (v.max() - v.min()) - 1).astype(np.float32)      # src/data.jl:342-343
+
+
+class GriddedDataset:
+    """NCData (src/data.jl:148-170, ctor :250-369) resident on the device."""
+
+    def __init__(self, ctx: Context, lon, lat, days, data_full, train=False, obs_err_std=None, jitter_std=None,
+                 ntime_win=3, isoutput=None, remove_mean=True, mean_data=None, mask=None, cycle_periods=(365.25,)):
+        if len(cycle_periods) != 1:
+            raise NotImplementedError("exactly one cycle period is supported (4 meta channels, src/data.jl:199)")
+        self.ctx, self._lib = ctx, ctx._lib
+        data_full = np.asfortranarray(data_full, np.float32)
+        if data_full.ndim != 4:
+            raise ValueError("data_full must be (W,H,V,N)")
+        W, H, V, N = data_full.shape
+        self.shape = (W, H, V, N)
+        self.train, self.ntime_win = train, ntime_win
+        self.isoutput = (np.arange(V) == 0) if isoutput is None else np.asarray(isoutput, bool)
+        self.noutput = int(self.isoutput.sum())
+        oes = np.ones(V, np.float32) if obs_err_std is None else np.ascontiguousarray(obs_err_std, np.float32)
+        js = np.full(V, 0.05, np.float32) if jitter_std is None else np.ascontiguousarray(jitter_std, np.float32)
+        iso = np.ascontiguousarray(self.isoutput, np.uint8)
+        tc, ts = time_cos_sin(days, cycle_periods[0])
+        lm = None if mask is None else np.asfortranarray(mask, np.uint8)
+        md = None if mean_data is None else _f32(mean_data)
+        self.lon_scaled, self.lat_scaled = scale_pm1(lon), scale_pm1(lat)
+        h = C.c_void_p()
+        L.check(self._lib.dincae_gridded_create(ctx.handle, L.ptr(data_full), W, H, V, N, L.ptr(oes), L.ptr(js), L.ptr(iso),
+                                                int(remove_mean), L.ptr(md), L.ptr(lm), L.ptr(self.lon_scaled), L.ptr(self.lat_scaled),
+                                                L.ptr(tc), L.ptr(ts), ntime_win, L.HOST, C.byref(h)))
+        self.handle = h
+        self.mask = mask
+
+    def __len__(self):
+        return self.shape[3]
+
+    def sizex(self):
+        W, H, V, N = self.shape
+        return (W, H, 4 + 2 * V * self.ntime_win)
+
+    def sizey(self):
+        W, H, V, N = self.shape
+        return (W, H, 2 * self.noutput)
+
+    @property
+    def meandata(self):
+        W, H, V, N = self.shape
+        out = np.zeros((W, H, V), np.float32, order="F")
+        L.check(self._lib.dincae_gridded_get_mean(self.handle, L.ptr(out)))
+        return out
+
+    def valid_counts(self, v=0):
+        out = np.zeros(self.shape[3], np.int64)
+        L.check(self._lib.dincae_gridded_valid_counts(self.handle, v, L.ptr(out)))
+        return out
+
+    def assemble(self, time_idx, imask=None, seed=0, sample_ctr0=0, xin=None, xtrue=None):
+        """One mini-batch (getxy! for every sample of DataBatches.iterate); host arrays unless device buffers are given."""
+        time_idx = np.ascontiguousarray(time_idx, np.int64)
+        B = len(time_idx)
+        im = None if imask is None else np.ascontiguousarray(imask, np.int64)
+        if xin is None:
+            xin = np.zeros(self.sizex() + (B,), np.float32, order="F")
+            xtrue = np.zeros(self.sizey() + (B,), np.float32, order="F")
+            loc = L.HOST
+        else:
+            loc = L.DEVICE
+        L.check(self._lib.dincae_gridded_assemble(self.handle, L.ptr(time_idx), L.ptr(im), seed, sample_ctr0, B, L.ptr(xin), L.ptr(xtrue), loc))
+        return xin, xtrue
+
+    def close(self):
+        if self.handle:
+            self._lib.dincae_gridded_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class DataBatches:
+    """DataBatches (src/data.jl:771-868): mini-batches in `perm` order, partial last batch kept.
+
+    The integer draws (perm, imask) come from a host numpy Generator; the float jitter comes from the
+    library's Philox stream keyed by (seed, global sample counter)."""
+
+    def __init__(self, ds: GriddedDataset, batch_size, rng: Optional[np.random.Generator] = None, seed=0,
+                 device_buffers=None, rank=0, world_size=1):
+        self.ds, self.batch_size = ds, batch_size
+        self.rng = rng or np.random.default_rng(seed)
+        self.seed = seed
+        self.shuffle = ds.train
+        n = len(ds)
+        self.perm = self.rng.permutation(n) if self.shuffle else np.arange(n)
+        self.device_buffers = device_buffers
+        self.rank, self.world_size = rank, world_size
+        self.sample_ctr = 0
+
+    def __len__(self):
+        return -(-len(self.ds) // self.batch_size)        # partial = true (src/data.jl:803)
+
+    def shuffle_(self):                                   # Random.shuffle!(d), src/data.jl:796-799
+        if self.shuffle:
+            self.perm = self.rng.permutation(len(self.ds))
+
+    def batches(self):
+        """Yield (time_idx, imask, sample_ctr0) of every mini-batch: the integer work of one epoch."""
+        n = len(self.ds)
+        for start in range(0, n, self.batch_size):
+            idx = self.perm[start:start + self.batch_size]
+            imask = self.rng.integers(0, n, size=len(idx)) if self.ds.train else None      # rand(1:ntime), src/data.jl:471
+            ctr = self.sample_ctr
+            self.sample_ctr += len(idx)
+            yield idx, imask, ctr
+
+    def shard(self, idx, imask):
+        """This rank's contiguous share of a mini-batch (data-parallel training)."""
+        if self.world_size == 1:
+            return idx, imask, 0
+        per = -(-len(idx) // self.world_size)
+        lo, hi = min(self.rank * per, len(idx)), min((self.rank + 1) * per, len(idx))
+        return idx[lo:hi], (None if imask is None else imask[lo:hi]), lo
+
+    def __iter__(self):
+        for idx, imask, ctr in self.batches():
+            if self.device_buffers is None:
+                yield self.ds.assemble(idx, imask, self.seed, ctr) + (len(idx),)
+            else:
+                xin, xtrue = self.device_buffers
+                self.ds.assemble(idx, imask, self.seed, ctr, xin, xtrue)
+                yield xin, xtrue, len(idx)
+
+
+def learning_rate(lr0, epoch, decay_epoch):
+    """lr of epoch e (1-based), src/model.jl:590."""
+    return lr0 * 0.5 ** (epoch / decay_epoch)
+
+
+def train_epoch(model: Model, batches, lr):
+    """train_epoch! (src/flux.jl:24-40): mean of the per-batch losses, partial batch included (T17)."""
+    loss_sum, n = 0.0, 0
+    for xin, xtrue, B in batches:
+        loss_sum += model.train_step(xin, xtrue, lr, B=B)
+        n += 1
+    return loss_sum / n
+
+
+def reconstruct_range(model: Model, ds: GriddedDataset, t0, t1, count=1, fill_value=-9999.0, m_out=None, sigma_out=None):
+    """Save loop of reconstruct (src/model.jl:624-644) + savesample arithmetic (src/data.jl:615-675) for steps [t0,t1)."""
+    W, H, V, N = ds.shape
+    if m_out is None:
+        m_out = np.zeros((W, H, t1 - t0, ds.noutput), np.float32, order="F")
+        sigma_out = np.zeros_like(m_out, order="F")
+    loc = L.HOST if isinstance(m_out, np.ndarray) else L.DEVICE
+    L.check(model._lib.dincae_reconstruct_range(model.handle, ds.handle, int(t0), int(t1), int(count), float(fill_value),
+                                                L.ptr(m_out), L.ptr(sigma_out), loc))
+    return m_out, sigma_out
+
+
+def _device_batch_buffers(ds, batch_size):
+    import torch
+    dev = torch.device("cuda", ds.ctx.device)
+    W, H, C_ = ds.sizex()
+    xin = torch.empty(batch_size * C_ * H * W, dtype=torch.float32, device=dev)
+    xtrue = torch.empty(batch_size * 2 * ds.noutput * H * W, dtype=torch.float32, device=dev)
+    return xin, xtrue
+
+
+def reconstruct(ctx, data_all, fnames_rec=None, *,
+                epochs=1000, batch_size=50, truth_uncertain=False, enc_nfilter_internal=(16, 24, 36, 54),
+                skipconnections=None, clip_grad=5.0, regularization_L1_beta=0, regularization_L2_beta=0,
+                save_epochs=None, is3D=False, upsampling_method="nearest", ntime_win=3, learning_rate=0.001,
+                learning_rate_decay_epoch=math.inf, min_std_err=0.006737946999085467, loss_weights_refine=(1.0,),
+                cycle_periods=(365.25,), output_ndims=1, direction_obs=None, remove_mean=True, paramfile=None,
+                laplacian_penalty=0, laplacian_error_penalty=None, modeldir=None,
+                seed=0, precision="tf32", init_params=None, progress=None):
+    """DINCAE.reconstruct (src/model.jl:446-679) with its keyword surface kept verbatim.
+
+    `ctx` takes the place of `Atype`.  File I/O is out of scope: every entry of `data_all`
+    is a list of dicts with in-memory fields {lon, lat, time (days since 1970), data (W,H,N) with NaN,
+    mask (W,H) optional, obs_err_std, jitter_std, isoutput}; data_all[0] trains, data_all[1:] are
+    reconstructed at save_epochs.  Returns (losses, results) where results[k] = dict(mean, sigma, count)
+    holds what savesample would have written to fnames_rec[k]; if fnames_rec is given they are saved as .npz.
+    """
+    if save_epochs is None:
+        save_epochs = range(min(epochs, 200), epochs + 1, 10)
+    save_epochs = list(save_epochs)
+    if len(save_epochs) == 0 or epochs < min(save_epochs):
+        raise ValueError("No output will be saved. Consider to adjust save_epochs (currently %s) or epochs (currently %d)."
+                         % (save_epochs, epochs))                     # src/model.jl:475-477
+    if is3D or output_ndims != 1 or direction_obs is not None:
+        raise L.DincaeError(L.EUNSUPPORTED, "is3D=true / output_ndims=2 / direction_obs are outside the hot path (SURVEY section 8f N4)")
+
+    def make(dlist, train, mean_data=None):
+        d0 = dlist[0]
+        data = np.stack([np.asarray(d["data"], np.float32) for d in dlist], axis=2)      # (W,H,V,N)
+        return GriddedDataset(ctx, d0["lon"], d0["lat"], d0["time"], data, train=train,
+                              obs_err_std=[d.get("obs_err_std", 1.0) for d in dlist],
+                              jitter_std=[d.get("jitter_std", 0.05) for d in dlist],
+                              ntime_win=ntime_win, isoutput=[d.get("isoutput", i == 0) for i, d in enumerate(dlist)],
+                              remove_mean=remove_mean, mean_data=mean_data, mask=d0.get("mask"), cycle_periods=cycle_periods)
+
+    train_data = make(data_all[0], True)
+    train_mean = train_data.meandata
+    tests = [make(d, False, train_mean) for d in data_all[1:]]         # use common mean, src/model.jl:503-504
+    W, H, Cin = train_data.sizex()
+    cfg = ModelConfig(W=W, H=H, ninput=Cin, noutput=train_data.noutput, enc_nfilter_internal=tuple(enc_nfilter_internal),
+                      skipconnections=skipconnections, upsampling_method=str(upsampling_method).lstrip(":"),
+                      loss_weights_refine=tuple(loss_weights_refine), min_std_err=min_std_err, truth_uncertain=truth_uncertain,
+                      regularization_L1_beta=regularization_L1_beta, regularization_L2_beta=regularization_L2_beta,
+                      laplacian_penalty=laplacian_penalty, laplacian_error_penalty=laplacian_error_penalty,
+                      clip_grad=clip_grad, precision=precision, max_batch=batch_size)
+    model = Model(ctx, cfg, seed=seed)
+    if init_params is not None:
+        model.set_params(init_params)
+    bufs = _device_batch_buffers(train_data, batch_size)
+    train = DataBatches(train_data, batch_size, seed=seed, device_buffers=bufs)
+    losses = []
+    results = [dict(mean=None, sigma=None, count=0) for _ in tests]
+    for e in range(1, epochs + 1):
+        lr = learning_rate * 0.5 ** (e / learning_rate_decay_epoch)    # src/model.jl:590
+        losses.append(train_epoch(model, train, lr))
+        if progress:
+            progress("epoch: %5d loss %5.4f" % (e, losses[-1]))        # src/model.jl:596
+        if e in save_epochs:
+            for ds_, res in zip(tests, results):
+                res["count"] += 1                                      # ds.attrib["count"] += 1, src/data.jl:621-623
+                res["mean"], res["sigma"] = reconstruct_range(model, ds_, 0, len(ds_), res["count"], -9999.0, res["mean"], res["sigma"])
+        train.shuffle_()                                               # src/model.jl:650
+    if fnames_rec is not None:
+        for fn, res in zip(fnames_rec, results):
+            np.savez(fn, **{k: v for k, v in res.items() if v is not None})
+    if paramfile is not None:
+        np.savez(paramfile, losses=np.asarray(losses), epochs=epochs, batch_size=batch_size)
+    reconstruct.last_model = model
+    return losses, results
+
+
+# ---- point clouds ---------------------------------------------------------------------------------
+class PointDataset:
+    """PointCloud (src/points.jl:137-227) on the device; construction filters with posindices!."""
+
+    def __init__(self, ctx: Context, grid, lon, lat, values, ids, dayofyear, ntime_win=9, probability_skip_for_training=0.2,
+                 jitter_std_pos=(5.0, 5.0), auxdata=None, train=True):
+        self.ctx, self._lib = ctx, ctx._lib
+        self.grid = grid
+        self.sz = (len(grid[0]), len(grid[1]))
+        N = len(values)
+        self.pos, self.x, self.id = [], [], []
+        for n in range(N):
+            p, inside = posindices(grid, lon[n], lat[n], ctx)
+            v = np.asarray(values[n], np.float32)[inside]
+            xx = np.zeros((len(v), 2), np.float32)
+            xx[:, 0] = np.where(np.isnan(v), 0, v)              # src/points.jl:188
+            xx[:, 1] = 1 - np.isnan(v).astype(np.float32)       # src/points.jl:189
+            self.pos.append(p[inside]); self.x.append(xx); self.id.append(np.asarray(ids[n], np.int64)[inside])
+        self.offsets = np.zeros(N + 1, np.int64)
+        self.offsets[1:] = np.cumsum([len(p) for p in self.pos])
+        pos_all = np.ascontiguousarray(np.concatenate(self.pos)) if self.offsets[-1] else np.zeros((0, 2), np.float32)
+        x_all = np.asfortranarray(np.concatenate(self.x)) if self.offsets[-1] else np.zeros((0, 2), np.float32, order="F")
+        self.ntime_win, self.train, self.pskip = ntime_win, train, probability_skip_for_training
+        d = np.asarray(dayofyear, np.float64)
+        dcos = np.cos(2 * np.pi * d / 365.25).astype(np.float32)          # src/points.jl:199-202
+        dsin = np.sin(2 * np.pi * d / 365.25).astype(np.float32)
+        W, H = self.sz
+        self.naux = 0 if auxdata is None else auxdata.shape[2]
+        aux = None if auxdata is None else _f32(auxdata)
+        lon_s, lat_s = scale_pm1(grid[0]), scale_pm1(grid[1])             # src/points.jl:195-196
+        h = C.c_void_p()
+        L.check(self._lib.dincae_points_create(ctx.handle, W, H, N, L.ptr(pos_all), L.ptr(x_all), L.ptr(self.offsets), L.ptr(aux), self.naux,
+                                               L.ptr(lon_s), L.ptr(lat_s), L.ptr(dcos), L.ptr(dsin), ntime_win,
+                                               float(jitter_std_pos[0]), float(jitter_std_pos[1]), C.byref(h)))
+        self.handle = h
+
+    def __len__(self):
+        return len(self.pos)
+
+    def sizex(self):
+        return (self.sz[0], self.sz[1], 4 + 2 * self.ntime_win + self.naux)       # src/points.jl:345-352
+
+    def draw_track_keep(self, ind, rng):
+        """Track dropout of the centre step (src/points.jl:284-300): integer work drawn on the host."""
+        ids = self.id[ind]
+        sel = np.ones(len(ids), bool)
+        uniq = list(dict.fromkeys(ids.tolist()))                                   # unique(d.id[ind]) keeps first-seen order
+        for uid in uniq:
+            if rng.random() < self.pskip:
+                sel[ids == uid] = False
+        if sel.sum() == 0 and len(uniq) > 0:
+            sel[ids == uniq[rng.integers(0, len(uniq))]] = True                    # at least one track
+        return sel
+
+    def assemble(self, time_idx, seed=0, sample_ctr0=0, keep=None, perturb=None):
+        time_idx = np.ascontiguousarray(time_idx, np.int64)
+        B = len(time_idx)
+        perturb = self.train if perturb is None else perturb
+        kp = ko = None
+        if keep is not None:
+            ko = np.zeros(B + 1, np.int64)
+            ko[1:] = np.cumsum([len(k) for k in keep])
+            kp = np.ascontiguousarray(np.concatenate(keep) if ko[-1] else np.zeros(0), np.uint8)
+        xin = np.zeros(self.sizex() + (B,), np.float32, order="F")
+        L.check(self._lib.dincae_points_assemble(self.handle, L.ptr(time_idx), B, int(perturb), seed, sample_ctr0,
+                                                 L.ptr(kp), L.ptr(ko), L.ptr(xin), L.HOST))
+        truth = [(self.pos[i], self.x[i]) for i in time_idx]                       # xtrue = (pos[ind], x[ind]), src/points.jl:310
+        return xin, truth
+
+    def close(self):
+        if self.handle:
+            self._lib.dincae_points_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def reconstruct_points(ctx, data, grid, fnames_rec=None, *,
+                       epochs=60, batch_size=32, truth_uncertain=False, enc_nfilter_internal=(10, 20, 30, 40, 50),
+                       skipconnections=None, clip_grad=5.0, regularization_L1_beta=0, regularization_L2_beta=0,
+                       save_epochs=None, upsampling_method="nearest", probability_skip_for_training=0.2,
+                       jitter_std_pos=(5.0, 5.0), ntime_win=9, learning_rate=0.001, learning_rate_decay_epoch=math.inf,
+                       min_std_err=0.006737946999085467, loss_weights_refine=(1.0,), auxdata=None, paramfile=None,
+                       savesnapshot=False, laplacian_penalty=0, laplacian_error_penalty=None,
+                       seed=0, precision="tf32", init_params=None, progress=None):
+    """DINCAE.reconstruct_points (src/points.jl:509-696), keyword surface verbatim.
+
+    `data` = dict(lon, lat, values, id: lists of per-time-step vectors; dayofyear: (N,)) replaces the ragged
+    NetCDF file; `auxdata` (W,H,2*naux,N) replaces auxdata_files (already normalised)."""
+    if save_epochs is None:
+        save_epochs = range(min(epochs, 60), epochs + 1, 10)
+    save_epochs = list(save_epochs)
+    if len(save_epochs) == 0 or epochs < min(save_epochs):
+        raise ValueError("No output will be saved. Consider to adjust save_epochs (currently %s) or epochs (currently %d)."
+                         % (save_epochs, epochs))                     # src/points.jl:535-537
+    kw = dict(ntime_win=ntime_win, probability_skip_for_training=probability_skip_for_training,
+              jitter_std_pos=jitter_std_pos, auxdata=auxdata)
+    train = PointDataset(ctx, grid, data["lon"], data["lat"], data["values"], data["id"], data["dayofyear"], train=True, **kw)
+    test = PointDataset(ctx, grid, data["lon"], data["lat"], data["values"], data["id"], data["dayofyear"], train=False, **kw)
+    W, H, nvar = train.sizex()
+    cfg = ModelConfig(W=W, H=H, ninput=nvar, noutput=1, enc_nfilter_internal=tuple(enc_nfilter_internal),
+                      skipconnections=skipconnections, upsampling_method=str(upsampling_method).lstrip(":"),
+                      loss_weights_refine=tuple(loss_weights_refine), min_std_err=min_std_err, truth_uncertain=truth_uncertain,
+                      regularization_L1_beta=regularization_L1_beta, regularization_L2_beta=regularization_L2_beta,
+                      laplacian_penalty=laplacian_penalty, laplacian_error_penalty=laplacian_error_penalty,
+                      clip_grad=clip_grad, precision=precision, max_batch=batch_size)
+    model = Model(ctx, cfg, seed=seed)
+    if init_params is not None:
+        model.set_params(init_params)
+    rng = np.random.default_rng(seed)
+    N = len(train)
+    perm = rng.permutation(N)                                          # randperm(ntime), src/points.jl:204-209 (never reshuffled)
+    losses = []
+    result = dict(mean=None, sigma=None, count=0)
+    ctr = 0
+    for e in range(1, epochs + 1):
+        lr = learning_rate * 0.5 ** (e / learning_rate_decay_epoch)    # src/points.jl:622
+        s, nb = 0.0, 0
+        for start in range(0, N, batch_size):
+            idx = perm[start:start + batch_size]
+            keep = [train.draw_track_keep(int(i), rng) for i in idx]
+            xin, truth = train.assemble(idx, seed, ctr, keep)
+            ctr += len(idx)
+            s += model.train_step_points(xin, truth, lr)
+            nb += 1
+        losses.append(s / nb)
+        if progress:
+            progress("epoch: %5d loss %5.4f" % (e, losses[-1]))
+        if e in save_epochs:
+            result["count"] += 1
+            if result["mean"] is None:
+                result["mean"] = np.zeros((W, H, N), np.float32, order="F"); result["sigma"] = np.zeros((W, H, N), np.float32, order="F")
+            c = result["count"]
+            for start in range(0, N, batch_size):
+                idx = np.arange(start, min(start + batch_size, N))
+                xin, _ = test.assemble(idx, perturb=False)
+                xrec = model(xin)
+                with np.errstate(invalid="ignore"):
+                    m, sg = xrec[:, :, 0, :], np.sqrt(xrec[:, :, 1, :])          # meandata = zeros, src/points.jl:613
+                for name, new in (("mean", m), ("sigma", sg)):                     # accumulate!, src/data.jl:615-619
+                    old = result[name][:, :, idx]
+                    v = (np.float32(c - 1) * old + new) / np.float32(c)
+                    result[name][:, :, idx] = np.where(np.isnan(v), np.float32(-9999.0), v)
+    if fnames_rec is not None:
+        np.savez(fnames_rec[0], **{k: v for k, v in result.items() if v is not None})
+    if paramfile is not None:
+        np.savez(paramfile, losses=np.asarray(losses), epochs=epochs, batch_size=batch_size)
+    reconstruct_points.last_model = model
+    return losses, result

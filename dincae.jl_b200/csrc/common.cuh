@@ -1,0 +1,112 @@
+// Shared plumbing of libdincae_b200: context, error convention, launch accounting, Philox.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/dincae_b200.h"
+
+struct dincae_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int64_t launches = 0;
+    int num_sms = 148;
+    // reusable device scratch (grown on demand, never shrunk)
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
+    // pinned staging for small host<->device scalars
+    void* pinned = nullptr;
+    size_t pinned_bytes = 0;
+};
+
+void dincae_set_error(const char* fmt, ...);
+
+#define DC_CHECK_CUDA(expr)                                                                         \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess) {                                                                    \
+            dincae_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return DINCAE_ECUDA;                                                                    \
+        }                                                                                           \
+    } while (0)
+
+#define DC_REQUIRE(cond, code, ...)     \
+    do {                                \
+        if (!(cond)) {                  \
+            dincae_set_error(__VA_ARGS__); \
+            return (code);              \
+        }                               \
+    } while (0)
+
+#define DC_TRY(expr)                    \
+    do {                                \
+        int32_t _s = (expr);            \
+        if (_s != DINCAE_OK) return _s; \
+    } while (0)
+
+// every kernel launch of the library goes through this so that gpu_launches is a count, not a guess
+#define DC_LAUNCH(ctx, kernel, grid, block, smem, ...)                        \
+    do {                                                                      \
+        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);      \
+        (ctx)->launches++;                                                    \
+    } while (0)
+
+#define DC_CHECK_LAUNCH()                                                                 \
+    do {                                                                                  \
+        cudaError_t _e = cudaGetLastError();                                              \
+        if (_e != cudaSuccess) {                                                          \
+            dincae_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return DINCAE_ECUDA;                                                          \
+        }                                                                                 \
+    } while (0)
+
+int32_t dc_scratch(dincae_ctx* ctx, size_t bytes, void** out);       // grow-only device scratch
+int32_t dc_pinned(dincae_ctx* ctx, size_t bytes, void** out);        // grow-only pinned host staging
+
+static inline int64_t dc_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int dc_round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+// RAII-less helper: device buffer that is either the caller's (loc == DEVICE) or a staged copy of host memory
+struct DevIn {
+    const void* ptr = nullptr;
+    void* owned = nullptr;
+};
+int32_t dc_stage_in(dincae_ctx* ctx, const void* src, size_t bytes, int32_t loc, DevIn* out);
+void dc_stage_free(dincae_ctx* ctx, DevIn* b);
+
+#ifdef __CUDACC__
+// ---- Philox4x32-10 (counter-based; oracle/philox.py is the CPU twin) ------------------------
+struct Philox4 {
+    uint32_t v[4];
+};
+__device__ __forceinline__ Philox4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0; k1 += W1;
+    }
+    Philox4 o;
+    o.v[0] = c0; o.v[1] = c1; o.v[2] = c2; o.v[3] = c3;
+    return o;
+}
+__device__ __forceinline__ float philox_unit(uint32_t x) { return ((float)(x >> 8) + 0.5f) * 5.9604644775390625e-08f; }
+// four N(0,1) draws of counter (c0,c1,c2,c3): Box-Muller on (x0,x1) and (x2,x3)
+__device__ __forceinline__ void philox_normal4(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint64_t seed, float z[4]) {
+    Philox4 r = philox4x32_10(c0, c1, c2, c3, (uint32_t)seed, (uint32_t)(seed >> 32));
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        float u1 = philox_unit(r.v[2 * h]), u2 = philox_unit(r.v[2 * h + 1]);
+        float rad = sqrtf(-2.0f * logf(u1));
+        float s, c;
+        sincosf(6.283185307179586f * u2, &s, &c);
+        z[2 * h] = rad * c;
+        z[2 * h + 1] = rad * s;
+    }
+}
+#endif

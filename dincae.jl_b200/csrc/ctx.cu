@@ -1,0 +1,123 @@
+// Context, error convention and staging helpers of libdincae_b200.
+#include "common.cuh"
+#include <stdarg.h>
+#include <string.h>
+
+static thread_local char g_err[1024] = "";
+
+void dincae_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* dincae_last_error(void) { return g_err; }
+extern "C" int32_t dincae_version(void) { return 100; }
+
+extern "C" int32_t dincae_ctx_create(int32_t device, dincae_ctx** out) {
+    DC_REQUIRE(out != nullptr, DINCAE_EINVAL, "dincae_ctx_create: out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        dincae_set_error("dincae_ctx_create: no CUDA device (%s); this library has no CPU path", cudaGetErrorString(e));
+        return DINCAE_ECUDA;
+    }
+    DC_REQUIRE(device >= 0 && device < n, DINCAE_EINVAL, "dincae_ctx_create: device %d out of range [0,%d)", device, n);
+    DC_CHECK_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    DC_CHECK_CUDA(cudaGetDeviceProperties(&prop, device));
+    DC_REQUIRE(prop.major >= 10, DINCAE_EUNSUPPORTED,
+               "dincae_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major, prop.minor);
+    dincae_ctx* c = new dincae_ctx();
+    c->device = device;
+    c->num_sms = prop.multiProcessorCount;
+    DC_CHECK_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    c->own_stream = true;
+    *out = c;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_ctx_destroy(dincae_ctx* c) {
+    if (!c) return DINCAE_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->scratch) cudaFree(c->scratch);
+    if (c->pinned) cudaFreeHost(c->pinned);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_ctx_set_stream(dincae_ctx* c, void* s) {
+    DC_REQUIRE(c != nullptr, DINCAE_EINVAL, "dincae_ctx_set_stream: ctx is NULL");
+    DC_CHECK_CUDA(cudaStreamSynchronize(c->stream));
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    c->stream = (cudaStream_t)s;
+    c->own_stream = false;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_sync(dincae_ctx* c) {
+    DC_REQUIRE(c != nullptr, DINCAE_EINVAL, "dincae_sync: ctx is NULL");
+    DC_CHECK_CUDA(cudaStreamSynchronize(c->stream));
+    DC_CHECK_CUDA(cudaGetLastError());
+    return DINCAE_OK;
+}
+
+extern "C" int64_t dincae_launch_count(dincae_ctx* c) { return c ? c->launches : -1; }
+
+int32_t dc_scratch(dincae_ctx* ctx, size_t bytes, void** out) {
+    if (bytes > ctx->scratch_bytes) {
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->scratch) cudaFree(ctx->scratch);
+        ctx->scratch = nullptr;
+        ctx->scratch_bytes = 0;
+        size_t want = bytes + bytes / 4 + 4096;
+        cudaError_t e = cudaMalloc(&ctx->scratch, want);
+        if (e != cudaSuccess) {
+            dincae_set_error("scratch allocation of %zu bytes failed: %s", want, cudaGetErrorString(e));
+            return DINCAE_ENOMEM;
+        }
+        ctx->scratch_bytes = want;
+    }
+    *out = ctx->scratch;
+    return DINCAE_OK;
+}
+
+int32_t dc_pinned(dincae_ctx* ctx, size_t bytes, void** out) {
+    if (bytes > ctx->pinned_bytes) {
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->pinned) cudaFreeHost(ctx->pinned);
+        ctx->pinned = nullptr;
+        ctx->pinned_bytes = 0;
+        size_t want = bytes < 4096 ? 4096 : bytes;
+        DC_CHECK_CUDA(cudaMallocHost(&ctx->pinned, want));
+        ctx->pinned_bytes = want;
+    }
+    *out = ctx->pinned;
+    return DINCAE_OK;
+}
+
+int32_t dc_stage_in(dincae_ctx* ctx, const void* src, size_t bytes, int32_t loc, DevIn* out) {
+    out->owned = nullptr;
+    out->ptr = nullptr;
+    if (src == nullptr || bytes == 0) return DINCAE_OK;
+    if (loc == DINCAE_DEVICE) {
+        out->ptr = src;
+        return DINCAE_OK;
+    }
+    cudaError_t e = cudaMallocAsync(&out->owned, bytes, ctx->stream);
+    if (e != cudaSuccess) {
+        dincae_set_error("staging allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+        return DINCAE_ENOMEM;
+    }
+    DC_CHECK_CUDA(cudaMemcpyAsync(out->owned, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    out->ptr = out->owned;
+    return DINCAE_OK;
+}
+
+void dc_stage_free(dincae_ctx* ctx, DevIn* b) {
+    if (b->owned) cudaFreeAsync(b->owned, ctx->stream);
+    b->owned = nullptr;
+}

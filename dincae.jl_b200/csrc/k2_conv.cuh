@@ -1,0 +1,88 @@
+// K2: 3x3 convolution family (forward, data-gradient, weight-gradient) and the element-wise
+// pool / upsample / crop / skip operators of the U-Net level (recmodel4, src/model.jl:242-284).
+//
+// Internal activation layout: NHWC Float32, channels padded to a multiple of 4 ("Cp"), i.e.
+// t[((b*H + y)*W + x)*Cp + c] with x = lon index (Julia dim 1) and y = lat index (Julia dim 2).
+// Internal weight layout of one Conv: w[(tap*Cin_p + ci)*Cout_p + co], tap = ky*3+kx of the
+// cross-correlation out[y,x] = sum w[tap] * in[y+ky-1, x+kx-1]; Flux's true convolution kernel
+// W[a,b,ci,co] (src/model.jl:267) maps to tap (ky,kx) = (2-b, 2-a)  (SURVEY T8).
+#pragma once
+#include "common.cuh"
+
+enum { SRC_DIRECT = 0, SRC_UP_NEAREST = 1 };
+enum { ACT_NONE = 0, ACT_RELU = 1 };
+
+// Producer description: the conv input at output-resolution coordinates (b,y,x,c).
+//   SRC_DIRECT     : src0[b,y,x,c]                       (+ src1[b,y,x,c] if given)
+//   SRC_UP_NEAREST : src0[b,y>>1,x>>1,c] (+ src1[...])   = Upsample(:nearest,scale=2) then croppadding
+//                    (src/flux.jl:4, src/model.jl:270-271) and SumSkip of the level below (:277-279)
+struct ConvSrc {
+    const float* src0;
+    const float* src1;
+    int mode;
+    int Hs, Ws;   // spatial size of the source tensors
+    int C;        // padded channel count of the source tensors
+};
+
+struct ConvArgs {
+    ConvSrc in;
+    int B, H, W;          // conv input == output spatial size
+    const float* wgt;     // [Kpad][Cout_p], Kpad = round_up(9*Cin_p, 16), zero padded
+    const float* bias;    // [Cout_p] or NULL
+    int Cout_p;
+    int act;
+    float slope;          // leaky slope (0 = ReLU)
+    const float* addend;  // optional [B,H,W,Cout_p], added AFTER the activation
+    float* dst;           // [B,H,W,Cout_p]
+};
+
+struct WgradArgs {
+    ConvSrc in;
+    int B, H, W;
+    const float* gout;    // [B,H,W,Cout_p] gradient w.r.t. the conv output (pre-activation)
+    int Cout_p;
+    float* dW;            // [9*Cin_p][Cout_p]
+    float* db;            // [Cout_p]
+    float* partial;       // split-K scratch
+    int splits;
+    int64_t pix_per_split;
+};
+
+// small-Cout forward (Cout_p in {4,8}): NHWC in -> planar out[b][co][y][x] (co < Cout real)
+struct ConvSmallArgs {
+    ConvSrc in;
+    int B, H, W;
+    const float* wgt;     // element (k, j) at wgt[k*ldw + j], k = tap*Cin_p + ci, j < NCO
+    int ldw;
+    const float* bias;    // or NULL
+    int Cout;             // real output channels written
+    int accumulate;       // 0: out = v ; 1: out += v
+    float* out;           // planar [B][Cout][H][W]
+};
+
+int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);
+size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
+int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);
+int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco);
+// weight gradient for gout with NCO (4 or 8) padded channels
+int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, size_t scratch_bytes);
+
+// planar (Julia WHCN) -> NHWC padded; channels [0,C0) from src0, [C0,C0+C1) from src1 (cat(xout,xin,dims=3), src/model.jl:186)
+int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp);
+// MeanPool((2,2), pad=odd): count-include-pad (src/model.jl:268)
+int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, float* x);
+// backward of nearest-upsample + crop (+ activation mask of r): G = up^T(gu); gd = G * act'(r)
+int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd);
+// backward of mean-pool + activation mask: gc = 0.25 * xg[(y+oh)>>1,(x+ow)>>1] * act'(a)
+int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc);
+// bilinear (align_corners=true) upsample+crop of (src0 + src1) and its transpose
+int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);
+int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, int Hs, int Ws, const float* r, float slope, float* G, float* gd);
+
+// table-driven weight transpose+flip for the data-gradient convs
+struct WLayerDesc {
+    int64_t w_off, wT_off;
+    int Cin_p, Cout_p;
+    int64_t n;   // 9*Cin_p*Cout_p
+};
+int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, const WLayerDesc* d_table, int nlayers, int64_t total);

@@ -1,0 +1,693 @@
+// K2 (FP32 CUDA-core path): implicit-GEMM 3x3 convolution, its weight gradient and the
+// element-wise level operators.  This is the exact-arithmetic path (DINCAE_PREC_FP32) and the
+// path for the HBM-bound edge convolutions (Cin <= 16 or Cout = 2*noutput); the tensor-core
+// (tcgen05) implicit GEMM for the wide middle layers lives in k2_conv_tc.cu.
+#include "k2_conv.cuh"
+
+namespace {
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+__device__ __forceinline__ float4 src_load4(const ConvSrc& s, int b, int y, int x, int c) {
+    if (s.mode == SRC_UP_NEAREST) { y >>= 1; x >>= 1; }
+    size_t off = (((size_t)b * s.Hs + y) * s.Ws + x) * s.C + c;
+    float4 v = ldg4(s.src0 + off);
+    if (s.src1) {
+        float4 w = ldg4(s.src1 + off);
+        v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w;
+    }
+    return v;
+}
+__device__ __forceinline__ float src_load1(const ConvSrc& s, int b, int y, int x, int c) {
+    if (s.mode == SRC_UP_NEAREST) { y >>= 1; x >>= 1; }
+    size_t off = (((size_t)b * s.Hs + y) * s.Ws + x) * s.C + c;
+    float v = __ldg(s.src0 + off);
+    if (s.src1) v += __ldg(s.src1 + off);
+    return v;
+}
+
+__device__ __forceinline__ float act_apply(float v, int act, float slope) { return (act == ACT_RELU && v < 0.f) ? v * slope : v; }
+__device__ __forceinline__ float act_grad(float a, float slope) { return a > 0.f ? 1.f : slope; }
+
+// ---------------------------------------------------------------------------------------------
+// generic forward: tile 128 pixels x BN couts, K chunk 16, 256 threads, 8 x (BN/16) per thread
+template <int BN>
+__global__ void __launch_bounds__(256) conv3x3_simt(ConvArgs a, int Mtot, int nchunks) {
+    constexpr int BM = 128, BK = 16, TM = 8, TN = BN / 16;
+    __shared__ __align__(16) float As[BK][BM + 4];
+    __shared__ __align__(16) float Bs[BK][BN + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int Cin_p = a.in.C, C4 = Cin_p >> 2;
+    const int HW = a.H * a.W;
+
+    int pb[2], py[2], px[2];
+    bool pv[2];
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+        int m = m0 + (tid >> 2) + 64 * j;
+        pv[j] = m < Mtot;
+        int mm = pv[j] ? m : 0;
+        pb[j] = mm / HW;
+        int r = mm - pb[j] * HW;
+        py[j] = r / a.W;
+        px[j] = r - py[j] * a.W;
+    }
+    int tap = 0, c4 = tid & 3;      // K position of this thread's float4 in the current chunk
+    while (c4 >= C4) { c4 -= C4; tap++; }
+
+    constexpr int NB4 = BK * BN / 4;
+    float4 ra[2], rb;
+    float acc[TM][TN];
+#pragma unroll
+    for (int i = 0; i < TM; i++)
+#pragma unroll
+        for (int j = 0; j < TN; j++) acc[i][j] = 0.f;
+
+    auto load_chunk = [&](int kc) {
+        int ky = tap / 3, kx = tap - ky * 3;
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            int yy = py[j] + ky - 1, xx = px[j] + kx - 1;
+            bool ok = pv[j] && tap < 9 && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
+            ra[j] = ok ? src_load4(a.in, pb[j], yy, xx, c4 * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (tid < NB4) {
+            int k = tid / (BN / 4), n4 = tid - k * (BN / 4);
+            int n = n0 + n4 * 4;
+            rb = (n < a.Cout_p) ? ldg4(a.wgt + (size_t)(kc * BK + k) * a.Cout_p + n) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        c4 += 4;
+        while (c4 >= C4) { c4 -= C4; tap++; }
+    };
+
+    load_chunk(0);
+    for (int kc = 0; kc < nchunks; kc++) {
+        {
+            int kr = (tid & 3) * 4;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                int pl = (tid >> 2) + 64 * j;
+                As[kr + 0][pl] = ra[j].x; As[kr + 1][pl] = ra[j].y; As[kr + 2][pl] = ra[j].z; As[kr + 3][pl] = ra[j].w;
+            }
+            if (tid < NB4) {
+                int k = tid / (BN / 4), n4 = tid - k * (BN / 4);
+                *reinterpret_cast<float4*>(&Bs[k][n4 * 4]) = rb;
+            }
+        }
+        __syncthreads();
+        if (kc + 1 < nchunks) load_chunk(kc + 1);
+#pragma unroll
+        for (int k = 0; k < BK; k++) {
+            float av[TM], bv[TN];
+            float4 a0 = *reinterpret_cast<const float4*>(&As[k][ty * TM]);
+            float4 a1 = *reinterpret_cast<const float4*>(&As[k][ty * TM + 4]);
+            av[0] = a0.x; av[1] = a0.y; av[2] = a0.z; av[3] = a0.w; av[4] = a1.x; av[5] = a1.y; av[6] = a1.z; av[7] = a1.w;
+            if (TN == 4) {
+                float4 b0 = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+                bv[0] = b0.x; bv[1] = b0.y; bv[2] = b0.z; bv[3] = b0.w;
+            } else {
+                float2 b0 = *reinterpret_cast<const float2*>(&Bs[k][tx * 2]);
+                bv[0] = b0.x; bv[1] = b0.y;
+            }
+#pragma unroll
+            for (int i = 0; i < TM; i++)
+#pragma unroll
+                for (int j = 0; j < TN; j++) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+
+    const int n = n0 + tx * TN;
+    if (n >= a.Cout_p) return;
+    float bias[TN];
+#pragma unroll
+    for (int j = 0; j < TN; j++) bias[j] = a.bias ? __ldg(a.bias + n + j) : 0.f;
+#pragma unroll
+    for (int i = 0; i < TM; i++) {
+        int m = m0 + ty * TM + i;
+        if (m >= Mtot) continue;
+        float o[TN];
+#pragma unroll
+        for (int j = 0; j < TN; j++) o[j] = act_apply(acc[i][j] + bias[j], a.act, a.slope);
+        size_t off = (size_t)m * a.Cout_p + n;
+        if (a.addend) {
+#pragma unroll
+            for (int j = 0; j < TN; j++) o[j] += __ldg(a.addend + off + j);
+        }
+        if (TN == 4) *reinterpret_cast<float4*>(a.dst + off) = make_float4(o[0], o[1], o[2], o[3]);
+        else *reinterpret_cast<float2*>(a.dst + off) = make_float2(o[0], o[1]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight gradient: dW[k][n] = sum_m im2col(in)[m][k] * gout[m][n];  tile 64 x 64, pixel chunk 16,
+// split over pixel ranges (blockIdx.z) with a deterministic second-stage reduction.
+__global__ void __launch_bounds__(256) wgrad_simt(WgradArgs a, int Mtot, int Krows, int Kt, int Nt) {
+    constexpr int BP = 16;
+    __shared__ __align__(16) float As[BP][64 + 4];
+    __shared__ __align__(16) float Gs[BP][64 + 4];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int k0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
+    const int Cin_p = a.in.C;
+    const int HW = a.H * a.W;
+    int64_t mlo = (int64_t)blockIdx.z * a.pix_per_split;
+    int64_t mhi = mlo + a.pix_per_split;
+    if (mhi > Mtot) mhi = Mtot;
+
+    // loader roles: pixel pl = tid>>4 of the chunk, float4 column q = tid&15
+    const int pl = tid >> 4, q = tid & 15;
+    const int kk = k0 + q * 4;
+    const bool kvalid = kk < Krows;
+    const int tap = kvalid ? kk / Cin_p : 0, ci = kvalid ? kk - tap * Cin_p : 0;
+    const int ky = tap / 3, kx = tap - ky * 3;
+    const int nn = n0 + q * 4;
+    const bool nvalid = nn < a.Cout_p;
+
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    float bsum = 0.f;
+
+    for (int64_t mc = mlo; mc < mhi; mc += BP) {
+        int64_t m = mc + pl;
+        float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vg = va;
+        if (m < mhi) {
+            int b = (int)(m / HW);
+            int r = (int)(m - (int64_t)b * HW);
+            int y = r / a.W, x = r - y * a.W;
+            int yy = y + ky - 1, xx = x + kx - 1;
+            if (kvalid && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W) va = src_load4(a.in, b, yy, xx, ci);
+            if (nvalid) vg = ldg4(a.gout + (size_t)m * a.Cout_p + nn);
+        }
+        __syncthreads();
+        *reinterpret_cast<float4*>(&As[pl][q * 4]) = va;
+        *reinterpret_cast<float4*>(&Gs[pl][q * 4]) = vg;
+        __syncthreads();
+#pragma unroll
+        for (int p = 0; p < BP; p++) {
+            float4 av = *reinterpret_cast<const float4*>(&As[p][ty * 4]);
+            float4 gv = *reinterpret_cast<const float4*>(&Gs[p][tx * 4]);
+            float aa[4] = {av.x, av.y, av.z, av.w}, gg[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) acc[i][j] = fmaf(aa[i], gg[j], acc[i][j]);
+        }
+        if (blockIdx.x == 0 && tid < 64) {
+#pragma unroll
+            for (int p = 0; p < BP; p++) bsum += Gs[p][tid];
+        }
+    }
+    // write (partial) result
+    float* dst = (a.splits == 1) ? a.dW : a.partial + (size_t)blockIdx.z * ((size_t)Kt * 64 * Nt * 64 + (size_t)Nt * 64);
+    const int ld = (a.splits == 1) ? a.Cout_p : Nt * 64;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        int k = k0 + ty * 4 + i;
+        int n = n0 + tx * 4;
+        if (a.splits == 1) {
+            if (k < Krows && n < a.Cout_p) *reinterpret_cast<float4*>(dst + (size_t)k * ld + n) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        } else {
+            *reinterpret_cast<float4*>(dst + (size_t)k * ld + n) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
+    }
+    if (blockIdx.x == 0 && tid < 64) {
+        int n = n0 + tid;
+        if (a.splits == 1) {
+            if (n < a.Cout_p) a.db[n] = bsum;
+        } else {
+            dst[(size_t)Kt * 64 * ld + n] = bsum;
+        }
+    }
+}
+
+__global__ void wgrad_reduce(const float* __restrict__ partial, int splits, size_t stride, int ld, int Krows, int Cout_p,
+                             float* __restrict__ dW, float* __restrict__ db, size_t bias_off) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int64_t nW = (int64_t)Krows * Cout_p;
+    if (i < nW) {
+        int k = (int)(i / Cout_p), n = (int)(i - (int64_t)k * Cout_p);
+        float s = 0.f;
+        for (int z = 0; z < splits; z++) s += partial[(size_t)z * stride + (size_t)k * ld + n];
+        dW[i] = s;
+    } else if (i < nW + Cout_p) {
+        int n = (int)(i - nW);
+        float s = 0.f;
+        for (int z = 0; z < splits; z++) s += partial[(size_t)z * stride + bias_off + n];
+        db[n] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// small-Cout forward: one thread per pixel, all NCO outputs; weights in shared memory
+template <int NCO>
+__global__ void __launch_bounds__(256) conv3x3_small(ConvSmallArgs a, int Mtot, int Krows) {
+    extern __shared__ float ws[];   // [Krows][NCO]
+    for (int i = threadIdx.x; i < Krows * NCO; i += blockDim.x) {
+        int k = i / NCO, j = i - k * NCO;
+        ws[i] = __ldg(a.wgt + (size_t)k * a.ldw + j);
+    }
+    __syncthreads();
+    int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= Mtot) return;
+    const int HW = a.H * a.W, Cin_p = a.in.C;
+    int b = m / HW, r = m - b * HW, y = r / a.W, x = r - y * a.W;
+    float acc[NCO];
+#pragma unroll
+    for (int j = 0; j < NCO; j++) acc[j] = 0.f;
+    for (int tap = 0; tap < 9; tap++) {
+        int ky = tap / 3, kx = tap - ky * 3;
+        int yy = y + ky - 1, xx = x + kx - 1;
+        if (yy < 0 || yy >= a.H || xx < 0 || xx >= a.W) continue;
+        const float* w = ws + (size_t)tap * Cin_p * NCO;
+        for (int c = 0; c < Cin_p; c += 4) {
+            float4 v = src_load4(a.in, b, yy, xx, c);
+            float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int e = 0; e < 4; e++)
+#pragma unroll
+                for (int j = 0; j < NCO; j++) acc[j] = fmaf(vv[e], w[(c + e) * NCO + j], acc[j]);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < NCO; j++) {
+        if (j < a.Cout) {
+            float v = acc[j] + (a.bias ? __ldg(a.bias + j) : 0.f);
+            size_t off = ((size_t)b * a.Cout + j) * HW + r;
+            a.out[off] = a.accumulate ? a.out[off] + v : v;
+        }
+    }
+}
+
+// small-Cout weight gradient: gout has NCO padded channels.  Thread = one K row; block = pixel range.
+template <int NCO>
+__global__ void __launch_bounds__(256) wgrad_small(WgradArgs a, int Mtot, int Krows) {
+    const int HW = a.H * a.W, Cin_p = a.in.C;
+    int64_t mlo = (int64_t)blockIdx.x * a.pix_per_split, mhi = mlo + a.pix_per_split;
+    if (mhi > Mtot) mhi = Mtot;
+    float* dst = a.partial + (size_t)blockIdx.x * (size_t)(Krows + 1) * NCO;
+    for (int k = threadIdx.x; k <= Krows; k += blockDim.x) {
+        const bool ones = (k == Krows);     // virtual row of ones = bias gradient
+        int tap = ones ? 4 : k / Cin_p, ci = ones ? 0 : k - tap * Cin_p;
+        int ky = tap / 3, kx = tap - ky * 3;
+        float acc[NCO];
+#pragma unroll
+        for (int j = 0; j < NCO; j++) acc[j] = 0.f;
+        int b = (int)(mlo / HW);
+        int r = (int)(mlo - (int64_t)b * HW);
+        int y = r / a.W, x = r - y * a.W;
+        for (int64_t m = mlo; m < mhi; m++) {
+            int yy = y + ky - 1, xx = x + kx - 1;
+            if (yy >= 0 && yy < a.H && xx >= 0 && xx < a.W) {
+                float v = ones ? 1.f : src_load1(a.in, b, yy, xx, ci);
+                const float* g = a.gout + (size_t)m * NCO;
+                if (NCO == 4) {
+                    float4 gv = ldg4(g);
+                    acc[0] = fmaf(v, gv.x, acc[0]); acc[1] = fmaf(v, gv.y, acc[1]); acc[2] = fmaf(v, gv.z, acc[2]); acc[3] = fmaf(v, gv.w, acc[3]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < NCO; j++) acc[j] = fmaf(v, __ldg(g + j), acc[j]);
+                }
+            }
+            if (++x == a.W) { x = 0; if (++y == a.H) { y = 0; b++; } }
+        }
+#pragma unroll
+        for (int j = 0; j < NCO; j++) dst[(size_t)k * NCO + j] = acc[j];
+    }
+}
+
+__global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits, int Krows, int nco, int Cout_p,
+                                   float* __restrict__ dW, float* __restrict__ db) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (Krows + 1) * nco) return;
+    int k = i / nco, j = i - k * nco;
+    float s = 0.f;
+    for (int z = 0; z < splits; z++) s += partial[(size_t)z * (Krows + 1) * nco + i];
+    if (j < Cout_p) {
+        if (k < Krows) dW[(size_t)k * Cout_p + j] = s;
+        else db[j] = s;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+__global__ void pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
+                                   int B, int HW, float* __restrict__ dst, int Cp) {
+    int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (m >= (int64_t)B * HW) return;
+    int b = (int)(m / HW), r = (int)(m - (int64_t)b * HW);
+    for (int c = 0; c < Cp; c += 4) {
+        float v[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            int cc = c + e;
+            v[e] = cc < C0 ? __ldg(s0 + ((size_t)b * C0 + cc) * HW + r)
+                 : (cc < C0 + C1 ? __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r) : 0.f);
+        }
+        *reinterpret_cast<float4*>(dst + (size_t)m * Cp + c) = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+__global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * H2 * W2 * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int x2 = (int)(p % W2);
+    p /= W2;
+    int y2 = (int)(p % H2);
+    int b = (int)(p / H2);
+    int oh = H & 1, ow = W & 1;
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int dy = 0; dy < 2; dy++)
+#pragma unroll
+        for (int dx = 0; dx < 2; dx++) {
+            int yy = 2 * y2 + dy - oh, xx = 2 * x2 + dx - ow;
+            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+                float4 v = ldg4(a + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        }
+    s.x *= 0.25f; s.y *= 0.25f; s.z *= 0.25f; s.w *= 0.25f;
+    *reinterpret_cast<float4*>(x + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4) = s;
+}
+
+// gu at (H,W); outputs at (Hs,Ws) = (H/2 + H%2, W/2 + W%2)
+__global__ void upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
+                             const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * Hs * Ws * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int xs = (int)(p % Ws);
+    p /= Ws;
+    int ys = (int)(p % Hs);
+    int b = (int)(p / Hs);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int dy = 0; dy < 2; dy++)
+#pragma unroll
+        for (int dx = 0; dx < 2; dx++) {
+            int yy = 2 * ys + dy, xx = 2 * xs + dx;
+            if (yy < H && xx < W) {
+                float4 v = ldg4(gu + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        }
+    size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + c4 * 4;
+    if (G) *reinterpret_cast<float4*>(G + off) = s;
+    if (gd) {
+        if (r) {
+            float4 rv = ldg4(r + off);
+            s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
+        }
+        *reinterpret_cast<float4*>(gd + off) = s;
+    }
+}
+
+__global__ void poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
+                               int H2, int W2, float slope, float* __restrict__ gc) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * H * W * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int x = (int)(p % W);
+    p /= W;
+    int y = (int)(p % H);
+    int b = (int)(p / H);
+    int y2 = (y + (H & 1)) >> 1, x2 = (x + (W & 1)) >> 1;
+    float4 g = ldg4(xg + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4);
+    size_t off = (((size_t)b * H + y) * W + x) * Cp + c4 * 4;
+    float4 av = ldg4(a + off);
+    g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
+    g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+    *reinterpret_cast<float4*>(gc + off) = g;
+}
+
+// bilinear, align_corners = true (NNlib.upsample_bilinear default), full size (2Hs,2Ws) cropped to (H,W)
+__device__ __forceinline__ void bil_coord(int o, int nin, int nout_full, int& i0, int& i1, float& f) {
+    float s = (nout_full > 1) ? (float)o * (float)(nin - 1) / (float)(nout_full - 1) : 0.f;
+    i0 = (int)floorf(s);
+    if (i0 > nin - 1) i0 = nin - 1;
+    i1 = i0 + 1 < nin ? i0 + 1 : nin - 1;
+    f = s - (float)i0;
+}
+__global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
+                                   int H, int W, float* __restrict__ dst) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * H * W * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int x = (int)(p % W);
+    p /= W;
+    int y = (int)(p % H);
+    int b = (int)(p / H);
+    int x0, x1, y0, y1;
+    float fx, fy;
+    bil_coord(x, Ws, 2 * Ws, x0, x1, fx);
+    bil_coord(y, Hs, 2 * Hs, y0, y1, fy);
+    auto L = [&](int yy, int xx) {
+        size_t off = (((size_t)b * Hs + yy) * Ws + xx) * Cp + c4 * 4;
+        float4 v = ldg4(s0 + off);
+        if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+        return v;
+    };
+    float4 v00 = L(y0, x0), v01 = L(y0, x1), v10 = L(y1, x0), v11 = L(y1, x1);
+    float w00 = (1 - fy) * (1 - fx), w01 = (1 - fy) * fx, w10 = fy * (1 - fx), w11 = fy * fx;
+    float4 o;
+    o.x = w00 * v00.x + w01 * v01.x + w10 * v10.x + w11 * v11.x;
+    o.y = w00 * v00.y + w01 * v01.y + w10 * v10.y + w11 * v11.y;
+    o.z = w00 * v00.z + w01 * v01.z + w10 * v10.z + w11 * v11.z;
+    o.w = w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w;
+    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = o;
+}
+// transpose: each low-res cell gathers from the high-res cells whose stencil touches it (deterministic)
+__global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
+                                       const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * Hs * Ws * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int xs = (int)(p % Ws);
+    p /= Ws;
+    int ys = (int)(p % Hs);
+    int b = (int)(p / Hs);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    // candidate high-res rows/cols: source coordinate within (ys-1, ys+1)  =>  o in about [2ys-3, 2ys+3]
+    for (int y = max(0, 2 * ys - 3); y <= min(H - 1, 2 * ys + 3); y++) {
+        int y0, y1; float fy;
+        bil_coord(y, Hs, 2 * Hs, y0, y1, fy);
+        float wy = (y0 == ys ? (1 - fy) : 0.f) + (y1 == ys ? fy : 0.f);
+        if (wy == 0.f) continue;
+        for (int x = max(0, 2 * xs - 3); x <= min(W - 1, 2 * xs + 3); x++) {
+            int x0, x1; float fx;
+            bil_coord(x, Ws, 2 * Ws, x0, x1, fx);
+            float wx = (x0 == xs ? (1 - fx) : 0.f) + (x1 == xs ? fx : 0.f);
+            if (wx == 0.f) continue;
+            float4 v = ldg4(gu + (((size_t)b * H + y) * W + x) * Cp + c4 * 4);
+            float w = wy * wx;
+            s.x += w * v.x; s.y += w * v.y; s.z += w * v.z; s.w += w * v.w;
+        }
+    }
+    size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + c4 * 4;
+    if (G) *reinterpret_cast<float4*>(G + off) = s;
+    if (gd) {
+        if (r) {
+            float4 rv = ldg4(r + off);
+            s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
+        }
+        *reinterpret_cast<float4*>(gd + off) = s;
+    }
+}
+
+__global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, const WLayerDesc* __restrict__ tab, int nlayers, int64_t total) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    int l = 0;
+    int64_t base = 0;
+    while (l < nlayers - 1 && i >= base + tab[l].n) { base += tab[l].n; l++; }
+    int64_t j = i - base;                       // index into wT of layer l: (tapT*Cout_p + co)*Cin_p + ci
+    int Cin_p = tab[l].Cin_p, Cout_p = tab[l].Cout_p;
+    int ci = (int)(j % Cin_p);
+    int64_t t = j / Cin_p;
+    int co = (int)(t % Cout_p);
+    int tapT = (int)(t / Cout_p);
+    wT[tab[l].wT_off + j] = w[tab[l].w_off + ((size_t)(8 - tapT) * Cin_p + ci) * Cout_p + co];
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
+    int Mtot = a.B * a.H * a.W;
+    if (Mtot == 0) return DINCAE_OK;
+    int Kpad = dc_round_up(9 * a.in.C, 16);
+    int nchunks = Kpad / 16;
+    if (a.Cout_p <= 32) {
+        dim3 grid((unsigned)dc_cdiv(Mtot, 128), (unsigned)dc_cdiv(a.Cout_p, 32));
+        DC_LAUNCH(ctx, conv3x3_simt<32>, grid, 256, 0, a, Mtot, nchunks);
+    } else {
+        dim3 grid((unsigned)dc_cdiv(Mtot, 128), (unsigned)dc_cdiv(a.Cout_p, 64));
+        DC_LAUNCH(ctx, conv3x3_simt<64>, grid, 256, 0, a, Mtot, nchunks);
+    }
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+static void wgrad_plan(int num_sms, int Mtot, int Krows, int Cout_p, int& Kt, int& Nt, int& splits, int64_t& pps) {
+    Kt = (int)dc_cdiv(Krows, 64);
+    Nt = (int)dc_cdiv(Cout_p, 64);
+    int tiles = Kt * Nt;
+    splits = (4 * num_sms + tiles - 1) / tiles;
+    int maxs = (int)dc_cdiv(Mtot, 256);
+    if (splits > maxs) splits = maxs;
+    if (splits < 1) splits = 1;
+    pps = dc_cdiv(dc_cdiv(Mtot, splits), 16) * 16;
+    splits = (int)dc_cdiv(Mtot, pps);
+}
+
+size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p) {
+    int Kt, Nt, splits;
+    int64_t pps;
+    wgrad_plan(num_sms, B * H * W, 9 * Cin_p, Cout_p, Kt, Nt, splits, pps);
+    size_t big = (size_t)splits * ((size_t)Kt * 64 * Nt * 64 + (size_t)Nt * 64) * sizeof(float);
+    // small path: one block per pixel range
+    size_t small = (size_t)(8 * num_sms) * (size_t)(9 * Cin_p + 1) * 8 * sizeof(float);
+    return big > small ? big : small;
+}
+
+int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes) {
+    int Mtot = a.B * a.H * a.W;
+    int Krows = 9 * a.in.C;
+    int Kt, Nt, splits;
+    int64_t pps;
+    wgrad_plan(ctx->num_sms, Mtot, Krows, a.Cout_p, Kt, Nt, splits, pps);
+    a.splits = splits;
+    a.pix_per_split = pps;
+    a.partial = (float*)scratch;
+    size_t stride = (size_t)Kt * 64 * Nt * 64 + (size_t)Nt * 64;
+    if (splits > 1)
+        DC_REQUIRE(scratch_bytes >= stride * splits * sizeof(float), DINCAE_ESIZE, "k2_wgrad: scratch too small");
+    dim3 grid(Kt, Nt, splits);
+    DC_LAUNCH(ctx, wgrad_simt, grid, 256, 0, a, Mtot, Krows, Kt, Nt);
+    DC_CHECK_LAUNCH();
+    if (splits > 1) {
+        int64_t n = (int64_t)Krows * a.Cout_p + a.Cout_p;
+        DC_LAUNCH(ctx, wgrad_reduce, (unsigned)dc_cdiv(n, 256), 256, 0, a.partial, splits, stride, Nt * 64, Krows, a.Cout_p, a.dW, a.db,
+                  (size_t)Kt * 64 * Nt * 64);
+        DC_CHECK_LAUNCH();
+    }
+    return DINCAE_OK;
+}
+
+int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco) {
+    int Mtot = a.B * a.H * a.W;
+    if (Mtot == 0) return DINCAE_OK;
+    int Krows = 9 * a.in.C;
+    size_t smem = (size_t)Krows * nco * sizeof(float);
+    DC_REQUIRE(smem <= 200 * 1024, DINCAE_EUNSUPPORTED, "k2_conv_small: %d input channels do not fit shared memory", a.in.C);
+    if (nco == 4) {
+        if (smem > 48 * 1024) DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_small<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DC_LAUNCH(ctx, conv3x3_small<4>, (unsigned)dc_cdiv(Mtot, 256), 256, smem, a, Mtot, Krows);
+    } else if (nco == 8) {
+        if (smem > 48 * 1024) DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_small<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        DC_LAUNCH(ctx, conv3x3_small<8>, (unsigned)dc_cdiv(Mtot, 256), 256, smem, a, Mtot, Krows);
+    } else {
+        DC_REQUIRE(false, DINCAE_EUNSUPPORTED, "k2_conv_small: nco=%d", nco);
+    }
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, size_t scratch_bytes) {
+    int Mtot = a.B * a.H * a.W;
+    int Krows = 9 * a.in.C;
+    int splits = 8 * ctx->num_sms;
+    int64_t pps = dc_cdiv(Mtot, splits);
+    if (pps < 64) pps = 64;
+    splits = (int)dc_cdiv(Mtot, pps);
+    DC_REQUIRE(scratch_bytes >= (size_t)splits * (Krows + 1) * nco * sizeof(float), DINCAE_ESIZE, "k2_wgrad_small: scratch too small");
+    a.partial = (float*)scratch;
+    a.pix_per_split = pps;
+    a.splits = splits;
+    int threads = Krows + 1 < 256 ? dc_round_up(Krows + 1, 32) : 256;
+    if (nco == 4) DC_LAUNCH(ctx, wgrad_small<4>, splits, threads, 0, a, Mtot, Krows);
+    else if (nco == 8) DC_LAUNCH(ctx, wgrad_small<8>, splits, threads, 0, a, Mtot, Krows);
+    else DC_REQUIRE(false, DINCAE_EUNSUPPORTED, "k2_wgrad_small: nco=%d", nco);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, wgrad_small_reduce, (unsigned)dc_cdiv((Krows + 1) * nco, 256), 256, 0, a.partial, splits, Krows, nco, a.Cout_p, a.dW, a.db);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
+    int64_t M = (int64_t)B * H * W;
+    if (M == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, float* x) {
+    int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
+    int64_t n = (int64_t)B * H2 * W2 * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, pool_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, a, B, H, W, Cp, H2, W2, x);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd) {
+    int Hs = H / 2 + H % 2, Ws = W / 2 + W % 2;
+    int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, upbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc) {
+    int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
+    int64_t n = (int64_t)B * H * W * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, poolbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
+    int64_t n = (int64_t)B * H * W * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, up_bilinear_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, int Hs, int Ws, const float* r, float slope,
+                           float* G, float* gd) {
+    int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, up_bilinear_bwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, const WLayerDesc* d_table, int nlayers, int64_t total) {
+    if (total == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, make_wT_kernel, (unsigned)dc_cdiv(total, 256), 256, 0, w, wT, d_table, nlayers, total);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}

@@ -1,0 +1,361 @@
+// K3: head + masked Gaussian NLL + Laplacian + regularisers + ClipGrad/Adam (see k3_loss.cuh).
+// Derivatives follow SURVEY.md Appendix A, derived from src/model.jl:16-29 and :79-92.
+#include "k3_loss.cuh"
+
+namespace {
+
+constexpr int RED_THREADS = 256;
+constexpr int RED_MAX_BLOCKS = 1024;
+
+__device__ __forceinline__ double block_sum(double v) {
+    __shared__ double sh[RED_THREADS / 32];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (threadIdx.x == 0)
+        for (int i = 0; i < RED_THREADS / 32; i++) s += sh[i];
+    return s;   // valid on thread 0
+}
+
+__global__ void final_sum_kernel(const double* __restrict__ part, int n, double* __restrict__ acc) {
+    __shared__ double sh[256];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) s += part[i];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) acc[0] += sh[0];
+}
+
+__global__ void count_valid_kernel(const float* __restrict__ xtrue, int B, int nout, int64_t npix, unsigned long long* __restrict__ n_valid) {
+    // grid: (blocks, nout)
+    int v = blockIdx.y;
+    int64_t total = (int64_t)B * npix;
+    unsigned int c = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t b = i / npix, p = i - b * npix;
+        c += (xtrue[(b * 2 * nout + 2 * v + 1) * npix + p] != 0.f) ? 1u : 0u;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&n_valid[v], (unsigned long long)c);   // integer atomics: exact, order-free
+}
+
+struct HeadVals {
+    float p, q, s2, m;
+    bool open;     // d q / d b != 0
+};
+__device__ __forceinline__ HeadVals head_eval(float a, float l, float gamma) {
+    HeadVals h;
+    h.p = expf(fminf(l, gamma));            // invσ² = exp(min(x2, γ)), src/model.jl:21
+    h.q = fmaxf(h.p, 1e-3f);                // sinv clamp, src/model.jl:7-10
+    h.s2 = 1.0f / h.q;
+    h.m = a * h.s2;                         // m = x1 .* σ², src/model.jl:23
+    h.open = (l < gamma) && (h.p > 1e-3f);
+    return h;
+}
+
+__global__ void head_kernel(const float* __restrict__ raw, int64_t nvb, int64_t npix, float gamma, float* __restrict__ ms) {
+    int64_t total = nvb * npix;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t vb = i / npix, p = i - vb * npix;
+        size_t o = (size_t)(2 * vb) * npix + p;
+        HeadVals h = head_eval(raw[o], raw[o + npix], gamma);
+        ms[o] = h.m;
+        ms[o + npix] = h.s2;
+    }
+}
+
+// NLL terms of one observation given (m, s2) and the target pair (xt1, xt2); returns cost term, sets gm, gs (unnormalised by n)
+__device__ __forceinline__ float nll_terms(float m, float s2, float xt1, float xt2, int truth_uncertain, float& gm, float& gs) {
+    if (xt2 == 0.f) { gm = 0.f; gs = 0.f; return 0.f; }       // mask_noncloud, src/model.jl:114
+    float s2t = 1.0f / fmaxf(xt2, 1e-3f);                         // :109
+    float mt = xt1 * s2t;                                         // :110
+    float d = m - mt;
+    float inv = 1.0f / s2;
+    float num = truth_uncertain ? (d * d + s2t) : d * d;          // :83 / :90
+    float cost = (truth_uncertain ? logf(s2 / s2t) : logf(s2)) + num * inv;   // :86 / :92
+    gm = 2.f * d * inv;
+    gs = inv - num * inv * inv;
+    return cost;
+}
+
+// chain rule through the head: (gm, gs) -> (d/da, d/dl)
+__device__ __forceinline__ void head_chain(float a, const HeadVals& h, float gm, float gs, float& ga, float& gl) {
+    ga = gm * h.s2;
+    float gs2 = gs + gm * a;              // m = a*s2
+    float gq = -gs2 * h.s2 * h.s2;        // s2 = 1/q
+    gl = h.open ? gq * h.p : 0.f;
+}
+
+template <bool FUSE_BWD>
+__global__ void __launch_bounds__(RED_THREADS) loss_grid_kernel(const float* __restrict__ raw, const float* __restrict__ xtrue, int B, int nout,
+                                                               int64_t npix, HeadParams hp, const float* __restrict__ inv_n, float weight,
+                                                               double* __restrict__ part, float* __restrict__ gout) {
+    int64_t total = (int64_t)B * nout * npix;
+    double acc = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t vb = i / npix, p = i - vb * npix;
+        int v = (int)(vb % nout);
+        size_t o = (size_t)(2 * vb) * npix + p;
+        float a = raw[o], l = raw[o + npix];
+        HeadVals h = head_eval(a, l, hp.gamma);
+        float gm, gs;
+        float c = nll_terms(h.m, h.s2, xtrue[o], xtrue[o + npix], hp.truth_uncertain, gm, gs);
+        float sc = weight * inv_n[v];
+        acc += (double)c * (double)sc;
+        if (gout) {
+            gm *= sc; gs *= sc;
+            if (FUSE_BWD) {
+                float ga, gl;
+                head_chain(a, h, gm, gs, ga, gl);
+                gout[o] = ga;
+                gout[o + npix] = gl;
+            } else {
+                gout[o] = gm;
+                gout[o + npix] = gs;
+            }
+        }
+    }
+    double s = block_sum(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+__global__ void __launch_bounds__(RED_THREADS) loss_points_kernel(const float* __restrict__ mv, const float* __restrict__ x, int64_t P, HeadParams hp,
+                                                                 const float* __restrict__ inv_n, float weight, double* __restrict__ part,
+                                                                 float* __restrict__ gms) {
+    double acc = 0.0;
+    float sc = weight * inv_n[0];
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) {
+        float gm, gs;
+        float c = nll_terms(mv[p], mv[P + p], x[p], x[P + p], hp.truth_uncertain, gm, gs);
+        acc += (double)c * (double)sc;
+        if (gms) { gms[p] = gm * sc; gms[P + p] = gs * sc; }
+    }
+    double s = block_sum(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+// second difference along one axis and its adjoint applied to itself: returns [D^T D u]_i and adds (D u)_i^2 to pen
+__device__ __forceinline__ float lap_axis(const float* __restrict__ u, int i, int n, int64_t stride, float& pen) {
+    auto dd = [&](int k) -> float {     // (D u)_k for 1 <= k <= n-2, else 0
+        if (k < 1 || k > n - 2) return 0.f;
+        return u[(int64_t)(k - 1 - i) * stride] - 2.f * u[(int64_t)(k - i) * stride] + u[(int64_t)(k + 1 - i) * stride];
+    };
+    float d0 = dd(i);
+    pen += d0 * d0;
+    return dd(i - 1) - 2.f * d0 + dd(i + 1);
+}
+
+__global__ void __launch_bounds__(RED_THREADS) head_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ ms, const float* g_ms,
+                                                              int B, int nout, int W, int H, HeadParams hp, float weight,
+                                                              double* __restrict__ part, float* graw) {
+    int64_t npix = (int64_t)W * H;
+    int64_t total = (int64_t)B * nout * npix;
+    double acc = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t vb = i / npix, p = i - vb * npix;
+        int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+        size_t o = (size_t)(2 * vb) * npix + p;
+        float a = raw[o], l = raw[o + npix];
+        HeadVals h = head_eval(a, l, hp.gamma);
+        float gm = g_ms ? g_ms[o] : 0.f, gs = g_ms ? g_ms[o + npix] : 0.f;
+        if (hp.lap != 0.f) {        // sum_laplacian_penalty(laplacian_penalty, m_rec), src/model.jl:44-52,:99
+            float pen = 0.f;
+            float g = lap_axis(ms + o, x, W, 1, pen) + lap_axis(ms + o, y, H, W, pen);
+            gm += weight * 2.f * hp.lap * g;
+            acc += (double)weight * (double)hp.lap * (double)pen;
+        }
+        if (hp.lap_err != 0.f) {    // ... (laplacian_error_penalty, σ2_rec), src/model.jl:100
+            float pen = 0.f;
+            float g = lap_axis(ms + o + npix, x, W, 1, pen) + lap_axis(ms + o + npix, y, H, W, pen);
+            gs += weight * 2.f * hp.lap_err * g;
+            acc += (double)weight * (double)hp.lap_err * (double)pen;
+        }
+        if (graw) {
+            float ga, gl;
+            head_chain(a, h, gm, gs, ga, gl);
+            graw[o] = ga;
+            graw[o + npix] = gl;
+        }
+    }
+    double s = block_sum(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+template <bool UPDATE>
+__global__ void __launch_bounds__(RED_THREADS) adam_kernel(float* __restrict__ w, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                                          int64_t n, AdamParams p, double* __restrict__ part) {
+    double acc = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float wi = w[i];
+        if (p.l1 != 0.f) acc += (double)p.l1 * fabs((double)wi);
+        if (p.l2 != 0.f) acc += (double)p.l2 * (double)wi * (double)wi;
+        if (UPDATE) {
+            float gi = g[i];
+            if (p.l2 != 0.f) gi += 2.f * p.l2 * wi;                       // d/dw beta*sum(abs2,w), src/model.jl:215-217
+            if (p.l1 != 0.f) gi += p.l1 * (wi > 0.f ? 1.f : (wi < 0.f ? -1.f : 0.f));
+            if (p.clip > 0.f) gi = fminf(fmaxf(gi, -p.clip), p.clip);    // ClipGrad(delta): element clamp
+            float mi = p.beta1 * m[i] + (1.f - p.beta1) * gi;
+            float vi = p.beta2 * v[i] + (1.f - p.beta2) * gi * gi;
+            m[i] = mi;
+            v[i] = vi;
+            w[i] = wi - p.lr * (mi * p.inv_bc1) / (sqrtf(vi * p.inv_bc2) + p.eps);
+        }
+    }
+    double s = block_sum(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+__global__ void savesample_kernel(const float* __restrict__ ms, int B, int nout, int64_t npix, const float* __restrict__ mean,
+                                  const uint8_t* __restrict__ landmask, int count, float fill, float* __restrict__ m_out,
+                                  float* __restrict__ s_out, int64_t var_stride) {
+    int64_t total = (int64_t)B * nout * npix;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int64_t vb = i / npix, p = i - vb * npix;
+        int v = (int)(vb % nout);
+        int64_t b = vb / nout;
+        size_t o = (size_t)(2 * vb) * npix + p;
+        float rec = ms[o] + mean[(size_t)v * npix + p];       // recdata = batch_m_rec .+ meandata, src/data.jl:661
+        float sig = sqrtf(ms[o + npix]);                      // :662
+        if (rec != rec) sig = nanf("");                       // :664
+        if (landmask && !landmask[p]) { rec = nanf(""); sig = rec; }   // :668-669
+        size_t q = (size_t)v * var_stride + (size_t)b * npix + p;
+        float om = count > 1 ? m_out[q] : 0.f, os = count > 1 ? s_out[q] : 0.f;
+        float nm = ((float)(count - 1) * om + rec) / (float)count;      // accumulate!, :615-619
+        float ns = ((float)(count - 1) * os + sig) / (float)count;
+        m_out[q] = (nm != nm) ? fill : nm;
+        s_out[q] = (ns != ns) ? fill : ns;
+    }
+}
+
+int red_blocks(dincae_ctx* ctx, int64_t n) {
+    int64_t b = dc_cdiv(n, RED_THREADS * 4);
+    int64_t cap = 8 * (int64_t)ctx->num_sms;
+    if (cap > RED_MAX_BLOCKS) cap = RED_MAX_BLOCKS;
+    if (b > cap) b = cap;
+    if (b < 1) b = 1;
+    return (int)b;
+}
+
+}  // namespace
+
+size_t k3_scratch_bytes(int64_t) { return RED_MAX_BLOCKS * sizeof(double); }
+
+int32_t k3_count_valid(dincae_ctx* ctx, const float* xtrue, int B, int nout, int64_t npix, unsigned long long* n_valid) {
+    DC_CHECK_CUDA(cudaMemsetAsync(n_valid, 0, sizeof(unsigned long long) * nout, ctx->stream));
+    if (B == 0) return DINCAE_OK;
+    dim3 grid(red_blocks(ctx, (int64_t)B * npix), nout);
+    DC_LAUNCH(ctx, count_valid_kernel, grid, 256, 0, xtrue, B, nout, npix, n_valid);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k3_head(dincae_ctx* ctx, const float* raw, int B, int nout, int64_t npix, float gamma, float* ms) {
+    int64_t n = (int64_t)B * nout * npix;
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, head_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, raw, (int64_t)B * nout, npix, gamma, ms);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k3_loss_grid(dincae_ctx* ctx, const float* raw, const float* xtrue, const float* ms, int B, int nout, int W, int H,
+                     const HeadParams& hp, const float* inv_n, float weight, double* loss_acc, float* graw,
+                     void* scratch, size_t scratch_bytes) {
+    int64_t npix = (int64_t)W * H;
+    int64_t n = (int64_t)B * nout * npix;
+    if (n == 0) return DINCAE_OK;
+    DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(n), DINCAE_ESIZE, "k3_loss_grid: scratch too small");
+    double* part = (double*)scratch;
+    int nb = red_blocks(ctx, n);
+    bool lap = hp.lap != 0.f || hp.lap_err != 0.f;
+    if (!lap) {
+        DC_LAUNCH(ctx, loss_grid_kernel<true>, nb, RED_THREADS, 0, raw, xtrue, B, nout, npix, hp, inv_n, weight, part, graw);
+        DC_CHECK_LAUNCH();
+        DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
+        DC_CHECK_LAUNCH();
+        return DINCAE_OK;
+    }
+    DC_REQUIRE(ms != nullptr, DINCAE_EINVAL, "k3_loss_grid: Laplacian penalty needs head(raw)");
+    // (gm, gs) into graw's storage first, then the Laplacian + chain rule in place
+    DC_LAUNCH(ctx, loss_grid_kernel<false>, nb, RED_THREADS, 0, raw, xtrue, B, nout, npix, hp, inv_n, weight, part, graw);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
+    DC_CHECK_LAUNCH();
+    return k3_head_bwd(ctx, raw, ms, graw, B, nout, W, H, hp, weight, loss_acc, graw, scratch, scratch_bytes);
+}
+
+int32_t k3_loss_points(dincae_ctx* ctx, const float* mv, const float* x, int64_t P, const HeadParams& hp, const float* inv_n,
+                       float weight, double* loss_acc, float* gms, void* scratch, size_t scratch_bytes) {
+    if (P == 0) return DINCAE_OK;
+    DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(P), DINCAE_ESIZE, "k3_loss_points: scratch too small");
+    double* part = (double*)scratch;
+    int nb = red_blocks(ctx, P);
+    DC_LAUNCH(ctx, loss_points_kernel, nb, RED_THREADS, 0, mv, x, P, hp, inv_n, weight, part, gms);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k3_head_bwd(dincae_ctx* ctx, const float* raw, const float* ms, const float* g_ms, int B, int nout, int W, int H,
+                    const HeadParams& hp, float weight, double* loss_acc, float* graw, void* scratch, size_t scratch_bytes) {
+    int64_t n = (int64_t)B * nout * W * H;
+    if (n == 0) return DINCAE_OK;
+    DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(n), DINCAE_ESIZE, "k3_head_bwd: scratch too small");
+    double* part = (double*)scratch;
+    int nb = red_blocks(ctx, n);
+    // in-place use (g_ms == graw) is safe: each thread reads its own two elements before writing them
+    DC_LAUNCH(ctx, head_bwd_kernel, nb, RED_THREADS, 0, raw, ms, g_ms, B, nout, W, H, hp, weight, part, graw);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k3_adam(dincae_ctx* ctx, float* w, const float* g, float* m, float* v, int64_t n, const AdamParams& p,
+                double* reg_acc, void* scratch, size_t scratch_bytes) {
+    if (n == 0) return DINCAE_OK;
+    DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(n), DINCAE_ESIZE, "k3_adam: scratch too small");
+    double* part = (double*)scratch;
+    int nb = red_blocks(ctx, n);
+    DC_LAUNCH(ctx, adam_kernel<true>, nb, RED_THREADS, 0, w, g, m, v, n, p, part);
+    DC_CHECK_LAUNCH();
+    if (reg_acc && (p.l1 != 0.f || p.l2 != 0.f)) {
+        DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, reg_acc);
+        DC_CHECK_LAUNCH();
+    }
+    return DINCAE_OK;
+}
+
+int32_t k3_reg(dincae_ctx* ctx, const float* w, int64_t n, float l1, float l2, double* reg_acc, void* scratch, size_t scratch_bytes) {
+    if (n == 0 || (l1 == 0.f && l2 == 0.f)) return DINCAE_OK;
+    DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(n), DINCAE_ESIZE, "k3_reg: scratch too small");
+    double* part = (double*)scratch;
+    int nb = red_blocks(ctx, n);
+    AdamParams p{};
+    p.l1 = l1;
+    p.l2 = l2;
+    DC_LAUNCH(ctx, adam_kernel<false>, nb, RED_THREADS, 0, const_cast<float*>(w), nullptr, nullptr, nullptr, n, p, part);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, reg_acc);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k3_savesample(dincae_ctx* ctx, const float* ms, int B, int nout, int64_t npix, const float* meandata_out,
+                      const uint8_t* landmask, int count, float fill_value, float* m_out, float* sigma_out, int64_t var_stride) {
+    int64_t n = (int64_t)B * nout * npix;
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, savesample_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, ms, B, nout, npix, meandata_out, landmask, count, fill_value,
+              m_out, sigma_out, var_stride);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}

@@ -1,0 +1,782 @@
+// Model orchestration of libdincae_b200: StepModel forward (src/model.jl:182-189), loss_function
+// (:192-222), reverse pass (replaces Zygote's tape, src/flux.jl:29-31) and the optimiser step (:33).
+#include "model.cuh"
+#include "k1_assemble.cuh"
+#include "k4_interp.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace {
+
+__global__ void inv_n_kernel(const unsigned long long* __restrict__ n, int nout, float* __restrict__ inv_n) {
+    int v = threadIdx.x;
+    if (v < nout) inv_n[v] = 1.0f / (float)n[v];     // "/ n_noncloud", src/model.jl:86,92 (Inf for n = 0, as the reference)
+}
+__global__ void store_loss_kernel(const double* __restrict__ acc, float* __restrict__ slot) { slot[0] = (float)acc[0]; }
+__global__ void total_loss_kernel(const float* __restrict__ slot, const double* __restrict__ acc, float* __restrict__ out_f, double* __restrict__ out_d) {
+    double t = (slot ? (double)slot[0] : acc[0]) + acc[1];
+    if (out_f) out_f[0] = (float)t;
+    if (out_d) out_d[0] = t;
+}
+__global__ void plane_of_kernel(const int64_t* __restrict__ offsets, int B, int64_t P, int32_t* __restrict__ plane_of) {
+    int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    int lo = 0, hi = B;          // largest b with offsets[b] <= p
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (offsets[mid] <= p) lo = mid; else hi = mid;
+    }
+    plane_of[p] = lo;
+}
+__global__ void count_pts_kernel(const float* __restrict__ x2, int64_t P, unsigned long long* __restrict__ n) {
+    unsigned int c = 0;
+    for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < P; p += (int64_t)gridDim.x * blockDim.x) c += x2[p] != 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(n, (unsigned long long)c);
+}
+
+inline bool has_skip(const dincae_model* M, int l) { return l >= 1 && l < M->L && ((M->cfg.skip_mask >> l) & 1u); }
+
+// the producer of conv_dec_l: upsample(+crop) of y_{l+1} = R[l+1] (+ X[l+1] when level l+1 has a skip) or X[L]
+int32_t dec_source(dincae_model* M, int c, int l, int B, bool materialise, ConvSrc* s) {
+    ChainBufs& cb = M->cb[c];
+    const float* src0 = (l + 1 == M->L) ? cb.X[M->L] : cb.R[l + 1];
+    const float* src1 = has_skip(M, l + 1) ? cb.X[l + 1] : nullptr;
+    int Cp = M->dec[c][l].Cin_p;
+    if (M->cfg.upsampling == DINCAE_UP_NEAREST) {
+        *s = ConvSrc{src0, src1, SRC_UP_NEAREST, M->Hl[l + 1], M->Wl[l + 1], Cp};
+    } else {
+        if (materialise) DC_TRY(k2_up_bilinear(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
+        *s = ConvSrc{cb.U[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], Cp};
+    }
+    return DINCAE_OK;
+}
+
+int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
+    dincae_ctx* ctx = M->ctx;
+    ChainBufs& cb = M->cb[c];
+    const int L = M->L;
+    const float slope = M->cfg.leaky_slope;
+    if (c == 0) DC_TRY(k2_pack(ctx, d_xin, M->cfg.ninput, nullptr, 0, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_p));
+    else DC_TRY(k2_pack(ctx, M->cb[c - 1].RAW, 2 * M->O, d_xin, M->cfg.ninput, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_p));   // cat(xout,xin), T9
+    for (int l = 0; l < L; l++) {
+        const LayerInfo& e = M->enc[c][l];
+        ConvArgs a{};
+        a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
+        a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
+        a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
+        a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
+        DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
+        DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
+    }
+    for (int l = L - 1; l >= 0; l--) {
+        const LayerInfo& d = M->dec[c][l];
+        ConvSrc s;
+        DC_TRY(dec_source(M, c, l, B, true, &s));                                  // Upsample + croppadding (+ SumSkip below), :270-271
+        if (l > 0) {
+            ConvArgs a{};
+            a.in = s; a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
+            a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
+            a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
+            DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
+        } else {
+            ConvSmallArgs a{};
+            a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
+            a.wgt = M->w + d.w_off; a.ldw = d.Cout_p; a.bias = M->w + d.b_off; a.Cout = 2 * M->O; a.accumulate = 0; a.out = cb.RAW;
+            DC_TRY(k2_conv_small(ctx, a, M->nco));                                 // Conv(..., identity) at l == 1, :251-256
+        }
+    }
+    return DINCAE_OK;
+}
+
+int32_t ensure_wT(dincae_model* M) {
+    if (!M->wT_dirty) return DINCAE_OK;
+    DC_TRY(k2_make_wT(M->ctx, M->w, M->wT, M->d_wtab, M->n_wlayers, M->n_wT_copy));
+    M->wT_dirty = false;
+    return DINCAE_OK;
+}
+
+int32_t chain_backward(dincae_model* M, int c, int B) {
+    dincae_ctx* ctx = M->ctx;
+    ChainBufs& cb = M->cb[c];
+    const int L = M->L;
+    const float slope = M->cfg.leaky_slope;
+    const bool nearest = M->cfg.upsampling == DINCAE_UP_NEAREST;
+    // ---- decoder, top (l = 0) to bottom
+    DC_TRY(k2_pack(ctx, cb.GRAW, 2 * M->O, nullptr, 0, B, M->Hl[0], M->Wl[0], M->GD0, M->nco));
+    for (int l = 0; l < L; l++) {
+        const LayerInfo& d = M->dec[c][l];
+        const float* gd = (l == 0) ? M->GD0 : M->GD[l];
+        if (l > 0) {
+            // G[l] = up^T(GU[l-1]); GD[l] = G[l] * relu'(R[l])
+            if (nearest) DC_TRY(k2_upbwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, cb.R[l], slope, M->G[l], M->GD[l]));
+            else DC_TRY(k2_up_bilinear_bwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, M->Hl[l], M->Wl[l], cb.R[l], slope, M->G[l], M->GD[l]));
+        }
+        ConvSrc s;
+        DC_TRY(dec_source(M, c, l, B, false, &s));
+        WgradArgs wa{};
+        wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
+        wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
+        if (l == 0) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
+        else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
+        ConvArgs a{};
+        a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
+        a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
+        a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
+        DC_TRY(k2_conv(ctx, a));
+    }
+    {   // G[L] = gradient w.r.t. X[L] (the innermost level is the identity, src/model.jl:263-264)
+        const LayerInfo& d = M->dec[c][L - 1];
+        if (nearest) DC_TRY(k2_upbwd(ctx, M->GU[L - 1], B, M->Hl[L - 1], M->Wl[L - 1], d.Cin_p, nullptr, slope, M->G[L], nullptr));
+        else DC_TRY(k2_up_bilinear_bwd(ctx, M->GU[L - 1], B, M->Hl[L - 1], M->Wl[L - 1], d.Cin_p, M->Hl[L], M->Wl[L], nullptr, slope, M->G[L], nullptr));
+    }
+    // ---- encoder, bottom to top
+    const float* xg = M->G[L];
+    for (int l = L - 1; l >= 0; l--) {
+        const LayerInfo& e = M->enc[c][l];
+        DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l]));
+        WgradArgs wa{};
+        wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
+        wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
+        wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
+        DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
+        if (l >= 1) {
+            ConvArgs a{};
+            a.in = ConvSrc{M->GC[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cout_p};
+            a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
+            a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f;
+            a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
+            a.dst = M->XG[l];
+            DC_TRY(k2_conv(ctx, a));
+            xg = M->XG[l];
+        } else if (c >= 1) {
+            // gradient w.r.t. the first 2*nout input channels of the refinement chain = raw output of chain c-1
+            ConvSmallArgs a{};
+            a.in = ConvSrc{M->GC[0], nullptr, SRC_DIRECT, M->Hl[0], M->Wl[0], e.Cout_p};
+            a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
+            a.wgt = M->wT + e.wT_off; a.ldw = e.Cin_p; a.bias = nullptr; a.Cout = 2 * M->O; a.accumulate = 1; a.out = M->cb[c - 1].GRAW;
+            DC_TRY(k2_conv_small(ctx, a, M->nco));
+        }
+    }
+    return DINCAE_OK;
+}
+
+HeadParams head_params(const dincae_model* M) {
+    HeadParams hp;
+    hp.gamma = M->cfg.gamma;
+    hp.truth_uncertain = M->cfg.truth_uncertain;
+    hp.lap = M->cfg.laplacian_penalty;
+    hp.lap_err = M->cfg.laplacian_error_penalty;
+    return hp;
+}
+
+int32_t check_batch(const dincae_model* M, int B, const char* who) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "%s: model is NULL", who);
+    DC_REQUIRE(B >= 1 && B <= M->maxB, DINCAE_ESIZE, "%s: batch %d outside [1, max_batch=%d]", who, B, M->maxB);
+    return DINCAE_OK;
+}
+
+// bring a (W,H,C,B) host/device tensor to the device
+int32_t stage_batch(dincae_model* M, const float* src, int C, int B, int32_t loc, float* staging, const float** out) {
+    if (loc == DINCAE_DEVICE) { *out = src; return DINCAE_OK; }
+    size_t n = (size_t)M->cfg.W * M->cfg.H * C * B;
+    DC_CHECK_CUDA(cudaMemcpyAsync(staging, src, sizeof(float) * n, cudaMemcpyHostToDevice, M->ctx->stream));
+    *out = staging;
+    return DINCAE_OK;
+}
+
+// gridded loss of all chains (+ gradients w.r.t. the raw chain outputs when train)
+int32_t gridded_loss(dincae_model* M, const float* d_xtrue, int B, const int64_t* n_valid_global, bool train) {
+    dincae_ctx* ctx = M->ctx;
+    const int64_t npix = (int64_t)M->cfg.W * M->cfg.H;
+    if (n_valid_global) {
+        unsigned long long tmp[16];
+        for (int v = 0; v < M->O; v++) tmp[v] = (unsigned long long)n_valid_global[v];
+        DC_CHECK_CUDA(cudaMemcpyAsync(M->d_nvalid, tmp, sizeof(unsigned long long) * M->O, cudaMemcpyHostToDevice, ctx->stream));
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));     // tmp is a stack buffer
+    } else {
+        DC_TRY(k3_count_valid(ctx, d_xtrue, B, M->O, npix, M->d_nvalid));
+    }
+    DC_LAUNCH(ctx, inv_n_kernel, 1, 32, 0, M->d_nvalid, M->O, M->d_inv_n);
+    DC_CHECK_LAUNCH();
+    HeadParams hp = head_params(M);
+    const bool lap = hp.lap != 0.f || hp.lap_err != 0.f;
+    for (int c = 0; c < M->nchains; c++) {
+        if (lap) DC_TRY(k3_head(ctx, M->cb[c].RAW, B, M->O, npix, hp.gamma, M->MS));
+        DC_TRY(k3_loss_grid(ctx, M->cb[c].RAW, d_xtrue, lap ? M->MS : nullptr, B, M->O, M->cfg.W, M->cfg.H, hp, M->d_inv_n,
+                            M->cfg.loss_weights[c], M->d_loss, train ? M->cb[c].GRAW : nullptr, M->red_scratch, M->red_scratch_bytes));
+    }
+    return DINCAE_OK;
+}
+
+struct PointTruth {
+    const float* pos = nullptr;     // device (P,2)
+    const float* x = nullptr;       // device (P,2) column-major
+    int32_t* plane_of = nullptr;    // device (P)
+    int64_t P = 0;
+    DevIn spos, sx;
+};
+
+int32_t point_workspace(dincae_model* M, int64_t P) {
+    if ((size_t)P <= M->pt_cap) return DINCAE_OK;
+    DC_CHECK_CUDA(cudaStreamSynchronize(M->ctx->stream));
+    if (M->pt_buf) cudaFree(M->pt_buf);
+    M->pt_buf = nullptr;
+    M->pt_cap = 0;
+    size_t cap = (size_t)P + (size_t)P / 4 + 1024;
+    // mv[2P] gathered (m,s2); gms[2P] their gradients; plane_of[P]; offsets
+    cudaError_t e = cudaMalloc((void**)&M->pt_buf, sizeof(float) * (5 * cap) + sizeof(int64_t) * (M->maxB + 2));
+    if (e != cudaSuccess) { dincae_set_error("point workspace allocation failed: %s", cudaGetErrorString(e)); return DINCAE_ENOMEM; }
+    M->pt_cap = cap;
+    return DINCAE_OK;
+}
+
+int32_t stage_points(dincae_model* M, const float* pos, const float* x, const int64_t* offsets, int B, int32_t loc, PointTruth* pt) {
+    dincae_ctx* ctx = M->ctx;
+    DC_REQUIRE(offsets != nullptr, DINCAE_EINVAL, "point truth: offsets is NULL (host array of B+1 int64)");
+    DC_REQUIRE(offsets[0] == 0, DINCAE_EINVAL, "point truth: offsets[0] must be 0");
+    for (int b = 0; b < B; b++) DC_REQUIRE(offsets[b + 1] >= offsets[b], DINCAE_EINVAL, "point truth: offsets not monotone at %d", b);
+    pt->P = offsets[B];
+    DC_TRY(point_workspace(M, pt->P));
+    DC_TRY(dc_stage_in(ctx, pos, sizeof(float) * 2 * pt->P, loc, &pt->spos));
+    DC_TRY(dc_stage_in(ctx, x, sizeof(float) * 2 * pt->P, loc, &pt->sx));
+    pt->pos = (const float*)pt->spos.ptr;
+    pt->x = (const float*)pt->sx.ptr;
+    pt->plane_of = (int32_t*)(M->pt_buf + 4 * M->pt_cap);
+    int64_t* d_off = (int64_t*)(M->pt_buf + 5 * M->pt_cap);
+    DC_CHECK_CUDA(cudaMemcpyAsync(d_off, offsets, sizeof(int64_t) * (B + 1), cudaMemcpyHostToDevice, ctx->stream));
+    if (pt->P > 0) {
+        DC_LAUNCH(ctx, plane_of_kernel, (unsigned)dc_cdiv(pt->P, 256), 256, 0, d_off, B, pt->P, pt->plane_of);
+        DC_CHECK_LAUNCH();
+    }
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));    // offsets is caller memory (pageable)
+    return DINCAE_OK;
+}
+
+// point-cloud cost of all chains (src/points.jl:354-426) (+ gradients w.r.t. raw when train)
+int32_t points_loss(dincae_model* M, PointTruth& pt, int B, int64_t n_valid_global, bool train) {
+    dincae_ctx* ctx = M->ctx;
+    DC_REQUIRE(M->O == 1, DINCAE_EUNSUPPORTED, "point loss supports noutput == 1 (src/points.jl:573)");
+    const int W = M->cfg.W, H = M->cfg.H;
+    const int64_t npix = (int64_t)W * H;
+    const int64_t P = pt.P;
+    float* mv = M->pt_buf;
+    float* gms = M->pt_buf + 2 * M->pt_cap;
+    if (n_valid_global >= 0) {
+        unsigned long long tmp = (unsigned long long)n_valid_global;
+        DC_CHECK_CUDA(cudaMemcpyAsync(M->d_nvalid, &tmp, sizeof(tmp), cudaMemcpyHostToDevice, ctx->stream));
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    } else {
+        DC_CHECK_CUDA(cudaMemsetAsync(M->d_nvalid, 0, sizeof(unsigned long long), ctx->stream));
+        if (P > 0) {
+            DC_LAUNCH(ctx, count_pts_kernel, 64, 256, 0, pt.x + P, P, M->d_nvalid);
+            DC_CHECK_LAUNCH();
+        }
+    }
+    DC_LAUNCH(ctx, inv_n_kernel, 1, 32, 0, M->d_nvalid, 1, M->d_inv_n);
+    DC_CHECK_LAUNCH();
+    HeadParams hp = head_params(M);
+    K4Batch kb{pt.pos, pt.plane_of, nullptr, P, W, H, B, 2 * npix, npix, 2};
+    void* sc = nullptr;
+    if (train) DC_TRY(dc_scratch(ctx, k4_scatter_scratch_bytes(P), &sc));
+    for (int c = 0; c < M->nchains; c++) {
+        const float wgt = M->cfg.loss_weights[c];
+        DC_TRY(k3_head(ctx, M->cb[c].RAW, B, 1, npix, hp.gamma, M->MS));
+        DC_TRY(k4_gather(ctx, kb, M->MS, mv));                                     // interpnd of m and sigma2, src/points.jl:399-402
+        DC_TRY(k3_loss_points(ctx, mv, pt.x, P, hp, M->d_inv_n, wgt, M->d_loss, train ? gms : nullptr, M->red_scratch, M->red_scratch_bytes));
+        if (train) {
+            // pullback of interpnd = interp_adjn (src/points.jl:36-43), both fields in one sorted pass
+            DC_TRY(k4_scatter_sorted(ctx, kb, gms, gms + P, M->GMS, sc, ctx->scratch_bytes));
+        }
+        DC_TRY(k3_head_bwd(ctx, M->cb[c].RAW, M->MS, train ? M->GMS : nullptr, B, 1, W, H, hp, wgt, M->d_loss, train ? M->cb[c].GRAW : nullptr,
+                           M->red_scratch, M->red_scratch_bytes));
+    }
+    return DINCAE_OK;
+}
+
+int32_t backward_all(dincae_model* M, int B) {
+    DC_TRY(ensure_wT(M));
+    for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
+    DC_LAUNCH(M->ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t read_loss(dincae_model* M, bool from_slot, float* out_f, double* out_d) {
+    dincae_ctx* ctx = M->ctx;
+    void* pin = nullptr;
+    DC_TRY(dc_pinned(ctx, 64, &pin));
+    float* df = (float*)(M->d_loss + 2);
+    double* dd = M->d_loss + 3;
+    DC_LAUNCH(ctx, total_loss_kernel, 1, 1, 0, from_slot ? M->g + M->n_int : (const float*)nullptr, M->d_loss, df, dd);
+    DC_CHECK_LAUNCH();
+    DC_CHECK_CUDA(cudaMemcpyAsync(pin, M->d_loss + 2, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (out_f) *out_f = *(float*)pin;
+    if (out_d) *out_d = *(double*)((char*)pin + 8);
+    return DINCAE_OK;
+}
+
+// Flux order <-> internal padded layout (host side)
+void flux_to_internal(const dincae_model* M, const float* flux, std::vector<float>& internal) {
+    internal.assign((size_t)M->n_int + 1, 0.f);
+    for (int c = 0; c < M->nchains; c++)
+        for (int kind = 0; kind < 2; kind++)
+            for (int l = 0; l < M->L; l++) {
+                const LayerInfo& y = kind == 0 ? M->enc[c][l] : M->dec[c][l];
+                for (int co = 0; co < y.Cout; co++) {
+                    for (int ci = 0; ci < y.Cin; ci++)
+                        for (int b = 0; b < 3; b++)
+                            for (int a = 0; a < 3; a++) {
+                                int ky = 2 - b, kx = 2 - a;      // true convolution -> cross-correlation taps
+                                internal[y.w_off + ((size_t)(ky * 3 + kx) * y.Cin_p + ci) * y.Cout_p + co] =
+                                    flux[y.flux_w_off + a + 3 * (b + 3 * (ci + (size_t)y.Cin * co))];
+                            }
+                    internal[y.b_off + co] = flux[y.flux_b_off + co];
+                }
+            }
+}
+void internal_to_flux(const dincae_model* M, const std::vector<float>& internal, float* flux) {
+    for (int c = 0; c < M->nchains; c++)
+        for (int kind = 0; kind < 2; kind++)
+            for (int l = 0; l < M->L; l++) {
+                const LayerInfo& y = kind == 0 ? M->enc[c][l] : M->dec[c][l];
+                for (int co = 0; co < y.Cout; co++) {
+                    for (int ci = 0; ci < y.Cin; ci++)
+                        for (int b = 0; b < 3; b++)
+                            for (int a = 0; a < 3; a++) {
+                                int ky = 2 - b, kx = 2 - a;
+                                flux[y.flux_w_off + a + 3 * (b + 3 * (ci + (size_t)y.Cin * co))] =
+                                    internal[y.w_off + ((size_t)(ky * 3 + kx) * y.Cin_p + ci) * y.Cout_p + co];
+                            }
+                    flux[y.flux_b_off + co] = internal[y.b_off + co];
+                }
+            }
+}
+
+int32_t upload_internal(dincae_model* M, float* dst, const float* flux) {
+    std::vector<float> tmp;
+    flux_to_internal(M, flux, tmp);
+    DC_CHECK_CUDA(cudaMemcpyAsync(dst, tmp.data(), sizeof(float) * M->n_int, cudaMemcpyHostToDevice, M->ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(M->ctx->stream));
+    return DINCAE_OK;
+}
+int32_t download_internal(dincae_model* M, const float* src, float* flux) {
+    std::vector<float> tmp((size_t)M->n_int + 1);
+    DC_CHECK_CUDA(cudaMemcpyAsync(tmp.data(), src, sizeof(float) * M->n_int, cudaMemcpyDeviceToHost, M->ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(M->ctx->stream));
+    internal_to_flux(M, tmp, flux);
+    return DINCAE_OK;
+}
+
+}  // namespace
+
+int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool) {
+    for (int c = 0; c < M->nchains; c++) DC_TRY(chain_forward(M, c, d_xin, B));
+    return DINCAE_OK;
+}
+
+int32_t model_head_last(dincae_model* M, int B, float* d_out) {
+    return k3_head(M->ctx, M->cb[M->nchains - 1].RAW, B, M->O, (int64_t)M->cfg.W * M->cfg.H, M->cfg.gamma, d_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg, dincae_model** out) {
+    DC_REQUIRE(ctx && cfg && out, DINCAE_EINVAL, "dincae_model_create: NULL argument");
+    DC_REQUIRE(cfg->W >= 2 && cfg->H >= 2 && cfg->ninput >= 1, DINCAE_EINVAL, "dincae_model_create: bad W/H/ninput");
+    DC_REQUIRE(cfg->nlevels >= 1 && cfg->nlevels <= DINCAE_MAX_LEVELS, DINCAE_EINVAL, "dincae_model_create: nlevels %d outside [1,%d]", cfg->nlevels, DINCAE_MAX_LEVELS);
+    DC_REQUIRE(cfg->nchains >= 1 && cfg->nchains <= DINCAE_MAX_CHAINS, DINCAE_EINVAL, "dincae_model_create: nchains %d outside [1,%d]", cfg->nchains, DINCAE_MAX_CHAINS);
+    DC_REQUIRE(cfg->noutput >= 1 && cfg->noutput <= 4, DINCAE_EUNSUPPORTED, "dincae_model_create: noutput %d outside [1,4]", cfg->noutput);
+    DC_REQUIRE(cfg->upsampling == DINCAE_UP_NEAREST || cfg->upsampling == DINCAE_UP_BILINEAR, DINCAE_EUNSUPPORTED, "dincae_model_create: unknown upsampling_method %d", cfg->upsampling);
+    DC_REQUIRE(!(cfg->skip_mask & 1u), DINCAE_EUNSUPPORTED, "dincae_model_create: a skip connection at level 1 needs ninput == 2*noutput and is not supported");
+    DC_REQUIRE(cfg->max_batch >= 1, DINCAE_EINVAL, "dincae_model_create: max_batch < 1");
+    DC_REQUIRE(cfg->precision == DINCAE_PREC_FP32 || cfg->precision == DINCAE_PREC_TF32, DINCAE_EUNSUPPORTED, "dincae_model_create: unknown precision %d", cfg->precision);
+    for (int l = 0; l < cfg->nlevels; l++) DC_REQUIRE(cfg->nfilter[l] >= 1, DINCAE_EINVAL, "dincae_model_create: nfilter[%d] < 1", l);
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+
+    dincae_model* M = new dincae_model();
+    M->ctx = ctx; M->cfg = *cfg; M->L = cfg->nlevels; M->nchains = cfg->nchains; M->O = cfg->noutput; M->maxB = cfg->max_batch;
+    M->nco = dc_round_up(2 * M->O, 4);
+    const int L = M->L;
+    M->Hl[0] = cfg->H; M->Wl[0] = cfg->W;
+    for (int l = 0; l < L; l++) { M->Hl[l + 1] = M->Hl[l] / 2 + M->Hl[l] % 2; M->Wl[l + 1] = M->Wl[l] / 2 + M->Wl[l] % 2; }   // sz_small, src/model.jl:258-261
+
+    // ---- topology and parameter layout (Flux.trainables order: enc1..encL, decL..dec1 per chain)
+    M->enc.resize(M->nchains); M->dec.resize(M->nchains);
+    int64_t off = 0, foff = 0, toff = 0;
+    std::vector<WLayerDesc> wtab;
+    for (int c = 0; c < M->nchains; c++) {
+        std::vector<int> encf(L + 1), decf(L + 1);
+        encf[0] = cfg->ninput + (c > 0 ? 2 * M->O : 0);            // enc_nfilter2[1] += dec_nfilter[1], src/model.jl:333
+        decf[0] = 2 * M->O;
+        for (int l = 0; l < L; l++) { encf[l + 1] = cfg->nfilter[l]; decf[l + 1] = cfg->nfilter[l]; }
+        M->enc[c].resize(L); M->dec[c].resize(L);
+        auto fill = [&](LayerInfo& y, int cin, int cout) {
+            y.Cin = cin; y.Cout = cout; y.Cin_p = dc_round_up(cin, 4); y.Cout_p = dc_round_up(cout, 4);
+            y.Kpad = dc_round_up(9 * y.Cin_p, 16); y.KpadT = dc_round_up(9 * y.Cout_p, 16);
+            y.w_off = off; off += (int64_t)y.Kpad * y.Cout_p;
+            y.b_off = off; off += y.Cout_p;
+            y.flux_w_off = foff; foff += (int64_t)9 * cin * cout;
+            y.flux_b_off = foff; foff += cout;
+            y.wT_off = toff; toff += (int64_t)y.KpadT * y.Cin_p;
+        };
+        for (int l = 0; l < L; l++) fill(M->enc[c][l], encf[l], encf[l + 1]);
+        for (int l = L - 1; l >= 0; l--) fill(M->dec[c][l], decf[l + 1], decf[l]);
+    }
+    M->n_int = off; M->n_flux = foff; M->n_wT = toff;
+    // table for the transposed copies, in wT order; each entry copies 9*Cin_p*Cout_p values
+    {
+        // make_wT walks layers by cumulative n, so wT offsets must be visited in the same order as the table
+        std::vector<const LayerInfo*> order;
+        for (int c = 0; c < M->nchains; c++) {
+            for (int l = 0; l < L; l++) order.push_back(&M->enc[c][l]);
+            for (int l = L - 1; l >= 0; l--) order.push_back(&M->dec[c][l]);
+        }
+        int64_t tot = 0;
+        for (const LayerInfo* y : order) {
+            WLayerDesc d;
+            d.w_off = y->w_off; d.wT_off = y->wT_off; d.Cin_p = y->Cin_p; d.Cout_p = y->Cout_p; d.n = (int64_t)9 * y->Cin_p * y->Cout_p;
+            wtab.push_back(d);
+            tot += d.n;
+        }
+        M->n_wT_copy = tot;
+        M->n_wlayers = (int)wtab.size();
+    }
+
+    // ---- workspace plan: one allocation
+    struct Want { void** p; size_t bytes; };
+    std::vector<Want> wants;
+    auto want = [&](void** p, size_t bytes) { wants.push_back(Want{p, (bytes + 255) / 256 * 256}); };
+    const size_t Bm = (size_t)M->maxB;
+    auto act = [&](int l, int Cp) { return sizeof(float) * Bm * M->Hl[l] * M->Wl[l] * Cp; };
+    want((void**)&M->w, sizeof(float) * (M->n_int + 4));
+    want((void**)&M->g, sizeof(float) * (M->n_int + 4));
+    want((void**)&M->m, sizeof(float) * (M->n_int + 4));
+    want((void**)&M->v, sizeof(float) * (M->n_int + 4));
+    want((void**)&M->wT, sizeof(float) * (M->n_wT + 4));
+    want((void**)&M->d_wtab, sizeof(WLayerDesc) * wtab.size());
+    const size_t planar_out = sizeof(float) * Bm * 2 * M->O * cfg->W * cfg->H;
+    const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR;
+    for (int c = 0; c < M->nchains; c++) {
+        ChainBufs& cb = M->cb[c];
+        memset(&cb, 0, sizeof(cb));
+        want((void**)&cb.X[0], act(0, M->enc[c][0].Cin_p));
+        for (int l = 0; l < L; l++) {
+            want((void**)&cb.A[l], act(l, M->enc[c][l].Cout_p));
+            want((void**)&cb.X[l + 1], act(l + 1, M->enc[c][l].Cout_p));
+            if (l >= 1) want((void**)&cb.R[l], act(l, M->dec[c][l].Cout_p));
+            if (bil) want((void**)&cb.U[l], act(l, M->dec[c][l].Cin_p));
+        }
+        want((void**)&cb.RAW, planar_out);
+        want((void**)&cb.GRAW, planar_out);
+    }
+    {
+        // gradient workspace: channel counts are the same for every chain except enc[.][0].Cin_p (unused here)
+        const std::vector<LayerInfo>& e = M->enc[0];
+        const std::vector<LayerInfo>& d = M->dec[0];
+        want((void**)&M->GD0, act(0, M->nco));
+        for (int l = 0; l < L; l++) {
+            want((void**)&M->GU[l], act(l, d[l].Cin_p));
+            want((void**)&M->GC[l], act(l, e[l].Cout_p));
+            if (l >= 1) {
+                want((void**)&M->G[l], act(l, d[l].Cout_p));
+                want((void**)&M->GD[l], act(l, d[l].Cout_p));
+                want((void**)&M->XG[l], act(l, e[l].Cin_p));
+            }
+        }
+        want((void**)&M->G[L], act(L, d[L - 1].Cin_p));
+    }
+    want((void**)&M->MS, planar_out);
+    want((void**)&M->GMS, planar_out);
+    want((void**)&M->d_loss, sizeof(double) * 8);
+    want((void**)&M->d_inv_n, sizeof(float) * 16);
+    want((void**)&M->d_nvalid, sizeof(unsigned long long) * 16);
+    M->red_scratch_bytes = k3_scratch_bytes(0);
+    want(&M->red_scratch, M->red_scratch_bytes);
+    size_t wgb = 0;
+    for (int c = 0; c < M->nchains; c++)
+        for (int l = 0; l < L; l++) {
+            size_t a = k2_wgrad_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
+            size_t b = k2_wgrad_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
+            wgb = a > wgb ? a : wgb;
+            wgb = b > wgb ? b : wgb;
+        }
+    M->wg_scratch_bytes = wgb;
+    want(&M->wg_scratch, wgb);
+    want((void**)&M->in_xin, sizeof(float) * Bm * cfg->ninput * cfg->W * cfg->H);
+    want((void**)&M->in_xtrue, planar_out);
+    size_t total = 0;
+    for (auto& wnt : wants) total += wnt.bytes;
+    cudaError_t e = cudaMalloc(&M->all_mem, total);
+    if (e != cudaSuccess) {
+        dincae_set_error("dincae_model_create: cannot allocate %.1f MB of workspace for max_batch=%d: %s", total / 1048576.0, M->maxB, cudaGetErrorString(e));
+        delete M;
+        return DINCAE_ENOMEM;
+    }
+    DC_CHECK_CUDA(cudaMemsetAsync(M->all_mem, 0, total, ctx->stream));
+    {
+        char* p = (char*)M->all_mem;
+        for (auto& wnt : wants) { *wnt.p = p; p += wnt.bytes; }
+    }
+    DC_CHECK_CUDA(cudaMemcpyAsync(M->d_wtab, wtab.data(), sizeof(WLayerDesc) * wtab.size(), cudaMemcpyHostToDevice, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out = M;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_model_destroy(dincae_model* M) {
+    if (!M) return DINCAE_OK;
+    cudaSetDevice(M->ctx->device);
+    cudaStreamSynchronize(M->ctx->stream);
+    if (M->all_mem) cudaFree(M->all_mem);
+    if (M->pt_buf) cudaFree(M->pt_buf);
+    delete M;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_model_num_params(dincae_model* M, int64_t* n) {
+    DC_REQUIRE(M && n, DINCAE_EINVAL, "dincae_model_num_params: NULL argument");
+    *n = M->n_flux;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_model_get_params(dincae_model* M, float* host, int64_t n) {
+    DC_REQUIRE(M && host, DINCAE_EINVAL, "dincae_model_get_params: NULL argument");
+    DC_REQUIRE(n == M->n_flux, DINCAE_ESIZE, "dincae_model_get_params: n=%lld but the model has %lld parameters", (long long)n, (long long)M->n_flux);
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    return download_internal(M, M->w, host);
+}
+
+extern "C" int32_t dincae_model_set_params(dincae_model* M, const float* host, int64_t n) {
+    DC_REQUIRE(M && host, DINCAE_EINVAL, "dincae_model_set_params: NULL argument");
+    DC_REQUIRE(n == M->n_flux, DINCAE_ESIZE, "dincae_model_set_params: n=%lld but the model has %lld parameters", (long long)n, (long long)M->n_flux);
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    M->wT_dirty = true;
+    return upload_internal(M, M->w, host);
+}
+
+extern "C" int32_t dincae_model_init_glorot(dincae_model* M, uint64_t seed) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_model_init_glorot: model is NULL");
+    // Flux glorot_uniform: U(-s, s), s = sqrt(6 / (fan_in + fan_out)), fan = 9*cin / 9*cout; biases zero.
+    // Host-side splitmix64 stream (one-time set-up, not the hot path).
+    std::vector<float> flux((size_t)M->n_flux, 0.f);
+    uint64_t st = seed * 0x9E3779B97F4A7C15ull + 0x1234567ull;
+    auto next = [&]() {
+        st += 0x9E3779B97F4A7C15ull;
+        uint64_t z = st;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        return z ^ (z >> 31);
+    };
+    for (int c = 0; c < M->nchains; c++)
+        for (int kind = 0; kind < 2; kind++)
+            for (int l = 0; l < M->L; l++) {
+                const LayerInfo& y = kind == 0 ? M->enc[c][l] : M->dec[c][l];
+                double s = sqrt(6.0 / (9.0 * y.Cin + 9.0 * y.Cout));
+                for (int64_t i = 0; i < (int64_t)9 * y.Cin * y.Cout; i++) {
+                    double u = (double)(next() >> 11) * (1.0 / 9007199254740992.0);
+                    flux[y.flux_w_off + i] = (float)((2.0 * u - 1.0) * s);
+                }
+            }
+    return dincae_model_set_params(M, flux.data(), M->n_flux);
+}
+
+extern "C" int32_t dincae_model_get_opt_state(dincae_model* M, float* host_m, float* host_v, int64_t n, int64_t* t) {
+    DC_REQUIRE(M && host_m && host_v && t, DINCAE_EINVAL, "dincae_model_get_opt_state: NULL argument");
+    DC_REQUIRE(n == M->n_flux, DINCAE_ESIZE, "dincae_model_get_opt_state: wrong length");
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    DC_TRY(download_internal(M, M->m, host_m));
+    DC_TRY(download_internal(M, M->v, host_v));
+    *t = M->t_step;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_model_set_opt_state(dincae_model* M, const float* host_m, const float* host_v, int64_t n, int64_t t) {
+    DC_REQUIRE(M && host_m && host_v, DINCAE_EINVAL, "dincae_model_set_opt_state: NULL argument");
+    DC_REQUIRE(n == M->n_flux && t >= 0, DINCAE_ESIZE, "dincae_model_set_opt_state: wrong length or negative t");
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    DC_TRY(upload_internal(M, M->m, host_m));
+    DC_TRY(upload_internal(M, M->v, host_v));
+    M->t_step = t;
+    M->bt1 = pow((double)M->cfg.adam_beta1, (double)t);
+    M->bt2 = pow((double)M->cfg.adam_beta2, (double)t);
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_forward(dincae_model* M, const float* xin, int32_t B, float* out, int32_t loc) {
+    DC_TRY(check_batch(M, B, "dincae_forward"));
+    DC_REQUIRE(xin && out, DINCAE_EINVAL, "dincae_forward: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float* dx;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(model_forward(M, dx, B, false));
+    if (loc == DINCAE_DEVICE) return model_head_last(M, B, out);
+    DC_TRY(model_head_last(M, B, M->MS));
+    DC_CHECK_CUDA(cudaMemcpyAsync(out, M->MS, sizeof(float) * (size_t)B * 2 * M->O * M->cfg.W * M->cfg.H, cudaMemcpyDeviceToHost, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_count_valid(dincae_model* M, const float* xtrue, int32_t B, int32_t loc, int64_t* n_valid) {
+    DC_TRY(check_batch(M, B, "dincae_count_valid"));
+    DC_REQUIRE(xtrue && n_valid, DINCAE_EINVAL, "dincae_count_valid: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float* dy;
+    DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
+    DC_TRY(k3_count_valid(ctx, dy, B, M->O, (int64_t)M->cfg.W * M->cfg.H, M->d_nvalid));
+    unsigned long long tmp[16];
+    DC_CHECK_CUDA(cudaMemcpyAsync(tmp, M->d_nvalid, sizeof(unsigned long long) * M->O, cudaMemcpyDeviceToHost, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int v = 0; v < M->O; v++) n_valid[v] = (int64_t)tmp[v];
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_loss(dincae_model* M, const float* xin, const float* xtrue, int32_t B, int32_t loc, double* loss) {
+    DC_TRY(check_batch(M, B, "dincae_loss"));
+    DC_REQUIRE(xin && xtrue && loss, DINCAE_EINVAL, "dincae_loss: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float *dx, *dy;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
+    DC_TRY(model_forward(M, dx, B, false));
+    DC_TRY(gridded_loss(M, dy, B, nullptr, false));
+    DC_TRY(k3_reg(ctx, M->w, M->n_int, M->cfg.l1_beta, M->cfg.l2_beta, M->d_loss + 1, M->red_scratch, M->red_scratch_bytes));
+    return read_loss(M, false, nullptr, loss);
+}
+
+extern "C" int32_t dincae_grad_step(dincae_model* M, const float* xin, const float* xtrue, int32_t B,
+                                    const int64_t* n_valid_global, int32_t loc) {
+    DC_TRY(check_batch(M, B, "dincae_grad_step"));
+    DC_REQUIRE(xin && xtrue, DINCAE_EINVAL, "dincae_grad_step: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float *dx, *dy;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
+    DC_TRY(model_forward(M, dx, B, true));
+    DC_TRY(gridded_loss(M, dy, B, n_valid_global, true));
+    return backward_all(M, B);
+}
+
+extern "C" int32_t dincae_grad_buffer(dincae_model* M, float** dev_ptr, int64_t* n) {
+    DC_REQUIRE(M && dev_ptr && n, DINCAE_EINVAL, "dincae_grad_buffer: NULL argument");
+    *dev_ptr = M->g;
+    *n = M->n_int + 1;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_apply_step: model is NULL");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    M->t_step += 1;
+    M->bt1 *= (double)M->cfg.adam_beta1;
+    M->bt2 *= (double)M->cfg.adam_beta2;
+    AdamParams p;
+    p.lr = lr; p.beta1 = M->cfg.adam_beta1; p.beta2 = M->cfg.adam_beta2; p.eps = M->cfg.adam_eps;
+    p.clip = M->cfg.clip_grad; p.l1 = M->cfg.l1_beta; p.l2 = M->cfg.l2_beta;
+    p.inv_bc1 = (float)(1.0 / (1.0 - M->bt1));
+    p.inv_bc2 = (float)(1.0 / (1.0 - M->bt2));
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss + 1, 0, sizeof(double), ctx->stream));
+    DC_TRY(k3_adam(ctx, M->w, M->g, M->m, M->v, M->n_int, p, M->d_loss + 1, M->red_scratch, M->red_scratch_bytes));
+    M->wT_dirty = true;
+    if (loss) return read_loss(M, true, loss, nullptr);
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_train_step(dincae_model* M, const float* xin, const float* xtrue, int32_t B, float lr,
+                                     int32_t loc, float* loss) {
+    DC_TRY(dincae_grad_step(M, xin, xtrue, B, nullptr, loc));
+    return dincae_apply_step(M, lr, loss);
+}
+
+extern "C" int32_t dincae_loss_points(dincae_model* M, const float* xin, const float* pos, const float* x,
+                                      const int64_t* offsets, int32_t B, int32_t loc, double* loss) {
+    DC_TRY(check_batch(M, B, "dincae_loss_points"));
+    DC_REQUIRE(xin && loss, DINCAE_EINVAL, "dincae_loss_points: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float* dx;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    PointTruth pt;
+    DC_TRY(stage_points(M, pos, x, offsets, B, loc, &pt));
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
+    DC_TRY(model_forward(M, dx, B, false));
+    int32_t st = points_loss(M, pt, B, -1, false);
+    dc_stage_free(ctx, &pt.spos);
+    dc_stage_free(ctx, &pt.sx);
+    DC_TRY(st);
+    DC_TRY(k3_reg(ctx, M->w, M->n_int, M->cfg.l1_beta, M->cfg.l2_beta, M->d_loss + 1, M->red_scratch, M->red_scratch_bytes));
+    return read_loss(M, false, nullptr, loss);
+}
+
+extern "C" int32_t dincae_grad_step_points(dincae_model* M, const float* xin, const float* pos, const float* x,
+                                           const int64_t* offsets, int32_t B, int64_t n_valid_global, int32_t loc) {
+    DC_TRY(check_batch(M, B, "dincae_grad_step_points"));
+    DC_REQUIRE(xin != nullptr, DINCAE_EINVAL, "dincae_grad_step_points: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float* dx;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    PointTruth pt;
+    DC_TRY(stage_points(M, pos, x, offsets, B, loc, &pt));
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
+    DC_TRY(model_forward(M, dx, B, true));
+    int32_t st = points_loss(M, pt, B, n_valid_global, true);
+    dc_stage_free(ctx, &pt.spos);
+    dc_stage_free(ctx, &pt.sx);
+    DC_TRY(st);
+    return backward_all(M, B);
+}
+
+extern "C" int32_t dincae_train_step_points(dincae_model* M, const float* xin, const float* pos, const float* x,
+                                            const int64_t* offsets, int32_t B, float lr, int32_t loc, float* loss) {
+    DC_TRY(dincae_grad_step_points(M, xin, pos, x, offsets, B, -1, loc));
+    return dincae_apply_step(M, lr, loss);
+}
+
+extern "C" int32_t dincae_reconstruct_range(dincae_model* M, dincae_gridded* ds, int64_t t0, int64_t t1,
+                                            int32_t count, float fill_value, float* m_out, float* sigma_out, int32_t loc) {
+    DC_REQUIRE(M && ds && m_out && sigma_out, DINCAE_EINVAL, "dincae_reconstruct_range: NULL argument");
+    DC_REQUIRE(0 <= t0 && t0 <= t1 && t1 <= ds->N, DINCAE_EINVAL, "dincae_reconstruct_range: bad range [%lld,%lld) of %lld", (long long)t0, (long long)t1, (long long)ds->N);
+    DC_REQUIRE(count >= 1, DINCAE_EINVAL, "dincae_reconstruct_range: count must be >= 1 (ds.attrib[\"count\"], src/data.jl:621-624)");
+    DC_REQUIRE(ds->W == M->cfg.W && ds->H == M->cfg.H && 4 + 2 * ds->T * ds->V == M->cfg.ninput && ds->nout == M->O, DINCAE_EINVAL,
+               "dincae_reconstruct_range: dataset (W=%d,H=%d,channels=%d,nout=%d) does not match the model", ds->W, ds->H, 4 + 2 * ds->T * ds->V, ds->nout);
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const int64_t npix = (int64_t)ds->W * ds->H, nsteps = t1 - t0;
+    if (nsteps == 0) return DINCAE_OK;
+    float *dm = m_out, *dsg = sigma_out;
+    const size_t nres = (size_t)npix * nsteps * M->O;
+    if (loc == DINCAE_HOST) {
+        DC_CHECK_CUDA(cudaMallocAsync((void**)&dm, sizeof(float) * 2 * nres, ctx->stream));
+        dsg = dm + nres;
+        if (count > 1) {
+            DC_CHECK_CUDA(cudaMemcpyAsync(dm, m_out, sizeof(float) * nres, cudaMemcpyHostToDevice, ctx->stream));
+            DC_CHECK_CUDA(cudaMemcpyAsync(dsg, sigma_out, sizeof(float) * nres, cudaMemcpyHostToDevice, ctx->stream));
+        }
+    }
+    std::vector<int64_t> idx(M->maxB);
+    for (int64_t s = 0; s < nsteps; s += M->maxB) {
+        int B = (int)(nsteps - s < M->maxB ? nsteps - s : M->maxB);
+        for (int b = 0; b < B; b++) idx[b] = t0 + s + b;          // DataBatches(train=false): sequential, no perturbation
+        DC_TRY(k1_assemble(ds, idx.data(), nullptr, 0, 0, B, M->in_xin, M->in_xtrue));
+        DC_TRY(model_forward(M, M->in_xin, B, false));
+        DC_TRY(model_head_last(M, B, M->MS));
+        DC_TRY(k3_savesample(ctx, M->MS, B, M->O, npix, ds->d_mean_out, ds->d_landmask, count, fill_value,
+                             dm + (size_t)s * npix, dsg + (size_t)s * npix, npix * nsteps));
+    }
+    if (loc == DINCAE_HOST) {
+        DC_CHECK_CUDA(cudaMemcpyAsync(m_out, dm, sizeof(float) * nres, cudaMemcpyDeviceToHost, ctx->stream));
+        DC_CHECK_CUDA(cudaMemcpyAsync(sigma_out, dsg, sizeof(float) * nres, cudaMemcpyDeviceToHost, ctx->stream));
+        DC_CHECK_CUDA(cudaFreeAsync(dm, ctx->stream));
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return DINCAE_OK;
+}

@@ -1,0 +1,61 @@
+// Model object of libdincae_b200: topology (genmodel/recmodel4, src/model.jl:242-363), flat parameter /
+// gradient / Adam buffers and the per-level activation workspace.
+#pragma once
+#include "common.cuh"
+#include "k2_conv.cuh"
+#include "k3_loss.cuh"
+#include <vector>
+
+struct LayerInfo {
+    int Cin, Cout, Cin_p, Cout_p;
+    int Kpad;            // round_up(9*Cin_p,16): rows of the forward weight matrix
+    int KpadT;           // round_up(9*Cout_p,16): rows of the transposed matrix used by the data gradient
+    int64_t w_off, b_off;    // offsets in the internal flat parameter buffer
+    int64_t wT_off;          // offset in the transposed-weight buffer
+    int64_t flux_w_off, flux_b_off;   // offsets in the Flux.trainables order
+};
+
+struct ChainBufs {
+    float* X[DINCAE_MAX_LEVELS + 1];   // X[l]: input of level l (X[0] = packed input), NHWC
+    float* A[DINCAE_MAX_LEVELS];       // relu(conv_enc_l)
+    float* R[DINCAE_MAX_LEVELS];       // relu(conv_dec_l), l >= 1
+    float* U[DINCAE_MAX_LEVELS];       // bilinear only: materialised upsampled input of conv_dec_l
+    float* RAW;                        // planar (W,H,2*nout,B): raw chain output
+    float* GRAW;                       // planar gradient w.r.t. RAW
+};
+
+struct dincae_model {
+    dincae_ctx* ctx = nullptr;
+    dincae_config cfg;
+    int L = 0, nchains = 0, O = 0, nco = 4, maxB = 0;
+    int Hl[DINCAE_MAX_LEVELS + 1], Wl[DINCAE_MAX_LEVELS + 1];
+    std::vector<std::vector<LayerInfo>> enc, dec;     // [chain][level]
+    int64_t n_flux = 0, n_int = 0, n_wT = 0, n_wT_copy = 0;
+    float *w = nullptr, *g = nullptr, *m = nullptr, *v = nullptr, *wT = nullptr;
+    WLayerDesc* d_wtab = nullptr;
+    int n_wlayers = 0;
+    bool wT_dirty = true;
+    ChainBufs cb[DINCAE_MAX_CHAINS];
+    // gradient workspace shared by all chains
+    float* GD0 = nullptr;
+    float *GU[DINCAE_MAX_LEVELS], *G[DINCAE_MAX_LEVELS + 1], *GD[DINCAE_MAX_LEVELS], *GC[DINCAE_MAX_LEVELS], *XG[DINCAE_MAX_LEVELS + 1];
+    float* MS = nullptr;               // planar (m, sigma2)
+    float* GMS = nullptr;              // planar gradient w.r.t. (m, sigma2) (point loss)
+    double* d_loss = nullptr;          // [0] cost terms, [1] regularisation
+    float* d_inv_n = nullptr;          // [nout]
+    unsigned long long* d_nvalid = nullptr;
+    void* red_scratch = nullptr;
+    size_t red_scratch_bytes = 0;
+    void* wg_scratch = nullptr;
+    size_t wg_scratch_bytes = 0;
+    float *in_xin = nullptr, *in_xtrue = nullptr;     // device staging of host mini-batches
+    // point-loss workspace (grown on demand)
+    float* pt_buf = nullptr;
+    size_t pt_cap = 0;                 // in points
+    void* all_mem = nullptr;
+    int64_t t_step = 0;
+    double bt1 = 1.0, bt2 = 1.0;       // beta^t
+};
+
+int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool train);
+int32_t model_head_last(dincae_model* M, int B, float* d_out);    // (m, sigma2) of the last chain into d_out (planar)

@@ -1,0 +1,288 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle.  Tolerances:
+integer work (cells, masks, inside flags) bit-exact; interp/adjoint bit-exact vs the sequential C loop;
+float outputs (m, sigma2, loss, gradients) rtol 1e-3 (north_star), tighter where the path is FP32."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import model as OM, data as OD, points as OP, cbind
+
+
+@pytest.fixture(scope="module")
+def ctx(pkg):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return pkg.Context(0)
+
+
+# ---------------------------------------------------------------- K4
+def test_interp_adjoint_golden(pkg, ctx):
+    # test/test_interp_adjoint.jl:20-47
+    pos = np.array([[1.5, 2.0], [5.0, 2.3]], np.float32)
+    A = pkg.interp_adjn(pos, np.array([3, 4], np.float32), (6, 7), ctx)
+    ref = np.zeros((6, 7), np.float32)
+    ref[0, 1] = ref[1, 1] = 1.5; ref[4, 1] = 0.7 * 4; ref[4, 2] = 0.3 * 4
+    np.testing.assert_allclose(A, ref, rtol=1e-6)
+    dA = pkg.interp_adjn(pos, np.ones(2, np.float32), (6, 7), ctx)      # gradient of sum(interpnd(pos,B)) w.r.t. B
+    ref = np.zeros((6, 7), np.float32)
+    ref[0, 1] = ref[1, 1] = 0.5; ref[4, 1] = 0.7; ref[4, 2] = 0.3
+    np.testing.assert_allclose(dA, ref, rtol=1e-6)
+
+
+@pytest.mark.parametrize("W,H,P", [(6, 7, 2), (37, 23, 500), (177, 69, 3000), (300, 200, 100000), (1024, 1024, 50000)])
+def test_interp_and_adjoint_vs_oracle(pkg, ctx, W, H, P):
+    rng = np.random.default_rng(P)
+    pos = np.stack([rng.uniform(1, W, P), rng.uniform(1, H, P)], 1).astype(np.float32)
+    pos = np.minimum(pos, np.nextafter(np.array([W, H], np.float32), 0)).astype(np.float32)
+    if P >= 500:                       # collisions: many points in the same cell, some exactly on nodes
+        pos[:P // 10] = pos[0]
+        pos[P // 10:P // 5] = np.floor(pos[P // 10:P // 5])
+    A = rng.standard_normal((W, H)).astype(np.float32)
+    v = rng.standard_normal(P).astype(np.float32)
+    # integer part bit-exact
+    assert np.array_equal(pkg.api.interp_cells(pos, ctx), OP.interp_cells(pos).astype(np.int32))
+    # gather: same arithmetic order as the reference loop -> bit-exact vs the plain-C restatement
+    assert np.array_equal(pkg.interpnd(pos, A, ctx), cbind.interpnd(pos, A))
+    # adjoint: sorted segmented sum keeps the sequential (point, corner) order -> bit-exact, no float atomics
+    out = pkg.interp_adjn(pos, v, (W, H), ctx)
+    assert np.array_equal(out, cbind.interp_adjn(pos, v, (W, H)))
+    assert np.array_equal(out, pkg.interp_adjn(pos, v, (W, H), ctx))          # run-to-run deterministic
+    # adjoint identity (test/test_interp_adjoint.jl:49-65)
+    lhs = float(np.dot(v.astype(np.float64), pkg.interpnd(pos, A, ctx).astype(np.float64)))
+    rhs = float(np.sum(A.astype(np.float64) * out.astype(np.float64)))
+    assert lhs == pytest.approx(rhs, rel=1e-4, abs=1e-3)
+
+
+def test_interp_edge_cases(pkg, ctx):
+    assert pkg.interpnd(np.zeros((0, 2), np.float32), np.ones((4, 4), np.float32), ctx).shape == (0,)
+    out = pkg.interp_adjn(np.zeros((0, 2), np.float32), np.zeros(0, np.float32), (4, 5), ctx)
+    assert out.shape == (4, 5) and not out.any()
+    # out-of-domain points are skipped (precondition of src/points.jl:45-50 violated): nothing is written out of bounds
+    pos = np.array([[0.5, 2.0], [4.0, 5.0], [2.5, 2.5], [np.nan, 1.0]], np.float32)
+    out = pkg.interp_adjn(pos, np.ones(4, np.float32), (4, 5), ctx)
+    assert np.isfinite(out).all() and out[1, 1] == 0.25
+    with pytest.raises(ValueError):
+        pkg.interp_adjn(np.ones((3, 2), np.float32), np.ones(2, np.float32), (4, 4), ctx)
+
+
+def test_posindices_bit_exact(pkg, ctx):
+    rng = np.random.default_rng(0)
+    grid = (np.arange(-7, 37.001, 0.25), np.arange(29, 46.001, 0.25))        # test/test_reconstruct_points.jl:27-31
+    lon = rng.uniform(-9, 39, 20000).astype(np.float32); lat = rng.uniform(27, 48, 20000).astype(np.float32)
+    lon[:4] = [-7, 37, -7.0001, 36.75]; lat[:4] = [29, 46, 29, 45.75]
+    pos, inside = pkg.api.posindices(grid, lon, lat, ctx)
+    pos_o, inside_o = OP.posindices(grid, lon, lat)
+    assert np.array_equal(inside, inside_o)
+    assert np.array_equal(pos, pos_o)
+
+
+# ---------------------------------------------------------------- K1
+def _cube(rng, W, H, V, N):
+    data = (rng.standard_normal((W, H, V, N)) + 15).astype(np.float32)
+    data[rng.random((W, H, V, N)) < 0.4] = np.nan
+    data[0, 0] = np.nan                              # a pixel never observed: NaN mean
+    return data
+
+
+@pytest.mark.parametrize("W,H,V,N,T", [(20, 14, 1, 12, 3), (33, 17, 2, 9, 5), (7, 5, 3, 4, 1)])
+def test_assembly_bit_exact(pkg, ctx, W, H, V, N, T):
+    rng = np.random.default_rng(W)
+    data = _cube(rng, W, H, V, N)
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    iso = [True] + [bool(v % 2) for v in range(1, V)]
+    kw = dict(train=True, ntime_win=T, isoutput=iso, obs_err_std=[1.0, 2.0, 0.5][:V], jitter_std=[0.05, 0.1, 0.2][:V])
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, **kw)
+    od = OD.NCData(lon, lat, days, data, **kw)
+    np.testing.assert_array_equal(ds.meandata, od.meandata)
+    idx = np.array([0, N - 1, N // 2, 1, 0])
+    xin, xtrue = ds.assemble(idx)                                     # train=false path: integer/copy work, bit-exact
+    xin_o, xtrue_o = od.batch(idx)
+    assert np.array_equal(xin, xin_o) and np.array_equal(xtrue, xtrue_o)
+    imask = np.array([3 % N, 0, N - 1, 2 % N, 1 % N])
+    xin, xtrue = ds.assemble(idx, imask, seed=77, sample_ctr0=1000)
+    xin_o, xtrue_o = od.batch(idx, imask, seed=77, sample_ctr0=1000)
+    assert np.array_equal(xtrue, xtrue_o)
+    assert np.array_equal(xin == 0, xin_o == 0)                       # transplanted cloud mask: bit-exact selection
+    np.testing.assert_allclose(xin, xin_o, rtol=0, atol=2e-6)         # jitter = Philox normals (logf/sincosf ulp differences)
+    cnt = ds.valid_counts(0)
+    assert np.array_equal(cnt, (~np.isnan(data[:, :, 0, :])).sum(axis=(0, 1)))
+    m = pkg.Model(ctx, pkg.ModelConfig(W=W, H=H, ninput=xin.shape[2], noutput=od.sizey()[2] // 2, enc_nfilter_internal=(4,), max_batch=8))
+    assert np.array_equal(m.count_valid(xtrue), (xtrue[:, :, 1::2] != 0).sum(axis=(0, 1, 3)))
+
+
+# ---------------------------------------------------------------- K2/K3: model, loss, gradients, Adam
+def _problem(rng, W, H, Cin, O, B):
+    xin = np.asfortranarray(rng.standard_normal((W, H, Cin, B)).astype(np.float32))
+    xt = np.asfortranarray(rng.standard_normal((W, H, 2 * O, B)).astype(np.float32))
+    xt[:, :, 1::2] = np.where(rng.random((W, H, O, B)) < 0.4, 0, rng.uniform(0.5, 2, (W, H, O, B))).astype(np.float32)
+    xt[:, :, 0::2] *= (xt[:, :, 1::2] != 0)
+    return xin, xt
+
+
+CASES = [
+    # W, H, Cin, O, filters, method, refine, l2, lap, truth_uncertain, B
+    (16, 16, 10, 1, (8, 16), "nearest", False, 0.0, 0.0, False, 3),
+    (20, 14, 10, 1, (8, 12, 16), "nearest", True, 1e-3, 0.0, False, 4),
+    (17, 9, 6, 1, (5, 7), "nearest", True, 1e-3, 0.0, False, 2),          # odd sizes: pad-including pool, crop-last (T12)
+    (23, 19, 16, 2, (6, 10), "nearest", False, 0.0, 0.0, True, 2),        # two outputs, truth_uncertain
+    (15, 18, 7, 1, (6, 9), "bilinear", True, 1e-4, 0.0, False, 2),        # bilinear align_corners (T13)
+    (14, 13, 8, 1, (5, 6), "nearest", False, 1e-4, 0.1, False, 2),        # Laplacian penalties
+    (177, 69, 60, 1, (25, 50, 75), "nearest", False, 1e-4, 0.0, False, 2),  # cfg4 shapes (Appendix B)
+]
+
+
+@pytest.mark.parametrize("W,H,Cin,O,F,method,refine,l2,lap,tu,B", CASES)
+def test_forward_loss_grad_vs_oracle(pkg, ctx, W, H, Cin, O, F, method, refine, l2, lap, tu, B):
+    rng = np.random.default_rng(W * H)
+    lw = (0.3, 0.7) if refine else (1.0,)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=Cin, noutput=O, enc_nfilter_internal=F, upsampling_method=method, loss_weights_refine=lw,
+                          regularization_L2_beta=l2, laplacian_penalty=lap, truth_uncertain=tu, max_batch=B, precision="fp32")
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=Cin, noutput=O, nfilter=list(F), upsampling_method=method, loss_weights_refine=lw,
+                          regularization_L2_beta=l2, laplacian_penalty=lap, truth_uncertain=tu)
+    model = pkg.Model(ctx, cfg, seed=5)
+    assert model.num_params == OM.num_params(ocfg)
+    flat = OM.init_params(ocfg, 11) + (rng.standard_normal(model.num_params) * 0.02).astype(np.float32)
+    model.set_params(flat)
+    assert np.array_equal(model.get_params(), flat)                    # Flux-order round trip
+    xin, xt = _problem(rng, W, H, Cin, O, B)
+    y = model(xin)
+    y_o = OM.forward(ocfg, flat, xin)
+    np.testing.assert_allclose(y, y_o, rtol=1e-3, atol=1e-5 * np.abs(y_o).max())
+    loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, xt)
+    assert model.loss(xin, xt) == pytest.approx(loss_o, rel=1e-4)
+    # one train step: loss, then compare the update against the oracle's ClipGrad+Adam on the oracle gradient
+    loss = model.train_step(xin, xt, 1e-3)
+    assert loss == pytest.approx(loss_o, rel=1e-4)
+    opt = OM.Adam(flat.size, clip_grad=5.0)
+    w_o = opt.step(flat, g_o, 1e-3)
+    w = model.get_params()
+    big = np.abs(g_o) > 1e-4 * np.abs(g_o).max()
+    np.testing.assert_allclose((w - flat)[big], (w_o - flat)[big], rtol=2e-3, atol=2e-6)
+    m, v, t = model.get_opt_state()
+    assert t == 1
+    gc = np.clip(g_o, -5, 5)
+    np.testing.assert_allclose(m, 0.1 * gc, rtol=1e-3, atol=1e-6 * np.abs(gc).max())      # m = (1-beta1) g: the gradient itself
+
+
+def test_gradient_clip_and_padding_stay_zero(pkg, ctx):
+    rng = np.random.default_rng(1)
+    cfg = pkg.ModelConfig(W=12, H=12, ninput=5, enc_nfilter_internal=(6,), clip_grad=1e-3, max_batch=2, precision="fp32")
+    model = pkg.Model(ctx, cfg, seed=1)
+    xin, xt = _problem(rng, 12, 12, 5, 1, 2)
+    w0 = model.get_params()
+    model.train_step(xin, xt, 1e-2)
+    m, v, t = model.get_opt_state()
+    assert np.abs(m).max() <= 0.1 * 1e-3 * (1 + 1e-6)                     # element-wise clamp to [-delta, delta] (T4)
+    assert np.abs(model.get_params() - w0).max() <= 1e-2 * (1 + 1e-5)
+
+
+def test_multi_step_loss_curve(pkg, ctx):
+    """Seeded multi-epoch loss curve: GPU library vs oracle sharing perm, imask and the Philox jitter."""
+    rng = np.random.default_rng(3)
+    W, H, V, N, T, Bsz, epochs = 24, 20, 1, 22, 3, 8, 3
+    data = _cube(rng, W, H, V, N)
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, train=True, ntime_win=T)
+    od = OD.NCData(lon, lat, days, data, train=True, ntime_win=T)
+    kw = dict(loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=10, enc_nfilter_internal=(8, 12), max_batch=Bsz, precision="fp32", **kw)
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=10, nfilter=[8, 12], **kw)
+    model = pkg.Model(ctx, cfg, seed=9)
+    flat = model.get_params()
+    opt = OM.Adam(flat.size)
+    batches = pkg.api.DataBatches(ds, Bsz, seed=4)
+    losses, losses_o = [], []
+    for e in range(1, epochs + 1):
+        lr = pkg.api.learning_rate(1e-3, e, 2.0)                    # learning_rate_decay_epoch = 2 (T16)
+        s = so = 0.0
+        nb = 0
+        for idx, imask, ctr in batches.batches():                   # includes the partial last batch (T17)
+            xin, xt = ds.assemble(idx, imask, 4, ctr)
+            s += model.train_step(xin, xt, lr)
+            xin_o, xt_o = od.batch(idx, imask, 4, ctr)
+            lo, flat = OM.train_step(ocfg, flat, opt, xin_o, xt_o, lr)
+            so += lo
+            nb += 1
+        losses.append(s / nb); losses_o.append(so / nb)
+        batches.shuffle_()
+    np.testing.assert_allclose(losses, losses_o, rtol=1e-3)
+
+
+def test_data_parallel_split_equals_full_batch(pkg, ctx):
+    """grad_step on two shards with the global n_noncloud + SUM == train_step on the whole mini-batch."""
+    rng = np.random.default_rng(8)
+    W, H, Cin, B = 16, 12, 10, 6
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=Cin, enc_nfilter_internal=(6, 8), loss_weights_refine=(0.3, 0.7),
+                          regularization_L2_beta=1e-3, max_batch=B, precision="fp32")
+    xin, xt = _problem(rng, W, H, Cin, 1, B)
+    full = pkg.Model(ctx, cfg, seed=2)
+    w0 = full.get_params()
+    loss_full = full.train_step(xin, xt, 1e-3)
+    nv = full.count_valid(xt)
+    models, grads = [], []
+    for lo, hi in ((0, 4), (4, 6)):                                   # uneven shards
+        m = pkg.Model(ctx, cfg, seed=2)
+        m.set_params(w0)
+        m.grad_step(np.asfortranarray(xin[..., lo:hi]), np.asfortranarray(xt[..., lo:hi]), n_valid_global=nv)
+        ctx.sync()
+        models.append(m)
+        grads.append(m.grad_tensor())                                 # zero-copy torch view of the flat gradient buffer
+    total = grads[0] + grads[1]                                       # the all-reduce (SUM)
+    torch.cuda.synchronize()
+    m = models[0]
+    m.grad_tensor().copy_(total)
+    torch.cuda.synchronize()
+    loss_dp = m.apply_step(1e-3)
+    assert loss_dp == pytest.approx(loss_full, rel=1e-5)
+    np.testing.assert_allclose(m.get_params(), full.get_params(), rtol=0, atol=2e-6)
+
+
+# ---------------------------------------------------------------- reconstruction epilogue
+def test_reconstruct_range_matches_forward_and_savesample(pkg, ctx):
+    rng = np.random.default_rng(5)
+    W, H, V, N, T = 18, 11, 1, 13, 3
+    data = _cube(rng, W, H, V, N)
+    mask = rng.random((W, H)) > 0.2
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, train=False, ntime_win=T, mask=mask)
+    od = OD.NCData(lon, lat, days, data, train=False, ntime_win=T, mask=mask)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=10, enc_nfilter_internal=(6, 8), loss_weights_refine=(0.3, 0.7), max_batch=5, precision="fp32")
+    model = pkg.Model(ctx, cfg, seed=4)
+    m1, s1 = pkg.api.reconstruct_range(model, ds, 0, N, count=1)
+    xin, _ = od.batch(np.arange(N))
+    xrec = model(np.asfortranarray(xin[..., :5]))
+    z = np.zeros((W, H, 5), np.float32)
+    mo, so = OD.savesample_accumulate(z, z, xrec, od.meandata[:, :, 0], mask, 1)
+    np.testing.assert_allclose(m1[:, :, :5, 0], mo, rtol=1e-6, atol=1e-6)
+    np.testing.assert_allclose(s1[:, :, :5, 0], so, rtol=1e-6, atol=1e-6)
+    assert np.all(m1[~mask] == -9999) and m1[0, 0, 0, 0] == -9999            # land + never-observed pixel -> fill
+    # second save epoch: running mean with count = 2 (self-consistency check of test/test_DINCAE_SST.jl:184-185)
+    model.set_params(model.get_params() * np.float32(1.01))
+    m_new, s_new = pkg.api.reconstruct_range(model, ds, 0, N, count=1)
+    m2, s2 = pkg.api.reconstruct_range(model, ds, 0, N, count=2, m_out=m1.copy(order="F"), sigma_out=s1.copy(order="F"))
+    ok = m1 != -9999
+    np.testing.assert_allclose(m2[ok], ((m1 + m_new) / 2)[ok], rtol=1e-5, atol=1e-5)
+    np.testing.assert_allclose(s2[ok], ((s1 + s_new) / 2)[ok], rtol=1e-5, atol=1e-5)
+    # time sharding: two half ranges == the full record (no communication needed)
+    ma, sa = pkg.api.reconstruct_range(model, ds, 0, 6)
+    mb, sb = pkg.api.reconstruct_range(model, ds, 6, N)
+    assert np.array_equal(np.concatenate([ma, mb], axis=2), m_new) and np.array_equal(np.concatenate([sa, sb], axis=2), s_new)
+
+
+def test_error_paths(pkg, ctx):
+    with pytest.raises(pkg.lib.DincaeError) as e:
+        pkg.Model(ctx, pkg.ModelConfig(W=8, H=8, ninput=2, enc_nfilter_internal=(4,), skipconnections=(1, 2), max_batch=1))
+    assert e.value.code == pkg.lib.EUNSUPPORTED
+    m = pkg.Model(ctx, pkg.ModelConfig(W=8, H=8, ninput=2, enc_nfilter_internal=(4,), max_batch=2))
+    with pytest.raises(pkg.lib.DincaeError) as e:
+        m(np.zeros((8, 8, 2, 3), np.float32, order="F"))           # batch larger than max_batch
+    assert e.value.code == pkg.lib.ESIZE
+    with pytest.raises(pkg.lib.DincaeError):
+        m.set_params(np.zeros(3, np.float32))
+
+
+def test_smoke(pkg, ctx):
+    r = pkg.selftest.smoke(verbose=False)
+    assert r["launches"] > 0

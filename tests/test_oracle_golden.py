@@ -1,0 +1,223 @@
+"""Pins the oracle against every numeric fixture the reference's tests hold for the
+hot path, and cross-checks its two independent restatements."""
+import numpy as np
+import pytest
+import torch
+from oracle import model as M, points as P, data as D, cbind, philox
+
+
+# ---- test/test_interp_adjoint.jl:20-47 (golden vectors) -------------------------
+POS = np.array([[1.5, 2.0], [5.0, 2.3]], np.float32)
+VALUES = np.array([3.0, 4.0], np.float32)
+SZ = (6, 7)
+RTOL_JULIA = 3.5e-4          # Julia's `≈` default: rtol = sqrt(eps(Float32))
+
+
+def _a_ref():
+    A = np.zeros(SZ, np.float32)
+    A[0, 1] = A[1, 1] = 0.5 * 3
+    A[4, 1] = 0.7 * 4
+    A[4, 2] = 0.3 * 4
+    return A
+
+
+def _da_ref():
+    A = np.zeros(SZ, np.float32)
+    A[0, 1] = A[1, 1] = 0.5
+    A[4, 1] = 0.7
+    A[4, 2] = 0.3
+    return A
+
+
+@pytest.mark.parametrize("impl", ["numpy", "numpy_fast", "c"])
+def test_interp_adjn_golden(impl):
+    f = {"numpy": P.interp_adjn, "numpy_fast": lambda p, v, s: P.interp_adjn_fast(p, v, s, np.float32),
+         "c": cbind.interp_adjn}[impl]
+    np.testing.assert_allclose(f(POS, VALUES, SZ), _a_ref(), rtol=1e-6)
+
+
+def test_interp_gradient_golden():
+    # gradient(sum(interpnd(pos,B)), B) == dA_ref  (test/test_interp_adjoint.jl:42-46)
+    B = torch.ones(SZ[1], SZ[0], dtype=torch.float32, requires_grad=True)
+    M.interp_torch(POS, B).sum().backward()
+    np.testing.assert_allclose(B.grad.numpy().T, _da_ref(), rtol=1e-6)
+    # and the rrule itself: pullback of ones through interp_adjn (src/points.jl:36-43)
+    np.testing.assert_allclose(P.interp_adjn(POS, np.ones(2, np.float32), SZ), _da_ref(), rtol=1e-6)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_adjoint_identity(seed):
+    # test/test_interp_adjoint.jl:49-54
+    rng = np.random.default_rng(seed)
+    A = rng.standard_normal(SZ).astype(np.float32)
+    dAi = rng.standard_normal(len(POS)).astype(np.float32)
+    for interp, adj in ((P.interpnd, P.interp_adjn), (cbind.interpnd, cbind.interp_adjn)):
+        lhs = float(np.dot(dAi, interp(POS, A)))
+        rhs = float(np.sum(A * adj(POS, dAi, SZ)))
+        assert lhs == pytest.approx(rhs, rel=RTOL_JULIA)
+
+
+def test_adjoint_identity_random_cloud():
+    rng = np.random.default_rng(5)
+    W, H, n = 37, 23, 500
+    pos = np.stack([rng.uniform(1, W - 1e-3, n), rng.uniform(1, H - 1e-3, n)], 1).astype(np.float32)
+    pos = np.minimum(pos, np.array([W, H], np.float32) - np.float32(1e-3)).astype(np.float32)
+    A = rng.standard_normal((W, H)).astype(np.float32)
+    v = rng.standard_normal(n).astype(np.float32)
+    assert float(np.dot(v, P.interpnd(pos, A))) == pytest.approx(float(np.sum(A * P.interp_adjn_fast(pos, v, (W, H)))), rel=1e-4)
+    np.testing.assert_allclose(cbind.interpnd(pos, A), P.interpnd(pos, A), rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(cbind.interp_adjn(pos, v, (W, H)), P.interp_adjn_fast(pos, v, (W, H)), rtol=1e-4, atol=1e-5)
+
+
+# ---- test/test_utils.jl:4-13 ---------------------------------------------------
+def test_normalize2_golden():
+    np.testing.assert_array_equal(D.normalize2([1, 2, 3]), [-1, 0, 1])
+    assert np.all(np.isfinite(D.normalize2(np.zeros((10, 10)))))
+
+
+def test_sumskip_catskip_golden():
+    # SumSkip(x -> 2x)(a) == 3a ; CatSkip(x -> 2x)(a) == cat(2a, a, dims=3)
+    # The oracle's level with an identity-free inner chain: use a 1-level model whose
+    # convs are hand-set so that inner(x) == 2x, and check level(x) == 3x.
+    cfg = M.ModelConfig(W=4, H=4, ninput=1, nfilter=[1], skipconnections=(1,))
+    a = torch.ones(1, 1, 4, 4, dtype=torch.float64)
+    w_id = torch.zeros(1, 1, 3, 3, dtype=torch.float64); w_id[0, 0, 1, 1] = 1.0
+    p = {"enc": [(w_id, torch.zeros(1, dtype=torch.float64))], "dec": [(2 * w_id, torch.zeros(1, dtype=torch.float64))]}
+    y = M._level(a, p, cfg, 0)      # conv(id)->relu->pool(avg of ones = 1)->up->conv(2*id) + skip
+    assert torch.equal(y, 3 * a)
+    c = torch.cat([2 * a, a], dim=1)            # refinement concat puts the chain output FIRST (T9)
+    assert torch.equal(c[:, 0], 2 * a[:, 0]) and torch.equal(c[:, 1], a[:, 0])
+
+
+# ---- two independent restatements agree (torch ops vs plain C loops) ---------------
+@pytest.mark.parametrize("W,H,method,refine", [(8, 8, "nearest", False), (7, 9, "nearest", True),
+                                               (9, 6, "bilinear", False), (5, 5, "bilinear", True)])
+def test_torch_vs_c_forward(W, H, method, refine):
+    cfg = M.ModelConfig(W=W, H=H, ninput=6, nfilter=[3, 5], upsampling_method=method,
+                        loss_weights_refine=(0.3, 0.7) if refine else (1.0,))
+    rng = np.random.default_rng(3)
+    flat = M.init_params(cfg, 7)
+    flat = flat + rng.standard_normal(flat.size).astype(np.float32) * 0.05       # non-zero biases too
+    xin = np.asfortranarray(rng.standard_normal((W, H, 6, 2)).astype(np.float32))
+    yt = M.forward(cfg, flat, xin)
+    yc = cbind.chain_forward(cfg, flat, xin)
+    np.testing.assert_allclose(yc, yt, rtol=2e-5, atol=1e-6)
+
+
+def test_pool_upsample_shapes_odd():
+    # 7 -> 4 -> 8 -> crop 7; first pooled cell = (pad + x1)/4
+    x = np.asfortranarray(np.arange(7 * 7, dtype=np.float32).reshape(7, 7, 1, 1, order="F"))
+    p = cbind.meanpool2(x)
+    assert p.shape == (4, 4, 1, 1)
+    assert p[0, 0, 0, 0] == x[0, 0, 0, 0] / 4
+    assert p[1, 1, 0, 0] == (x[1, 1, 0, 0] + x[2, 1, 0, 0] + x[1, 2, 0, 0] + x[2, 2, 0, 0]) / 4
+    u = cbind.upsample2_crop(p, 0, 7, 7)
+    assert u.shape == (7, 7, 1, 1) and u[6, 6, 0, 0] == p[3, 3, 0, 0] and u[5, 5, 0, 0] == p[2, 2, 0, 0]
+    xt = torch.as_tensor(np.transpose(x, (3, 2, 1, 0)).copy())
+    pt = torch.nn.functional.avg_pool2d(xt, 2, 2, padding=(1, 1), count_include_pad=True)
+    np.testing.assert_allclose(np.transpose(pt.numpy(), (3, 2, 1, 0)), p)
+
+
+def test_costfun_torch_vs_c():
+    rng = np.random.default_rng(0)
+    xrec = np.asfortranarray(rng.standard_normal((9, 7, 4, 3)).astype(np.float32))
+    xrec[:, :, 1::2] = np.exp(xrec[:, :, 1::2])
+    xt = np.asfortranarray(rng.standard_normal((9, 7, 4, 3)).astype(np.float32))
+    xt[:, :, 1::2] = np.where(rng.random((9, 7, 2, 3)) < 0.4, 0, 1).astype(np.float32)
+    xt[:, :, 0::2] *= xt[:, :, 1::2]
+    for tu in (False, True):
+        cfg = M.ModelConfig(W=9, H=7, ninput=1, noutput=2, truth_uncertain=tu)
+        t = lambda a: torch.as_tensor(np.transpose(a, (3, 2, 1, 0)).copy(), dtype=torch.float64)
+        lt = float(M.costfun(t(xrec), t(xt), cfg))
+        assert cbind.costfun(xrec, xt, tu) == pytest.approx(lt, rel=1e-6)
+
+
+def test_head_gradient_finite_difference():
+    # float64 finite-difference check of head+loss incl. both clamps, truth_uncertain, Laplacian
+    rng = np.random.default_rng(1)
+    for tu in (False, True):
+        cfg = M.ModelConfig(W=6, H=5, ninput=1, truth_uncertain=tu, laplacian_penalty=0.1, laplacian_error_penalty=0.05)
+        r0 = rng.standard_normal((2, 2, 5, 6))
+        r0[0, 1, 0, 0] = 12.0        # beyond the gamma clamp  (min(b, gamma), gamma = 10)
+        r0[1, 1, 2, 3] = -9.0        # below the 1e-3 floor    (max(exp(b), 1e-3))
+        raw = torch.tensor(r0, dtype=torch.float64, requires_grad=True)
+        xt = torch.tensor(rng.standard_normal((2, 2, 5, 6)), dtype=torch.float64)
+        xt[:, 1] = (torch.rand(2, 5, 6, dtype=torch.float64) > 0.3).double()
+        f = lambda r: M.costfun(M.transform_msigma2(r, cfg.gamma), xt, cfg)
+        g, = torch.autograd.grad(f(raw), raw)
+        for k in range(5):          # central differences along random directions
+            v = torch.tensor(rng.standard_normal(r0.shape))
+            eps = 1e-6
+            fd = (f(raw.detach() + eps * v) - f(raw.detach() - eps * v)) / (2 * eps)
+            assert float(fd) == pytest.approx(float((g * v).sum()), rel=1e-5)
+        # clamped entries carry no gradient through the sigma2 channel
+        assert g[0, 1, 0, 0] == 0 and g[1, 1, 2, 3] == 0
+
+
+def test_adam_numpy_vs_c():
+    rng = np.random.default_rng(2)
+    n = 1000
+    w = rng.standard_normal(n).astype(np.float32); g = (rng.standard_normal(n) * 4).astype(np.float32)
+    opt = M.Adam(n, clip_grad=5.0)
+    wc, m, v = w.copy(), np.zeros(n, np.float32), np.zeros(n, np.float32)
+    w1 = w
+    for t in range(1, 4):
+        w1 = opt.step(w1, g, 1e-3)
+        cbind.adam(wc, g, m, v, 1e-3, 5.0, 0.9, 0.999, 1e-8, 0.9 ** t, 0.999 ** t)
+    np.testing.assert_allclose(wc, w1, rtol=1e-5, atol=1e-7)
+    # known answer: the first bias-corrected Adam step moves every weight by lr*sign(g)
+    opt2 = M.Adam(n, clip_grad=None)
+    np.testing.assert_allclose(opt2.step(w, g, 1e-3), w - 1e-3 * np.sign(g), atol=2e-7)
+
+
+def test_philox_known_answer():
+    # Random123 known-answer vectors for philox4x32-10
+    out = philox.philox4x32(np.uint32(0), np.uint32(0), np.uint32(0), np.uint32(0), 0, 0)
+    assert [int(x) for x in out] == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    out = philox.philox4x32(np.uint32(0xffffffff), np.uint32(0xffffffff), np.uint32(0xffffffff), np.uint32(0xffffffff),
+                            0xffffffff, 0xffffffff)
+    assert [int(x) for x in out] == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    z = philox.normal_field(200000, np.uint32(1), np.uint32(2), np.uint32(3), 1234)
+    assert abs(z.mean()) < 0.01 and abs(z.std() - 1) < 0.01
+
+
+def test_getxy_numpy_vs_c_and_perturbation():
+    rng = np.random.default_rng(4)
+    W, H, V, N, T = 6, 5, 2, 9, 3
+    data = rng.standard_normal((W, H, V, N)).astype(np.float32) + 10
+    data[rng.random((W, H, V, N)) < 0.4] = np.nan
+    dd = D.NCData(np.linspace(-7, -1, W), np.linspace(30, 40, H), np.arange(N) + 11000.0, data,
+                  train=True, ntime_win=T, isoutput=[True, False], obs_err_std=[1.0, 2.0])
+    for ind in (0, 4, 8):
+        xin, xtrue = dd.getxy(ind)
+        xin_c = np.zeros_like(xin, order="F"); xt_c = np.zeros_like(xtrue, order="F")
+        cbind.lib().orc_getxy(dd.x.ctypes, W, H, V, N, T, dd.lon_scaled.ctypes, dd.lat_scaled.ctypes,
+                              cbind.C.c_float(dd.time_cos[ind]), cbind.C.c_float(dd.time_sin[ind]), ind,
+                              np.asarray(dd.isoutput, np.uint8).ctypes, xin_c.ctypes, xt_c.ctypes)
+        np.testing.assert_array_equal(xin, xin_c)
+        np.testing.assert_array_equal(xtrue, xt_c)
+    # perturbation: zero first (centre step, every variable, mask of variable 1), noise after (T10)
+    xin0, _ = dd.getxy(4)
+    xin1, _ = dd.getxy(4, imask=2, seed=9, sample_ctr=5)
+    mm = dd.missingmask[:, :, 2]
+    for v in range(V):
+        c = 4 + 2 * (v * T + 1)
+        assert np.all(xin1[:, :, c + 1][mm] == 0)
+        noise = xin1[:, :, c] - np.where(mm, 0, xin0[:, :, c])
+        np.testing.assert_allclose(noise, dd.jitter_std[v] * D.jitter_noise(W * H, v * T + 1, 9, 5).reshape((W, H), order="F"), atol=1e-6)
+    # time channels use HOURS since the origin (T6)
+    assert dd.time_cos[3] == np.float32(np.cos(2 * np.pi * (11003.0 * 24) / 365.25))
+
+
+def test_savesample_running_mean():
+    rng = np.random.default_rng(6)
+    W, H, B = 4, 3, 2
+    xrec = np.abs(rng.standard_normal((W, H, 2, B))).astype(np.float32)
+    mean = rng.standard_normal((W, H)).astype(np.float32); mean[0, 0] = np.nan
+    mask = np.ones((W, H), bool); mask[1, 1] = False
+    m1, s1 = D.savesample_accumulate(np.zeros((W, H, B), np.float32), np.zeros((W, H, B), np.float32), xrec, mean, mask, 1)
+    assert m1[0, 0, 0] == -9999 and s1[0, 0, 0] == -9999 and m1[1, 1, 1] == -9999
+    np.testing.assert_allclose(m1[2, 2], xrec[2, 2, 0] + mean[2, 2], rtol=1e-6)
+    np.testing.assert_allclose(s1[2, 2], np.sqrt(xrec[2, 2, 1]), rtol=1e-6)
+    m2, s2 = D.savesample_accumulate(m1, s1, 2 * xrec, mean, mask, 2)
+    np.testing.assert_allclose(m2[2, 2], (m1[2, 2] + 2 * xrec[2, 2, 0] + mean[2, 2]) / 2, rtol=1e-6)
