@@ -7,7 +7,17 @@
 #include <vector>
 #include "../../include/dincae_b200.h"
 
+struct ProfRec {
+    const char* name;
+    cudaEvent_t a, b;
+    double flops, bytes;
+};
+
 struct dincae_ctx {
+    // per-launch CUDA-event profile (dincae_profile_begin/_end): off by default
+    bool prof = false;
+    std::vector<ProfRec> prof_recs;
+    double cur_flops = 0.0, cur_bytes = 0.0;     // algorithmic work of the NEXT launch (set by DC_WORK)
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
@@ -49,9 +59,21 @@ void dincae_set_error(const char* fmt, ...);
 // every kernel launch of the library goes through this so that gpu_launches is a count, not a guess
 #define DC_LAUNCH(ctx, kernel, grid, block, smem, ...)                        \
     do {                                                                      \
+        if ((ctx)->prof) dc_prof_begin((ctx), #kernel);                       \
         kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);      \
+        if ((ctx)->prof) dc_prof_end((ctx));                                  \
+        (ctx)->cur_flops = 0.0;                                               \
+        (ctx)->cur_bytes = 0.0;                                               \
         (ctx)->launches++;                                                    \
     } while (0)
+// algorithmic FLOPs / bytes of the next launch (reported by dincae_profile_end, used for rooflines)
+#define DC_WORK(ctx, fl, by)        \
+    do {                            \
+        (ctx)->cur_flops = (fl);    \
+        (ctx)->cur_bytes = (by);    \
+    } while (0)
+void dc_prof_begin(dincae_ctx* ctx, const char* name);
+void dc_prof_end(dincae_ctx* ctx);
 
 #define DC_CHECK_LAUNCH()                                                                 \
     do {                                                                                  \

@@ -2,6 +2,8 @@
 #include "common.cuh"
 #include <stdarg.h>
 #include <string.h>
+#include <map>
+#include <string>
 
 static thread_local char g_err[1024] = "";
 
@@ -120,4 +122,56 @@ int32_t dc_stage_in(dincae_ctx* ctx, const void* src, size_t bytes, int32_t loc,
 void dc_stage_free(dincae_ctx* ctx, DevIn* b) {
     if (b->owned) cudaFreeAsync(b->owned, ctx->stream);
     b->owned = nullptr;
+}
+
+// ---- per-launch CUDA-event profile ---------------------------------------------------------------
+void dc_prof_begin(dincae_ctx* ctx, const char* name) {
+    ProfRec r;
+    r.name = name;
+    r.flops = ctx->cur_flops;
+    r.bytes = ctx->cur_bytes;
+    cudaEventCreate(&r.a);
+    cudaEventCreate(&r.b);
+    cudaEventRecord(r.a, ctx->stream);
+    ctx->prof_recs.push_back(r);
+}
+void dc_prof_end(dincae_ctx* ctx) { cudaEventRecord(ctx->prof_recs.back().b, ctx->stream); }
+
+extern "C" int32_t dincae_profile_begin(dincae_ctx* ctx) {
+    DC_REQUIRE(ctx != nullptr, DINCAE_EINVAL, "dincae_profile_begin: ctx is NULL");
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (auto& r : ctx->prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+    ctx->prof_recs.clear();
+    ctx->prof = true;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_profile_end(dincae_ctx* ctx, char* json, int64_t cap) {
+    DC_REQUIRE(ctx && json && cap > 2, DINCAE_EINVAL, "dincae_profile_end: bad arguments");
+    ctx->prof = false;
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    struct Agg { int64_t n = 0; double ms = 0, flops = 0, bytes = 0; };
+    std::map<std::string, Agg> agg;
+    for (auto& r : ctx->prof_recs) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        Agg& a = agg[r.name];
+        a.n++; a.ms += ms; a.flops += r.flops; a.bytes += r.bytes;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    ctx->prof_recs.clear();
+    std::string out = "[";
+    bool first = true;
+    for (auto& kv : agg) {
+        char buf[512];
+        snprintf(buf, sizeof(buf), "%s{\"kernel\": \"%s\", \"launches\": %lld, \"ms\": %.6f, \"flops\": %.6e, \"bytes\": %.6e}",
+                 first ? "" : ", ", kv.first.c_str(), (long long)kv.second.n, kv.second.ms, kv.second.flops, kv.second.bytes);
+        out += buf;
+        first = false;
+    }
+    out += "]";
+    DC_REQUIRE((int64_t)out.size() + 1 <= cap, DINCAE_ESIZE, "dincae_profile_end: buffer too small (%zu needed)", out.size() + 1);
+    memcpy(json, out.c_str(), out.size() + 1);
+    return DINCAE_OK;
 }

@@ -43,6 +43,8 @@ SIGNATURES = {
     "dincae_last_error": (C.c_char_p, []),
     "dincae_version": (i32, []),
     "dincae_launch_count": (i64, [vp]),
+    "dincae_profile_begin": (i32, [vp]),
+    "dincae_profile_end": (i32, [vp, C.c_char_p, i64]),
     "dincae_interp": (i32, [vp, vp, i64, vp, i32, i32, vp, i32]),
     "dincae_interp_adjoint": (i32, [vp, vp, vp, i64, i32, i32, vp, i32]),
     "dincae_interp_cells": (i32, [vp, vp, i64, vp, i32]),

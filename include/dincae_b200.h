@@ -65,6 +65,11 @@ const char* dincae_last_error(void);
 int32_t dincae_version(void);
 /* number of kernels this library has launched on ctx since creation (bench.py's gpu_launches) */
 int64_t dincae_launch_count(dincae_ctx* ctx);
+/* measurement aid (no counterpart in the reference, which only wraps loops in @time, src/model.jl:588,625):
+ * between _begin and _end every kernel launch is bracketed by CUDA events on the context's stream; _end writes a
+ * JSON array [{kernel, launches, ms, flops, bytes}] (flops/bytes = algorithmic work declared by the launcher). */
+int32_t dincae_profile_begin(dincae_ctx* ctx);
+int32_t dincae_profile_end(dincae_ctx* ctx, char* json, int64_t cap);
 
 /* ---- K4: point gather / adjoint scatter (src/points.jl:6-77; ext/CUDAExt.jl:8-81) ---------------
  * interp:  out[p] = sum over the 4 corners of A[floor(pos)+off] * w      (interpnd!, overwrites out)
