@@ -34,6 +34,7 @@ struct ConvArgs {
     float slope;          // leaky slope (0 = ReLU)
     const float* addend;  // optional [B,H,W,Cout_p], added AFTER the activation
     float* dst;           // [B,H,W,Cout_p]
+    double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
 };
 
 struct WgradArgs {
@@ -46,6 +47,7 @@ struct WgradArgs {
     float* partial;       // split-K scratch
     int splits;
     int64_t pix_per_split;
+    double work_flops;
 };
 
 // small-Cout forward (Cout_p in {4,8}): NHWC in -> planar out[b][co][y][x] (co < Cout real)
@@ -58,6 +60,7 @@ struct ConvSmallArgs {
     int Cout;             // real output channels written
     int accumulate;       // 0: out = v ; 1: out += v
     float* out;           // planar [B][Cout][H][W]
+    double work_flops;
 };
 
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);

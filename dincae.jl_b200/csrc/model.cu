@@ -36,6 +36,7 @@ __global__ void count_pts_kernel(const float* __restrict__ x2, int64_t P, unsign
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(n, (unsigned long long)c);
 }
 
+inline double cflops(const LayerInfo& y, int B, int H, int W) { return 2.0 * 9 * y.Cin * y.Cout * (double)B * H * W; }
 inline bool has_skip(const dincae_model* M, int l) { return l >= 1 && l < M->L && ((M->cfg.skip_mask >> l) & 1u); }
 
 // the producer of conv_dec_l: upsample(+crop) of y_{l+1} = R[l+1] (+ X[l+1] when level l+1 has a skip) or X[L]
@@ -67,6 +68,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
+        a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
         DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
     }
@@ -79,11 +81,13 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             a.in = s; a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
             a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
+            a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
         } else {
             ConvSmallArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
             a.wgt = M->w + d.w_off; a.ldw = d.Cout_p; a.bias = M->w + d.b_off; a.Cout = 2 * M->O; a.accumulate = 0; a.out = cb.RAW;
+            a.work_flops = cflops(d, B, M->Hl[0], M->Wl[0]);
             DC_TRY(k2_conv_small(ctx, a, M->nco));                                 // Conv(..., identity) at l == 1, :251-256
         }
     }
@@ -118,12 +122,14 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         WgradArgs wa{};
         wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
         wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
+        wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         if (l == 0) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
         else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         ConvArgs a{};
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
+        a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
     {   // G[L] = gradient w.r.t. X[L] (the innermost level is the identity, src/model.jl:263-264)
@@ -140,6 +146,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
         wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
+        wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         if (l >= 1) {
             ConvArgs a{};
@@ -148,6 +155,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f;
             a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
             a.dst = M->XG[l];
+            a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));
             xg = M->XG[l];
         } else if (c >= 1) {
@@ -156,6 +164,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.in = ConvSrc{M->GC[0], nullptr, SRC_DIRECT, M->Hl[0], M->Wl[0], e.Cout_p};
             a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
             a.wgt = M->wT + e.wT_off; a.ldw = e.Cin_p; a.bias = nullptr; a.Cout = 2 * M->O; a.accumulate = 1; a.out = M->cb[c - 1].GRAW;
+            a.work_flops = 2.0 * 9 * 2 * M->O * e.Cout * (double)B * M->Hl[0] * M->Wl[0];
             DC_TRY(k2_conv_small(ctx, a, M->nco));
         }
     }
