@@ -93,6 +93,19 @@ def interp_adjn(pos, values, sz, ctx: Optional[Context] = None):
     return out
 
 
+def interp_adjn_noalloc(pos_dev, values_dev, P, sz, out_dev, ctx: Optional[Context] = None):
+    """interp_adjn for callers that may not allocate GPU memory (their device memory belongs to another
+    pool, as under CUDA.jl's allocator around a ccall).  All three buffers are device memory the caller
+    owns (torch tensors or raw addresses): pos (P,2), values (P,), out (W,H) which is cleared and filled.
+    The scratch is a fixed array inside the library: at most 65536 points per call (more raises
+    DincaeError/ESIZE), shared by every call on the device -- do not let two calls overlap on the GPU.
+    The first call per device resolves the array's address and should happen before any stream capture.
+    Asynchronous on the context's stream; bit-identical to interp_adjn."""
+    ctx = ctx or default_context()
+    L.check(ctx._lib.dincae_interp_adjoint_noalloc(ctx.handle, L.ptr(pos_dev), L.ptr(values_dev), int(P), sz[0], sz[1], L.ptr(out_dev)))
+    return out_dev
+
+
 def interp_cells(pos, ctx: Optional[Context] = None):
     ctx = ctx or default_context()
     pos = np.ascontiguousarray(pos, np.float32).reshape(-1, 2)

@@ -9,6 +9,7 @@
 //      multiply/add and writes the cell once.  No float atomics => bit-reproducible, and
 //      bit-identical to the sequential CPU loop.
 #include "k4_interp.cuh"
+#include <mutex>
 
 namespace {
 
@@ -341,4 +342,71 @@ extern "C" int32_t dincae_interp_cells(dincae_ctx* ctx, const float* pos, int64_
     }
     dc_stage_free(ctx, &dpos);
     return DINCAE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Adjoint scatter-add for callers that must not allocate device memory.
+//
+// Who needs this: a host program whose GPU memory is owned by somebody else's pool.  The typical case
+// is the Julia side of DINCAE itself: CUDA.jl's caching allocator may already hold nearly the whole
+// device, so a foreign cudaMalloc issued from inside a ccall can fail with out-of-memory (or force the
+// pool to trim) exactly when the pullback of interpnd runs in the middle of a training step.  The same
+// holds for any embedding application that gives a plug-in a fixed memory budget of zero.
+//
+// The sort buffers and digit histograms that dincae_interp_adjoint takes from the context's grow-only
+// scratch live here in a fixed array inside the library image instead.  Every GPU that loads the
+// library carries the array (NOALLOC_SCRATCH_BYTES, about 4.1 MiB) until the process exits.
+namespace {
+constexpr int64_t NOALLOC_MAX_POINTS = 65536;
+constexpr size_t noalloc_align(size_t v) { return (v + 255) / 256 * 256; }
+constexpr size_t NOALLOC_ENTRIES = 4 * (size_t)NOALLOC_MAX_POINTS;
+constexpr size_t NOALLOC_NBLK = (NOALLOC_ENTRIES + SORT_TILE - 1) / SORT_TILE;
+constexpr size_t NOALLOC_SCRATCH_BYTES = 4 * noalloc_align(NOALLOC_ENTRIES * 4) + noalloc_align(256 * NOALLOC_NBLK * 4);
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mutex;
+void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a kernel can use:
+// the device address has to be asked for, once per device, while that device is current.
+int32_t noalloc_scratch_address(int device, void** out) {
+    DC_REQUIRE(device >= 0 && device < NOALLOC_MAX_DEVICES, DINCAE_EINVAL, "dincae_interp_adjoint_noalloc: device %d out of range", device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_ptr[device] == nullptr) {
+        void* p = nullptr;
+        DC_CHECK_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        DC_REQUIRE(p != nullptr, DINCAE_ECUDA, "dincae_interp_adjoint_noalloc: cudaGetSymbolAddress returned NULL on device %d", device);
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return DINCAE_OK;
+}
+}  // namespace
+
+extern "C" int32_t dincae_interp_adjoint_noalloc(dincae_ctx* ctx, const float* d_pos, const float* d_values, int64_t P,
+                                                 int32_t W, int32_t H, float* d_out) {
+    DC_REQUIRE(ctx && d_out && (P == 0 || (d_pos && d_values)), DINCAE_EINVAL, "dincae_interp_adjoint_noalloc: NULL argument");
+    DC_REQUIRE(P >= 0 && W >= 2 && H >= 2, DINCAE_EINVAL, "dincae_interp_adjoint_noalloc: bad sizes P=%lld W=%d H=%d", (long long)P, W, H);
+    DC_REQUIRE(P <= NOALLOC_MAX_POINTS, DINCAE_ESIZE,
+               "dincae_interp_adjoint_noalloc: %lld points exceed the built-in scratch (at most %lld points per call); "
+               "split the call or use dincae_interp_adjoint, which allocates",
+               (long long)P, (long long)NOALLOC_MAX_POINTS);
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    void* scratch = nullptr;
+    DC_TRY(noalloc_scratch_address(ctx->device, &scratch));
+    DC_REQUIRE(k4_scatter_scratch_bytes(P) <= NOALLOC_SCRATCH_BYTES, DINCAE_ESIZE, "dincae_interp_adjoint_noalloc: internal scratch layout mismatch");
+    // The array still holds whatever the previous call left in it.  Nothing in it has to start at zero:
+    // keys and indices are rewritten for all 4*P entries and every histogram cell is overwritten by its
+    // block before the scan reads it; the only zero-initialised memory is the caller's grid, cleared below
+    // by k4_scatter_sorted.  The per-launch event profile creates CUDA events, so it is bypassed here.
+    const bool prof = ctx->prof;
+    ctx->prof = false;
+    K4Batch b{d_pos, nullptr, nullptr, P, W, H, 1, (int64_t)W * H, (int64_t)W * H, 1};
+    int32_t st = k4_scatter_sorted(ctx, b, d_values, nullptr, d_out, scratch, NOALLOC_SCRATCH_BYTES);
+    ctx->prof = prof;
+    return st;
 }

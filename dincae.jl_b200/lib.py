@@ -47,6 +47,7 @@ SIGNATURES = {
     "dincae_profile_end": (i32, [vp, C.c_char_p, i64]),
     "dincae_interp": (i32, [vp, vp, i64, vp, i32, i32, vp, i32]),
     "dincae_interp_adjoint": (i32, [vp, vp, vp, i64, i32, i32, vp, i32]),
+    "dincae_interp_adjoint_noalloc": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "dincae_interp_cells": (i32, [vp, vp, i64, vp, i32]),
     "dincae_model_create": (i32, [vp, C.POINTER(Config), pp]),
     "dincae_model_destroy": (i32, [vp]),

@@ -81,6 +81,20 @@ int32_t dincae_interp(dincae_ctx* ctx, const float* pos, int64_t P, const float*
                       float* out, int32_t loc);
 int32_t dincae_interp_adjoint(dincae_ctx* ctx, const float* pos, const float* values, int64_t P,
                               int32_t W, int32_t H, float* out, int32_t loc);
+/* dincae_interp_adjoint without any device allocation (no counterpart in the reference: its interp_adjn! gets
+ * its temporaries from Julia's own GPU pool).  For hosts whose device memory is held by another allocator --
+ * e.g. CUDA.jl's caching pool around a ccall, where a foreign cudaMalloc can fail or make the pool trim in the
+ * middle of a training step -- or that give a plug-in no memory budget at all.
+ *   - pos, values and out are DEVICE pointers the caller owns; out (W,H) is cleared, then accumulated into.
+ *   - the sort scratch is a fixed array inside the library image (about 4.1 MiB on every GPU that loads the
+ *     library, held until exit); at most 65536 points per call, more returns DINCAE_ESIZE.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call outside of, and before, any stream capture.
+ *   - all calls on a device share the one array: calls that may overlap on the GPU (different streams or
+ *     contexts) race on it and must be serialised by the caller.
+ *   - asynchronous on the context's stream, same bit-exact result as dincae_interp_adjoint. */
+int32_t dincae_interp_adjoint_noalloc(dincae_ctx* ctx, const float* pos, const float* values, int64_t P,
+                                      int32_t W, int32_t H, float* out);
 /* integer part only: cell[p] = (floor(x), floor(y)) 1-based int32 pairs (bit-exact check) */
 int32_t dincae_interp_cells(dincae_ctx* ctx, const float* pos, int64_t P, int32_t* cells, int32_t loc);
 
