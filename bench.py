@@ -313,13 +313,14 @@ def main():
 
     # ---- per-kernel CUDA-event profile of the same step (separate pass, so the timed region stays unperturbed) ----
     roof, kern_table = None, None
+    lib = pkg.lib.load()
+    import ctypes
+    nprof = 5
     if rank == 0:
-        lib = pkg.lib.load()
-        import ctypes
         pkg.lib.check(lib.dincae_profile_begin(ctx.handle))
-        nprof = 5
-        for _ in range(nprof):
-            step_device()
+    for _ in range(nprof):          # every rank runs the steps (they contain the all-reduce); only rank 0 records events
+        step_device()
+    if rank == 0:
         buf = ctypes.create_string_buffer(1 << 16)
         pkg.lib.check(lib.dincae_profile_end(ctx.handle, buf, len(buf)))
         kern_table = json.loads(buf.value.decode())

@@ -28,6 +28,8 @@ struct ConvArgs {
     ConvSrc in;
     int B, H, W;          // conv input == output spatial size
     const float* wgt;     // [Kpad][Cout_p], Kpad = round_up(9*Cin_p, 16), zero padded
+    const float* wgtK;    // tensor-core path: K-major copy [Cout_p][ldk] (values pre-rounded to TF32), or NULL
+    int ldk;              // 9*Cin_p
     const float* bias;    // [Cout_p] or NULL
     int Cout_p;
     int act;
@@ -63,7 +65,9 @@ struct ConvSmallArgs {
     double work_flops;
 };
 
-int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);
+int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);        // dispatches to the tcgen05 kernel when eligible
+bool k2_conv_tc_eligible(const ConvArgs& a);
+int32_t k2_conv_tc(dincae_ctx* ctx, const ConvArgs& a);
 size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
 int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);
 int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco);
@@ -87,5 +91,8 @@ struct WLayerDesc {
     int64_t w_off, wT_off;
     int Cin_p, Cout_p;
     int64_t n;   // 9*Cin_p*Cout_p
+    int64_t wk_off;   // offset of this layer in the K-major copies (both have n elements)
 };
-int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, const WLayerDesc* d_table, int nlayers, int64_t total);
+// wT: transposed + tap-flipped [9*Cout_p][Cin_p] (FP32 path).  If wK/wTK are given also the K-major TF32-rounded copies:
+//   wK [Cout_p][9*Cin_p] for the forward conv, wTK [Cin_p][9*Cout_p] (tap-flipped) for the data gradient.
+int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, float* wK, float* wTK, const WLayerDesc* d_table, int nlayers, int64_t total);

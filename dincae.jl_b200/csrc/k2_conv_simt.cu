@@ -513,7 +513,13 @@ __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int 
     }
 }
 
-__global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, const WLayerDesc* __restrict__ tab, int nlayers, int64_t total) {
+__device__ __forceinline__ float round_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, float* __restrict__ wK, float* __restrict__ wTK,
+                               const WLayerDesc* __restrict__ tab, int nlayers, int64_t total) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= total) return;
     int l = 0;
@@ -525,7 +531,14 @@ __global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ 
     int64_t t = j / Cin_p;
     int co = (int)(t % Cout_p);
     int tapT = (int)(t / Cout_p);
-    wT[tab[l].wT_off + j] = w[tab[l].w_off + ((size_t)(8 - tapT) * Cin_p + ci) * Cout_p + co];
+    float v = w[tab[l].w_off + ((size_t)(8 - tapT) * Cin_p + ci) * Cout_p + co];
+    wT[tab[l].wT_off + j] = v;
+    if (wK) {
+        float r = round_tf32(v);
+        int tap = 8 - tapT;
+        wK[tab[l].wk_off + (size_t)co * (9 * Cin_p) + (size_t)tap * Cin_p + ci] = r;
+        wTK[tab[l].wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = r;
+    }
 }
 
 }  // namespace
@@ -534,6 +547,7 @@ __global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ 
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
     int Mtot = a.B * a.H * a.W;
     if (Mtot == 0) return DINCAE_OK;
+    if (k2_conv_tc_eligible(a)) return k2_conv_tc(ctx, a);
     int Kpad = dc_round_up(9 * a.in.C, 16);
     int nchunks = Kpad / 16;
     DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, 0.0);
@@ -689,9 +703,9 @@ int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W
     return DINCAE_OK;
 }
 
-int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, const WLayerDesc* d_table, int nlayers, int64_t total) {
+int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, float* wK, float* wTK, const WLayerDesc* d_table, int nlayers, int64_t total) {
     if (total == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, make_wT_kernel, (unsigned)dc_cdiv(total, 256), 256, 0, w, wT, d_table, nlayers, total);
+    DC_LAUNCH(ctx, make_wT_kernel, (unsigned)dc_cdiv(total, 256), 256, 0, w, wT, wK, wTK, d_table, nlayers, total);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -67,6 +67,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
+        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p;
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
@@ -80,6 +81,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             ConvArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
+            a.wgtK = M->wK ? M->wK + d.wk_off : nullptr; a.ldk = 9 * d.Cin_p;
             a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
             a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
@@ -96,7 +98,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
 
 int32_t ensure_wT(dincae_model* M) {
     if (!M->wT_dirty) return DINCAE_OK;
-    DC_TRY(k2_make_wT(M->ctx, M->w, M->wT, M->d_wtab, M->n_wlayers, M->n_wT_copy));
+    DC_TRY(k2_make_wT(M->ctx, M->w, M->wT, M->wK, M->wTK, M->d_wtab, M->n_wlayers, M->n_wT_copy));
     M->wT_dirty = false;
     return DINCAE_OK;
 }
@@ -129,6 +131,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
+        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p;
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
@@ -153,6 +156,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.in = ConvSrc{M->GC[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cout_p};
             a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f;
+            a.wgtK = M->wTK ? M->wTK + e.wk_off : nullptr; a.ldk = 9 * e.Cout_p;
             a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
             a.dst = M->XG[l];
             a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
@@ -382,6 +386,7 @@ int32_t download_internal(dincae_model* M, const float* src, float* flux) {
 }  // namespace
 
 int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool) {
+    if (M->wK) DC_TRY(ensure_wT(M));        // the tensor-core forward reads the K-major TF32 weight copy
     for (int c = 0; c < M->nchains; c++) DC_TRY(chain_forward(M, c, d_xin, B));
     return DINCAE_OK;
 }
@@ -413,7 +418,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
 
     // ---- topology and parameter layout (Flux.trainables order: enc1..encL, decL..dec1 per chain)
     M->enc.resize(M->nchains); M->dec.resize(M->nchains);
-    int64_t off = 0, foff = 0, toff = 0;
+    int64_t off = 0, foff = 0, toff = 0, koff = 0;
     std::vector<WLayerDesc> wtab;
     for (int c = 0; c < M->nchains; c++) {
         std::vector<int> encf(L + 1), decf(L + 1);
@@ -429,11 +434,12 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             y.flux_w_off = foff; foff += (int64_t)9 * cin * cout;
             y.flux_b_off = foff; foff += cout;
             y.wT_off = toff; toff += (int64_t)y.KpadT * y.Cin_p;
+            y.wk_off = koff; koff += (int64_t)9 * y.Cin_p * y.Cout_p;
         };
         for (int l = 0; l < L; l++) fill(M->enc[c][l], encf[l], encf[l + 1]);
         for (int l = L - 1; l >= 0; l--) fill(M->dec[c][l], decf[l + 1], decf[l]);
     }
-    M->n_int = off; M->n_flux = foff; M->n_wT = toff;
+    M->n_int = off; M->n_flux = foff; M->n_wT = toff; M->n_wk = koff;
     // table for the transposed copies, in wT order; each entry copies 9*Cin_p*Cout_p values
     {
         // make_wT walks layers by cumulative n, so wT offsets must be visited in the same order as the table
@@ -445,7 +451,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         int64_t tot = 0;
         for (const LayerInfo* y : order) {
             WLayerDesc d;
-            d.w_off = y->w_off; d.wT_off = y->wT_off; d.Cin_p = y->Cin_p; d.Cout_p = y->Cout_p; d.n = (int64_t)9 * y->Cin_p * y->Cout_p;
+            d.w_off = y->w_off; d.wT_off = y->wT_off; d.Cin_p = y->Cin_p; d.Cout_p = y->Cout_p; d.n = (int64_t)9 * y->Cin_p * y->Cout_p; d.wk_off = y->wk_off;
             wtab.push_back(d);
             tot += d.n;
         }
@@ -464,6 +470,10 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     want((void**)&M->m, sizeof(float) * (M->n_int + 4));
     want((void**)&M->v, sizeof(float) * (M->n_int + 4));
     want((void**)&M->wT, sizeof(float) * (M->n_wT + 4));
+    if (cfg->precision == DINCAE_PREC_TF32) {
+        want((void**)&M->wK, sizeof(float) * (M->n_wk + 4));
+        want((void**)&M->wTK, sizeof(float) * (M->n_wk + 4));
+    }
     want((void**)&M->d_wtab, sizeof(WLayerDesc) * wtab.size());
     const size_t planar_out = sizeof(float) * Bm * 2 * M->O * cfg->W * cfg->H;
     const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR;

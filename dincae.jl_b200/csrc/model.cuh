@@ -12,6 +12,7 @@ struct LayerInfo {
     int KpadT;           // round_up(9*Cout_p,16): rows of the transposed matrix used by the data gradient
     int64_t w_off, b_off;    // offsets in the internal flat parameter buffer
     int64_t wT_off;          // offset in the transposed-weight buffer
+    int64_t wk_off;          // offset in the K-major TF32 copies wK / wTK (tensor-core path)
     int64_t flux_w_off, flux_b_off;   // offsets in the Flux.trainables order
 };
 
@@ -32,6 +33,8 @@ struct dincae_model {
     std::vector<std::vector<LayerInfo>> enc, dec;     // [chain][level]
     int64_t n_flux = 0, n_int = 0, n_wT = 0, n_wT_copy = 0;
     float *w = nullptr, *g = nullptr, *m = nullptr, *v = nullptr, *wT = nullptr;
+    float *wK = nullptr, *wTK = nullptr;     // K-major TF32-rounded copies (NULL in FP32 mode)
+    int64_t n_wk = 0;
     WLayerDesc* d_wtab = nullptr;
     int n_wlayers = 0;
     bool wT_dirty = true;
