@@ -18,6 +18,7 @@ struct dincae_ctx {
     bool prof = false;
     std::vector<ProfRec> prof_recs;
     double cur_flops = 0.0, cur_bytes = 0.0;     // algorithmic work of the NEXT launch (set by DC_WORK)
+    bool tf32_acts = false;     // element-wise producers of conv inputs round to TF32 on store (set by the model, TF32 mode)
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;

@@ -30,6 +30,7 @@ struct ConvArgs {
     const float* wgt;     // [Kpad][Cout_p], Kpad = round_up(9*Cin_p, 16), zero padded
     const float* wgtK;    // tensor-core path: K-major copy [Cout_p][ldk] (values pre-rounded to TF32), or NULL
     int ldk;              // 9*Cin_p
+    int in_is_tf32;       // the input tensor already holds TF32-representable values (TMA path needs no producer math)
     const float* bias;    // [Cout_p] or NULL
     int Cout_p;
     int act;
@@ -68,6 +69,8 @@ struct ConvSmallArgs {
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);        // dispatches to the tcgen05 kernel when eligible
 bool k2_conv_tc_eligible(const ConvArgs& a);
 int32_t k2_conv_tc(dincae_ctx* ctx, const ConvArgs& a);
+bool k2_conv_tma_eligible(const ConvArgs& a);
+int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a);
 size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
 int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);
 int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco);

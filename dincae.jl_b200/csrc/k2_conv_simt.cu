@@ -28,6 +28,14 @@ __device__ __forceinline__ float src_load1(const ConvSrc& s, int b, int y, int x
 
 __device__ __forceinline__ float act_apply(float v, int act, float slope) { return (act == ACT_RELU && v < 0.f) ? v * slope : v; }
 __device__ __forceinline__ float act_grad(float a, float slope) { return a > 0.f ? 1.f : slope; }
+__device__ __forceinline__ float round_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 round_tf32(float4 v, int on) {
+    return on ? make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w)) : v;
+}
 
 // ---------------------------------------------------------------------------------------------
 // generic forward: tile 128 pixels x BN couts, K chunk 16, 256 threads, 8 x (BN/16) per thread
@@ -350,7 +358,7 @@ __global__ void pack_planar_kernel(const float* __restrict__ s0, int C0, const f
     }
 }
 
-__global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x) {
+__global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x, int rnd) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * H2 * W2 * C4;
@@ -374,12 +382,12 @@ __global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, in
             }
         }
     s.x *= 0.25f; s.y *= 0.25f; s.z *= 0.25f; s.w *= 0.25f;
-    *reinterpret_cast<float4*>(x + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4) = s;
+    *reinterpret_cast<float4*>(x + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4) = round_tf32(s, rnd);
 }
 
 // gu at (H,W); outputs at (Hs,Ws) = (H/2 + H%2, W/2 + W%2)
 __global__ void upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
-                             const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd) {
+                             const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * Hs * Ws * C4;
@@ -408,12 +416,12 @@ __global__ void upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, 
             float4 rv = ldg4(r + off);
             s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
         }
-        *reinterpret_cast<float4*>(gd + off) = s;
+        *reinterpret_cast<float4*>(gd + off) = round_tf32(s, rnd);
     }
 }
 
 __global__ void poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
-                               int H2, int W2, float slope, float* __restrict__ gc) {
+                               int H2, int W2, float slope, float* __restrict__ gc, int rnd) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * H * W * C4;
@@ -430,7 +438,7 @@ __global__ void poolbwd_kernel(const float* __restrict__ xg, const float* __rest
     float4 av = ldg4(a + off);
     g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
     g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
-    *reinterpret_cast<float4*>(gc + off) = g;
+    *reinterpret_cast<float4*>(gc + off) = round_tf32(g, rnd);
 }
 
 // bilinear, align_corners = true (NNlib.upsample_bilinear default), full size (2Hs,2Ws) cropped to (H,W)
@@ -474,7 +482,7 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
 }
 // transpose: each low-res cell gathers from the high-res cells whose stencil touches it (deterministic)
 __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
-                                       const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd) {
+                                       const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * Hs * Ws * C4;
@@ -509,15 +517,10 @@ __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int 
             float4 rv = ldg4(r + off);
             s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
         }
-        *reinterpret_cast<float4*>(gd + off) = s;
+        *reinterpret_cast<float4*>(gd + off) = round_tf32(s, rnd);
     }
 }
 
-__device__ __forceinline__ float round_tf32(float x) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-    return __uint_as_float(r);
-}
 __global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, float* __restrict__ wK, float* __restrict__ wTK,
                                const WLayerDesc* __restrict__ tab, int nlayers, int64_t total) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
@@ -547,6 +550,7 @@ __global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ 
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
     int Mtot = a.B * a.H * a.W;
     if (Mtot == 0) return DINCAE_OK;
+    if (k2_conv_tma_eligible(a)) return k2_conv_tma(ctx, a);
     if (k2_conv_tc_eligible(a)) return k2_conv_tc(ctx, a);
     int Kpad = dc_round_up(9 * a.in.C, 16);
     int nchunks = Kpad / 16;
@@ -663,7 +667,7 @@ int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, fl
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H2 * W2 * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pool_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, a, B, H, W, Cp, H2, W2, x);
+    DC_LAUNCH(ctx, pool_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -672,7 +676,7 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
     int Hs = H / 2 + H % 2, Ws = W / 2 + W % 2;
     int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, upbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd);
+    DC_LAUNCH(ctx, upbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -681,7 +685,7 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, poolbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc);
+    DC_LAUNCH(ctx, poolbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -698,7 +702,7 @@ int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W
                            float* G, float* gd) {
     int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, up_bilinear_bwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd);
+    DC_LAUNCH(ctx, up_bilinear_bwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -75,7 +75,6 @@ template <int BN, int STAGES>
 __global__ void __launch_bounds__(128) conv3x3_tc(ConvArgs a, int Mtot, int nkc) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int A_BYTES = TC_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr int BROWS = (BN + 127) / 128;           // weight rows copied per thread
     __shared__ uint64_t bar_empty[STAGES];
     __shared__ uint64_t bar_done;
     __shared__ uint32_t tmem_base_s;
@@ -102,58 +101,54 @@ __global__ void __launch_bounds__(128) conv3x3_tc(ConvArgs a, int Mtot, int nkc)
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_d = tmem_base_s;
 
-    // this thread's pixel row
-    const int m = m0 + t;
-    const bool pv = m < Mtot;
-    int pb = 0, py = 0, px = 0;
-    if (pv) { pb = m / HW; int r = m - pb * HW; py = r / a.W; px = r - py * a.W; }
-    const uint32_t row_off = (uint32_t)((t >> 3) * 1024 + (t & 7) * 128);
-    const int sw = t & 7;
+    // Producer mapping (coalesced): in pass j a thread moves 16 B chunk (t & 7) of tile row j*16 + (t >> 3), so a warp
+    // reads 4 full 128-byte rows per request and a quarter-warp writes one full swizzled smem row (conflict-free).
+    const int ch = t & 7;
+    int rb_[8], ry[8], rx[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int mr = m0 + j * 16 + (t >> 3);
+        if (mr < Mtot) {
+            rb_[j] = mr / HW;
+            int r = mr - rb_[j] * HW;
+            ry[j] = r / a.W;
+            rx[j] = r - ry[j] * a.W;
+        } else {
+            rb_[j] = -1; ry[j] = 0; rx[j] = 0;
+        }
+    }
 
     // instruction descriptor: D = F32, A = B = TF32, both K-major, N = BN, M = 128
     constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    constexpr int BPASS = BN / 16;                   // weight-tile passes (16 rows per pass)
 
     float4 ra[8], ra1[8];
-    float4 rb[BROWS][8];
-    bool have1 = false;
+    float4 rb[BPASS];
+    const bool have1 = a.in.src1 != nullptr;
 
     auto prefetch = [&](int i) {
         const int tap = i / nkc, kc = i - tap * nkc;
         const int ky = tap / 3, kx = tap - ky * 3;
-        const int c0 = kc * TC_KC;
-        int yy = py + ky - 1, xx = px + kx - 1;
-        const bool ok = pv && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
-        if (ok) {
-            if (a.in.mode == SRC_UP_NEAREST) { yy >>= 1; xx >>= 1; }
-            const size_t off = (((size_t)pb * a.in.Hs + yy) * a.in.Ws + xx) * Cin_p + c0;
-            const float4* p0 = reinterpret_cast<const float4*>(a.in.src0 + off);
+        const int c0 = kc * TC_KC + ch * 4;
 #pragma unroll
-            for (int c = 0; c < 8; c++) ra[c] = __ldg(p0 + c);
-            have1 = a.in.src1 != nullptr;
-            if (have1) {
-                const float4* p1 = reinterpret_cast<const float4*>(a.in.src1 + off);
-#pragma unroll
-                for (int c = 0; c < 8; c++) ra1[c] = __ldg(p1 + c);
+        for (int j = 0; j < 8; j++) {
+            int yy = ry[j] + ky - 1, xx = rx[j] + kx - 1;
+            const bool ok = rb_[j] >= 0 && yy >= 0 && yy < a.H && xx >= 0 && xx < a.W;
+            if (ok) {
+                if (a.in.mode == SRC_UP_NEAREST) { yy >>= 1; xx >>= 1; }
+                const size_t off = (((size_t)rb_[j] * a.in.Hs + yy) * a.in.Ws + xx) * Cin_p + c0;
+                ra[j] = __ldg(reinterpret_cast<const float4*>(a.in.src0 + off));
+                if (have1) ra1[j] = __ldg(reinterpret_cast<const float4*>(a.in.src1 + off));
+            } else {
+                ra[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (have1) ra1[j] = ra[j];
             }
-        } else {
-#pragma unroll
-            for (int c = 0; c < 8; c++) ra[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-            have1 = false;
         }
 #pragma unroll
-        for (int j = 0; j < BROWS; j++) {
-            const int r = t + 128 * j;
-            if (r < BN) {
-                const int n = n0 + r;
-                if (n < a.Cout_p) {
-                    const float4* pw = reinterpret_cast<const float4*>(a.wgtK + (size_t)n * a.ldk + (size_t)tap * Cin_p + c0);
-#pragma unroll
-                    for (int c = 0; c < 8; c++) rb[j][c] = __ldg(pw + c);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < 8; c++) rb[j][c] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            }
+        for (int j = 0; j < BPASS; j++) {
+            const int n = n0 + j * 16 + (t >> 3);
+            rb[j] = (n < a.Cout_p) ? __ldg(reinterpret_cast<const float4*>(a.wgtK + (size_t)n * a.ldk + (size_t)tap * Cin_p + c0))
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
         }
     };
 
@@ -164,19 +159,16 @@ __global__ void __launch_bounds__(128) conv3x3_tc(ConvArgs a, int Mtot, int nkc)
         uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
         uint8_t* sb = sa + A_BYTES;
 #pragma unroll
-        for (int c = 0; c < 8; c++) {       // skip add (SumSkip of the level below) and TF32 rounding happen here, after the loads have landed
-            float4 v = ra[c];
-            if (have1) { v.x += ra1[c].x; v.y += ra1[c].y; v.z += ra1[c].z; v.w += ra1[c].w; }
-            *reinterpret_cast<float4*>(sa + row_off + ((c ^ sw) << 4)) = to_tf32(v);
+        for (int j = 0; j < 8; j++) {       // skip add (SumSkip of the level below) and TF32 rounding happen here, after the loads have landed
+            float4 v = ra[j];
+            if (have1) { v.x += ra1[j].x; v.y += ra1[j].y; v.z += ra1[j].z; v.w += ra1[j].w; }
+            const int r = j * 16 + (t >> 3);
+            *reinterpret_cast<float4*>(sa + (r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4)) = to_tf32(v);
         }
 #pragma unroll
-        for (int j = 0; j < BROWS; j++) {
-            const int r = t + 128 * j;
-            if (r < BN) {
-                const uint32_t boff = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128);
-#pragma unroll
-                for (int c = 0; c < 8; c++) *reinterpret_cast<float4*>(sb + boff + ((c ^ (r & 7)) << 4)) = rb[j][c];
-            }
+        for (int j = 0; j < BPASS; j++) {
+            const int r = j * 16 + (t >> 3);
+            *reinterpret_cast<float4*>(sb + (r >> 3) * 1024 + (r & 7) * 128 + ((ch ^ (r & 7)) << 4)) = rb[j];
         }
         if (i + 1 < nchunks) prefetch(i + 1);                             // next chunk's global loads fly during the MMAs
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the tensor core
@@ -192,6 +184,9 @@ __global__ void __launch_bounds__(128) conv3x3_tc(ConvArgs a, int Mtot, int nkc)
             if (i == nchunks - 1) umma_commit(&bar_done);
         }
     }
+    // epilogue row of this thread: TMEM lane t = tile row t
+    const int m = m0 + t;
+    const bool pv = m < Mtot;
     mbar_wait(&bar_done, 0);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 

@@ -1,0 +1,276 @@
+// K2 (TMA-fed tensor-core path): 3x3 convolution of a plain NHWC tensor as an implicit GEMM.
+//   * one elected thread streams, per K chunk, a (32 ch x PW x PH x 1) activation box and a (32 x BN) weight box
+//     with cp.async.bulk.tensor (TMA) into a SWIZZLE_128B smem ring; the 3x3 taps are just shifted box
+//     coordinates and the conv zero-padding is TMA's out-of-bounds zero fill;
+//   * one elected thread issues tcgen05.mma.kind::tf32 into a TMEM accumulator (128 pixels x BN channels);
+//   * four warps drain TMEM with tcgen05.ld and fuse bias + (leaky-)ReLU + residual add into the NHWC store.
+// Operands must already be TF32-representable (the kernels that produce conv inputs round on store in TF32 mode;
+// weights come from the rounded K-major copy).  Used by the encoder convs and all data-gradient convs.
+#include "k2_conv.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int TM_BM = 128;
+constexpr int TM_KC = 32;
+
+struct TmaConvArgs {
+    int B, H, W;
+    int PW, PH, ptx, pty;      // pixel patch PW x PH = 128 and patches per image
+    int Cin_p, Cout_p;
+    const float* bias;
+    int act;
+    float slope;
+    const float* addend;
+    float* dst;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}" : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+    }
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ float act_apply(float v, int act, float slope) { return (act == ACT_RELU && v < 0.f) ? v * slope : v; }
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(128) conv3x3_tma(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int A_BYTES = TM_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int n0 = blockIdx.y * BN;
+    const int patches = p.ptx * p.pty;
+    const int b = blockIdx.x / patches;
+    const int pr = blockIdx.x - b * patches;
+    const int y0 = (pr / p.ptx) * p.PH, x0 = (pr - (pr / p.ptx) * p.ptx) * p.PW;
+    const int nkc = p.Cin_p / TM_KC;
+    const int nchunks = 9 * nkc;
+
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
+
+    if (t == 0) {
+        // ===== TMA producer =====
+        for (int i = 0; i < nchunks; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int tap = i / nkc, kc = i - tap * nkc;
+            const int ky = tap / 3, kx = tap - ky * 3;
+            uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
+            mbar_expect_tx(&bar_full[s], (uint32_t)STAGE_BYTES);
+            tma_load_4d(sa, &tmA, &bar_full[s], kc * TM_KC, x0 + kx - 1, y0 + ky - 1, b);     // OOB -> zeros = conv padding
+            tma_load_2d(sa + A_BYTES, &tmB, &bar_full[s], tap * p.Cin_p + kc * TM_KC, n0);
+        }
+    } else if (t == 32) {
+        // ===== MMA issuer =====
+        for (int i = 0; i < nchunks; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t da = make_desc_k_sw128(smem_base + (uint32_t)(s * STAGE_BYTES));
+            const uint64_t db = make_desc_k_sw128(smem_base + (uint32_t)(s * STAGE_BYTES + A_BYTES));
+#pragma unroll
+            for (int k = 0; k < TM_KC / 8; k++)
+                umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (i | k) != 0 ? 1u : 0u);
+            umma_commit(&bar_empty[s]);
+        }
+        umma_commit(&bar_done);
+    }
+    __syncwarp();
+    mbar_wait(&bar_done, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    // ===== epilogue: thread t <-> TMEM lane t <-> patch pixel (t / PW, t % PW)
+    const int h = t / p.PW, w = t - h * p.PW;
+    const int y = y0 + h, x = x0 + w;
+    const bool pv = y < p.H && x < p.W;
+    const size_t m = ((size_t)b * p.H + y) * p.W + x;
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int cb = 0; cb < BN; cb += 16) {
+        uint32_t r[16];
+        tmem_ld16(lane_addr + (uint32_t)cb, r);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int n = n0 + cb;
+        if (pv && n < p.Cout_p) {
+            const size_t off = m * p.Cout_p + n;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                float4 o;
+                o.x = __uint_as_float(r[4 * q + 0]); o.y = __uint_as_float(r[4 * q + 1]);
+                o.z = __uint_as_float(r[4 * q + 2]); o.w = __uint_as_float(r[4 * q + 3]);
+                if (p.bias) {
+                    float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * q));
+                    o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                }
+                o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
+                o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
+                if (p.addend) {
+                    float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * q));
+                    o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
+                }
+                *reinterpret_cast<float4*>(p.dst + off + 4 * q) = o;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+// NHWC activation tensor (C, W, H, B), box (32, PW, PH, 1), 128-byte swizzle, zero fill out of bounds
+int32_t make_tmap_act(CUtensorMap* m, const float* ptr, int C, int W, int H, int B, int PW, int PH) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, (cuuint32_t)PW, (cuuint32_t)PH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(activation C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
+    return DINCAE_OK;
+}
+// K-major weight matrix [rows][ldk], box (32, BN)
+int32_t make_tmap_w(CUtensorMap* m, const float* ptr, int ldk, int rows, int BN) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[2] = {(cuuint64_t)ldk, (cuuint64_t)rows};
+    cuuint64_t gstr[1] = {(cuuint64_t)ldk * 4};
+    cuuint32_t box[2] = {32, (cuuint32_t)BN};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(weights ldk=%d rows=%d) failed: %d", ldk, rows, (int)r);
+    return DINCAE_OK;
+}
+
+template <int BN, int STAGES>
+constexpr int tm_smem_bytes() { return STAGES * (TM_BM * 128 + BN * 128) + 1024; }
+
+}  // namespace
+
+#define TMA_LAUNCH(BN_, ST_)                                                                                               \
+    do {                                                                                                                   \
+        auto conv3x3_tma_bn##BN_ = conv3x3_tma<BN_, ST_>;                                                                  \
+        constexpr int smem = tm_smem_bytes<BN_, ST_>();                                                                    \
+        static bool attr_set = false;                                                                                      \
+        if (!attr_set) {                                                                                                   \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_tma_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));   \
+            attr_set = true;                                                                                               \
+        }                                                                                                                  \
+        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_LAUNCH(ctx, conv3x3_tma_bn##BN_, grid, 128, smem, tmA, tmB, p);                                                 \
+        DC_CHECK_LAUNCH();                                                                                                 \
+        return DINCAE_OK;                                                                                                  \
+    } while (0)
+
+bool k2_conv_tma_eligible(const ConvArgs& a) {
+    return a.wgtK != nullptr && a.in.mode == SRC_DIRECT && a.in.src1 == nullptr && (a.in.C % TM_KC) == 0 && (a.Cout_p % 32) == 0 &&
+           a.in_is_tf32 && get_encode() != nullptr;
+}
+
+int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
+    if (a.B * a.H * a.W == 0) return DINCAE_OK;
+    TmaConvArgs p;
+    p.B = a.B; p.H = a.H; p.W = a.W;
+    p.PW = a.W > 8 ? 16 : 8;
+    p.PH = TM_BM / p.PW;
+    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
+    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
+    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
+    alignas(64) CUtensorMap tmA, tmB;
+    DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
+    if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
+    if (a.Cout_p % 128 == 0) TMA_LAUNCH(128, 3);
+    if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
+    TMA_LAUNCH(32, 5);
+}

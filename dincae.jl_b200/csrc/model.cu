@@ -67,7 +67,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
-        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p;
+        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = (l >= 1);     // X[l>=1] comes from pool_kernel (rounded)
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
@@ -131,7 +131,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
-        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p;
+        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = (l >= 1);   // GD[l>=1] from upbwd (rounded)
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
@@ -156,7 +156,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.in = ConvSrc{M->GC[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cout_p};
             a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f;
-            a.wgtK = M->wTK ? M->wTK + e.wk_off : nullptr; a.ldk = 9 * e.Cout_p;
+            a.wgtK = M->wTK ? M->wTK + e.wk_off : nullptr; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;        // GC[l] from poolbwd (rounded)
             a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
             a.dst = M->XG[l];
             a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
@@ -309,6 +309,7 @@ int32_t points_loss(dincae_model* M, PointTruth& pt, int B, int64_t n_valid_glob
 }
 
 int32_t backward_all(dincae_model* M, int B) {
+    M->ctx->tf32_acts = M->wK != nullptr;
     DC_TRY(ensure_wT(M));
     for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
     DC_LAUNCH(M->ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
@@ -386,6 +387,7 @@ int32_t download_internal(dincae_model* M, const float* src, float* flux) {
 }  // namespace
 
 int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool) {
+    M->ctx->tf32_acts = M->wK != nullptr;
     if (M->wK) DC_TRY(ensure_wT(M));        // the tensor-core forward reads the K-major TF32 weight copy
     for (int c = 0; c < M->nchains; c++) DC_TRY(chain_forward(M, c, d_xin, B));
     return DINCAE_OK;
