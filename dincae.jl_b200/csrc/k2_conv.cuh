@@ -51,6 +51,7 @@ struct WgradArgs {
     int splits;
     int64_t pix_per_split;
     double work_flops;
+    int tf32;             // operands are TF32-representable: the TMA/tcgen05 kernel may be used
 };
 
 // small-Cout forward (Cout_p in {4,8}): NHWC in -> planar out[b][co][y][x] (co < Cout real)
@@ -72,7 +73,10 @@ int32_t k2_conv_tc(dincae_ctx* ctx, const ConvArgs& a);
 bool k2_conv_tma_eligible(const ConvArgs& a);
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a);
 size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
-int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);
+int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);   // dispatches to the tcgen05 kernel when eligible
+bool k2_wgrad_tma_eligible(const WgradArgs& a);
+size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
+int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t scratch_bytes);
 int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco);
 // weight gradient for gout with NCO (4 or 8) padded channels
 int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, size_t scratch_bytes);
@@ -86,6 +90,8 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
 // backward of mean-pool + activation mask: gc = 0.25 * xg[(y+oh)>>1,(x+ow)>>1] * act'(a)
 int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc);
 // bilinear (align_corners=true) upsample+crop of (src0 + src1) and its transpose
+// nearest upsample x2 + crop of (src0 + src1), materialised (TF32 mode: feeds the TMA kernels)
+int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);
 int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);
 int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, int Hs, int Ws, const float* r, float slope, float* G, float* gd);
 

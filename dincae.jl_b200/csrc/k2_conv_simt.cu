@@ -450,7 +450,7 @@ __device__ __forceinline__ void bil_coord(int o, int nin, int nout_full, int& i0
     f = s - (float)i0;
 }
 __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
-                                   int H, int W, float* __restrict__ dst) {
+                                   int H, int W, float* __restrict__ dst, int rnd) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * H * W * C4;
@@ -478,7 +478,24 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
     o.y = w00 * v00.y + w01 * v01.y + w10 * v10.y + w11 * v11.y;
     o.z = w00 * v00.z + w01 * v01.z + w10 * v10.z + w11 * v11.z;
     o.w = w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w;
-    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = o;
+    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(o, rnd);
+}
+__global__ void up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
+                                  int H, int W, float* __restrict__ dst, int rnd) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * H * W * C4;
+    if (i >= total) return;
+    int c4 = (int)(i % C4);
+    int64_t p = i / C4;
+    int x = (int)(p % W);
+    p /= W;
+    int y = (int)(p % H);
+    int b = (int)(p / H);
+    size_t off = (((size_t)b * Hs + (y >> 1)) * Ws + (x >> 1)) * Cp + c4 * 4;
+    float4 v = ldg4(s0 + off);
+    if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(v, rnd);
 }
 // transpose: each low-res cell gathers from the high-res cells whose stencil touches it (deterministic)
 __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
@@ -589,6 +606,7 @@ size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int C
 }
 
 int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes) {
+    if (k2_wgrad_tma_eligible(a)) return k2_wgrad_tma(ctx, a, scratch, scratch_bytes);
     int Mtot = a.B * a.H * a.W;
     int Krows = 9 * a.in.C;
     int Kt, Nt, splits;
@@ -693,7 +711,15 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
 int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, up_bilinear_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst);
+    DC_LAUNCH(ctx, up_bilinear_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
+    int64_t n = (int64_t)B * H * W * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, up_nearest_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -274,3 +274,299 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
     TMA_LAUNCH(32, 5);
 }
+
+// =================================================================================================
+// Weight gradient on the tensor cores:  dW[tap][ci][co] = sum over pixels of in[pixel + tap][ci] * g[pixel][co].
+// Both operands are pixel-major NHWC tensors, i.e. MN-major for the MMA (channels contiguous, the reduction index
+// = pixel is the slow one).  Per stage one 8x4 pixel patch is streamed by TMA as 32-channel boxes (4 KB each, 32 pixel
+// rows x 128 B, 128B swizzle with 32B atoms = the canonical MN-major TF32 layout: 4-row atoms 512 B apart, 32-channel blocks LBO apart);
+// the tap is a shift of the `in` box, padding is TMA zero fill.  D (128 x N, FP32) lives in TMEM; the reduction over
+// pixels is split over CTAs and finished by a deterministic second-stage sum (no float atomics).
+namespace {
+
+constexpr int WG_KP = 32;             // pixels per stage (8 wide x 4 high)
+constexpr int WG_BLOCK = WG_KP * 128; // bytes of one 32-channel block of a stage
+
+struct WgradTmaArgs {
+    int B, H, W;
+    int ptx, pty;            // 8x4 patches per image
+    int Cin_p, Cout_p;
+    int in_is_m;             // 1: M = ci (in), N = co (g);  0: M = co (g), N = ci (in)
+    int m_ch, n_ch;          // channels of the M / N operand
+    int64_t npatches, patches_per_split;
+    float* partial;          // [splits][9*Cin_p*Cout_p]
+};
+
+// MN-major TF32 operands must use the 128-byte swizzle with 32-byte atomicity (layout type SWIZZLE_128B_BASE32B,
+// Swizzle<2,5,2>: the 32-byte chunk index is XORed with the pixel-row index mod 4); its K atom is 4 rows (512 B), so one
+// K = 8 MMA spans two atoms SBO apart.  TMA writes the same pattern with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+__device__ __forceinline__ uint64_t make_desc_mn_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(WG_BLOCK >> 4) << 16;             // leading byte offset: next 32-channel block
+    d |= (uint64_t)(512 >> 4) << 32;                  // stride byte offset: next 4 pixel rows
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;                           // SWIZZLE_128B_BASE32B
+    return d;
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(128) wgrad_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int A_BYTES = 4 * WG_BLOCK, B_BYTES = (BN / 32) * WG_BLOCK, STAGE_BYTES = A_BYTES + B_BYTES;
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int split = blockIdx.x, m0 = blockIdx.y * 128;
+    const int ntiles = (p.n_ch + BN - 1) / BN;
+    const int tap = blockIdx.z / ntiles, n0 = (blockIdx.z - tap * ntiles) * BN;
+    const int ky = tap / 3, kx = tap - ky * 3;
+    const int64_t p_lo = (int64_t)split * p.patches_per_split;
+    int64_t p_hi = p_lo + p.patches_per_split;
+    if (p_hi > p.npatches) p_hi = p.npatches;
+    const int nst = (int)(p_hi - p_lo);
+    const int mblocks = min(4, (p.m_ch - m0) / 32), nblocks = min(BN / 32, (p.n_ch - n0) / 32);
+
+    // zero the channel blocks that no TMA box will ever fill (operand narrower than the MMA tile)
+    if (mblocks < 4 || nblocks < BN / 32) {
+        for (int s = 0; s < STAGES; s++) {
+            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+            for (int i = t; i < (4 - mblocks) * WG_BLOCK / 16; i += 128)
+                reinterpret_cast<float4*>(st + mblocks * WG_BLOCK)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = t; i < (BN / 32 - nblocks) * WG_BLOCK / 16; i += 128)
+                reinterpret_cast<float4*>(st + A_BYTES + nblocks * WG_BLOCK)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    // D = F32, A = B = TF32, both MN-major (bits 15, 16), N = BN, M = 128
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+    if (t == 0) {
+        // ===== TMA producer =====
+        const CUtensorMap* mapM = p.in_is_m ? &tmIn : &tmG;
+        const CUtensorMap* mapN = p.in_is_m ? &tmG : &tmIn;
+        const int sxM = p.in_is_m ? kx - 1 : 0, syM = p.in_is_m ? ky - 1 : 0;     // the tap shifts the `in` operand only
+        const int sxN = p.in_is_m ? 0 : kx - 1, syN = p.in_is_m ? 0 : ky - 1;
+        const int per_img = p.ptx * p.pty;
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int64_t pp = p_lo + i;
+            const int b = (int)(pp / per_img);
+            const int r = (int)(pp - (int64_t)b * per_img);
+            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+            mbar_expect_tx(&bar_full[s], (uint32_t)((mblocks + nblocks) * WG_BLOCK));
+            for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * WG_BLOCK, mapM, &bar_full[s], m0 + j * 32, x0 + sxM, y0 + syM, b);
+            for (int j = 0; j < nblocks; j++) tma_load_4d(st + A_BYTES + j * WG_BLOCK, mapN, &bar_full[s], n0 + j * 32, x0 + sxN, y0 + syN, b);
+        }
+    } else if (t == 32) {
+        // ===== MMA issuer =====
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t da = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES));
+            const uint64_t db = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES + A_BYTES));
+#pragma unroll
+            for (int k = 0; k < WG_KP / 8; k++)          // 8 pixel rows per MMA: advance by one 1024-byte atom
+                umma_tf32(tmem_d, da + (uint64_t)(64 * k), db + (uint64_t)(64 * k), IDESC, (i | k) != 0 ? 1u : 0u);
+            umma_commit(&bar_empty[s]);
+        }
+        umma_commit(&bar_done);
+    }
+    __syncwarp();
+    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
+    const int mch = m0 + t;
+    if (nst > 0) {
+        mbar_wait(&bar_done, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int cb = 0; cb < BN; cb += 16) {
+        uint32_t r[16];
+        if (nst > 0) {
+            tmem_ld16(lane_addr + (uint32_t)cb, r);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        } else {
+#pragma unroll
+            for (int q = 0; q < 16; q++) r[q] = 0u;
+        }
+        if (mch < p.m_ch) {
+#pragma unroll
+            for (int q = 0; q < 16; q++) {
+                const int nch = n0 + cb + q;
+                if (nch < p.n_ch) {
+                    const int ci = p.in_is_m ? mch : nch, co = p.in_is_m ? nch : mch;
+                    out[((size_t)tap * p.Cin_p + ci) * p.Cout_p + co] = __uint_as_float(r[q]);
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
+}
+
+__global__ void reduce_splits_kernel(const float* __restrict__ partial, int splits, int64_t n, float* __restrict__ dst) {
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = 0.f;
+    for (int z = 0; z < splits; z++) s += partial[(size_t)z * n + i];
+    dst[i] = s;
+}
+
+// bias gradient: column sums of columns [c0, c0+Cw) of g [M][C] in two deterministic stages
+__global__ void colsum_partial_kernel(const float* __restrict__ g, int64_t M, int C, int c0, int Cw, int64_t rows_per_block, float* __restrict__ part) {
+    const int c = threadIdx.x % Cw, lane_rows = blockDim.x / Cw, r0 = threadIdx.x / Cw;
+    __shared__ float sh[256];
+    int64_t lo = (int64_t)blockIdx.x * rows_per_block, hi = lo + rows_per_block;
+    if (hi > M) hi = M;
+    float s = 0.f;
+    for (int64_t r = lo + r0; r < hi; r += lane_rows) s += g[r * C + c0 + c];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x < Cw) {
+        float tot = 0.f;
+        for (int k = 0; k < lane_rows; k++) tot += sh[k * Cw + threadIdx.x];
+        part[(size_t)blockIdx.x * C + c0 + threadIdx.x] = tot;
+    }
+}
+
+int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, 8, 4, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(patch C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
+    return DINCAE_OK;
+}
+
+template <int BN, int STAGES>
+constexpr int wg_smem_bytes() { return STAGES * (4 * WG_BLOCK + (BN / 32) * WG_BLOCK) + 1024; }
+
+void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64_t& npatches, int64_t& pps, int& in_is_m) {
+    const int Cin_p = a.in.C, Cout_p = a.Cout_p;
+    in_is_m = Cin_p >= Cout_p;
+    const int m_ch = in_is_m ? Cin_p : Cout_p, n_ch = in_is_m ? Cout_p : Cin_p;
+    bn = n_ch % 256 == 0 ? 256 : (n_ch % 128 == 0 ? 128 : (n_ch % 64 == 0 ? 64 : 32));
+    const int mtiles = (m_ch + 127) / 128, ntiles = n_ch / bn;
+    npatches = (int64_t)a.B * dc_cdiv(a.H, 4) * dc_cdiv(a.W, 8);
+    int tiles = mtiles * ntiles * 9;
+    splits = (3 * num_sms + tiles - 1) / tiles;
+    int64_t maxs = dc_cdiv(npatches, 4);
+    if (splits > maxs) splits = (int)maxs;
+    if (splits < 1) splits = 1;
+    pps = dc_cdiv(npatches, splits);
+    splits = (int)dc_cdiv(npatches, pps);
+}
+
+}  // namespace
+
+bool k2_wgrad_tma_eligible(const WgradArgs& a) {
+    return a.tf32 && a.in.mode == SRC_DIRECT && a.in.src1 == nullptr && (a.in.C % 32) == 0 && (a.Cout_p % 32) == 0 && get_encode() != nullptr;
+}
+
+size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p) {
+    if (Cin_p % 32 || Cout_p % 32) return 0;
+    WgradArgs a{};
+    a.in.C = Cin_p; a.Cout_p = Cout_p; a.B = B; a.H = H; a.W = W;
+    int bn, splits, in_is_m;
+    int64_t np, pps;
+    wgrad_tma_plan(num_sms, a, bn, splits, np, pps, in_is_m);
+    return ((size_t)splits * 9 * Cin_p * Cout_p + 1024 * (size_t)Cout_p) * sizeof(float);
+}
+
+#define WG_LAUNCH(BN_, ST_)                                                                                                \
+    do {                                                                                                                   \
+        auto wgrad_tma_bn##BN_ = wgrad_tma<BN_, ST_>;                                                                      \
+        constexpr int smem = wg_smem_bytes<BN_, ST_>();                                                                    \
+        static bool attr_set = false;                                                                                      \
+        if (!attr_set) {                                                                                                   \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tma_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));     \
+            attr_set = true;                                                                                               \
+        }                                                                                                                  \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_LAUNCH(ctx, wgrad_tma_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                  \
+        DC_CHECK_LAUNCH();                                                                                                 \
+    } while (0)
+
+int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t scratch_bytes) {
+    const int Cin_p = a.in.C, Cout_p = a.Cout_p;
+    int bn, splits, in_is_m;
+    int64_t np, pps;
+    wgrad_tma_plan(ctx->num_sms, a, bn, splits, np, pps, in_is_m);
+    const int64_t nW = (int64_t)9 * Cin_p * Cout_p;
+    const int64_t M = (int64_t)a.B * a.H * a.W;
+    const int cs_blocks = (int)(M < 1024 * 64 ? dc_cdiv(M, 64) : 1024);
+    DC_REQUIRE(scratch_bytes >= ((size_t)splits * nW + (size_t)cs_blocks * Cout_p) * sizeof(float), DINCAE_ESIZE, "k2_wgrad_tma: scratch too small");
+    WgradTmaArgs p;
+    p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, 4);
+    p.Cin_p = Cin_p; p.Cout_p = Cout_p; p.in_is_m = in_is_m;
+    p.m_ch = in_is_m ? Cin_p : Cout_p; p.n_ch = in_is_m ? Cout_p : Cin_p;
+    p.npatches = np; p.patches_per_split = pps; p.partial = (float*)scratch;
+    alignas(64) CUtensorMap tmIn, tmG;
+    DC_TRY(make_tmap_patch(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
+    DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
+    dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(9 * (p.n_ch / bn)));
+    if (bn == 256) WG_LAUNCH(256, 2);
+    else if (bn == 128) WG_LAUNCH(128, 3);
+    else if (bn == 64) WG_LAUNCH(64, 4);
+    else WG_LAUNCH(32, 4);
+    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 256), 256, 0, p.partial, splits, nW, a.dW);
+    DC_CHECK_LAUNCH();
+    // bias gradient
+    float* cpart = p.partial + (size_t)splits * nW;
+    const int64_t rpb = dc_cdiv(M, cs_blocks);
+    for (int c0 = 0; c0 < Cout_p; c0 += 256) {
+        const int Cw = Cout_p - c0 < 256 ? Cout_p - c0 : 256;
+        const int threads = (256 / Cw) * Cw;
+        DC_LAUNCH(ctx, colsum_partial_kernel, cs_blocks, threads, 0, a.gout, M, Cout_p, c0, Cw, rpb, cpart);
+        DC_CHECK_LAUNCH();
+    }
+    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(Cout_p, 256), 256, 0, cpart, cs_blocks, (int64_t)Cout_p, a.db);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+// ---- test hook (not part of the public header): run one weight gradient through either kernel family ----------
+extern "C" int32_t dincae_debug_wgrad(dincae_ctx* ctx, const float* d_in, const float* d_g, int32_t B, int32_t H, int32_t W,
+                                      int32_t Cin_p, int32_t Cout_p, float* d_dW, float* d_db, int32_t use_tma) {
+    DC_REQUIRE(ctx && d_in && d_g && d_dW && d_db, DINCAE_EINVAL, "dincae_debug_wgrad: NULL argument");
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    WgradArgs a{};
+    a.in = ConvSrc{d_in, nullptr, SRC_DIRECT, H, W, Cin_p};
+    a.B = B; a.H = H; a.W = W; a.gout = d_g; a.Cout_p = Cout_p; a.dW = d_dW; a.db = d_db; a.tf32 = use_tma;
+    size_t need = k2_wgrad_scratch_bytes(ctx->num_sms, B, H, W, Cin_p, Cout_p);
+    size_t need2 = k2_wgrad_tma_scratch_bytes(ctx->num_sms, B, H, W, Cin_p, Cout_p);
+    if (need2 > need) need = need2;
+    void* sc = nullptr;
+    DC_TRY(dc_scratch(ctx, need, &sc));
+    return k2_wgrad(ctx, a, sc, ctx->scratch_bytes);
+}

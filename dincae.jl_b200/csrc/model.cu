@@ -45,10 +45,14 @@ int32_t dec_source(dincae_model* M, int c, int l, int B, bool materialise, ConvS
     const float* src0 = (l + 1 == M->L) ? cb.X[M->L] : cb.R[l + 1];
     const float* src1 = has_skip(M, l + 1) ? cb.X[l + 1] : nullptr;
     int Cp = M->dec[c][l].Cin_p;
-    if (M->cfg.upsampling == DINCAE_UP_NEAREST) {
-        *s = ConvSrc{src0, src1, SRC_UP_NEAREST, M->Hl[l + 1], M->Wl[l + 1], Cp};
+    if (M->cfg.upsampling == DINCAE_UP_NEAREST && !M->wK) {
+        *s = ConvSrc{src0, src1, SRC_UP_NEAREST, M->Hl[l + 1], M->Wl[l + 1], Cp};       // FP32 path: fused into the conv producer
     } else {
-        if (materialise) DC_TRY(k2_up_bilinear(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
+        // bilinear, or TF32 mode: materialise u_l = crop(upsample(y_{l+1})) once (TF32-rounded), it feeds the TMA conv + wgrad
+        if (materialise) {
+            if (M->cfg.upsampling == DINCAE_UP_NEAREST) DC_TRY(k2_up_nearest(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
+            else DC_TRY(k2_up_bilinear(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
+        }
         *s = ConvSrc{cb.U[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], Cp};
     }
     return DINCAE_OK;
@@ -81,7 +85,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             ConvArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
-            a.wgtK = M->wK ? M->wK + d.wk_off : nullptr; a.ldk = 9 * d.Cin_p;
+            a.wgtK = M->wK ? M->wK + d.wk_off : nullptr; a.ldk = 9 * d.Cin_p; a.in_is_tf32 = M->wK != nullptr;   // U[l] is rounded on store
             a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
             a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
@@ -125,6 +129,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
         wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
         wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
+        wa.tf32 = M->wK != nullptr;
         if (l == 0) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
         else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         ConvArgs a{};
@@ -150,6 +155,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
         wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
+        wa.tf32 = M->wK != nullptr && l >= 1;
         DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         if (l >= 1) {
             ConvArgs a{};
@@ -478,7 +484,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     }
     want((void**)&M->d_wtab, sizeof(WLayerDesc) * wtab.size());
     const size_t planar_out = sizeof(float) * Bm * 2 * M->O * cfg->W * cfg->H;
-    const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR;
+    const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR || cfg->precision == DINCAE_PREC_TF32;   // U[l] materialised
     for (int c = 0; c < M->nchains; c++) {
         ChainBufs& cb = M->cb[c];
         memset(&cb, 0, sizeof(cb));
@@ -522,6 +528,10 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             size_t b = k2_wgrad_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
             wgb = a > wgb ? a : wgb;
             wgb = b > wgb ? b : wgb;
+            size_t ta = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
+            size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
+            wgb = ta > wgb ? ta : wgb;
+            wgb = tb > wgb ? tb : wgb;
         }
     M->wg_scratch_bytes = wgb;
     want(&M->wg_scratch, wgb);
