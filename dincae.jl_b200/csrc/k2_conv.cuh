@@ -36,7 +36,10 @@ struct ConvArgs {
     int act;
     float slope;          // leaky slope (0 = ReLU)
     const float* addend;  // optional [B,H,W,Cout_p], added AFTER the activation
-    float* dst;           // [B,H,W,Cout_p]
+    float* dst;           // [B,H,W,Cout_p] (may be NULL when planar_out is given)
+    float* planar_out;    // optional planar (Julia WHCN) output [B][planar_C][H][W] of the first planar_C channels (TMA kernel only)
+    int planar_C;
+    int planar_accumulate;   // 1: planar_out += value
     double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
 };
 

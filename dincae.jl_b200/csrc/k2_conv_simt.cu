@@ -342,7 +342,7 @@ __global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits
 
 // ---------------------------------------------------------------------------------------------
 __global__ void pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
-                                   int B, int HW, float* __restrict__ dst, int Cp) {
+                                   int B, int HW, float* __restrict__ dst, int Cp, int rnd) {
     int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (m >= (int64_t)B * HW) return;
     int b = (int)(m / HW), r = (int)(m - (int64_t)b * HW);
@@ -354,7 +354,7 @@ __global__ void pack_planar_kernel(const float* __restrict__ s0, int C0, const f
             v[e] = cc < C0 ? __ldg(s0 + ((size_t)b * C0 + cc) * HW + r)
                  : (cc < C0 + C1 ? __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r) : 0.f);
         }
-        *reinterpret_cast<float4*>(dst + (size_t)m * Cp + c) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(dst + (size_t)m * Cp + c) = round_tf32(make_float4(v[0], v[1], v[2], v[3]), rnd);
     }
 }
 
@@ -568,6 +568,7 @@ int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
     int Mtot = a.B * a.H * a.W;
     if (Mtot == 0) return DINCAE_OK;
     if (k2_conv_tma_eligible(a)) return k2_conv_tma(ctx, a);
+    DC_REQUIRE(a.planar_out == nullptr, DINCAE_EUNSUPPORTED, "k2_conv: planar output needs the TMA tensor-core kernel (driver without cuTensorMapEncodeTiled?)");
     if (k2_conv_tc_eligible(a)) return k2_conv_tc(ctx, a);
     int Kpad = dc_round_up(9 * a.in.C, 16);
     int nchunks = Kpad / 16;
@@ -676,7 +677,7 @@ int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, siz
 int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
     int64_t M = (int64_t)B * H * W;
     if (M == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp);
+    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

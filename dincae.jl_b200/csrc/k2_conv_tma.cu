@@ -23,6 +23,8 @@ struct TmaConvArgs {
     float slope;
     const float* addend;
     float* dst;
+    float* planar_out;
+    int planar_C, planar_accumulate;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -162,7 +164,20 @@ __global__ void __launch_bounds__(128) conv3x3_tma(const __grid_constant__ CUten
         tmem_ld16(lane_addr + (uint32_t)cb, r);
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         const int n = n0 + cb;
-        if (pv && n < p.Cout_p) {
+        if (pv && p.planar_out && n < p.planar_C) {
+            // planar (WHCN) output of the first planar_C channels: threads of a warp = consecutive x of one patch row -> coalesced
+#pragma unroll
+            for (int q = 0; q < 16; q++) {
+                const int co = n + q;
+                if (co < p.planar_C) {
+                    float v = __uint_as_float(r[q]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+                    v = act_apply(v, p.act, p.slope);
+                    const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
+                    p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
+                }
+            }
+        }
+        if (pv && p.dst && n < p.Cout_p) {
             const size_t off = m * p.Cout_p + n;
 #pragma unroll
             for (int q = 0; q < 4; q++) {
@@ -182,6 +197,7 @@ __global__ void __launch_bounds__(128) conv3x3_tma(const __grid_constant__ CUten
                 *reinterpret_cast<float4*>(p.dst + off + 4 * q) = o;
             }
         }
+        if (!p.dst && n + 16 >= p.planar_C) break;       // planar-only output: the remaining accumulator columns are not needed
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -267,6 +283,7 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
     if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);

@@ -71,7 +71,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
-        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = (l >= 1);     // X[l>=1] comes from pool_kernel (rounded)
+        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = 1;     // X[0] from pack, X[l>=1] from pool_kernel (both rounded on store)
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
@@ -89,6 +89,16 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
             a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
+        } else if (M->wK) {
+            // TF32 mode: the 2*nout-channel head conv runs on the tensor cores too (channels padded to 32), planar output
+            ConvArgs a{};
+            a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
+            a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
+            a.wgtK = M->wK + d.wk_off; a.ldk = 9 * d.Cin_p; a.in_is_tf32 = 1;
+            a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = nullptr;
+            a.planar_out = cb.RAW; a.planar_C = 2 * M->O; a.planar_accumulate = 0;
+            a.work_flops = cflops(d, B, M->Hl[0], M->Wl[0]);
+            DC_TRY(k2_conv(ctx, a));
         } else {
             ConvSmallArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
@@ -130,13 +140,13 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
         wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
-        if (l == 0) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
+        if (l == 0 && !M->wK) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
         else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         ConvArgs a{};
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
-        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = (l >= 1);   // GD[l>=1] from upbwd (rounded)
+        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = 1;   // GD[l>=1] from upbwd, GD0 from pack (both rounded on store)
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
@@ -155,7 +165,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
         wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
-        wa.tf32 = M->wK != nullptr && l >= 1;
+        wa.tf32 = M->wK != nullptr;
         DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         if (l >= 1) {
             ConvArgs a{};
@@ -168,6 +178,16 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));
             xg = M->XG[l];
+        } else if (c >= 1 && M->wK) {
+            // gradient w.r.t. the first 2*nout input channels of the refinement chain = raw output of chain c-1 (tensor cores, planar +=)
+            ConvArgs a{};
+            a.in = ConvSrc{M->GC[0], nullptr, SRC_DIRECT, M->Hl[0], M->Wl[0], e.Cout_p};
+            a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
+            a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = nullptr;
+            a.wgtK = M->wTK + e.wk_off; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;
+            a.planar_out = M->cb[c - 1].GRAW; a.planar_C = 2 * M->O; a.planar_accumulate = 1;
+            a.work_flops = 2.0 * 9 * 2 * M->O * e.Cout * (double)B * M->Hl[0] * M->Wl[0];
+            DC_TRY(k2_conv(ctx, a));
         } else if (c >= 1) {
             // gradient w.r.t. the first 2*nout input channels of the refinement chain = raw output of chain c-1
             ConvSmallArgs a{};
@@ -419,7 +439,8 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
 
     dincae_model* M = new dincae_model();
     M->ctx = ctx; M->cfg = *cfg; M->L = cfg->nlevels; M->nchains = cfg->nchains; M->O = cfg->noutput; M->maxB = cfg->max_batch;
-    M->nco = dc_round_up(2 * M->O, 4);
+    const int cpad = cfg->precision == DINCAE_PREC_TF32 ? 32 : 4;     // TF32 mode: every conv is tensor-core eligible (32-channel K chunks)
+    M->nco = dc_round_up(2 * M->O, cpad);
     const int L = M->L;
     M->Hl[0] = cfg->H; M->Wl[0] = cfg->W;
     for (int l = 0; l < L; l++) { M->Hl[l + 1] = M->Hl[l] / 2 + M->Hl[l] % 2; M->Wl[l + 1] = M->Wl[l] / 2 + M->Wl[l] % 2; }   // sz_small, src/model.jl:258-261
@@ -435,7 +456,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         for (int l = 0; l < L; l++) { encf[l + 1] = cfg->nfilter[l]; decf[l + 1] = cfg->nfilter[l]; }
         M->enc[c].resize(L); M->dec[c].resize(L);
         auto fill = [&](LayerInfo& y, int cin, int cout) {
-            y.Cin = cin; y.Cout = cout; y.Cin_p = dc_round_up(cin, 4); y.Cout_p = dc_round_up(cout, 4);
+            y.Cin = cin; y.Cout = cout; y.Cin_p = dc_round_up(cin, cpad); y.Cout_p = dc_round_up(cout, cpad);
             y.Kpad = dc_round_up(9 * y.Cin_p, 16); y.KpadT = dc_round_up(9 * y.Cout_p, 16);
             y.w_off = off; off += (int64_t)y.Kpad * y.Cout_p;
             y.b_off = off; off += y.Cout_p;
