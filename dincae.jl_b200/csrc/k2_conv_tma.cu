@@ -8,6 +8,7 @@
 // weights come from the rounded K-major copy).  Used by the encoder convs and all data-gradient convs.
 #include "k2_conv.cuh"
 #include <cuda.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -252,6 +253,210 @@ constexpr int tm_smem_bytes() { return STAGES * (TM_BM * 128 + BN * 128) + 1024;
 
 }  // namespace
 
+// -------------------------------------------------------------------------------------------------
+// Halo variant: per 32-channel K chunk the (8+2) x (16+2) pixel halo of the output patch is loaded ONCE; the nine
+// taps are nine descriptor views of that tile (start address shifted by (dy*10+dx) rows of 128 B, 8-pixel row groups
+// one halo pitch = 1280 B apart), so the activation operand crosses L2->SM once instead of nine times.  The weight
+// tiles (one per chunk and tap) stream through their own ring.
+namespace {
+
+constexpr int HL_PW = 8, HL_PH = 16, HL_HW = HL_PW + 2, HL_HH = HL_PH + 2;
+constexpr int HL_A_BYTES = HL_HW * HL_HH * 128;                // 23040
+constexpr int HL_A_STRIDE = (HL_A_BYTES + 1023) / 1024 * 1024;  // 23552
+
+__device__ __forceinline__ uint64_t make_desc_k_sw128_halo(uint32_t saddr, int use_base_offset) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((HL_HW * 128) >> 4) << 32;        // stride between 8-pixel row groups = one halo row pitch
+    d |= (uint64_t)1 << 46;
+    if (use_base_offset) d |= (uint64_t)((saddr >> 7) & 7) << 49;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+template <int BN, int ASTAGES, int BSTAGES>
+__global__ void __launch_bounds__(128) conv3x3_halo(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p, int use_base_offset) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int B_BYTES = BN * 128;
+    __shared__ uint64_t bar_fullA[ASTAGES], bar_emptyA[ASTAGES], bar_fullB[BSTAGES], bar_emptyB[BSTAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemB = smem + ASTAGES * HL_A_STRIDE;
+    const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int n0 = blockIdx.y * BN;
+    const int patches = p.ptx * p.pty;
+    const int b = blockIdx.x / patches;
+    const int pr = blockIdx.x - b * patches;
+    const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+    const int nkc = p.Cin_p / TM_KC;
+
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+#pragma unroll
+        for (int s = 0; s < ASTAGES; s++) { mbar_init(&bar_fullA[s], 1); mbar_init(&bar_emptyA[s], 1); }
+#pragma unroll
+        for (int s = 0; s < BSTAGES; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
+
+    if (t == 0) {
+        // ===== TMA producer =====
+        int ib = 0;
+        for (int kc = 0; kc < nkc; kc++) {
+            const int sa = kc % ASTAGES, ua = kc / ASTAGES;
+            if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+            mbar_expect_tx(&bar_fullA[sa], (uint32_t)HL_A_BYTES);
+            tma_load_4d(smem + (size_t)sa * HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x0 - 1, y0 - 1, b);   // OOB -> zeros = conv padding
+            for (int tap = 0; tap < 9; tap++, ib++) {
+                const int sb = ib % BSTAGES, ub = ib / BSTAGES;
+                if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
+                mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
+                tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
+            }
+        }
+    } else if (t == 32) {
+        // ===== MMA issuer =====
+        int ib = 0;
+        for (int kc = 0; kc < nkc; kc++) {
+            const int sa = kc % ASTAGES, ua = kc / ASTAGES;
+            mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
+            for (int tap = 0; tap < 9; tap++, ib++) {
+                const int sb = ib % BSTAGES, ub = ib / BSTAGES;
+                mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const int dy = tap / 3, dx = tap - dy * 3;
+                const uint32_t a_addr = smemA_u + (uint32_t)(sa * HL_A_STRIDE + (dy * HL_HW + dx) * 128);
+                const uint64_t da = make_desc_k_sw128_halo(a_addr, use_base_offset);
+                const uint64_t db = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
+#pragma unroll
+                for (int k = 0; k < TM_KC / 8; k++)
+                    umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (kc | tap | k) != 0 ? 1u : 0u);
+                umma_commit(&bar_emptyB[sb]);
+            }
+            umma_commit(&bar_emptyA[sa]);
+        }
+        umma_commit(&bar_done);
+    }
+    __syncwarp();
+    mbar_wait(&bar_done, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+    const int h = t / HL_PW, w = t - h * HL_PW;
+    const int y = y0 + h, x = x0 + w;
+    const bool pv = y < p.H && x < p.W;
+    const size_t m = ((size_t)b * p.H + y) * p.W + x;
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int cb = 0; cb < BN; cb += 16) {
+        uint32_t r[16];
+        tmem_ld16(lane_addr + (uint32_t)cb, r);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int n = n0 + cb;
+        if (pv && p.planar_out && n < p.planar_C) {
+#pragma unroll
+            for (int q = 0; q < 16; q++) {
+                const int co = n + q;
+                if (co < p.planar_C) {
+                    float v = __uint_as_float(r[q]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+                    v = act_apply(v, p.act, p.slope);
+                    const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
+                    p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
+                }
+            }
+        }
+        if (pv && p.dst && n < p.Cout_p) {
+            const size_t off = m * p.Cout_p + n;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                float4 o;
+                o.x = __uint_as_float(r[4 * q + 0]); o.y = __uint_as_float(r[4 * q + 1]);
+                o.z = __uint_as_float(r[4 * q + 2]); o.w = __uint_as_float(r[4 * q + 3]);
+                if (p.bias) {
+                    float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * q));
+                    o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                }
+                o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
+                o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
+                if (p.addend) {
+                    float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * q));
+                    o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
+                }
+                *reinterpret_cast<float4*>(p.dst + off + 4 * q) = o;
+            }
+        }
+        if (!p.dst && n + 16 >= p.planar_C) break;
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
+}
+
+int32_t make_tmap_halo(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, (cuuint32_t)HL_HW, (cuuint32_t)HL_HH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(halo C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
+    return DINCAE_OK;
+}
+
+template <int BN, int AS, int BS>
+constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; }
+
+}  // namespace
+
+#define HALO_LAUNCH(BN_, AS_, BS_)                                                                                         \
+    do {                                                                                                                   \
+        auto conv3x3_halo_bn##BN_ = conv3x3_halo<BN_, AS_, BS_>;                                                           \
+        constexpr int smem = hl_smem_bytes<BN_, AS_, BS_>();                                                               \
+        static bool attr_set = false;                                                                                      \
+        if (!attr_set) {                                                                                                   \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_halo_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));  \
+            attr_set = true;                                                                                               \
+        }                                                                                                                  \
+        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_LAUNCH(ctx, conv3x3_halo_bn##BN_, grid, 128, smem, tmA, tmB, p, halo_mode - 1);                                 \
+        DC_CHECK_LAUNCH();                                                                                                 \
+        return DINCAE_OK;                                                                                                  \
+    } while (0)
+
+static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
+    TmaConvArgs p;
+    p.B = a.B; p.H = a.H; p.W = a.W;
+    p.PW = HL_PW; p.PH = HL_PH;
+    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
+    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
+    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    alignas(64) CUtensorMap tmA, tmB;
+    DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
+    if (a.Cout_p % 256 == 0) HALO_LAUNCH(256, 2, 3);
+    if (a.Cout_p % 128 == 0) HALO_LAUNCH(128, 2, 4);
+    if (a.Cout_p % 64 == 0) HALO_LAUNCH(64, 2, 4);
+    HALO_LAUNCH(32, 2, 4);
+}
+
 #define TMA_LAUNCH(BN_, ST_)                                                                                               \
     do {                                                                                                                   \
         auto conv3x3_tma_bn##BN_ = conv3x3_tma<BN_, ST_>;                                                                  \
@@ -276,6 +481,10 @@ bool k2_conv_tma_eligible(const ConvArgs& a) {
 
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     if (a.B * a.H * a.W == 0) return DINCAE_OK;
+    // DINCAE_CONV_HALO: 0 = one activation box per tap; 1 = halo tile, shifted descriptors (default); 2 = same with base_offset set
+    static int halo_mode = -1;
+    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_HALO"); halo_mode = e ? atoi(e) : 1; }
+    if (halo_mode > 0) return k2_conv_halo(ctx, a, halo_mode);
     TmaConvArgs p;
     p.B = a.B; p.H = a.H; p.W = a.W;
     p.PW = a.W > 8 ? 16 : 8;
@@ -447,29 +656,228 @@ __global__ void __launch_bounds__(128) wgrad_tma(const __grid_constant__ CUtenso
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
 }
 
+// dst[i] = sum over splits of partial[z][i]: 8 independent partial sums (memory-level parallelism) combined in a fixed
+// order, so the result does not depend on scheduling (deterministic second stage of the split-K reduction)
 __global__ void reduce_splits_kernel(const float* __restrict__ partial, int splits, int64_t n, float* __restrict__ dst) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (i >= n) return;
-    float s = 0.f;
-    for (int z = 0; z < splits; z++) s += partial[(size_t)z * n + i];
-    dst[i] = s;
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) s[j] = 0.f;
+    int z = 0;
+    for (; z + 8 <= splits; z += 8) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = __ldg(partial + (size_t)(z + j) * n + i);
+#pragma unroll
+        for (int j = 0; j < 8; j++) s[j] += v[j];
+    }
+    for (int j = 0; z < splits; z++, j++) s[j] += __ldg(partial + (size_t)z * n + i);
+    dst[i] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
 }
 
-// bias gradient: column sums of columns [c0, c0+Cw) of g [M][C] in two deterministic stages
-__global__ void colsum_partial_kernel(const float* __restrict__ g, int64_t M, int C, int c0, int Cw, int64_t rows_per_block, float* __restrict__ part) {
-    const int c = threadIdx.x % Cw, lane_rows = blockDim.x / Cw, r0 = threadIdx.x / Cw;
-    __shared__ float sh[256];
-    int64_t lo = (int64_t)blockIdx.x * rows_per_block, hi = lo + rows_per_block;
-    if (hi > M) hi = M;
-    float s = 0.f;
-    for (int64_t r = lo + r0; r < hi; r += lane_rows) s += g[r * C + c0 + c];
-    sh[threadIdx.x] = s;
-    __syncthreads();
-    if (threadIdx.x < Cw) {
-        float tot = 0.f;
-        for (int k = 0; k < lane_rows; k++) tot += sh[k * Cw + threadIdx.x];
-        part[(size_t)blockIdx.x * C + c0 + threadIdx.x] = tot;
+// bias gradient: column sums of g [M][C] (C % 4 == 0) in two deterministic stages.
+// stage 1: block b sums rows b, b+gridDim, ... ; thread = (row lane, float4 column group); fixed-order smem combine.
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ g, int64_t M, int C, float* __restrict__ part) {
+    const int C4 = C >> 2;                       // float4 column groups (<= 64 per pass)
+    __shared__ float4 sh[256];
+    for (int cg0 = 0; cg0 < C4; cg0 += 64) {
+        const int ncg = C4 - cg0 < 64 ? C4 - cg0 : 64;
+        const int lanes = 256 / ncg;             // row lanes
+        const int cg = threadIdx.x % ncg, rl = threadIdx.x / ncg;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rl < lanes) {
+            const int64_t stride = (int64_t)gridDim.x * lanes;
+            int64_t r = (int64_t)blockIdx.x * lanes + rl;
+            for (; r + 3 * stride < M; r += 4 * stride) {
+                float4 v0 = __ldg(reinterpret_cast<const float4*>(g + r * C) + cg0 + cg);
+                float4 v1 = __ldg(reinterpret_cast<const float4*>(g + (r + stride) * C) + cg0 + cg);
+                float4 v2 = __ldg(reinterpret_cast<const float4*>(g + (r + 2 * stride) * C) + cg0 + cg);
+                float4 v3 = __ldg(reinterpret_cast<const float4*>(g + (r + 3 * stride) * C) + cg0 + cg);
+                s.x += (v0.x + v1.x) + (v2.x + v3.x); s.y += (v0.y + v1.y) + (v2.y + v3.y);
+                s.z += (v0.z + v1.z) + (v2.z + v3.z); s.w += (v0.w + v1.w) + (v2.w + v3.w);
+            }
+            for (; r < M; r += stride) {
+                float4 v = __ldg(reinterpret_cast<const float4*>(g + r * C) + cg0 + cg);
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        }
+        __syncthreads();
+        sh[threadIdx.x] = s;
+        __syncthreads();
+        if (threadIdx.x < ncg) {
+            float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < lanes; k++) { float4 v = sh[k * ncg + threadIdx.x]; tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w; }
+            reinterpret_cast<float4*>(part + (size_t)blockIdx.x * C)[cg0 + threadIdx.x] = tot;
+        }
     }
+}
+// stage 2: one warp per column; lane l sums partials l, l+32, ... then a fixed-order shuffle tree
+__global__ void colsum_final_kernel(const float* __restrict__ part, int nblocks, int C, float* __restrict__ out) {
+    const int col = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (col >= C) return;
+    float s = 0.f;
+    for (int b = lane; b < nblocks; b += 32) s += part[(size_t)b * C + col];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) out[col] = s;
+}
+
+// Three taps per CTA (dx = -1, 0, +1 of one kernel row ky): the `in` operand is loaded once per patch as a (32 ch x 10 x 4)
+// box with a one-pixel halo in x; the three taps are three descriptor views of it (start shifted by dx pixel rows of 128 B,
+// the four 8-pixel k-steps one box row = 1280 B apart) feeding three TMEM accumulators, while the g box is shared.
+constexpr int WH_INBLK = 10 * 4 * 128;      // bytes of one 32-channel block of the `in` halo box
+__device__ __forceinline__ uint64_t make_desc_mn_sw128_lbo(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(lbo_bytes >> 4) << 16;
+    d |= (uint64_t)(512 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)1 << 61;
+    return d;
+}
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(128) wgrad_halo(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int TCOLS = (3 * BN <= 128) ? 128 : (3 * BN <= 256 ? 256 : 512);
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+
+    const int mblk_bytes = p.in_is_m ? WH_INBLK : WG_BLOCK, nblk_bytes = p.in_is_m ? WG_BLOCK : WH_INBLK;
+    const int a_bytes = 4 * mblk_bytes, stage_bytes = a_bytes + (BN / 32) * nblk_bytes;
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int split = blockIdx.x, m0 = blockIdx.y * 128;
+    const int ntiles = (p.n_ch + BN - 1) / BN;
+    const int ky = blockIdx.z / ntiles, n0 = (blockIdx.z - ky * ntiles) * BN;
+    const int64_t p_lo = (int64_t)split * p.patches_per_split;
+    int64_t p_hi = p_lo + p.patches_per_split;
+    if (p_hi > p.npatches) p_hi = p.npatches;
+    const int nst = (int)(p_hi - p_lo);
+    const int mblocks = min(4, (p.m_ch - m0) / 32), nblocks = min(BN / 32, (p.n_ch - n0) / 32);
+
+    if (mblocks < 4 || nblocks < BN / 32) {
+        for (int s = 0; s < STAGES; s++) {
+            uint8_t* st = smem + (size_t)s * stage_bytes;
+            for (int i = t; i < (4 - mblocks) * mblk_bytes / 16; i += 128)
+                reinterpret_cast<float4*>(st + mblocks * mblk_bytes)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int i = t; i < (BN / 32 - nblocks) * nblk_bytes / 16; i += 128)
+                reinterpret_cast<float4*>(st + a_bytes + nblocks * nblk_bytes)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+    if (t == 0) {
+        // ===== TMA producer =====
+        const int per_img = p.ptx * p.pty;
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int64_t pp = p_lo + i;
+            const int b = (int)(pp / per_img);
+            const int r = (int)(pp - (int64_t)b * per_img);
+            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            uint8_t* st = smem + (size_t)s * stage_bytes;
+            mbar_expect_tx(&bar_full[s], (uint32_t)(mblocks * mblk_bytes + nblocks * nblk_bytes));
+            if (p.in_is_m) {
+                for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * mblk_bytes, &tmIn, &bar_full[s], m0 + j * 32, x0 - 1, y0 + ky - 1, b);
+                for (int j = 0; j < nblocks; j++) tma_load_4d(st + a_bytes + j * nblk_bytes, &tmG, &bar_full[s], n0 + j * 32, x0, y0, b);
+            } else {
+                for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * mblk_bytes, &tmG, &bar_full[s], m0 + j * 32, x0, y0, b);
+                for (int j = 0; j < nblocks; j++) tma_load_4d(st + a_bytes + j * nblk_bytes, &tmIn, &bar_full[s], n0 + j * 32, x0 - 1, y0 + ky - 1, b);
+            }
+        }
+    } else if (t == 32) {
+        // ===== MMA issuer =====
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t abase = smem_base + (uint32_t)(s * stage_bytes), bbase = abase + (uint32_t)a_bytes;
+#pragma unroll
+            for (int dx = 0; dx < 3; dx++) {
+#pragma unroll
+                for (int h = 0; h < 4; h++) {       // one k-step = the 8 pixels of box row h
+                    const uint32_t in_off = (uint32_t)(dx * 128 + h * 1280), g_off = (uint32_t)(h * 1024);
+                    const uint64_t da = make_desc_mn_sw128_lbo(abase + (p.in_is_m ? in_off : g_off), (uint32_t)mblk_bytes);
+                    const uint64_t db = make_desc_mn_sw128_lbo(bbase + (p.in_is_m ? g_off : in_off), (uint32_t)nblk_bytes);
+                    umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, (i | h) != 0 ? 1u : 0u);
+                }
+            }
+            umma_commit(&bar_empty[s]);
+        }
+        umma_commit(&bar_done);
+    }
+    __syncwarp();
+    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
+    const int mch = m0 + t;
+    if (nst > 0) {
+        mbar_wait(&bar_done, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+#pragma unroll 1
+    for (int dx = 0; dx < 3; dx++) {
+        const int tap = ky * 3 + dx;
+#pragma unroll 1
+        for (int cb = 0; cb < BN; cb += 16) {
+            uint32_t r[16];
+            if (nst > 0) {
+                tmem_ld16(lane_addr + (uint32_t)(dx * BN + cb), r);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            } else {
+#pragma unroll
+                for (int q = 0; q < 16; q++) r[q] = 0u;
+            }
+            if (mch < p.m_ch) {
+#pragma unroll
+                for (int q = 0; q < 16; q++) {
+                    const int nch = n0 + cb + q;
+                    if (nch < p.n_ch) {
+                        const int ci = p.in_is_m ? mch : nch, co = p.in_is_m ? nch : mch;
+                        out[((size_t)tap * p.Cin_p + ci) * p.Cout_p + co] = __uint_as_float(r[q]);
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
+}
+
+int32_t make_tmap_inhalo(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, 10, 4, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(in halo C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
+    return DINCAE_OK;
 }
 
 int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
@@ -495,10 +903,14 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
     bn = n_ch % 256 == 0 ? 256 : (n_ch % 128 == 0 ? 128 : (n_ch % 64 == 0 ? 64 : 32));
     const int mtiles = (m_ch + 127) / 128, ntiles = n_ch / bn;
     npatches = (int64_t)a.B * dc_cdiv(a.H, 4) * dc_cdiv(a.W, 8);
-    int tiles = mtiles * ntiles * 9;
-    splits = (3 * num_sms + tiles - 1) / tiles;
+    int tiles = mtiles * ntiles * (bn == 32 ? 3 : 9);     // three taps per CTA in the halo variant (narrow N only)
+    splits = ((bn == 32 ? 3 : 2) * num_sms + tiles - 1) / tiles;
     int64_t maxs = dc_cdiv(npatches, 4);
     if (splits > maxs) splits = (int)maxs;
+    // the split partials are written and re-read once: keep them below ~16 MB per layer
+    int64_t cap = (int64_t)(16 << 20) / ((int64_t)9 * Cin_p * Cout_p * 4);
+    if (cap < 1) cap = 1;
+    if (splits > cap) splits = (int)cap;
     if (splits < 1) splits = 1;
     pps = dc_cdiv(npatches, splits);
     splits = (int)dc_cdiv(npatches, pps);
@@ -534,6 +946,20 @@ size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, i
         DC_CHECK_LAUNCH();                                                                                                 \
     } while (0)
 
+#define WH_LAUNCH(BN_, ST_)                                                                                                \
+    do {                                                                                                                   \
+        auto wgrad_halo_bn##BN_ = wgrad_halo<BN_, ST_>;                                                                    \
+        constexpr int smem = ST_ * (4 * WH_INBLK + (BN_ / 32) * WH_INBLK) + 1024;                                          \
+        static bool attr_set = false;                                                                                      \
+        if (!attr_set) {                                                                                                   \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_halo_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));    \
+            attr_set = true;                                                                                               \
+        }                                                                                                                  \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_LAUNCH(ctx, wgrad_halo_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                 \
+        DC_CHECK_LAUNCH();                                                                                                 \
+    } while (0)
+
 int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t scratch_bytes) {
     const int Cin_p = a.in.C, Cout_p = a.Cout_p;
     int bn, splits, in_is_m;
@@ -541,7 +967,7 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     wgrad_tma_plan(ctx->num_sms, a, bn, splits, np, pps, in_is_m);
     const int64_t nW = (int64_t)9 * Cin_p * Cout_p;
     const int64_t M = (int64_t)a.B * a.H * a.W;
-    const int cs_blocks = (int)(M < 1024 * 64 ? dc_cdiv(M, 64) : 1024);
+    const int cs_blocks = (int)(M < (int64_t)4 * ctx->num_sms * 32 ? dc_cdiv(M, 32) : 4 * ctx->num_sms);
     DC_REQUIRE(scratch_bytes >= ((size_t)splits * nW + (size_t)cs_blocks * Cout_p) * sizeof(float), DINCAE_ESIZE, "k2_wgrad_tma: scratch too small");
     WgradTmaArgs p;
     p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, 4);
@@ -551,23 +977,23 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     alignas(64) CUtensorMap tmIn, tmG;
     DC_TRY(make_tmap_patch(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
     DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
-    dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(9 * (p.n_ch / bn)));
-    if (bn == 256) WG_LAUNCH(256, 2);
-    else if (bn == 128) WG_LAUNCH(128, 3);
-    else if (bn == 64) WG_LAUNCH(64, 4);
-    else WG_LAUNCH(32, 4);
+    if (bn == 32) {
+        DC_TRY(make_tmap_inhalo(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
+        dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(3 * (p.n_ch / bn)));
+        WH_LAUNCH(32, 4);
+    } else {
+        dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(9 * (p.n_ch / bn)));
+        if (bn == 256) WG_LAUNCH(256, 2);
+        else if (bn == 128) WG_LAUNCH(128, 3);
+        else WG_LAUNCH(64, 4);
+    }
     DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 256), 256, 0, p.partial, splits, nW, a.dW);
     DC_CHECK_LAUNCH();
     // bias gradient
     float* cpart = p.partial + (size_t)splits * nW;
-    const int64_t rpb = dc_cdiv(M, cs_blocks);
-    for (int c0 = 0; c0 < Cout_p; c0 += 256) {
-        const int Cw = Cout_p - c0 < 256 ? Cout_p - c0 : 256;
-        const int threads = (256 / Cw) * Cw;
-        DC_LAUNCH(ctx, colsum_partial_kernel, cs_blocks, threads, 0, a.gout, M, Cout_p, c0, Cw, rpb, cpart);
-        DC_CHECK_LAUNCH();
-    }
-    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(Cout_p, 256), 256, 0, cpart, cs_blocks, (int64_t)Cout_p, a.db);
+    DC_LAUNCH(ctx, colsum_partial_kernel, cs_blocks, 256, 0, a.gout, M, Cout_p, cpart);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, colsum_final_kernel, (unsigned)dc_cdiv(Cout_p, 8), 256, 0, cpart, cs_blocks, Cout_p, a.db);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
