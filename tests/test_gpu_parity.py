@@ -286,3 +286,86 @@ def test_error_paths(pkg, ctx):
 def test_smoke(pkg, ctx):
     r = pkg.selftest.smoke(verbose=False)
     assert r["launches"] > 0
+
+
+# ---------------------------------------------------------------- tensor-core (TF32 operands, FP32 accumulate) mode
+TF32_CASES = [
+    (24, 24, 10, 1, (32, 64), "nearest", False, 0.0, 0.0, 3),
+    (21, 17, 10, 1, (32, 64, 128), "nearest", True, 1e-3, 0.0, 4),           # odd sizes, refinement, L2
+    (20, 19, 16, 2, (32, 64), "bilinear", True, 1e-4, 0.0, 2),               # bilinear, two outputs
+    (45, 18, 60, 1, (25, 50, 75), "nearest", False, 1e-4, 0.0, 2),           # cfg4-like channel counts (padded to 32)
+    (112, 112, 10, 1, (32, 64, 128, 256), "nearest", True, 1e-3, 0.0, 4),    # cfg2 shapes
+]
+
+
+@pytest.mark.parametrize("W,H,Cin,O,F,method,refine,l2,lap,B", TF32_CASES)
+def test_tf32_tensor_core_path_vs_oracle(pkg, ctx, W, H, Cin, O, F, method, refine, l2, lap, B):
+    """The default precision: tcgen05 TF32 convs/wgrads (operands rounded to TF32, FP32 accumulation -- what cuDNN does for the
+    reference's CuArray path under CUDA.jl's default math mode).  Stated tolerance: (m, sigma2) rms error <= 1e-3 of their rms and
+    max error <= 2e-3 of their range (observed: rms <= 6e-4, max <= 1.2e-3); loss 1e-3 relative (observed <= 6e-5); gradients 1e-2 of range.
+    precision="fp32" (tests above) is the exact mode: 1e-5."""
+    rng = np.random.default_rng(W + H)
+    lw = (0.3, 0.7) if refine else (1.0,)
+    kw = dict(W=W, H=H, ninput=Cin, noutput=O, enc_nfilter_internal=F, upsampling_method=method, loss_weights_refine=lw,
+              regularization_L2_beta=l2, laplacian_penalty=lap, max_batch=B)
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=Cin, noutput=O, nfilter=list(F), upsampling_method=method, loss_weights_refine=lw,
+                          regularization_L2_beta=l2, laplacian_penalty=lap)
+    model = pkg.Model(ctx, pkg.ModelConfig(precision="tf32", **kw), seed=5)
+    flat = model.get_params()
+    xin, xt = _problem(rng, W, H, Cin, O, B)
+    y = model(xin)
+    y_o = OM.forward(ocfg, flat, xin)
+    for ch in range(2 * O):
+        err = np.abs(y[:, :, ch] - y_o[:, :, ch]).max() / np.abs(y_o[:, :, ch]).max()
+        rms = np.sqrt(np.mean((y[:, :, ch] - y_o[:, :, ch]) ** 2)) / np.sqrt(np.mean(y_o[:, :, ch] ** 2))
+        assert err < 2e-3 * (2 if lap else 1) and rms < 1e-3 * (2 if lap else 1), (ch, err, rms)
+    loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, xt)
+    assert model.loss(xin, xt) == pytest.approx(loss_o, rel=1e-3)
+    loss = model.train_step(xin, xt, 1e-3)
+    assert loss == pytest.approx(loss_o, rel=1e-3)
+    m, v, t = model.get_opt_state()
+    gc = np.clip(g_o, -5, 5)
+    assert np.abs(m * 10 - gc).max() < 1e-2 * np.abs(gc).max()
+    # parameters padded to 32 channels internally still round-trip exactly in Flux order
+    model.set_params(flat)
+    assert np.array_equal(model.get_params(), flat)
+
+
+def test_tf32_loss_curve_and_determinism(pkg, ctx):
+    rng = np.random.default_rng(3)
+    W, H, V, N, T, Bsz, epochs = 24, 20, 1, 22, 3, 8, 3
+    data = _cube(rng, W, H, V, N)
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, train=True, ntime_win=T)
+    od = OD.NCData(lon, lat, days, data, train=True, ntime_win=T)
+    kw = dict(loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3)
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=10, nfilter=[32, 64], **kw)
+    curves = []
+    for rep in range(2):
+        model = pkg.Model(ctx, pkg.ModelConfig(W=W, H=H, ninput=10, enc_nfilter_internal=(32, 64), max_batch=Bsz, precision="tf32", **kw), seed=9)
+        flat0 = model.get_params()
+        batches = pkg.api.DataBatches(ds, Bsz, seed=4)
+        losses = []
+        for e in range(1, epochs + 1):
+            s, nb = 0.0, 0
+            for idx, imask, ctr in batches.batches():
+                xin, xt = ds.assemble(idx, imask, 4, ctr)
+                s += model.train_step(xin, xt, 1e-3)
+                nb += 1
+            losses.append(s / nb)
+            batches.shuffle_()
+        curves.append(losses)
+    assert curves[0] == curves[1]                                   # bit-reproducible: no float atomics, fixed reduction orders
+    flat, opt = flat0, OM.Adam(flat0.size)
+    batches = pkg.api.DataBatches(ds, Bsz, seed=4)
+    losses_o = []
+    for e in range(1, epochs + 1):
+        so, nb = 0.0, 0
+        for idx, imask, ctr in batches.batches():
+            xin_o, xt_o = od.batch(idx, imask, 4, ctr)
+            lo, flat = OM.train_step(ocfg, flat, opt, xin_o, xt_o, 1e-3)
+            so += lo
+            nb += 1
+        losses_o.append(so / nb)
+        batches.shuffle_()
+    np.testing.assert_allclose(curves[0], losses_o, rtol=1e-3)     # seeded multi-epoch loss curve (north_star tolerance)
