@@ -330,23 +330,35 @@ def main():
             k["ms_per_launch"] = k["ms"] / k["launches"]
         kern_table.sort(key=lambda k: -k["ms"])
         top = kern_table[0]
-        peaks = {}
+        peaks, traffic = {}, {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except Exception:
             pass
-        if top["flops"] > 0:
-            peak = peaks.get("bf16_tflops_sustained", 1400.0)
-            ach = top["flops"] / (top["ms"] * 1e-3) / 1e12
-            roof = {"kernel": top["kernel"], "bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                    "traffic": None, "share_of_step": top["share"], "launches_per_step": top["launches"] / nprof,
-                    "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a long step)" if peaks else "fallback 1.4 PFLOP/s sustained",
-                    "note": "achieved = algorithmic FLOPs (2*9*Cin*Cout*B*H*W per launch, real channels) / CUDA-event time of all launches of this kernel"}
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))
+        except Exception:
+            pass
+        pk_t = peaks.get("bf16_tflops_sustained", 1400.0)
+        pk_b = peaks.get("hbm_gbs", 6650.0)
+        src = "MEASURED_PEAKS.json" if peaks else "fallback (6.65 TB/s, 1.4 PFLOP/s sustained)"
+        t_s = top["ms"] * 1e-3
+        t_flops = top["flops"] / (pk_t * 1e12)           # time the algorithmic FLOPs need at the tensor peak
+        t_bytes = top["bytes"] / (pk_b * 1e9)            # time the algorithmic bytes need at the HBM peak
+        tr = traffic.get(top["kernel"])
+        tr_val = max(tr, key=lambda e: e["dram_bytes"])["dram_bytes"] if tr else None
+        common = {"kernel": top["kernel"], "share_of_step": top["share"], "launches_per_step": top["launches"] / nprof,
+                  "algorithmic_flops_per_launch": top["flops"] / top["launches"], "algorithmic_bytes_per_launch": top["bytes"] / top["launches"],
+                  "avg_launch_us": 1e3 * top["ms"] / top["launches"], "traffic": tr_val,
+                  "traffic_note": "dram read+write bytes of the largest launch of this kernel in profiles/r01_ncu_full_top_kernels.csv (ncu --set full)" if tr else None,
+                  "note": "achieved = algorithmic work of all launches of this kernel in %d steps / their CUDA-event time (library per-launch profile)" % nprof}
+        if t_bytes >= t_flops:
+            ach = top["bytes"] / t_s / 1e9
+            roof = dict(common, bound="hbm", achieved=ach, peak=pk_b, unit="GB/s", frac=ach / pk_b, peak_source=src + " hbm_gbs")
         else:
-            peak = peaks.get("hbm_gbs", 6650.0)
-            ach = top["bytes"] / (top["ms"] * 1e-3) / 1e9
-            roof = {"kernel": top["kernel"], "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                    "share_of_step": top["share"], "launches_per_step": top["launches"] / nprof}
+            ach = top["flops"] / t_s / 1e12
+            roof = dict(common, bound="tensor", achieved=ach, peak=pk_t, unit="TFLOP/s", frac=ach / pk_t,
+                        peak_source=src + " bf16_tflops_sustained (kernel timed inside a long step; operands are TF32)")
 
     # ---- reconstruction throughput (time-sharded, no communication) ----
     recon = None

@@ -41,6 +41,7 @@ struct ConvArgs {
     int planar_C;
     int planar_accumulate;   // 1: planar_out += value
     double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
+    double work_bytes;    // algorithmic HBM bytes (input + output + weights, REAL channel counts)
 };
 
 struct WgradArgs {
@@ -54,6 +55,7 @@ struct WgradArgs {
     int splits;
     int64_t pix_per_split;
     double work_flops;
+    double work_bytes;
     int tf32;             // operands are TF32-representable: the TMA/tcgen05 kernel may be used
 };
 
@@ -68,6 +70,7 @@ struct ConvSmallArgs {
     int accumulate;       // 0: out = v ; 1: out += v
     float* out;           // planar [B][Cout][H][W]
     double work_flops;
+    double work_bytes;
 };
 
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);        // dispatches to the tcgen05 kernel when eligible

@@ -572,7 +572,7 @@ int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
     if (k2_conv_tc_eligible(a)) return k2_conv_tc(ctx, a);
     int Kpad = dc_round_up(9 * a.in.C, 16);
     int nchunks = Kpad / 16;
-    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, 0.0);
+    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, a.work_bytes);
     if (a.Cout_p <= 32) {
         dim3 grid((unsigned)dc_cdiv(Mtot, 128), (unsigned)dc_cdiv(a.Cout_p, 32));
         DC_LAUNCH(ctx, conv3x3_simt<32>, grid, 256, 0, a, Mtot, nchunks);
@@ -620,7 +620,7 @@ int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_byt
     if (splits > 1)
         DC_REQUIRE(scratch_bytes >= stride * splits * sizeof(float), DINCAE_ESIZE, "k2_wgrad: scratch too small");
     dim3 grid(Kt, Nt, splits);
-    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout_p * (double)Mtot, 0.0);
+    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout_p * (double)Mtot, a.work_bytes);
     DC_LAUNCH(ctx, wgrad_simt, grid, 256, 0, a, Mtot, Krows, Kt, Nt);
     DC_CHECK_LAUNCH();
     if (splits > 1) {
@@ -638,7 +638,7 @@ int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco) {
     int Krows = 9 * a.in.C;
     size_t smem = (size_t)Krows * nco * sizeof(float);
     DC_REQUIRE(smem <= 200 * 1024, DINCAE_EUNSUPPORTED, "k2_conv_small: %d input channels do not fit shared memory", a.in.C);
-    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout * (double)Mtot, 0.0);
+    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout * (double)Mtot, a.work_bytes);
     if (nco == 4) {
         if (smem > 48 * 1024) DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_small<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         DC_LAUNCH(ctx, conv3x3_small<4>, (unsigned)dc_cdiv(Mtot, 256), 256, smem, a, Mtot, Krows);
@@ -664,7 +664,7 @@ int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, siz
     a.pix_per_split = pps;
     a.splits = splits;
     int threads = Krows + 1 < 256 ? dc_round_up(Krows + 1, 32) : 256;
-    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout_p * (double)Mtot, 0.0);
+    DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * Krows * a.Cout_p * (double)Mtot, a.work_bytes);
     if (nco == 4) DC_LAUNCH(ctx, wgrad_small<4>, splits, threads, 0, a, Mtot, Krows);
     else if (nco == 8) DC_LAUNCH(ctx, wgrad_small<8>, splits, threads, 0, a, Mtot, Krows);
     else DC_REQUIRE(false, DINCAE_EUNSUPPORTED, "k2_wgrad_small: nco=%d", nco);

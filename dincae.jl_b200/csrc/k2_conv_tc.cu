@@ -239,7 +239,7 @@ constexpr int tc_smem_bytes() { return STAGES * (TC_BM * 128 + BN * 128) + 1024;
             attr_set = true;                                                                                              \
         }                                                                                                                 \
         dim3 grid((unsigned)dc_cdiv(Mtot, TC_BM), (unsigned)dc_cdiv(a.Cout_p, BN_));                                      \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, 0.0);                  \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, a.work_bytes);                  \
         DC_LAUNCH(ctx, conv3x3_tc_bn##BN_, grid, 128, smem, a, Mtot, a.in.C / TC_KC);                                     \
         DC_CHECK_LAUNCH();                                                                                                \
         return DINCAE_OK;                                                                                                 \

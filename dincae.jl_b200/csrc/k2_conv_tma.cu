@@ -435,7 +435,7 @@ constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; 
         }                                                                                                                  \
         DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
         dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
         DC_LAUNCH(ctx, conv3x3_halo_bn##BN_, grid, 128, smem, tmA, tmB, p, halo_mode - 1);                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
@@ -468,7 +468,7 @@ static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
         }                                                                                                                  \
         DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
         dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
         DC_LAUNCH(ctx, conv3x3_tma_bn##BN_, grid, 128, smem, tmA, tmB, p);                                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
@@ -941,7 +941,7 @@ size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, i
             DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tma_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));     \
             attr_set = true;                                                                                               \
         }                                                                                                                  \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
         DC_LAUNCH(ctx, wgrad_tma_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                  \
         DC_CHECK_LAUNCH();                                                                                                 \
     } while (0)
@@ -955,7 +955,7 @@ size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, i
             DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_halo_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));    \
             attr_set = true;                                                                                               \
         }                                                                                                                  \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, 0.0);        \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
         DC_LAUNCH(ctx, wgrad_halo_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
     } while (0)

@@ -37,6 +37,8 @@ __global__ void count_pts_kernel(const float* __restrict__ x2, int64_t P, unsign
 }
 
 inline double cflops(const LayerInfo& y, int B, int H, int W) { return 2.0 * 9 * y.Cin * y.Cout * (double)B * H * W; }
+// algorithmic HBM bytes of one conv / dgrad / wgrad call: both pixel tensors once + the weights (real channel counts)
+inline double cbytes(const LayerInfo& y, int B, int H, int W) { return 4.0 * ((double)(y.Cin + y.Cout) * B * H * W + 9.0 * y.Cin * y.Cout); }
 inline bool has_skip(const dincae_model* M, int l) { return l >= 1 && l < M->L && ((M->cfg.skip_mask >> l) & 1u); }
 
 // the producer of conv_dec_l: upsample(+crop) of y_{l+1} = R[l+1] (+ X[l+1] when level l+1 has a skip) or X[L]
@@ -74,6 +76,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = 1;     // X[0] from pack, X[l>=1] from pool_kernel (both rounded on store)
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
+        a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
         DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
     }
@@ -88,6 +91,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             a.wgtK = M->wK ? M->wK + d.wk_off : nullptr; a.ldk = 9 * d.Cin_p; a.in_is_tf32 = M->wK != nullptr;   // U[l] is rounded on store
             a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.R[l];
             a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
+            a.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));                                               // Conv(..., relu), :272
         } else if (M->wK) {
             // TF32 mode: the 2*nout-channel head conv runs on the tensor cores too (channels padded to 32), planar output
@@ -98,12 +102,14 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = nullptr;
             a.planar_out = cb.RAW; a.planar_C = 2 * M->O; a.planar_accumulate = 0;
             a.work_flops = cflops(d, B, M->Hl[0], M->Wl[0]);
+            a.work_bytes = cbytes(d, B, M->Hl[0], M->Wl[0]);
             DC_TRY(k2_conv(ctx, a));
         } else {
             ConvSmallArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
             a.wgt = M->w + d.w_off; a.ldw = d.Cout_p; a.bias = M->w + d.b_off; a.Cout = 2 * M->O; a.accumulate = 0; a.out = cb.RAW;
             a.work_flops = cflops(d, B, M->Hl[0], M->Wl[0]);
+            a.work_bytes = cbytes(d, B, M->Hl[0], M->Wl[0]);
             DC_TRY(k2_conv_small(ctx, a, M->nco));                                 // Conv(..., identity) at l == 1, :251-256
         }
     }
@@ -139,6 +145,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
         wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
         wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
+        wa.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
         if (l == 0 && !M->wK) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
         else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
@@ -148,6 +155,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
         a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = 1;   // GD[l>=1] from upbwd, GD0 from pack (both rounded on store)
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
+        a.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
     {   // G[L] = gradient w.r.t. X[L] (the innermost level is the identity, src/model.jl:263-264)
@@ -165,6 +173,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
         wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
+        wa.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
         DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
         if (l >= 1) {
@@ -176,6 +185,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
             a.dst = M->XG[l];
             a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
+            a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
             DC_TRY(k2_conv(ctx, a));
             xg = M->XG[l];
         } else if (c >= 1 && M->wK) {
