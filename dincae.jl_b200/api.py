@@ -264,6 +264,17 @@ class Model:
                                             C.byref(out) if want_loss else None))
         return out.value if want_loss else None
 
+    def upload(self, slot, xin, xtrue):
+        """Start the host->device copy of a mini-batch into prefetch slot 0/1 (PrefetchDataIter, src/data.jl:872-904)."""
+        xin = _f32(xin); xtrue = _f32(xtrue)
+        L.check(self._lib.dincae_batch_upload(self.handle, slot, L.ptr(xin), L.ptr(xtrue), xin.shape[3]))
+        return xin, xtrue            # keep these alive until train_step_slot returns
+
+    def train_step_slot(self, slot, B, lr, want_loss=True):
+        out = C.c_float()
+        L.check(self._lib.dincae_train_step_slot(self.handle, slot, B, lr, C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
+
     def grad_step(self, xin, xtrue, B=None, n_valid_global=None):
         xin, B = self._batch(xin, B)
         if isinstance(xtrue, np.ndarray):
@@ -493,6 +504,27 @@ def train_epoch(model: Model, batches, lr):
     for xin, xtrue, B in batches:
         loss_sum += model.train_step(xin, xtrue, lr, B=B)
         n += 1
+    return loss_sum / n
+
+
+def train_epoch_prefetch(model: Model, host_batches, lr):
+    """train_epoch!(MO, PrefetchDataIter(train), lr) (src/model.jl:592): host mini-batches, the next one is uploaded while
+    the current one trains."""
+    it = iter(host_batches)
+    cur = next(it, None)
+    if cur is None:
+        raise ValueError("empty data iterator")
+    keep = model.upload(0, cur[0], cur[1])
+    slot, loss_sum, n = 0, 0.0, 0
+    while cur is not None:
+        nxt = next(it, None)
+        if nxt is not None:
+            keep_next = model.upload(slot ^ 1, nxt[0], nxt[1])
+        loss_sum += model.train_step_slot(slot, cur[0].shape[3], lr)
+        n += 1
+        cur, slot = nxt, slot ^ 1
+        if nxt is not None:
+            keep = keep_next
     return loss_sum / n
 
 

@@ -593,6 +593,11 @@ extern "C" int32_t dincae_model_destroy(dincae_model* M) {
     cudaStreamSynchronize(M->ctx->stream);
     if (M->all_mem) cudaFree(M->all_mem);
     if (M->pt_buf) cudaFree(M->pt_buf);
+    if (M->copy_stream) {
+        cudaStreamSynchronize(M->copy_stream);
+        for (int s = 0; s < 2; s++) { cudaFree(M->up_buf[s]); cudaEventDestroy(M->up_done[s]); cudaEventDestroy(M->slot_free[s]); }
+        cudaStreamDestroy(M->copy_stream);
+    }
     delete M;
     return DINCAE_OK;
 }
@@ -755,6 +760,43 @@ extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
 extern "C" int32_t dincae_train_step(dincae_model* M, const float* xin, const float* xtrue, int32_t B, float lr,
                                      int32_t loc, float* loss) {
     DC_TRY(dincae_grad_step(M, xin, xtrue, B, nullptr, loc));
+    return dincae_apply_step(M, lr, loss);
+}
+
+// ---- one-batch-ahead prefetch (PrefetchDataIter, src/data.jl:872-904) ------------------------------------------
+extern "C" int32_t dincae_batch_upload(dincae_model* M, int32_t slot, const float* xin_host, const float* xtrue_host, int32_t B) {
+    DC_TRY(check_batch(M, B, "dincae_batch_upload"));
+    DC_REQUIRE(slot == 0 || slot == 1, DINCAE_EINVAL, "dincae_batch_upload: slot must be 0 or 1");
+    DC_REQUIRE(xin_host && xtrue_host, DINCAE_EINVAL, "dincae_batch_upload: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const size_t npix = (size_t)M->cfg.W * M->cfg.H;
+    const size_t nx = npix * M->cfg.ninput * M->maxB, ny = npix * 2 * M->O * M->maxB;
+    if (!M->copy_stream) {
+        DC_CHECK_CUDA(cudaStreamCreateWithFlags(&M->copy_stream, cudaStreamNonBlocking));
+        for (int s = 0; s < 2; s++) {
+            DC_CHECK_CUDA(cudaMalloc((void**)&M->up_buf[s], sizeof(float) * (nx + ny)));
+            DC_CHECK_CUDA(cudaEventCreateWithFlags(&M->up_done[s], cudaEventDisableTiming));
+            DC_CHECK_CUDA(cudaEventCreateWithFlags(&M->slot_free[s], cudaEventDisableTiming));
+        }
+    }
+    if (M->slot_used[slot]) DC_CHECK_CUDA(cudaStreamWaitEvent(M->copy_stream, M->slot_free[slot], 0));   // the step that read this slot has finished
+    DC_CHECK_CUDA(cudaMemcpyAsync(M->up_buf[slot], xin_host, sizeof(float) * npix * M->cfg.ninput * B, cudaMemcpyHostToDevice, M->copy_stream));
+    DC_CHECK_CUDA(cudaMemcpyAsync(M->up_buf[slot] + nx, xtrue_host, sizeof(float) * npix * 2 * M->O * B, cudaMemcpyHostToDevice, M->copy_stream));
+    DC_CHECK_CUDA(cudaEventRecord(M->up_done[slot], M->copy_stream));
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_train_step_slot(dincae_model* M, int32_t slot, int32_t B, float lr, float* loss) {
+    DC_TRY(check_batch(M, B, "dincae_train_step_slot"));
+    DC_REQUIRE((slot == 0 || slot == 1) && M->copy_stream, DINCAE_EINVAL, "dincae_train_step_slot: nothing was uploaded to slot %d", slot);
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const size_t nx = (size_t)M->cfg.W * M->cfg.H * M->cfg.ninput * M->maxB;
+    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, M->up_done[slot], 0));
+    DC_TRY(dincae_grad_step(M, M->up_buf[slot], M->up_buf[slot] + nx, B, nullptr, DINCAE_DEVICE));
+    DC_CHECK_CUDA(cudaEventRecord(M->slot_free[slot], ctx->stream));
+    M->slot_used[slot] = true;
     return dincae_apply_step(M, lr, loss);
 }
 

@@ -52,6 +52,11 @@ struct dincae_model {
     void* wg_scratch = nullptr;
     size_t wg_scratch_bytes = 0;
     float *in_xin = nullptr, *in_xtrue = nullptr;     // device staging of host mini-batches
+    // prefetch slots (dincae_batch_upload): the next mini-batch crosses PCIe on a copy stream while this one trains
+    float* up_buf[2] = {nullptr, nullptr};
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t up_done[2] = {nullptr, nullptr}, slot_free[2] = {nullptr, nullptr};
+    bool slot_used[2] = {false, false};
     // point-loss workspace (grown on demand)
     float* pt_buf = nullptr;
     size_t pt_cap = 0;                 // in points

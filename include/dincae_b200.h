@@ -117,6 +117,11 @@ int32_t dincae_loss(dincae_model* m, const float* xin, const float* xtrue, int32
 /* one mini-batch of train_epoch! (src/flux.jl:28-36): withgradient + ClipGrad + Adam; lr per call (src/flux.jl:25) */
 int32_t dincae_train_step(dincae_model* m, const float* xin, const float* xtrue, int32_t B, float lr,
                           int32_t loc, float* loss);
+/* one-batch-ahead prefetch (PrefetchDataIter, src/data.jl:872-904): upload mini-batch i+1 into the other slot (0/1) on a copy
+ * stream while mini-batch i trains; host buffers (pinned for a truly asynchronous copy) must stay valid until the matching
+ * dincae_train_step_slot returns. */
+int32_t dincae_batch_upload(dincae_model* m, int32_t slot, const float* xin_host, const float* xtrue_host, int32_t B);
+int32_t dincae_train_step_slot(dincae_model* m, int32_t slot, int32_t B, float lr, float* loss);
 /* point-cloud truth (src/points.jl:354-426): pos (sumP,2), x (sumP,2) = (value, 1/err var), offsets (B+1) int64 */
 int32_t dincae_loss_points(dincae_model* m, const float* xin, const float* pos, const float* x,
                            const int64_t* offsets, int32_t B, int32_t loc, double* loss);

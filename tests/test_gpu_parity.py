@@ -369,3 +369,17 @@ def test_tf32_loss_curve_and_determinism(pkg, ctx):
         losses_o.append(so / nb)
         batches.shuffle_()
     np.testing.assert_allclose(curves[0], losses_o, rtol=1e-3)     # seeded multi-epoch loss curve (north_star tolerance)
+
+
+def test_prefetch_slots_equal_plain_train_step(pkg, ctx):
+    """dincae_batch_upload + dincae_train_step_slot (one-batch-ahead prefetch) give the same losses and weights as train_step."""
+    rng = np.random.default_rng(12)
+    W, H, Cin, B = 16, 12, 10, 4
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=Cin, enc_nfilter_internal=(6, 8), loss_weights_refine=(0.3, 0.7), max_batch=B, precision="fp32")
+    batches = [_problem(rng, W, H, Cin, 1, b) for b in (4, 4, 3)]          # partial last batch
+    a = pkg.Model(ctx, cfg, seed=2)
+    b_ = pkg.Model(ctx, cfg, seed=2)
+    ref = [a.train_step(x, y, 1e-3) for x, y in batches]
+    got = pkg.api.train_epoch_prefetch(b_, batches, 1e-3)
+    assert got == pytest.approx(sum(ref) / 3, rel=1e-6)
+    assert np.array_equal(a.get_params(), b_.get_params())
