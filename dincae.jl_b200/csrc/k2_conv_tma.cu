@@ -66,6 +66,15 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
         "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// accumulate variant without the predicate set-up (D += A*B)
+__device__ __forceinline__ void umma_tf32_acc(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc) {
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "setp.eq.u32 p, 1, 1;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc) : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
@@ -424,6 +433,255 @@ constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; 
 
 }  // namespace
 
+// -------------------------------------------------------------------------------------------------
+// Persistent, warp-specialised form of the halo kernel: one CTA per SM loops over output tiles.
+//   warp 0 (one lane): TMA producer      warp 1 (one lane): tcgen05.mma issuer      warps 2-5: epilogue
+// The FP32 accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile i (tcgen05.ld, bias,
+// activation, stores) overlaps the TMA + MMA main loop of tile i+1.  When the whole K-major weight matrix of the
+// layer fits in shared memory (narrow layers) it is loaded once per CTA and stays resident; then only one 23 KB
+// activation halo per tile and K chunk crosses L2 -> SM.
+namespace {
+
+constexpr int PS_MAX_A = 4, PS_MAX_B = 8;
+
+struct PersistArgs {
+    int num_tiles, ntiles_n;
+    int a_stages, b_stages;
+    int b_resident;
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int BN>
+__global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p, PersistArgs q) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int B_BYTES = BN * 128;
+    constexpr int TCOLS = 2 * BN < 32 ? 32 : 2 * BN;
+    __shared__ uint64_t bar_fullA[PS_MAX_A], bar_emptyA[PS_MAX_A], bar_fullB[PS_MAX_B], bar_emptyB[PS_MAX_B];
+    __shared__ uint64_t bar_bres, bar_tfull[2], bar_tempty[2];
+    __shared__ uint32_t tmem_base_s;
+
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smemB = smem + q.a_stages * HL_A_STRIDE;
+    const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int patches = p.ptx * p.pty;
+    const int nkc = p.Cin_p / TM_KC;
+
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+        for (int s = 0; s < PS_MAX_A; s++) { mbar_init(&bar_fullA[s], 1); mbar_init(&bar_emptyA[s], 1); }
+        for (int s = 0; s < PS_MAX_B; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
+        mbar_init(&bar_bres, 1);
+        for (int s = 0; s < 2; s++) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            if (q.b_resident) {
+                mbar_expect_tx(&bar_bres, (uint32_t)(nkc * 9 * B_BYTES));
+                for (int kc = 0; kc < nkc; kc++)
+                    for (int tap = 0; tap < 9; tap++)
+                        tma_load_2d(smemB + (size_t)(kc * 9 + tap) * B_BYTES, &tmB, &bar_bres, tap * p.Cin_p + kc * TM_KC, 0);
+            }
+            int ia = 0, ib = 0;
+            for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x) {
+                const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
+                const int b = pi / patches, pr = pi - b * patches;
+                const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+                for (int kc = 0; kc < nkc; kc++, ia++) {
+                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                    if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+                    mbar_expect_tx(&bar_fullA[sa], (uint32_t)HL_A_BYTES);
+                    tma_load_4d(smem + (size_t)sa * HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x0 - 1, y0 - 1, b);
+                    if (!q.b_resident) {
+                        for (int tap = 0; tap < 9; tap++, ib++) {
+                            const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                            if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
+                            mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
+                            tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ===== MMA issuer =====
+            if (q.b_resident) mbar_wait(&bar_bres, 0);
+            int ia = 0, ib = 0, it = 0;
+            for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
+                const int acc = it & 1, ut = it >> 1;
+                if (ut > 0) mbar_wait(&bar_tempty[acc], (uint32_t)((ut - 1) & 1));      // the epilogue has drained this accumulator
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t dcol = tmem_d + (uint32_t)(acc * BN);
+                for (int kc = 0; kc < nkc; kc++, ia++) {
+                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                    mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    // descriptor bases once per chunk; the 36 (tap, k) offsets below are compile-time constants
+                    const uint64_t da0 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * HL_A_STRIDE), 0);
+                    if (q.b_resident) {
+                        const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(kc * 9 * B_BYTES));
+#pragma unroll
+                        for (int tap = 0; tap < 9; tap++) {
+#pragma unroll
+                            for (int k = 0; k < TM_KC / 8; k++) {
+                                const uint64_t da = da0 + (uint64_t)((((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4) + 2 * k);
+                                const uint64_t db = db0 + (uint64_t)((tap * B_BYTES >> 4) + 2 * k);
+                                if (tap == 0 && k == 0) umma_tf32(dcol, da, db, IDESC, kc != 0 ? 1u : 0u);
+                                else umma_tf32_acc(dcol, da, db, IDESC);
+                            }
+                        }
+                    } else {
+#pragma unroll
+                        for (int tap = 0; tap < 9; tap++, ib++) {
+                            const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                            mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
+#pragma unroll
+                            for (int k = 0; k < TM_KC / 8; k++) {
+                                const uint64_t da = da0 + (uint64_t)((((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4) + 2 * k);
+                                if (tap == 0 && k == 0) umma_tf32(dcol, da, db0, IDESC, kc != 0 ? 1u : 0u);
+                                else umma_tf32_acc(dcol, da, db0 + (uint64_t)(2 * k), IDESC);
+                            }
+                            umma_commit(&bar_emptyB[sb]);
+                        }
+                    }
+                    umma_commit(&bar_emptyA[sa]);
+                }
+                umma_commit(&bar_tfull[acc]);
+            }
+        }
+    } else {
+        // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
+        const int row = (warp & 3) * 32 + lane;              // tile row = TMEM lane
+        const int h = row / HL_PW, w = row - h * HL_PW;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
+            const int acc = it & 1, ut = it >> 1;
+            const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
+            const int b = pi / patches, pr = pi - b * patches;
+            const int y = (pr / p.ptx) * HL_PH + h, x = (pr - (pr / p.ptx) * p.ptx) * HL_PW + w;
+            const bool pv = y < p.H && x < p.W;
+            const size_t m = ((size_t)b * p.H + y) * p.W + x;
+            mbar_wait(&bar_tfull[acc], (uint32_t)(ut & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t lane_addr = tmem_d + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+            for (int cb = 0; cb < BN; cb += 16) {
+                uint32_t r[16];
+                tmem_ld16(lane_addr + (uint32_t)cb, r);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                const int n = n0 + cb;
+                if (pv && p.planar_out && n < p.planar_C) {
+#pragma unroll
+                    for (int k = 0; k < 16; k++) {
+                        const int co = n + k;
+                        if (co < p.planar_C) {
+                            float v = __uint_as_float(r[k]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+                            v = act_apply(v, p.act, p.slope);
+                            const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
+                            p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
+                        }
+                    }
+                }
+                if (pv && p.dst && n < p.Cout_p) {
+                    const size_t off = m * p.Cout_p + n;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        float4 o;
+                        o.x = __uint_as_float(r[4 * k + 0]); o.y = __uint_as_float(r[4 * k + 1]);
+                        o.z = __uint_as_float(r[4 * k + 2]); o.w = __uint_as_float(r[4 * k + 3]);
+                        if (p.bias) {
+                            float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * k));
+                            o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
+                        }
+                        o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
+                        o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
+                        if (p.addend) {
+                            float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * k));
+                            o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
+                        }
+                        *reinterpret_cast<float4*>(p.dst + off + 4 * k) = o;
+                    }
+                }
+                if (!p.dst && n + 16 >= p.planar_C) break;
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(&bar_tempty[acc]);                   // 128 arrivals free the accumulator for tile it+2
+        }
+    }
+    __syncwarp();
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
+}
+
+}  // namespace
+
+#define PERSIST_LAUNCH(BN_)                                                                                                \
+    do {                                                                                                                   \
+        auto conv3x3_persist_bn##BN_ = conv3x3_persist<BN_>;                                                               \
+        static int attr_smem = 0;                                                                                          \
+        if (smem > attr_smem) {                                                                                            \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_persist_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
+            attr_smem = smem;                                                                                              \
+        }                                                                                                                  \
+        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
+        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, 192, smem, tmA, tmB, p, q);                                          \
+        DC_CHECK_LAUNCH();                                                                                                 \
+        return DINCAE_OK;                                                                                                  \
+    } while (0)
+
+static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
+    TmaConvArgs p;
+    p.B = a.B; p.H = a.H; p.W = a.W;
+    p.PW = HL_PW; p.PH = HL_PH;
+    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
+    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
+    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    const int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
+    const int nkc = a.in.C / TM_KC;
+    PersistArgs q;
+    q.ntiles_n = a.Cout_p / bn;
+    q.num_tiles = p.ptx * p.pty * a.B * q.ntiles_n;
+    const int bbytes = bn * 128;
+    const int resident_bytes = nkc * 9 * bbytes;
+    q.b_resident = (q.ntiles_n == 1 && resident_bytes <= 112 * 1024) ? 1 : 0;
+    q.a_stages = 2;
+    q.b_stages = q.b_resident ? 0 : (bn == 256 ? 4 : (bn == 128 ? 4 : 6));
+    int smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 1024;
+    int per_sm = 1;                                   // persistent: one CTA per SM (two when both smem and TMEM allow)
+    if (2 * (smem + 2048) <= 227 * 1024 && 4 * bn <= 512) per_sm = 2;
+    int ctas = ctx->num_sms * per_sm;
+    if (ctas > q.num_tiles) ctas = q.num_tiles;
+    dim3 grid((unsigned)ctas);
+    alignas(64) CUtensorMap tmA, tmB;
+    DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
+    if (bn == 256) PERSIST_LAUNCH(256);
+    if (bn == 128) PERSIST_LAUNCH(128);
+    if (bn == 64) PERSIST_LAUNCH(64);
+    PERSIST_LAUNCH(32);
+}
+
 #define HALO_LAUNCH(BN_, AS_, BS_)                                                                                         \
     do {                                                                                                                   \
         auto conv3x3_halo_bn##BN_ = conv3x3_halo<BN_, AS_, BS_>;                                                           \
@@ -481,10 +739,11 @@ bool k2_conv_tma_eligible(const ConvArgs& a) {
 
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     if (a.B * a.H * a.W == 0) return DINCAE_OK;
-    // DINCAE_CONV_HALO: 0 = one activation box per tap; 1 = halo tile, shifted descriptors (default); 2 = same with base_offset set
+    // DINCAE_CONV_KERNEL: 0 = one activation box per tap; 1 = halo tile with shifted descriptors; 3 = persistent warp-specialised halo kernel (default)
     static int halo_mode = -1;
-    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_HALO"); halo_mode = e ? atoi(e) : 1; }
-    if (halo_mode > 0) return k2_conv_halo(ctx, a, halo_mode);
+    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
+    if (halo_mode == 3) return k2_conv_persist(ctx, a);
+    if (halo_mode > 0) return k2_conv_halo(ctx, a, 1);
     TmaConvArgs p;
     p.B = a.B; p.H = a.H; p.W = a.W;
     p.PW = a.W > 8 ? 16 : 8;
