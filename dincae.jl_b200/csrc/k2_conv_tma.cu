@@ -1074,15 +1074,26 @@ __global__ void __launch_bounds__(128) wgrad_halo(const __grid_constant__ CUtens
             mbar_wait(&bar_full[s], (uint32_t)(u & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t abase = smem_base + (uint32_t)(s * stage_bytes), bbase = abase + (uint32_t)a_bytes;
+            // descriptor bases once per stage; the 12 (dx, h) offsets are compile-time constants (single-thread issue rate matters)
+            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, (uint32_t)mblk_bytes), db0 = make_desc_mn_sw128_lbo(bbase, (uint32_t)nblk_bytes);
+            if (p.in_is_m) {
 #pragma unroll
-            for (int dx = 0; dx < 3; dx++) {
+                for (int dx = 0; dx < 3; dx++)
 #pragma unroll
-                for (int h = 0; h < 4; h++) {       // one k-step = the 8 pixels of box row h
-                    const uint32_t in_off = (uint32_t)(dx * 128 + h * 1280), g_off = (uint32_t)(h * 1024);
-                    const uint64_t da = make_desc_mn_sw128_lbo(abase + (p.in_is_m ? in_off : g_off), (uint32_t)mblk_bytes);
-                    const uint64_t db = make_desc_mn_sw128_lbo(bbase + (p.in_is_m ? g_off : in_off), (uint32_t)nblk_bytes);
-                    umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, (i | h) != 0 ? 1u : 0u);
-                }
+                    for (int h = 0; h < 4; h++) {       // one k-step = the 8 pixels of box row h
+                        const uint64_t da = da0 + (uint64_t)((dx * 128 + h * 1280) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
+                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, i != 0 ? 1u : 0u);
+                        else umma_tf32_acc(tmem_d + (uint32_t)(dx * BN), da, db, IDESC);
+                    }
+            } else {
+#pragma unroll
+                for (int dx = 0; dx < 3; dx++)
+#pragma unroll
+                    for (int h = 0; h < 4; h++) {
+                        const uint64_t da = da0 + (uint64_t)((h * 1024) >> 4), db = db0 + (uint64_t)((dx * 128 + h * 1280) >> 4);
+                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, i != 0 ? 1u : 0u);
+                        else umma_tf32_acc(tmem_d + (uint32_t)(dx * BN), da, db, IDESC);
+                    }
             }
             umma_commit(&bar_empty[s]);
         }
