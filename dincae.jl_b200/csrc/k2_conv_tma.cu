@@ -1150,6 +1150,130 @@ int32_t make_tmap_inhalo(CUtensorMap* m, const float* ptr, int C, int W, int H, 
     return DINCAE_OK;
 }
 
+// Narrow layers (Cin_p = Cout_p = 32, the full-resolution edge convs): ALL nine taps in one CTA.  The `in` halo box
+// (32 ch x 10 x 6) of an 8x4 patch is loaded once; the three dx taps are stacked in the MMA M dimension by giving the
+// MN-major descriptor a leading-dimension offset of ONE pixel row (128 B): "channel block" j of the operand is simply the
+// same tile shifted by j pixels.  Three accumulators (one per ky) of 32 columns each; D lane = dx*32 + ci.
+constexpr int W32_IN_ROWS = 64;                   // 10*6 = 60 halo rows + 4 rows read (never used) by the 4th M block
+constexpr int W32_IN_BYTES = W32_IN_ROWS * 128, W32_STAGE = W32_IN_BYTES + WG_BLOCK;
+
+template <int STAGES>
+__global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int split = blockIdx.x;
+    const int64_t p_lo = (int64_t)split * p.patches_per_split;
+    int64_t p_hi = p_lo + p.patches_per_split;
+    if (p_hi > p.npatches) p_hi = p.npatches;
+    const int nst = (int)(p_hi - p_lo);
+
+    // the 4 pad rows of every stage are read by the (discarded) 4th M block: keep them finite
+    for (int s = 0; s < STAGES; s++)
+        for (int i = t; i < 4 * 128 / 16; i += 128)
+            reinterpret_cast<float4*>(smem + (size_t)s * W32_STAGE + 60 * 128)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(128u));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+    if (t == 0) {
+        const int per_img = p.ptx * p.pty;
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int64_t pp = p_lo + i;
+            const int b = (int)(pp / per_img);
+            const int r = (int)(pp - (int64_t)b * per_img);
+            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            uint8_t* st = smem + (size_t)s * W32_STAGE;
+            mbar_expect_tx(&bar_full[s], (uint32_t)(60 * 128 + WG_BLOCK));
+            tma_load_4d(st, &tmIn, &bar_full[s], 0, x0 - 1, y0 - 1, b);               // (32, 10, 6, 1) halo box
+            tma_load_4d(st + W32_IN_BYTES, &tmG, &bar_full[s], 0, x0, y0, b);         // (32, 8, 4, 1)
+        }
+    } else if (t == 32) {
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t abase = smem_base + (uint32_t)(s * W32_STAGE);
+            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 128u);                 // M block j = the tile shifted by j pixel rows
+            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W32_IN_BYTES, (uint32_t)WG_BLOCK);
+#pragma unroll
+            for (int ky = 0; ky < 3; ky++)
+#pragma unroll
+                for (int h = 0; h < 4; h++) {
+                    const uint64_t da = da0 + (uint64_t)(((ky + h) * 10 * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
+                    if (h == 0) umma_tf32(tmem_d + (uint32_t)(ky * 32), da, db, IDESC, i != 0 ? 1u : 0u);
+                    else umma_tf32_acc(tmem_d + (uint32_t)(ky * 32), da, db, IDESC);
+                }
+            umma_commit(&bar_empty[s]);
+        }
+        umma_commit(&bar_done);
+    }
+    __syncwarp();
+    float* out = p.partial + (size_t)split * 9 * 32 * 32;
+    if (nst > 0) {
+        mbar_wait(&bar_done, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+    const int dx = t >> 5, ci = t & 31;
+#pragma unroll 1
+    for (int cb = 0; cb < 96; cb += 16) {
+        uint32_t r[16];
+        if (nst > 0) {
+            tmem_ld16(lane_addr + (uint32_t)cb, r);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        } else {
+#pragma unroll
+            for (int k = 0; k < 16; k++) r[k] = 0u;
+        }
+        if (dx < 3) {
+            const int ky = cb >> 5, co0 = cb & 31;
+            float* o = out + ((size_t)(ky * 3 + dx) * 32 + ci) * 32 + co0;
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                *reinterpret_cast<float4*>(o + 4 * k) = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u));
+}
+
+int32_t make_tmap_in32(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, 10, 6, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(in32 C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
+    return DINCAE_OK;
+}
+
 int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
     EncodeTiledFn enc = get_encode();
     DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
@@ -1174,6 +1298,7 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
     const int mtiles = (m_ch + 127) / 128, ntiles = n_ch / bn;
     npatches = (int64_t)a.B * dc_cdiv(a.H, 4) * dc_cdiv(a.W, 8);
     int tiles = mtiles * ntiles * (bn == 32 ? 3 : 9);     // three taps per CTA in the halo variant (narrow N only)
+    if (Cin_p == 32 && Cout_p == 32) tiles = 1;           // wgrad32_kernel: all nine taps in one CTA
     splits = ((bn == 32 ? 3 : 2) * num_sms + tiles - 1) / tiles;
     int64_t maxs = dc_cdiv(npatches, 4);
     if (splits > maxs) splits = (int)maxs;
@@ -1247,7 +1372,19 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     alignas(64) CUtensorMap tmIn, tmG;
     DC_TRY(make_tmap_patch(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
     DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
-    if (bn == 32) {
+    if (Cin_p == 32 && Cout_p == 32) {
+        DC_TRY(make_tmap_in32(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
+        auto wgrad32 = wgrad32_kernel<6>;
+        constexpr int smem = 6 * W32_STAGE + 1024;
+        static bool attr_set = false;
+        if (!attr_set) {
+            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            attr_set = true;
+        }
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * 32 * 32 * (double)a.B * a.H * a.W, a.work_bytes);
+        DC_LAUNCH(ctx, wgrad32, (unsigned)splits, 128, smem, tmIn, tmG, p);
+        DC_CHECK_LAUNCH();
+    } else if (bn == 32) {
         DC_TRY(make_tmap_inhalo(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
         dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(3 * (p.n_ch / bn)));
         WH_LAUNCH(32, 4);

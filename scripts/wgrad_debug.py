@@ -23,7 +23,7 @@ def tf32(x):
     return (x.view(torch.int32) + 0x1000 & ~0x1FFF).view(torch.float32) if False else x
 
 torch.manual_seed(0)
-for (B, H, W, Ci, Co) in [(1, 4, 8, 32, 32), (1, 4, 8, 128, 32), (1, 4, 8, 32, 128), (2, 9, 13, 64, 32), (4, 28, 28, 64, 128), (2, 14, 14, 256, 128)]:
+for (B, H, W, Ci, Co) in [(1, 4, 8, 32, 32), (3, 9, 13, 32, 32), (4, 112, 112, 32, 32), (1, 4, 8, 128, 32), (1, 4, 8, 32, 128), (2, 9, 13, 64, 32), (4, 28, 28, 64, 128), (2, 14, 14, 256, 128)]:
     xin = torch.randint(-4, 5, (B, H, W, Ci), device=dev).float()      # small integers: exact in TF32, exact sums
     g = torch.randint(-4, 5, (B, H, W, Co), device=dev).float()
     r0, b0 = run(xin, g, 0)
