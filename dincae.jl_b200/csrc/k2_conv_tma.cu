@@ -915,24 +915,30 @@ __global__ void __launch_bounds__(128) wgrad_tma(const __grid_constant__ CUtenso
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
 }
 
-// dst[i] = sum over splits of partial[z][i]: 8 independent partial sums (memory-level parallelism) combined in a fixed
-// order, so the result does not depend on scheduling (deterministic second stage of the split-K reduction)
-__global__ void reduce_splits_kernel(const float* __restrict__ partial, int splits, int64_t n, float* __restrict__ dst) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float s[8];
-#pragma unroll
-    for (int j = 0; j < 8; j++) s[j] = 0.f;
-    int z = 0;
-    for (; z + 8 <= splits; z += 8) {
-        float v[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) v[j] = __ldg(partial + (size_t)(z + j) * n + i);
-#pragma unroll
-        for (int j = 0; j < 8; j++) s[j] += v[j];
+// dst[i] = sum over splits of partial[z][i].  Block = 32 consecutive outputs x 8 split groups: thread (c, zg) sums the splits
+// z = zg, zg+8, ... (4 loads in flight), the 8 group sums are combined in a fixed order -> deterministic second stage.
+__global__ void __launch_bounds__(256) reduce_splits_kernel(const float* __restrict__ partial, int splits, int64_t n, float* __restrict__ dst) {
+    __shared__ float sh[8][32];
+    const int c = threadIdx.x & 31, zg = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * 32 + c;
+    float s = 0.f;
+    if (i < n) {
+        int z = zg;
+        for (; z + 24 < splits; z += 32) {
+            float v0 = __ldg(partial + (size_t)z * n + i), v1 = __ldg(partial + (size_t)(z + 8) * n + i);
+            float v2 = __ldg(partial + (size_t)(z + 16) * n + i), v3 = __ldg(partial + (size_t)(z + 24) * n + i);
+            s += (v0 + v1) + (v2 + v3);
+        }
+        for (; z < splits; z += 8) s += __ldg(partial + (size_t)z * n + i);
     }
-    for (int j = 0; z < splits; z++, j++) s[j] += __ldg(partial + (size_t)z * n + i);
-    dst[i] = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
+    sh[zg][c] = s;
+    __syncthreads();
+    if (zg == 0 && i < n) {
+        float tot = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) tot += sh[k][c];
+        dst[i] = tot;
+    }
 }
 
 // bias gradient: column sums of g [M][C] (C % 4 == 0) in two deterministic stages.
@@ -1394,7 +1400,7 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
         else if (bn == 128) WG_LAUNCH(128, 3);
         else WG_LAUNCH(64, 4);
     }
-    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 256), 256, 0, p.partial, splits, nW, a.dW);
+    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 32), 256, 0, p.partial, splits, nW, a.dW);
     DC_CHECK_LAUNCH();
     // bias gradient
     float* cpart = p.partial + (size_t)splits * nW;
