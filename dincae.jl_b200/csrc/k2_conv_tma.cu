@@ -1426,3 +1426,36 @@ extern "C" int32_t dincae_debug_wgrad(dincae_ctx* ctx, const float* d_in, const 
     DC_TRY(dc_scratch(ctx, need, &sc));
     return k2_wgrad(ctx, a, sc, ctx->scratch_bytes);
 }
+
+// ---- test hook (not part of the public header): one 3x3 convolution through a chosen kernel family ----------------
+//   variant 0: FP32 CUDA-core kernel   1: tcgen05 with software-gather producer   2: TMA, one activation box per tap
+//           3: TMA halo tile + shifted descriptors   4: persistent warp-specialised halo kernel
+// d_w: [round_up(9*Cin_p,16)][Cout_p] forward layout; d_wK: K-major [Cout_p][9*Cin_p] copy (TF32-representable values).
+extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const float* d_w, const float* d_wK, const float* d_bias,
+                                     int32_t B, int32_t H, int32_t W, int32_t Cin_p, int32_t Cout_p, int32_t relu, float* d_out, int32_t variant) {
+    DC_REQUIRE(ctx && d_in && d_w && d_wK && d_out, DINCAE_EINVAL, "dincae_debug_conv: NULL argument");
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    ConvArgs a{};
+    a.in = ConvSrc{d_in, nullptr, SRC_DIRECT, H, W, Cin_p};
+    a.B = B; a.H = H; a.W = W; a.wgt = d_w; a.wgtK = variant == 0 ? nullptr : d_wK; a.ldk = 9 * Cin_p; a.in_is_tf32 = variant >= 2;
+    a.bias = d_bias; a.Cout_p = Cout_p; a.act = relu ? ACT_RELU : ACT_NONE; a.slope = 0.f; a.dst = d_out;
+    if (variant == 0) return k2_conv(ctx, a);
+    if (variant == 1) { DC_REQUIRE(k2_conv_tc_eligible(a), DINCAE_EUNSUPPORTED, "dincae_debug_conv: shape not eligible"); return k2_conv_tc(ctx, a); }
+    DC_REQUIRE(k2_conv_tma_eligible(a), DINCAE_EUNSUPPORTED, "dincae_debug_conv: shape not eligible for the TMA kernels");
+    if (variant == 3) return k2_conv_halo(ctx, a, 1);
+    if (variant == 4) return k2_conv_persist(ctx, a);
+    // variant 2: the one-box-per-tap kernel
+    TmaConvArgs p;
+    p.B = a.B; p.H = a.H; p.W = a.W;
+    p.PW = a.W > 8 ? 16 : 8; p.PH = TM_BM / p.PW;
+    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
+    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
+    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
+    p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0;
+    alignas(64) CUtensorMap tmA, tmB;
+    DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
+    if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
+    if (a.Cout_p % 128 == 0) TMA_LAUNCH(128, 3);
+    if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
+    TMA_LAUNCH(32, 5);
+}
