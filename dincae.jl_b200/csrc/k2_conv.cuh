@@ -44,6 +44,22 @@ struct ConvArgs {
     double work_bytes;    // algorithmic HBM bytes (input + output + weights, REAL channel counts)
 };
 
+// deferred second-stage reductions: every weight gradient appends its split-K partial sums and its bias column partials here;
+// ONE batched kernel at the end of the backward pass finishes them all (deterministic fixed-order sums)
+struct RedEntry {
+    const float* part;   // [splits][n]
+    float* dst;          // [n]
+    int64_t n;
+    int splits;
+};
+constexpr int RED_MAX = 48;
+struct RedList {
+    RedEntry e[RED_MAX];
+    int blk_start[RED_MAX + 1];
+    int count;
+};
+int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list);
+
 struct WgradArgs {
     ConvSrc in;
     int B, H, W;
@@ -57,6 +73,9 @@ struct WgradArgs {
     double work_flops;
     double work_bytes;
     int tf32;             // operands are TF32-representable: the TMA/tcgen05 kernel may be used
+    RedList* defer;       // if set, the second-stage reductions are queued instead of launched
+    const float* colpart; // optional precomputed column partials of gout [colpart_blocks][Cout_p] (bias gradient)
+    int colpart_blocks;
 };
 
 // small-Cout forward (Cout_p in {4,8}): NHWC in -> planar out[b][co][y][x] (co < Cout real)

@@ -941,6 +941,33 @@ __global__ void __launch_bounds__(256) reduce_splits_kernel(const float* __restr
     }
 }
 
+__global__ void __launch_bounds__(256) reduce_batched_kernel(const __grid_constant__ RedList L) {
+    __shared__ float sh[8][32];
+    int e = 0;
+    while (e + 1 < L.count && (int)blockIdx.x >= L.blk_start[e + 1]) e++;
+    const RedEntry en = L.e[e];
+    const int c = threadIdx.x & 31, zg = threadIdx.x >> 5;
+    const int64_t i = (int64_t)((int)blockIdx.x - L.blk_start[e]) * 32 + c;
+    float s = 0.f;
+    if (i < en.n) {
+        int z = zg;
+        for (; z + 24 < en.splits; z += 32) {
+            float v0 = __ldg(en.part + (size_t)z * en.n + i), v1 = __ldg(en.part + (size_t)(z + 8) * en.n + i);
+            float v2 = __ldg(en.part + (size_t)(z + 16) * en.n + i), v3 = __ldg(en.part + (size_t)(z + 24) * en.n + i);
+            s += (v0 + v1) + (v2 + v3);
+        }
+        for (; z < en.splits; z += 8) s += __ldg(en.part + (size_t)z * en.n + i);
+    }
+    sh[zg][c] = s;
+    __syncthreads();
+    if (zg == 0 && i < en.n) {
+        float tot = 0.f;
+#pragma unroll
+        for (int k = 0; k < 8; k++) tot += sh[k][c];
+        en.dst[i] = tot;
+    }
+}
+
 // bias gradient: column sums of g [M][C] (C % 4 == 0) in two deterministic stages.
 // stage 1: block b sums rows b, b+gridDim, ... ; thread = (row lane, float4 column group); fixed-order smem combine.
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ g, int64_t M, int C, float* __restrict__ part) {
@@ -1400,14 +1427,26 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
         else if (bn == 128) WG_LAUNCH(128, 3);
         else WG_LAUNCH(64, 4);
     }
-    DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 32), 256, 0, p.partial, splits, nW, a.dW);
-    DC_CHECK_LAUNCH();
-    // bias gradient
-    float* cpart = p.partial + (size_t)splits * nW;
-    DC_LAUNCH(ctx, colsum_partial_kernel, cs_blocks, 256, 0, a.gout, M, Cout_p, cpart);
-    DC_CHECK_LAUNCH();
-    DC_LAUNCH(ctx, colsum_final_kernel, (unsigned)dc_cdiv(Cout_p, 8), 256, 0, cpart, cs_blocks, Cout_p, a.db);
-    DC_CHECK_LAUNCH();
+    // second stages: split-K sum of dW and column-partial sum of the bias gradient (queued when a.defer is set)
+    const float* cpart = a.colpart;
+    int cblocks = a.colpart_blocks;
+    if (!cpart) {
+        float* cp = p.partial + (size_t)splits * nW;
+        DC_LAUNCH(ctx, colsum_partial_kernel, cs_blocks, 256, 0, a.gout, M, Cout_p, cp);
+        DC_CHECK_LAUNCH();
+        cpart = cp;
+        cblocks = cs_blocks;
+    }
+    if (a.defer) {
+        DC_REQUIRE(a.defer->count + 2 <= RED_MAX, DINCAE_ESIZE, "k2_wgrad_tma: too many deferred reductions");
+        a.defer->e[a.defer->count++] = RedEntry{p.partial, a.dW, nW, splits};
+        a.defer->e[a.defer->count++] = RedEntry{cpart, a.db, (int64_t)Cout_p, cblocks};
+    } else {
+        DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(nW, 32), 256, 0, p.partial, splits, nW, a.dW);
+        DC_CHECK_LAUNCH();
+        DC_LAUNCH(ctx, reduce_splits_kernel, (unsigned)dc_cdiv(Cout_p, 32), 256, 0, cpart, cblocks, (int64_t)Cout_p, a.db);
+        DC_CHECK_LAUNCH();
+    }
     return DINCAE_OK;
 }
 
@@ -1458,4 +1497,18 @@ extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const f
     if (a.Cout_p % 128 == 0) TMA_LAUNCH(128, 3);
     if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
     TMA_LAUNCH(32, 5);
+}
+
+int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list) {
+    if (list.count == 0) return DINCAE_OK;
+    int blocks = 0;
+    for (int e = 0; e < list.count; e++) {
+        list.blk_start[e] = blocks;
+        blocks += (int)dc_cdiv(list.e[e].n, 32);
+    }
+    list.blk_start[list.count] = blocks;
+    DC_LAUNCH(ctx, reduce_batched_kernel, blocks, 256, 0, list);
+    DC_CHECK_LAUNCH();
+    list.count = 0;
+    return DINCAE_OK;
 }

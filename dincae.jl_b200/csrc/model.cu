@@ -123,6 +123,17 @@ int32_t ensure_wT(dincae_model* M) {
     return DINCAE_OK;
 }
 
+// weight gradient with its own scratch slice; in TF32 mode the second-stage reductions are queued in M->red
+int32_t run_wgrad(dincae_model* M, WgradArgs& wa) {
+    if (!M->wK) return k2_wgrad(M->ctx, wa, M->wg_scratch, M->wg_scratch_bytes);
+    size_t need = (k2_wgrad_tma_scratch_bytes(M->ctx->num_sms, wa.B, wa.H, wa.W, wa.in.C, wa.Cout_p) + 255) / 256 * 256;
+    DC_REQUIRE(M->wg_off + need <= M->wg_scratch_bytes, DINCAE_ESIZE, "weight-gradient scratch arena exhausted");
+    wa.defer = &M->red;
+    int32_t st = k2_wgrad(M->ctx, wa, (char*)M->wg_scratch + M->wg_off, need);
+    M->wg_off += need;
+    return st;
+}
+
 int32_t chain_backward(dincae_model* M, int c, int B) {
     dincae_ctx* ctx = M->ctx;
     ChainBufs& cb = M->cb[c];
@@ -148,7 +159,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
         if (l == 0 && !M->wK) DC_TRY(k2_wgrad_small(ctx, wa, M->nco, M->wg_scratch, M->wg_scratch_bytes));
-        else DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
+        else DC_TRY(run_wgrad(M, wa));
         ConvArgs a{};
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
@@ -175,7 +186,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         wa.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
-        DC_TRY(k2_wgrad(ctx, wa, M->wg_scratch, M->wg_scratch_bytes));
+        DC_TRY(run_wgrad(M, wa));
         if (l >= 1) {
             ConvArgs a{};
             a.in = ConvSrc{M->GC[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cout_p};
@@ -347,7 +358,10 @@ int32_t points_loss(dincae_model* M, PointTruth& pt, int B, int64_t n_valid_glob
 int32_t backward_all(dincae_model* M, int B) {
     M->ctx->tf32_acts = M->wK != nullptr;
     DC_TRY(ensure_wT(M));
+    M->wg_off = 0;
+    M->red.count = 0;
     for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
+    DC_TRY(k2_reduce_batched(M->ctx, M->red));
     DC_LAUNCH(M->ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -552,7 +566,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     want((void**)&M->d_nvalid, sizeof(unsigned long long) * 16);
     M->red_scratch_bytes = k3_scratch_bytes(0);
     want(&M->red_scratch, M->red_scratch_bytes);
-    size_t wgb = 0;
+    size_t wgb = 0, wg_sum = 0;
     for (int c = 0; c < M->nchains; c++)
         for (int l = 0; l < L; l++) {
             size_t a = k2_wgrad_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
@@ -561,9 +575,9 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             wgb = b > wgb ? b : wgb;
             size_t ta = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
             size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
-            wgb = ta > wgb ? ta : wgb;
-            wgb = tb > wgb ? tb : wgb;
+            wg_sum += ((ta + 255) / 256 * 256) + ((tb + 255) / 256 * 256);
         }
+    if (cfg->precision == DINCAE_PREC_TF32 && wg_sum > wgb) wgb = wg_sum;    // TF32 mode: one slice per layer (second stages are batched)
     M->wg_scratch_bytes = wgb;
     want(&M->wg_scratch, wgb);
     want((void**)&M->in_xin, sizeof(float) * Bm * cfg->ninput * cfg->W * cfg->H);

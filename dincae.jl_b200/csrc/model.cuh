@@ -49,8 +49,9 @@ struct dincae_model {
     unsigned long long* d_nvalid = nullptr;
     void* red_scratch = nullptr;
     size_t red_scratch_bytes = 0;
-    void* wg_scratch = nullptr;
-    size_t wg_scratch_bytes = 0;
+    void* wg_scratch = nullptr;        // arena: every weight gradient of a backward pass gets its own slice (deferred reductions)
+    size_t wg_scratch_bytes = 0, wg_off = 0;
+    RedList red;
     float *in_xin = nullptr, *in_xtrue = nullptr;     // device staging of host mini-batches
     // prefetch slots (dincae_batch_upload): the next mini-batch crosses PCIe on a copy stream while this one trains
     float* up_buf[2] = {nullptr, nullptr};
