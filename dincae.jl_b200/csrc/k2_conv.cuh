@@ -111,9 +111,11 @@ int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, i
 // MeanPool((2,2), pad=odd): count-include-pad (src/model.jl:268)
 int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, float* x);
 // backward of nearest-upsample + crop (+ activation mask of r): G = up^T(gu); gd = G * act'(r)
-int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd);
+// colpart (optional): [k2_colpart_blocks][Cp] per-block column sums of gd (the bias gradient's first stage, fused here)
+int k2_colpart_blocks(dincae_ctx* ctx, int64_t n_elems4, int Cp);
+int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd, float* colpart = nullptr);
 // backward of mean-pool + activation mask: gc = 0.25 * xg[(y+oh)>>1,(x+ow)>>1] * act'(a)
-int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc);
+int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc, float* colpart = nullptr);
 // bilinear (align_corners=true) upsample+crop of (src0 + src1) and its transpose
 // nearest upsample x2 + crop of (src0 + src1), materialised (TF32 mode: feeds the TMA kernels)
 int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);

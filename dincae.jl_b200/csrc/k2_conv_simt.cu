@@ -341,20 +341,39 @@ __global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits
 }
 
 // ---------------------------------------------------------------------------------------------
-__global__ void pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
-                                   int B, int HW, float* __restrict__ dst, int Cp, int rnd) {
-    int64_t m = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (m >= (int64_t)B * HW) return;
-    int b = (int)(m / HW), r = (int)(m - (int64_t)b * HW);
-    for (int c = 0; c < Cp; c += 4) {
-        float v[4];
-#pragma unroll
-        for (int e = 0; e < 4; e++) {
-            int cc = c + e;
-            v[e] = cc < C0 ? __ldg(s0 + ((size_t)b * C0 + cc) * HW + r)
-                 : (cc < C0 + C1 ? __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r) : 0.f);
+// planar (WHCN) -> NHWC: a warp moves 32 consecutive pixels; reads are coalesced along pixels (one channel plane at a time),
+// a padded smem tile transposes, writes are coalesced along channels (4 pixels x 128 B per store instruction)
+__global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
+                                                          int B, int HW, float* __restrict__ dst, int Cp, int rnd) {
+    __shared__ float tile[8][32][33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t total = (int64_t)B * HW;
+    const int64_t m0 = ((int64_t)blockIdx.x * 8 + warp) * 32;
+    if (m0 >= total) return;
+    const int64_t m = m0 + lane;
+    const bool pv = m < total;
+    const int b = pv ? (int)(m / HW) : 0, r = pv ? (int)(m - (int64_t)b * HW) : 0;
+    for (int cg = 0; cg < Cp; cg += 32) {
+        const int nc = Cp - cg < 32 ? Cp - cg : 32;
+        for (int c = 0; c < nc; c++) {
+            const int cc = cg + c;
+            float v = 0.f;
+            if (pv) {
+                if (cc < C0) v = __ldg(s0 + ((size_t)b * C0 + cc) * HW + r);
+                else if (cc < C0 + C1) v = __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r);
+            }
+            tile[warp][lane][c] = rnd ? round_tf32(v) : v;
         }
-        *reinterpret_cast<float4*>(dst + (size_t)m * Cp + c) = round_tf32(make_float4(v[0], v[1], v[2], v[3]), rnd);
+        __syncwarp();
+        const int chunks = nc >> 2;                         // float4 chunks per pixel row in this group
+        for (int i = lane; i < 32 * chunks; i += 32) {
+            const int px = i / chunks, ch = i - px * chunks;
+            if (m0 + px < total) {
+                float4 o = make_float4(tile[warp][px][4 * ch], tile[warp][px][4 * ch + 1], tile[warp][px][4 * ch + 2], tile[warp][px][4 * ch + 3]);
+                *reinterpret_cast<float4*>(dst + (size_t)(m0 + px) * Cp + cg + 4 * ch) = o;
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -385,60 +404,82 @@ __global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, in
     *reinterpret_cast<float4*>(x + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4) = round_tf32(s, rnd);
 }
 
-// gu at (H,W); outputs at (Hs,Ws) = (H/2 + H%2, W/2 + W%2)
-__global__ void upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
-                             const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    int C4 = Cp >> 2;
-    int64_t total = (int64_t)B * Hs * Ws * C4;
-    if (i >= total) return;
-    int c4 = (int)(i % C4);
-    int64_t p = i / C4;
-    int xs = (int)(p % Ws);
-    p /= Ws;
-    int ys = (int)(p % Hs);
-    int b = (int)(p / Hs);
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int dy = 0; dy < 2; dy++)
-#pragma unroll
-        for (int dx = 0; dx < 2; dx++) {
-            int yy = 2 * ys + dy, xx = 2 * xs + dx;
-            if (yy < H && xx < W) {
-                float4 v = ldg4(gu + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
-                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-            }
-        }
-    size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + c4 * 4;
-    if (G) *reinterpret_cast<float4*>(G + off) = s;
-    if (gd) {
-        if (r) {
-            float4 rv = ldg4(r + off);
-            s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
-        }
-        *reinterpret_cast<float4*>(gd + off) = round_tf32(s, rnd);
+// block-level column partial sums of the float4 each thread accumulated for ITS column group (requires 256 % C4 == 0 and a
+// grid stride that is a multiple of C4, so a thread always sees the same columns); fixed summation order -> deterministic
+__device__ __forceinline__ void block_colpart(float4 acc, int C4, int Cp, float* __restrict__ colpart) {
+    __shared__ float4 shp[256];
+    shp[threadIdx.x] = acc;
+    __syncthreads();
+    if ((int)threadIdx.x < C4) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = threadIdx.x; k < 256; k += C4) { float4 v = shp[k]; t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w; }
+        reinterpret_cast<float4*>(colpart + (size_t)blockIdx.x * Cp)[threadIdx.x] = t;
     }
 }
 
-__global__ void poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
-                               int H2, int W2, float slope, float* __restrict__ gc, int rnd) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+// gu at (H,W); outputs at (Hs,Ws) = (H/2 + H%2, W/2 + W%2)
+__global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
+                                                    const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd,
+                                                    float* __restrict__ colpart) {
+    int C4 = Cp >> 2;
+    int64_t total = (int64_t)B * Hs * Ws * C4;
+    float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int c4 = (int)(i % C4);
+        int64_t p = i / C4;
+        int xs = (int)(p % Ws);
+        p /= Ws;
+        int ys = (int)(p % Hs);
+        int b = (int)(p / Hs);
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int dy = 0; dy < 2; dy++)
+#pragma unroll
+            for (int dx = 0; dx < 2; dx++) {
+                int yy = 2 * ys + dy, xx = 2 * xs + dx;
+                if (yy < H && xx < W) {
+                    float4 v = ldg4(gu + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
+                    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+                }
+            }
+        size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + c4 * 4;
+        if (G) *reinterpret_cast<float4*>(G + off) = s;
+        if (gd) {
+            if (r) {
+                float4 rv = ldg4(r + off);
+                s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
+            }
+            s = round_tf32(s, rnd);
+            *reinterpret_cast<float4*>(gd + off) = s;
+            cacc.x += s.x; cacc.y += s.y; cacc.z += s.z; cacc.w += s.w;
+        }
+    }
+    if (colpart) block_colpart(cacc, C4, Cp, colpart);
+}
+
+__global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
+                                                      int H2, int W2, float slope, float* __restrict__ gc, int rnd, float* __restrict__ colpart) {
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * H * W * C4;
-    if (i >= total) return;
-    int c4 = (int)(i % C4);
-    int64_t p = i / C4;
-    int x = (int)(p % W);
-    p /= W;
-    int y = (int)(p % H);
-    int b = (int)(p / H);
-    int y2 = (y + (H & 1)) >> 1, x2 = (x + (W & 1)) >> 1;
-    float4 g = ldg4(xg + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4);
-    size_t off = (((size_t)b * H + y) * W + x) * Cp + c4 * 4;
-    float4 av = ldg4(a + off);
-    g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
-    g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
-    *reinterpret_cast<float4*>(gc + off) = round_tf32(g, rnd);
+    float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        int c4 = (int)(i % C4);
+        int64_t p = i / C4;
+        int x = (int)(p % W);
+        p /= W;
+        int y = (int)(p % H);
+        int b = (int)(p / H);
+        int y2 = (y + (H & 1)) >> 1, x2 = (x + (W & 1)) >> 1;
+        float4 g = ldg4(xg + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4);
+        size_t off = (((size_t)b * H + y) * W + x) * Cp + c4 * 4;
+        float4 av = ldg4(a + off);
+        g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
+        g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+        g = round_tf32(g, rnd);
+        *reinterpret_cast<float4*>(gc + off) = g;
+        cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
+    }
+    if (colpart) block_colpart(cacc, C4, Cp, colpart);
 }
 
 // bilinear, align_corners = true (NNlib.upsample_bilinear default), full size (2Hs,2Ws) cropped to (H,W)
@@ -677,7 +718,7 @@ int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, siz
 int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
     int64_t M = (int64_t)B * H * W;
     if (M == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, (int)ctx->tf32_acts);
+    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -691,20 +732,33 @@ int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, fl
     return DINCAE_OK;
 }
 
-int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd) {
+// number of blocks the producers use when they also emit bias column partials (0 = not supported for this channel count)
+int k2_colpart_blocks(dincae_ctx* ctx, int64_t n_elems4, int Cp) {
+    int C4 = Cp >> 2;
+    if (C4 < 1 || C4 > 256 || (256 % C4) != 0) return 0;
+    int64_t nb = dc_cdiv(n_elems4, 256);
+    int64_t cap = 8 * (int64_t)ctx->num_sms;
+    return (int)(nb < cap ? nb : cap);
+}
+
+int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd, float* colpart) {
     int Hs = H / 2 + H % 2, Ws = W / 2 + W % 2;
     int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, upbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts);
+    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : (int)dc_cdiv(n, 256);
+    DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_upbwd: column partials not supported for %d channels", Cp);
+    DC_LAUNCH(ctx, upbwd_kernel, nb, 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
 
-int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc) {
+int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc, float* colpart) {
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, poolbwd_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts);
+    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : (int)dc_cdiv(n, 256);
+    DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd: column partials not supported for %d channels", Cp);
+    DC_LAUNCH(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -941,29 +941,31 @@ __global__ void __launch_bounds__(256) reduce_splits_kernel(const float* __restr
     }
 }
 
+// One block = `cols` consecutive outputs x (256/cols) split groups.  Wide entries (dW) use 32 x 8, narrow entries with many
+// partial rows (bias column partials: n = C, splits ~ 1000) use 8 x 32 so that enough threads share the long sums.
 __global__ void __launch_bounds__(256) reduce_batched_kernel(const __grid_constant__ RedList L) {
-    __shared__ float sh[8][32];
+    __shared__ float sh[256];
     int e = 0;
     while (e + 1 < L.count && (int)blockIdx.x >= L.blk_start[e + 1]) e++;
     const RedEntry en = L.e[e];
-    const int c = threadIdx.x & 31, zg = threadIdx.x >> 5;
-    const int64_t i = (int64_t)((int)blockIdx.x - L.blk_start[e]) * 32 + c;
+    const int cols = en.n <= 512 ? 8 : 32, ngroups = 256 / cols;
+    const int c = threadIdx.x % cols, zg = threadIdx.x / cols;
+    const int64_t i = (int64_t)((int)blockIdx.x - L.blk_start[e]) * cols + c;
     float s = 0.f;
     if (i < en.n) {
         int z = zg;
-        for (; z + 24 < en.splits; z += 32) {
-            float v0 = __ldg(en.part + (size_t)z * en.n + i), v1 = __ldg(en.part + (size_t)(z + 8) * en.n + i);
-            float v2 = __ldg(en.part + (size_t)(z + 16) * en.n + i), v3 = __ldg(en.part + (size_t)(z + 24) * en.n + i);
+        for (; z + 3 * ngroups < en.splits; z += 4 * ngroups) {
+            float v0 = __ldg(en.part + (size_t)z * en.n + i), v1 = __ldg(en.part + (size_t)(z + ngroups) * en.n + i);
+            float v2 = __ldg(en.part + (size_t)(z + 2 * ngroups) * en.n + i), v3 = __ldg(en.part + (size_t)(z + 3 * ngroups) * en.n + i);
             s += (v0 + v1) + (v2 + v3);
         }
-        for (; z < en.splits; z += 8) s += __ldg(en.part + (size_t)z * en.n + i);
+        for (; z < en.splits; z += ngroups) s += __ldg(en.part + (size_t)z * en.n + i);
     }
-    sh[zg][c] = s;
+    sh[threadIdx.x] = s;
     __syncthreads();
     if (zg == 0 && i < en.n) {
         float tot = 0.f;
-#pragma unroll
-        for (int k = 0; k < 8; k++) tot += sh[k][c];
+        for (int k = 0; k < ngroups; k++) tot += sh[k * cols + c];
         en.dst[i] = tot;
     }
 }
@@ -1504,7 +1506,7 @@ int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list) {
     int blocks = 0;
     for (int e = 0; e < list.count; e++) {
         list.blk_start[e] = blocks;
-        blocks += (int)dc_cdiv(list.e[e].n, 32);
+        blocks += (int)dc_cdiv(list.e[e].n, list.e[e].n <= 512 ? 8 : 32);
     }
     list.blk_start[list.count] = blocks;
     DC_LAUNCH(ctx, reduce_batched_kernel, blocks, 256, 0, list);

@@ -123,6 +123,20 @@ int32_t ensure_wT(dincae_model* M) {
     return DINCAE_OK;
 }
 
+// bias column partials produced by the element-wise backward kernels: a slice of the same arena (TF32 mode only)
+float* colpart_alloc(dincae_model* M, int64_t n_elems4, int Cp, int* nblocks) {
+    *nblocks = 0;
+    if (!M->wK) return nullptr;
+    int nb = k2_colpart_blocks(M->ctx, n_elems4, Cp);
+    if (nb == 0) return nullptr;
+    size_t need = ((size_t)nb * Cp * sizeof(float) + 255) / 256 * 256;
+    if (M->wg_off + need > M->wg_scratch_bytes) return nullptr;
+    float* p = (float*)((char*)M->wg_scratch + M->wg_off);
+    M->wg_off += need;
+    *nblocks = nb;
+    return p;
+}
+
 // weight gradient with its own scratch slice; in TF32 mode the second-stage reductions are queued in M->red
 int32_t run_wgrad(dincae_model* M, WgradArgs& wa) {
     if (!M->wK) return k2_wgrad(M->ctx, wa, M->wg_scratch, M->wg_scratch_bytes);
@@ -145,9 +159,14 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
     for (int l = 0; l < L; l++) {
         const LayerInfo& d = M->dec[c][l];
         const float* gd = (l == 0) ? M->GD0 : M->GD[l];
+        float* colpart = nullptr;
+        int colblocks = 0;
         if (l > 0) {
-            // G[l] = up^T(GU[l-1]); GD[l] = G[l] * relu'(R[l])
-            if (nearest) DC_TRY(k2_upbwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, cb.R[l], slope, M->G[l], M->GD[l]));
+            // G[l] = up^T(GU[l-1]); GD[l] = G[l] * relu'(R[l])  (+ per-block column sums of GD[l] = first stage of the bias gradient)
+            if (nearest) {
+                colpart = colpart_alloc(M, (int64_t)B * M->Hl[l] * M->Wl[l] * (d.Cout_p / 4), d.Cout_p, &colblocks);
+                DC_TRY(k2_upbwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, cb.R[l], slope, M->G[l], M->GD[l], colpart));
+            }
             else DC_TRY(k2_up_bilinear_bwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, M->Hl[l], M->Wl[l], cb.R[l], slope, M->G[l], M->GD[l]));
         }
         ConvSrc s;
@@ -155,6 +174,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         WgradArgs wa{};
         wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
         wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
+        wa.colpart = colpart; wa.colpart_blocks = colblocks;
         wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         wa.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
@@ -178,11 +198,14 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
     const float* xg = M->G[L];
     for (int l = L - 1; l >= 0; l--) {
         const LayerInfo& e = M->enc[c][l];
-        DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l]));
+        int ecolblocks = 0;
+        float* ecolpart = colpart_alloc(M, (int64_t)B * M->Hl[l] * M->Wl[l] * (e.Cout_p / 4), e.Cout_p, &ecolblocks);
+        DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l], ecolpart));
         WgradArgs wa{};
         wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
         wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
+        wa.colpart = ecolpart; wa.colpart_blocks = ecolblocks;
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         wa.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
         wa.tf32 = M->wK != nullptr;
@@ -576,6 +599,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             size_t ta = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
             size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
             wg_sum += ((ta + 255) / 256 * 256) + ((tb + 255) / 256 * 256);
+            wg_sum += 2 * (((size_t)8 * ctx->num_sms * 512 * sizeof(float) + 255) / 256 * 256);      // bias column partials of both layers
         }
     if (cfg->precision == DINCAE_PREC_TF32 && wg_sum > wgb) wgb = wg_sum;    // TF32 mode: one slice per layer (second stages are batched)
     M->wg_scratch_bytes = wgb;
