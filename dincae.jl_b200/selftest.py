@@ -48,4 +48,21 @@ def smoke(verbose=True):
         print("smoke: forward rel err %.2e, loss %.6f vs oracle %.6f (rel %.2e), max |dw| after Adam %.2e, launches %d"
               % (err_f, loss, loss_o, err_l, err_w, ctx.launches))
     assert err_f < 1e-3 and err_l < 1e-3 and err_w < 2e-4, "train step differs from the oracle"
-    return dict(forward_rel_err=float(err_f), loss_rel_err=float(err_l), max_dw=float(err_w), launches=ctx.launches)
+    # --- the tensor-core path (tcgen05 + TMA, TF32 operands): same check with 32/64 filters
+    cfg2 = api.ModelConfig(W=W, H=H, ninput=xin.shape[2], enc_nfilter_internal=(32, 64), loss_weights_refine=(0.3, 0.7),
+                           regularization_L2_beta=1e-3, max_batch=B, precision="tf32")
+    ocfg2 = OM.ModelConfig(W=W, H=H, ninput=xin.shape[2], nfilter=[32, 64], loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3)
+    m2 = api.Model(ctx, cfg2, seed=3)
+    flat2 = m2.get_params()
+    y2 = m2(xin)
+    y2_o = OM.forward(ocfg2, flat2, xin)
+    err_tc = max(np.abs(y2[:, :, c] - y2_o[:, :, c]).max() / np.abs(y2_o[:, :, c]).max() for c in range(2))
+    loss2 = m2.train_step(xin, xtrue, 1e-3)
+    loss2_o, _ = OM.loss_and_grad(ocfg2, flat2, xin, xtrue)
+    err_l2 = abs(loss2 - loss2_o) / abs(loss2_o)
+    if verbose:
+        print("smoke: tcgen05/TMA path forward err %.2e of range, loss %.6f vs oracle %.6f (rel %.2e), launches %d"
+              % (err_tc, loss2, loss2_o, err_l2, ctx.launches))
+    assert err_tc < 2e-3 and err_l2 < 1e-3, "tensor-core train step differs from the oracle"
+    return dict(forward_rel_err=float(err_f), loss_rel_err=float(err_l), max_dw=float(err_w), tc_forward_err=float(err_tc),
+                tc_loss_rel_err=float(err_l2), launches=ctx.launches)
