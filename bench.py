@@ -152,7 +152,7 @@ def run_reference(args, rank, world):
                              "sample": "%d train steps of batch %d (oracle: numpy assembly + torch-CPU fwd/bwd + numpy Adam), cube of %d steps" % (args.steps, B, wl["N"])},
             "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "final_loss": float(loss)}
-    print(json.dumps(line))
+    emit(line)
 
 
 def workload_config(wl, world, where):
@@ -394,10 +394,18 @@ def main():
                 "kernels": [{kk: (round(v, 6) if isinstance(v, float) else v) for kk, v in k.items()} for k in (kern_table or [])[:12]]}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The JSON line is the only thing written to the real stdout (libraries such as NCCL print banners on fd 1)."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     main()
