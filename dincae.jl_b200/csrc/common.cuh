@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string>
 #include <vector>
 #include "../../include/dincae_b200.h"
@@ -89,6 +90,7 @@ int32_t dc_scratch(dincae_ctx* ctx, size_t bytes, void** out);       // grow-onl
 int32_t dc_pinned(dincae_ctx* ctx, size_t bytes, void** out);        // grow-only pinned host staging
 
 static inline int64_t dc_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int dc_env_int(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 static inline int dc_round_up(int a, int b) { return (a + b - 1) / b * b; }
 
 // RAII-less helper: device buffer that is either the caller's (loc == DEVICE) or a staged copy of host memory

@@ -442,43 +442,91 @@ constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; 
 // activation halo per tile and K chunk crosses L2 -> SM.
 namespace {
 
-constexpr int PS_MAX_A = 4, PS_MAX_B = 8;
+constexpr int PS_MAX_A = 4, PS_MAX_B = 8, PS_MAX_COUT = 512;
 
 struct PersistArgs {
     int num_tiles, ntiles_n;
     int a_stages, b_stages;
     int b_resident;
+    int o_stages;              // 16 KB output staging slabs for the TMA-store epilogue (1 or 2)
+    long long* trace;          // tuning aid (dincae_debug_conv): clock64 stamps of CTA 0, 3 roles x 64 slots; nullptr in production
 };
+
+#define PS_TRACE(role, idx) do { if (q.trace && blockIdx.x == 0 && (idx) < 64) q.trace[(role) * 64 + (idx)] = clock64(); } while (0)
+
+// TMA store of one (32 channel x 8 x 16 pixel) slab, shared -> global; pixels outside the image are clipped by the unit
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
+}
+// One 32-column slab of one accumulator row: bias, leaky ReLU as max(v, v * slope) (0 <= slope <= 1), optional addend, then
+// eight 16 B shared-memory stores at the 128B-swizzled chunk positions of this row.
+template <bool ADD>
+__device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* bs, float slope, const float* addp, uint32_t st_row, int sw) {
+    float4 av[ADD ? 8 : 1];
+    if (ADD) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) av[k] = addp ? __ldg(reinterpret_cast<const float4*>(addp + 4 * k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float4 o[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {                // all bias reads first: the shared loads overlap instead of serialising with the stores
+        const float4 bv = *reinterpret_cast<const float4*>(bs + 4 * k);
+        o[k].x = __uint_as_float(r[4 * k + 0]) + bv.x; o[k].y = __uint_as_float(r[4 * k + 1]) + bv.y;
+        o[k].z = __uint_as_float(r[4 * k + 2]) + bv.z; o[k].w = __uint_as_float(r[4 * k + 3]) + bv.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        o[k].x = fmaxf(o[k].x, o[k].x * slope); o[k].y = fmaxf(o[k].y, o[k].y * slope);
+        o[k].z = fmaxf(o[k].z, o[k].z * slope); o[k].w = fmaxf(o[k].w, o[k].w * slope);
+        if (ADD) { o[k].x += av[k].x; o[k].y += av[k].y; o[k].z += av[k].z; o[k].w += av[k].w; }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; k++) st_shared_v4(st_row + (uint32_t)((k ^ sw) << 4), o[k]);
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }      // the 4 epilogue warps only
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 template <int BN>
-__global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p, PersistArgs q) {
+__global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                                                       TmaConvArgs p, PersistArgs q) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int B_BYTES = BN * 128;
     constexpr int TCOLS = 2 * BN < 32 ? 32 : 2 * BN;
     __shared__ uint64_t bar_fullA[PS_MAX_A], bar_emptyA[PS_MAX_A], bar_fullB[PS_MAX_B], bar_emptyB[PS_MAX_B];
     __shared__ uint64_t bar_bres, bar_tfull[2], bar_tempty[2];
     __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float bias_s[PS_MAX_COUT];      // the layer's bias (zeros when absent): broadcast reads in the epilogue
 
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* smemB = smem + q.a_stages * HL_A_STRIDE;
+    uint8_t* smemO = smemB + (q.b_resident ? (p.Cin_p / TM_KC) * 9 : q.b_stages) * B_BYTES;     // 1024-aligned: B_BYTES is a multiple of 4 KB
     const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int patches = p.ptx * p.pty;
     const int nkc = p.Cin_p / TM_KC;
+    if (t == 64) PS_TRACE(2, 62);
 
     if (t == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+        if (p.dst) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmO)) : "memory");
         for (int s = 0; s < PS_MAX_A; s++) { mbar_init(&bar_fullA[s], 1); mbar_init(&bar_emptyA[s], 1); }
         for (int s = 0; s < PS_MAX_B; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
         mbar_init(&bar_bres, 1);
         for (int s = 0; s < 2; s++) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = t; i < p.Cout_p; i += 192) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -486,6 +534,7 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    if (t == 64) PS_TRACE(2, 63);
     const uint32_t tmem_d = tmem_base_s;
     constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
 
@@ -499,6 +548,7 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                         tma_load_2d(smemB + (size_t)(kc * 9 + tap) * B_BYTES, &tmB, &bar_bres, tap * p.Cin_p + kc * TM_KC, 0);
             }
             int ia = 0, ib = 0;
+            PS_TRACE(0, 0);
             for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x) {
                 const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
                 const int b = pi / patches, pr = pi - b * patches;
@@ -506,6 +556,7 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                 for (int kc = 0; kc < nkc; kc++, ia++) {
                     const int sa = ia % q.a_stages, ua = ia / q.a_stages;
                     if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+                    PS_TRACE(0, 1 + ia);
                     mbar_expect_tx(&bar_fullA[sa], (uint32_t)HL_A_BYTES);
                     tma_load_4d(smem + (size_t)sa * HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x0 - 1, y0 - 1, b);
                     if (!q.b_resident) {
@@ -522,7 +573,9 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
     } else if (warp == 1) {
         if (lane == 0) {
             // ===== MMA issuer =====
+            PS_TRACE(1, 0);
             if (q.b_resident) mbar_wait(&bar_bres, 0);
+            PS_TRACE(1, 1);
             int ia = 0, ib = 0, it = 0;
             for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
                 const int acc = it & 1, ut = it >> 1;
@@ -532,6 +585,7 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                 for (int kc = 0; kc < nkc; kc++, ia++) {
                     const int sa = ia % q.a_stages, ua = ia / q.a_stages;
                     mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
+                    PS_TRACE(1, 2 + 2 * ia);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     // descriptor bases once per chunk; the 36 (tap, k) offsets below are compile-time constants
                     const uint64_t da0 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * HL_A_STRIDE), 0);
@@ -564,76 +618,124 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                         }
                     }
                     umma_commit(&bar_emptyA[sa]);
+                    PS_TRACE(1, 3 + 2 * ia);
                 }
                 umma_commit(&bar_tfull[acc]);
             }
         }
     } else {
         // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
+        // NHWC output: each 32-channel slab of the tile is staged in shared memory in the 128B-swizzled box layout
+        // (conflict-free 16 B writes, one 128 B row per thread) and leaves with ONE TMA store, which also clips the
+        // pixels of edge patches that fall outside the image.  Planar output (<= 2*O channels) is written directly.
         const int row = (warp & 3) * 32 + lane;              // tile row = TMEM lane
         const int h = row / HL_PW, w = row - h * HL_PW;
-        int it = 0;
+        const bool elect = (t == 64);
+        const float slope = p.slope;
+        const int act_mode = p.act != ACT_RELU ? 0 : ((slope >= 0.f && slope < 1.f) ? 1 : 2);
+        const float slope_eff = act_mode == 0 ? 1.f : slope;     // max(v, v * 1) = v: no activation
+        const uint32_t smemO_u = smem_u32(smemO);
+        int it = 0, obuf = 0;
         for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
             const int acc = it & 1, ut = it >> 1;
             const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
             const int b = pi / patches, pr = pi - b * patches;
-            const int y = (pr / p.ptx) * HL_PH + h, x = (pr - (pr / p.ptx) * p.ptx) * HL_PW + w;
+            const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+            const int y = y0 + h, x = x0 + w;
             const bool pv = y < p.H && x < p.W;
             const size_t m = ((size_t)b * p.H + y) * p.W + x;
+            if (t == 64) PS_TRACE(2, 2 * it);
             mbar_wait(&bar_tfull[acc], (uint32_t)(ut & 1));
+            if (t == 64) PS_TRACE(2, 1 + 2 * it);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t lane_addr = tmem_d + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(acc * BN);
-#pragma unroll 1
-            for (int cb = 0; cb < BN; cb += 16) {
+            if (p.planar_out) {
                 uint32_t r[16];
-                tmem_ld16(lane_addr + (uint32_t)cb, r);
+                tmem_ld16(lane_addr, r);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                const int n = n0 + cb;
-                if (pv && p.planar_out && n < p.planar_C) {
+                if (pv && n0 == 0) {
 #pragma unroll
                     for (int k = 0; k < 16; k++) {
-                        const int co = n + k;
-                        if (co < p.planar_C) {
-                            float v = __uint_as_float(r[k]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+                        if (k < p.planar_C) {
+                            float v = __uint_as_float(r[k]) + bias_s[k];
                             v = act_apply(v, p.act, p.slope);
-                            const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
+                            const size_t po = (((size_t)b * p.planar_C + k) * p.H + y) * p.W + x;
                             p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
                         }
                     }
                 }
-                if (pv && p.dst && n < p.Cout_p) {
-                    const size_t off = m * p.Cout_p + n;
-#pragma unroll
-                    for (int k = 0; k < 4; k++) {
-                        float4 o;
-                        o.x = __uint_as_float(r[4 * k + 0]); o.y = __uint_as_float(r[4 * k + 1]);
-                        o.z = __uint_as_float(r[4 * k + 2]); o.w = __uint_as_float(r[4 * k + 3]);
-                        if (p.bias) {
-                            float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * k));
-                            o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
-                        }
-                        o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
-                        o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
-                        if (p.addend) {
-                            float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * k));
-                            o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
-                        }
-                        *reinterpret_cast<float4*>(p.dst + off + 4 * k) = o;
-                    }
-                }
-                if (!p.dst && n + 16 >= p.planar_C) break;
             }
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-            mbar_arrive(&bar_tempty[acc]);                   // 128 arrivals free the accumulator for tile it+2
+            if (p.dst) {
+                const float* addp = (p.addend && pv) ? p.addend + m * p.Cout_p + n0 : nullptr;
+                uint32_t r[32];
+                tmem_ld16(lane_addr, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+#pragma unroll 1
+                for (int sl = 0; sl < BN / 32; sl++) {
+                    const bool tr = (t == 64 && it == 2 && sl == 0);
+                    if (tr) PS_TRACE(2, 40);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (tr) PS_TRACE(2, 41);
+                    if (sl == BN / 32 - 1) {                 // accumulator drained: the MMA warp may start tile it+2
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        mbar_arrive(&bar_tempty[acc]);
+                    }
+                    if (elect) { if (q.o_stages == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
+                    if (tr) PS_TRACE(2, 42);
+                    epi_bar_sync();                          // the store that last used this slab has been read out
+                    if (tr) PS_TRACE(2, 43);
+                    const int nl = sl * 32;                  // column of this slab inside the tile
+                    const uint32_t st_row = smemO_u + (uint32_t)(obuf * 16384 + row * 128);
+                    const float* bs = &bias_s[n0 + nl];
+                    if (act_mode != 2) {
+                        if (p.addend) epi_slab<true>(r, bs, slope_eff, addp ? addp + nl : nullptr, st_row, row & 7);
+                        else epi_slab<false>(r, bs, slope_eff, nullptr, st_row, row & 7);
+                    } else {                                 // slopes outside [0, 1): the select form
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            float4 o;
+                            o.x = act_apply(__uint_as_float(r[4 * k + 0]) + bs[4 * k + 0], ACT_RELU, slope);
+                            o.y = act_apply(__uint_as_float(r[4 * k + 1]) + bs[4 * k + 1], ACT_RELU, slope);
+                            o.z = act_apply(__uint_as_float(r[4 * k + 2]) + bs[4 * k + 2], ACT_RELU, slope);
+                            o.w = act_apply(__uint_as_float(r[4 * k + 3]) + bs[4 * k + 3], ACT_RELU, slope);
+                            if (addp) {
+                                const float4 av = __ldg(reinterpret_cast<const float4*>(addp + nl + 4 * k));
+                                o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
+                            }
+                            st_shared_v4(st_row + (uint32_t)((k ^ (row & 7)) << 4), o);
+                        }
+                    }
+                    if (tr) PS_TRACE(2, 44);
+                    if (sl + 1 < BN / 32) {                  // next slab's TMEM read overlaps the fence, barrier and store below
+                        tmem_ld16(lane_addr + (uint32_t)(nl + 32), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                        tmem_ld16(lane_addr + (uint32_t)(nl + 48), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+                    }
+                    if (tr) PS_TRACE(2, 45);
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    if (tr) PS_TRACE(2, 46);
+                    epi_bar_sync();
+                    if (tr) PS_TRACE(2, 47);
+                    if (elect) { tma_store_4d(&tmO, smemO + (size_t)obuf * 16384, n0 + nl, x0, y0, b); tma_store_commit(); }
+                    if (tr) PS_TRACE(2, 48);
+                    obuf = (obuf + 1 == q.o_stages) ? 0 : obuf + 1;
+                }
+            } else {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                mbar_arrive(&bar_tempty[acc]);               // 128 arrivals free the accumulator for tile it+2
+            }
         }
+        if (elect) tma_store_wait_read<0>();                 // shared memory must outlive the last store's read
     }
     __syncwarp();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (t == 0) PS_TRACE(0, 63);
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
 }
 
 }  // namespace
+
+static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_trace only
 
 #define PERSIST_LAUNCH(BN_)                                                                                                \
     do {                                                                                                                   \
@@ -645,7 +747,7 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
         }                                                                                                                  \
         DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
-        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, 192, smem, tmA, tmB, p, q);                                          \
+        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, 192, smem, tmA, tmB, tmO, p, q);                                         \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
     } while (0)
@@ -658,7 +760,10 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
-    const int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
+    int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
+    static const int tune_bn = dc_env_int("DINCAE_TUNE_BN", 0), tune_bs = dc_env_int("DINCAE_TUNE_BSTAGES", 0),
+                     tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_persm = dc_env_int("DINCAE_TUNE_PERSM", 0);
+    if (tune_bn > 0 && tune_bn < bn) bn = tune_bn;
     const int nkc = a.in.C / TM_KC;
     PersistArgs q;
     q.ntiles_n = a.Cout_p / bn;
@@ -666,16 +771,28 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     const int bbytes = bn * 128;
     const int resident_bytes = nkc * 9 * bbytes;
     q.b_resident = (q.ntiles_n == 1 && resident_bytes <= 112 * 1024) ? 1 : 0;
-    q.a_stages = 2;
-    q.b_stages = q.b_resident ? 0 : (bn == 256 ? 4 : (bn == 128 ? 4 : 6));
+    q.trace = g_persist_trace;
+    q.a_stages = tune_as > 0 ? tune_as : 2;
+    q.b_stages = q.b_resident ? 0 : (tune_bs > 0 ? tune_bs : (bn == 256 ? 4 : (bn == 128 ? 4 : 6)));
     int smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 1024;
+    static const int tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
+    q.o_stages = 0;
+    if (a.dst) {                                      // output staging slabs of the TMA-store epilogue: two unless that costs the 2nd CTA per SM
+        q.o_stages = (2 * (smem + 16384 + 4096) <= 227 * 1024 && 2 * (smem + 32768 + 4096) > 227 * 1024) ? 1 : 2;
+        if (smem + q.o_stages * 16384 + 4096 > 227 * 1024) q.o_stages = 1;
+        if (tune_os > 0) q.o_stages = tune_os;
+        smem += q.o_stages * 16384;
+    }
     int per_sm = 1;                                   // persistent: one CTA per SM (two when both smem and TMEM allow)
-    if (2 * (smem + 2048) <= 227 * 1024 && 4 * bn <= 512) per_sm = 2;
+    if (2 * (smem + 4096) <= 227 * 1024 && 4 * bn <= 512) per_sm = 2;
+    if (tune_persm > 0) per_sm = tune_persm;
     int ctas = ctx->num_sms * per_sm;
     if (ctas > q.num_tiles) ctas = q.num_tiles;
     dim3 grid((unsigned)ctas);
-    alignas(64) CUtensorMap tmA, tmB;
+    alignas(64) CUtensorMap tmA, tmB, tmO;
     DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
+    if (a.dst) DC_TRY(make_tmap_act(&tmO, a.dst, a.Cout_p, a.W, a.H, a.B, HL_PW, HL_PH));
+    else tmO = tmA;
     if (bn == 256) PERSIST_LAUNCH(256);
     if (bn == 128) PERSIST_LAUNCH(128);
     if (bn == 64) PERSIST_LAUNCH(64);
@@ -742,7 +859,7 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     // DINCAE_CONV_KERNEL: 0 = one activation box per tap; 1 = halo tile with shifted descriptors; 3 = persistent warp-specialised halo kernel (default)
     static int halo_mode = -1;
     if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
-    if (halo_mode == 3) return k2_conv_persist(ctx, a);
+    if (halo_mode == 3 && (a.planar_out == nullptr || a.planar_C <= 16) && a.Cout_p <= 512) return k2_conv_persist(ctx, a);
     if (halo_mode > 0) return k2_conv_halo(ctx, a, 1);
     TmaConvArgs p;
     p.B = a.B; p.H = a.H; p.W = a.W;
@@ -1500,6 +1617,8 @@ extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const f
     if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
     TMA_LAUNCH(32, 5);
 }
+
+extern "C" int32_t dincae_debug_conv_trace(long long* d_trace) { g_persist_trace = d_trace; return DINCAE_OK; }
 
 int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list) {
     if (list.count == 0) return DINCAE_OK;
