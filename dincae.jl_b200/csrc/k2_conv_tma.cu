@@ -55,6 +55,18 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
 }
+// true in exactly one lane of a converged warp (the same lane every time)
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t"
+        ".reg .b32 rx;\n\t"
+        ".reg .pred px;\n\t"
+        "elect.sync rx|px, %1;\n\t"
+        "@px mov.s32 %0, 1;\n\t"
+        "}" : "+r"(pred) : "r"(0xFFFFFFFFu));
+    return pred != 0;
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -435,20 +447,24 @@ constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; 
 
 // -------------------------------------------------------------------------------------------------
 // Persistent, warp-specialised form of the halo kernel: one CTA per SM loops over output tiles.
-//   warp 0 (one lane): TMA producer      warp 1 (one lane): tcgen05.mma issuer      warps 2-5: epilogue
-// The FP32 accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile i (tcgen05.ld, bias,
-// activation, stores) overlaps the TMA + MMA main loop of tile i+1.  When the whole K-major weight matrix of the
+//   warp 0 (one lane): TMA producer      warp 1 (one lane): tcgen05.mma issuer
+//   warps 2 / 3 (one lane each): TMA-store issuer of epilogue group 0 / 1
+//   warps 4-7 / 8-11: epilogue group 0 / 1.  With two groups (one CTA per SM) group g drains TMEM accumulator g, i.e.
+//   every other tile of this CTA; narrow layers whose shared-memory plan allows two CTAs per SM run one group (256 threads).
+// The FP32 accumulator is double-buffered in TMEM (2 x BN columns), so the epilogues of tiles i and i+1 (tcgen05.ld, bias,
+// activation, swizzled shared staging, TMA store) overlap each other and the TMA + MMA main loop of tile i+2.  When the whole K-major weight matrix of the
 // layer fits in shared memory (narrow layers) it is loaded once per CTA and stays resident; then only one 23 KB
 // activation halo per tile and K chunk crosses L2 -> SM.
 namespace {
 
-constexpr int PS_MAX_A = 4, PS_MAX_B = 8, PS_MAX_COUT = 512;
+constexpr int PS_MAX_A = 4, PS_MAX_B = 8, PS_MAX_COUT = 512, PS_MAX_O = 2, PS_THREADS = 384;
 
 struct PersistArgs {
     int num_tiles, ntiles_n;
     int a_stages, b_stages;
     int b_resident;
-    int o_stages;              // 16 KB output staging slabs for the TMA-store epilogue (1 or 2)
+    int o_stages;              // 16 KB output staging slabs per epilogue group (1 or 2)
+    int groups;                // epilogue groups (1: 256 threads, 2: 384 threads)
     long long* trace;          // tuning aid (dincae_debug_conv): clock64 stamps of CTA 0, 3 roles x 64 slots; nullptr in production
 };
 
@@ -490,20 +506,20 @@ __device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* b
 #pragma unroll
     for (int k = 0; k < 8; k++) st_shared_v4(st_row + (uint32_t)((k ^ sw) << 4), o[k]);
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }      // the 4 epilogue warps only
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
 template <int BN>
-__global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+__global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
                                                        TmaConvArgs p, PersistArgs q) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int B_BYTES = BN * 128;
     constexpr int TCOLS = 2 * BN < 32 ? 32 : 2 * BN;
     __shared__ uint64_t bar_fullA[PS_MAX_A], bar_emptyA[PS_MAX_A], bar_fullB[PS_MAX_B], bar_emptyB[PS_MAX_B];
     __shared__ uint64_t bar_bres, bar_tfull[2], bar_tempty[2];
+    __shared__ uint64_t bar_ofull[2][PS_MAX_O], bar_oempty[2][PS_MAX_O];     // epilogue group -> its store issuer and back
     __shared__ uint32_t tmem_base_s;
     __shared__ __align__(16) float bias_s[PS_MAX_COUT];      // the layer's bias (zeros when absent): broadcast reads in the epilogue
 
@@ -524,9 +540,11 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
         for (int s = 0; s < PS_MAX_B; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
         mbar_init(&bar_bres, 1);
         for (int s = 0; s < 2; s++) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 128); }
+        for (int g = 0; g < 2; g++)
+            for (int s = 0; s < PS_MAX_O; s++) { mbar_init(&bar_ofull[g][s], 128); mbar_init(&bar_oempty[g][s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = t; i < p.Cout_p; i += 192) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
+    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -571,26 +589,27 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ===== MMA issuer =====
-            PS_TRACE(1, 0);
-            if (q.b_resident) mbar_wait(&bar_bres, 0);
-            PS_TRACE(1, 1);
-            int ia = 0, ib = 0, it = 0;
-            for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
-                const int acc = it & 1, ut = it >> 1;
-                if (ut > 0) mbar_wait(&bar_tempty[acc], (uint32_t)((ut - 1) & 1));      // the epilogue has drained this accumulator
+        // ===== MMA issuer: the whole warp walks the loop (warp-uniform control flow), one elected lane issues =====
+        // (inside a divergent `lane == 0` branch the compiler wraps every tcgen05.mma in its own elect/branch loop, ~50 cycles each)
+        if (lane == 0) PS_TRACE(1, 0);
+        if (q.b_resident) mbar_wait(&bar_bres, 0);
+        if (lane == 0) PS_TRACE(1, 1);
+        int ia = 0, ib = 0, it = 0;
+        for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
+            const int acc = it & 1, ut = it >> 1;
+            if (ut > 0) mbar_wait(&bar_tempty[acc], (uint32_t)((ut - 1) & 1));      // the epilogue has drained this accumulator
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t dcol = tmem_d + (uint32_t)(acc * BN);
+            for (int kc = 0; kc < nkc; kc++, ia++) {
+                const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
+                if (lane == 0) PS_TRACE(1, 2 + 2 * ia);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t dcol = tmem_d + (uint32_t)(acc * BN);
-                for (int kc = 0; kc < nkc; kc++, ia++) {
-                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
-                    mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
-                    PS_TRACE(1, 2 + 2 * ia);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    // descriptor bases once per chunk; the 36 (tap, k) offsets below are compile-time constants
-                    const uint64_t da0 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * HL_A_STRIDE), 0);
-                    if (q.b_resident) {
-                        const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(kc * 9 * B_BYTES));
+                // descriptor bases once per chunk; the 36 (tap, k) offsets below are compile-time constants
+                const uint64_t da0 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * HL_A_STRIDE), 0);
+                if (q.b_resident) {
+                    const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(kc * 9 * B_BYTES));
+                    if (elect_one_sync()) {
 #pragma unroll
                         for (int tap = 0; tap < 9; tap++) {
 #pragma unroll
@@ -601,42 +620,50 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                                 else umma_tf32_acc(dcol, da, db, IDESC);
                             }
                         }
-                    } else {
+                        umma_commit(&bar_emptyA[sa]);
+                        if (kc == nkc - 1) umma_commit(&bar_tfull[acc]);
+                    }
+                } else {
+#pragma unroll 1
+                    for (int tap = 0; tap < 9; tap++, ib++) {
+                        const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                        mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
+                        const uint64_t dat = da0 + (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                        if (elect_one_sync()) {
+                            if (tap == 0) umma_tf32(dcol, dat, db0, IDESC, kc != 0 ? 1u : 0u);
+                            else umma_tf32_acc(dcol, dat, db0, IDESC);
 #pragma unroll
-                        for (int tap = 0; tap < 9; tap++, ib++) {
-                            const int sb = ib % q.b_stages, ub = ib / q.b_stages;
-                            mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
-                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                            const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
-#pragma unroll
-                            for (int k = 0; k < TM_KC / 8; k++) {
-                                const uint64_t da = da0 + (uint64_t)((((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4) + 2 * k);
-                                if (tap == 0 && k == 0) umma_tf32(dcol, da, db0, IDESC, kc != 0 ? 1u : 0u);
-                                else umma_tf32_acc(dcol, da, db0 + (uint64_t)(2 * k), IDESC);
-                            }
+                            for (int k = 1; k < TM_KC / 8; k++) umma_tf32_acc(dcol, dat + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
                             umma_commit(&bar_emptyB[sb]);
+                            if (tap == 8) {
+                                umma_commit(&bar_emptyA[sa]);
+                                if (kc == nkc - 1) umma_commit(&bar_tfull[acc]);
+                            }
                         }
                     }
-                    umma_commit(&bar_emptyA[sa]);
-                    PS_TRACE(1, 3 + 2 * ia);
                 }
-                umma_commit(&bar_tfull[acc]);
+                __syncwarp();
+                if (lane == 0) PS_TRACE(1, 3 + 2 * ia);
             }
         }
-    } else {
-        // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
+    } else if (warp >= 4) {
+        // ===== epilogue warps 4..11: group g; TMEM lane quarter = warp % 4 =====
         // NHWC output: each 32-channel slab of the tile is staged in shared memory in the 128B-swizzled box layout
-        // (conflict-free 16 B writes, one 128 B row per thread) and leaves with ONE TMA store, which also clips the
-        // pixels of edge patches that fall outside the image.  Planar output (<= 2*O channels) is written directly.
+        // (conflict-free 16 B writes, one 128 B row per thread) and handed to the group's store issuer, whose single TMA
+        // store also clips the pixels of edge patches that fall outside the image.  Planar output (<= 16 channels) is
+        // written directly.
+        const int g = (warp - 4) >> 2;
         const int row = (warp & 3) * 32 + lane;              // tile row = TMEM lane
         const int h = row / HL_PW, w = row - h * HL_PW;
-        const bool elect = (t == 64);
         const float slope = p.slope;
         const int act_mode = p.act != ACT_RELU ? 0 : ((slope >= 0.f && slope < 1.f) ? 1 : 2);
         const float slope_eff = act_mode == 0 ? 1.f : slope;     // max(v, v * 1) = v: no activation
-        const uint32_t smemO_u = smem_u32(smemO);
-        int it = 0, obuf = 0;
-        for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x, it++) {
+        const uint32_t smemO_u = smem_u32(smemO) + (uint32_t)(g * q.o_stages * 16384);
+        const bool tr0 = (t == 128);
+        int obuf = 0, ouse = 0;
+        for (int tile = blockIdx.x + g * gridDim.x, it = g; tile < q.num_tiles; tile += q.groups * gridDim.x, it += q.groups) {
             const int acc = it & 1, ut = it >> 1;
             const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
             const int b = pi / patches, pr = pi - b * patches;
@@ -644,9 +671,9 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
             const int y = y0 + h, x = x0 + w;
             const bool pv = y < p.H && x < p.W;
             const size_t m = ((size_t)b * p.H + y) * p.W + x;
-            if (t == 64) PS_TRACE(2, 2 * it);
+            if (tr0) PS_TRACE(2, 2 * (it / q.groups));
             mbar_wait(&bar_tfull[acc], (uint32_t)(ut & 1));
-            if (t == 64) PS_TRACE(2, 1 + 2 * it);
+            if (tr0) PS_TRACE(2, 1 + 2 * (it / q.groups));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t lane_addr = tmem_d + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(acc * BN);
             if (p.planar_out) {
@@ -672,18 +699,12 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                 tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
 #pragma unroll 1
                 for (int sl = 0; sl < BN / 32; sl++) {
-                    const bool tr = (t == 64 && it == 2 && sl == 0);
-                    if (tr) PS_TRACE(2, 40);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    if (tr) PS_TRACE(2, 41);
                     if (sl == BN / 32 - 1) {                 // accumulator drained: the MMA warp may start tile it+2
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                         mbar_arrive(&bar_tempty[acc]);
                     }
-                    if (elect) { if (q.o_stages == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
-                    if (tr) PS_TRACE(2, 42);
-                    epi_bar_sync();                          // the store that last used this slab has been read out
-                    if (tr) PS_TRACE(2, 43);
+                    if (ouse > 0) mbar_wait(&bar_oempty[g][obuf], (uint32_t)((ouse - 1) & 1));   // the store that last used this slab has been read out
                     const int nl = sl * 32;                  // column of this slab inside the tile
                     const uint32_t st_row = smemO_u + (uint32_t)(obuf * 16384 + row * 128);
                     const float* bs = &bias_s[n0 + nl];
@@ -705,26 +726,36 @@ __global__ void __launch_bounds__(192) conv3x3_persist(const __grid_constant__ C
                             st_shared_v4(st_row + (uint32_t)((k ^ (row & 7)) << 4), o);
                         }
                     }
-                    if (tr) PS_TRACE(2, 44);
-                    if (sl + 1 < BN / 32) {                  // next slab's TMEM read overlaps the fence, barrier and store below
+                    if (sl + 1 < BN / 32) {                  // next slab's TMEM read overlaps the hand-off below
                         tmem_ld16(lane_addr + (uint32_t)(nl + 32), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
                         tmem_ld16(lane_addr + (uint32_t)(nl + 48), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
                     }
-                    if (tr) PS_TRACE(2, 45);
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    if (tr) PS_TRACE(2, 46);
-                    epi_bar_sync();
-                    if (tr) PS_TRACE(2, 47);
-                    if (elect) { tma_store_4d(&tmO, smemO + (size_t)obuf * 16384, n0 + nl, x0, y0, b); tma_store_commit(); }
-                    if (tr) PS_TRACE(2, 48);
-                    obuf = (obuf + 1 == q.o_stages) ? 0 : obuf + 1;
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the TMA store
+                    mbar_arrive(&bar_ofull[g][obuf]);
+                    if (++obuf == q.o_stages) { obuf = 0; ouse++; }
                 }
             } else {
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                 mbar_arrive(&bar_tempty[acc]);               // 128 arrivals free the accumulator for tile it+2
             }
         }
-        if (elect) tma_store_wait_read<0>();                 // shared memory must outlive the last store's read
+    } else if (lane == 0 && p.dst && warp - 2 < q.groups) {
+        // ===== store issuer of group g: one TMA store per staged slab, then hand the slab back once it has been read =====
+        const int g = warp - 2;
+        int obuf = 0, ouse = 0;
+        for (int tile = blockIdx.x + g * gridDim.x; tile < q.num_tiles; tile += q.groups * gridDim.x) {
+            const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
+            const int b = pi / patches, pr = pi - b * patches;
+            const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+            for (int sl = 0; sl < BN / 32; sl++) {
+                mbar_wait(&bar_ofull[g][obuf], (uint32_t)(ouse & 1));
+                tma_store_4d(&tmO, smemO + (size_t)(g * q.o_stages + obuf) * 16384, n0 + sl * 32, x0, y0, b);
+                tma_store_commit();
+                tma_store_wait_read<0>();
+                mbar_arrive(&bar_oempty[g][obuf]);
+                if (++obuf == q.o_stages) { obuf = 0; ouse++; }
+            }
+        }
     }
     __syncwarp();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -747,7 +778,7 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
         }                                                                                                                  \
         DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
-        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, 192, smem, tmA, tmB, tmO, p, q);                                         \
+        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, q.groups == 2 ? PS_THREADS : 256, smem, tmA, tmB, tmO, p, q);                                         \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
     } while (0)
@@ -762,31 +793,56 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
     int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
     static const int tune_bn = dc_env_int("DINCAE_TUNE_BN", 0), tune_bs = dc_env_int("DINCAE_TUNE_BSTAGES", 0),
-                     tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_persm = dc_env_int("DINCAE_TUNE_PERSM", 0);
+                     tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
+    const int m_tiles = p.ptx * p.pty * a.B;
+    while (bn > 64 && m_tiles * (a.Cout_p / bn) < ctx->num_sms) bn /= 2;     // few pixel tiles (deep levels): split N so every SM has work
     if (tune_bn > 0 && tune_bn < bn) bn = tune_bn;
     const int nkc = a.in.C / TM_KC;
     PersistArgs q;
     q.ntiles_n = a.Cout_p / bn;
-    q.num_tiles = p.ptx * p.pty * a.B * q.ntiles_n;
+    q.num_tiles = m_tiles * q.ntiles_n;
+    q.trace = g_persist_trace;
     const int bbytes = bn * 128;
     const int resident_bytes = nkc * 9 * bbytes;
-    q.b_resident = (q.ntiles_n == 1 && resident_bytes <= 112 * 1024) ? 1 : 0;
-    q.trace = g_persist_trace;
-    q.a_stages = tune_as > 0 ? tune_as : 2;
-    q.b_stages = q.b_resident ? 0 : (tune_bs > 0 ? tune_bs : (bn == 256 ? 4 : (bn == 128 ? 4 : 6)));
-    int smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 1024;
-    static const int tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
-    q.o_stages = 0;
-    if (a.dst) {                                      // output staging slabs of the TMA-store epilogue: two unless that costs the 2nd CTA per SM
-        q.o_stages = (2 * (smem + 16384 + 4096) <= 227 * 1024 && 2 * (smem + 32768 + 4096) > 227 * 1024) ? 1 : 2;
-        if (smem + q.o_stages * 16384 + 4096 > 227 * 1024) q.o_stages = 1;
-        if (tune_os > 0) q.o_stages = tune_os;
-        smem += q.o_stages * 16384;
+    // shared-memory plan.  Narrow resident layers: two CTAs per SM, each with one epilogue group, two activation stages and
+    // one staging slab (the second CTA hides the bubbles between tiles).  Everything else: one CTA per SM with two epilogue
+    // groups; resident weights if they fit beside two activation stages, else a ring of weight stages; whatever is left
+    // deepens the activation ring (TMA latency is 2-3k cycles).
+    static const int tune_groups = dc_env_int("DINCAE_TUNE_GROUPS", 0);
+    const int static_smem = 5120;                     // barriers + bias (~3.2 KB) and the 1 KB alignment slack, rounded up
+    const int small_plan = 2 * HL_A_STRIDE + resident_bytes + (a.dst ? 16384 : 0) + 1024;
+    const bool two_per_sm = q.ntiles_n == 1 && 2 * (small_plan + static_smem) <= 227 * 1024 && 4 * bn <= 512 && tune_groups != 2;
+    int smem, per_sm;
+    if (two_per_sm || tune_groups == 1) {
+        q.groups = 1; q.b_resident = 1; q.b_stages = 0; q.a_stages = 2; q.o_stages = a.dst ? 1 : 0;
+        DC_REQUIRE(q.ntiles_n == 1 && small_plan + static_smem <= 227 * 1024, DINCAE_EUNSUPPORTED, "conv3x3_persist: one-group plan does not fit");
+        smem = small_plan;
+        per_sm = two_per_sm ? 2 : 1;
+    } else {
+        q.groups = 2;
+        const int budget = 227 * 1024 - static_smem - 1024;
+        q.o_stages = a.dst ? 2 : 0;
+        if (tune_os > 0 && a.dst) q.o_stages = tune_os > PS_MAX_O ? PS_MAX_O : tune_os;
+        int left = budget - 2 * q.o_stages * 16384;
+        q.b_resident = (q.ntiles_n == 1 && resident_bytes + 2 * HL_A_STRIDE <= left) ? 1 : 0;
+        if (q.b_resident) {
+            q.b_stages = 0;
+            left -= resident_bytes;
+        } else {
+            int bs = (left - 2 * HL_A_STRIDE) / bbytes;
+            if (bs > PS_MAX_B) bs = PS_MAX_B;
+            if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
+            DC_REQUIRE(bs >= 2, DINCAE_EUNSUPPORTED, "conv3x3_persist: no room for two weight stages (BN=%d)", bn);
+            q.b_stages = bs;
+            left -= bs * bbytes;
+        }
+        q.a_stages = left / HL_A_STRIDE;
+        if (q.a_stages > PS_MAX_A) q.a_stages = PS_MAX_A;
+        if (tune_as > 0 && tune_as < q.a_stages) q.a_stages = tune_as;
+        smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 2 * q.o_stages * 16384 + 1024;
+        per_sm = 1;
     }
-    int per_sm = 1;                                   // persistent: one CTA per SM (two when both smem and TMEM allow)
-    if (2 * (smem + 4096) <= 227 * 1024 && 4 * bn <= 512) per_sm = 2;
-    if (tune_persm > 0) per_sm = tune_persm;
-    int ctas = ctx->num_sms * per_sm;
+    int ctas = ctx->num_sms * per_sm;                 // persistent
     if (ctas > q.num_tiles) ctas = q.num_tiles;
     dim3 grid((unsigned)ctas);
     alignas(64) CUtensorMap tmA, tmB, tmO;
@@ -983,20 +1039,25 @@ __global__ void __launch_bounds__(128) wgrad_tma(const __grid_constant__ CUtenso
             for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * WG_BLOCK, mapM, &bar_full[s], m0 + j * 32, x0 + sxM, y0 + syM, b);
             for (int j = 0; j < nblocks; j++) tma_load_4d(st + A_BYTES + j * WG_BLOCK, mapN, &bar_full[s], n0 + j * 32, x0 + sxN, y0 + syN, b);
         }
-    } else if (t == 32) {
-        // ===== MMA issuer =====
+    } else if (warp == 1) {
+        // ===== MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist) =====
         for (int i = 0; i < nst; i++) {
             const int s = i % STAGES, u = i / STAGES;
             mbar_wait(&bar_full[s], (uint32_t)(u & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint64_t da = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES));
             const uint64_t db = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES + A_BYTES));
+            if (elect_one_sync()) {
+                if (i == 0) umma_tf32(tmem_d, da, db, IDESC, 0u);
+                else umma_tf32_acc(tmem_d, da, db, IDESC);
 #pragma unroll
-            for (int k = 0; k < WG_KP / 8; k++)          // 8 pixel rows per MMA: advance by one 1024-byte atom
-                umma_tf32(tmem_d, da + (uint64_t)(64 * k), db + (uint64_t)(64 * k), IDESC, (i | k) != 0 ? 1u : 0u);
-            umma_commit(&bar_empty[s]);
+                for (int k = 1; k < WG_KP / 8; k++)      // 8 pixel rows per MMA: advance by one 1024-byte atom
+                    umma_tf32_acc(tmem_d, da + (uint64_t)(64 * k), db + (uint64_t)(64 * k), IDESC);
+                umma_commit(&bar_empty[s]);
+                if (i == nst - 1) umma_commit(&bar_done);
+            }
+            __syncwarp();
         }
-        umma_commit(&bar_done);
     }
     __syncwarp();
     float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
@@ -1058,32 +1119,43 @@ __global__ void __launch_bounds__(256) reduce_splits_kernel(const float* __restr
     }
 }
 
-// One block = `cols` consecutive outputs x (256/cols) split groups.  Wide entries (dW) use 32 x 8, narrow entries with many
+// One block = `cols` float4 column groups x (256/cols) split groups.  Wide entries (dW) use 32 x 8, narrow entries with many
 // partial rows (bias column partials: n = C, splits ~ 1000) use 8 x 32 so that enough threads share the long sums.
+// Every entry has n % 4 == 0 and 16-byte aligned rows (checked on the host), so each thread streams float4s; four rows are
+// in flight per thread.  The summation order is fixed: rows zg, zg + G, ... per thread, then groups 0..G-1.
 __global__ void __launch_bounds__(256) reduce_batched_kernel(const __grid_constant__ RedList L) {
-    __shared__ float sh[256];
+    __shared__ float4 sh[256];
     int e = 0;
     while (e + 1 < L.count && (int)blockIdx.x >= L.blk_start[e + 1]) e++;
     const RedEntry en = L.e[e];
     const int cols = en.n <= 512 ? 8 : 32, ngroups = 256 / cols;
     const int c = threadIdx.x % cols, zg = threadIdx.x / cols;
+    const int64_t n4 = en.n >> 2;
     const int64_t i = (int64_t)((int)blockIdx.x - L.blk_start[e]) * cols + c;
-    float s = 0.f;
-    if (i < en.n) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < n4) {
+        const float4* src = reinterpret_cast<const float4*>(en.part) + i;
         int z = zg;
         for (; z + 3 * ngroups < en.splits; z += 4 * ngroups) {
-            float v0 = __ldg(en.part + (size_t)z * en.n + i), v1 = __ldg(en.part + (size_t)(z + ngroups) * en.n + i);
-            float v2 = __ldg(en.part + (size_t)(z + 2 * ngroups) * en.n + i), v3 = __ldg(en.part + (size_t)(z + 3 * ngroups) * en.n + i);
-            s += (v0 + v1) + (v2 + v3);
+            const float4 v0 = __ldg(src + (size_t)z * n4), v1 = __ldg(src + (size_t)(z + ngroups) * n4);
+            const float4 v2 = __ldg(src + (size_t)(z + 2 * ngroups) * n4), v3 = __ldg(src + (size_t)(z + 3 * ngroups) * n4);
+            s.x += (v0.x + v1.x) + (v2.x + v3.x); s.y += (v0.y + v1.y) + (v2.y + v3.y);
+            s.z += (v0.z + v1.z) + (v2.z + v3.z); s.w += (v0.w + v1.w) + (v2.w + v3.w);
         }
-        for (; z < en.splits; z += ngroups) s += __ldg(en.part + (size_t)z * en.n + i);
+        for (; z < en.splits; z += ngroups) {
+            const float4 v = __ldg(src + (size_t)z * n4);
+            s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
     }
     sh[threadIdx.x] = s;
     __syncthreads();
-    if (zg == 0 && i < en.n) {
-        float tot = 0.f;
-        for (int k = 0; k < ngroups; k++) tot += sh[k * cols + c];
-        en.dst[i] = tot;
+    if (zg == 0 && i < n4) {
+        float4 tot = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int k = 0; k < ngroups; k++) {
+            const float4 v = sh[k * cols + c];
+            tot.x += v.x; tot.y += v.y; tot.z += v.z; tot.w += v.w;
+        }
+        reinterpret_cast<float4*>(en.dst)[i] = tot;
     }
 }
 
@@ -1219,15 +1291,16 @@ __global__ void __launch_bounds__(128) wgrad_halo(const __grid_constant__ CUtens
                 for (int j = 0; j < nblocks; j++) tma_load_4d(st + a_bytes + j * nblk_bytes, &tmIn, &bar_full[s], n0 + j * 32, x0 - 1, y0 + ky - 1, b);
             }
         }
-    } else if (t == 32) {
-        // ===== MMA issuer =====
+    } else if (warp == 1) {
+        // ===== MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist) =====
         for (int i = 0; i < nst; i++) {
             const int s = i % STAGES, u = i / STAGES;
             mbar_wait(&bar_full[s], (uint32_t)(u & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t abase = smem_base + (uint32_t)(s * stage_bytes), bbase = abase + (uint32_t)a_bytes;
-            // descriptor bases once per stage; the 12 (dx, h) offsets are compile-time constants (single-thread issue rate matters)
+            // descriptor bases once per stage; the 12 (dx, h) offsets are compile-time constants
             const uint64_t da0 = make_desc_mn_sw128_lbo(abase, (uint32_t)mblk_bytes), db0 = make_desc_mn_sw128_lbo(bbase, (uint32_t)nblk_bytes);
+            if (elect_one_sync()) {
             if (p.in_is_m) {
 #pragma unroll
                 for (int dx = 0; dx < 3; dx++)
@@ -1248,8 +1321,10 @@ __global__ void __launch_bounds__(128) wgrad_halo(const __grid_constant__ CUtens
                     }
             }
             umma_commit(&bar_empty[s]);
+            if (i == nst - 1) umma_commit(&bar_done);
+            }
+            __syncwarp();
         }
-        umma_commit(&bar_done);
     }
     __syncwarp();
     float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
@@ -1362,7 +1437,8 @@ __global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CU
             tma_load_4d(st, &tmIn, &bar_full[s], 0, x0 - 1, y0 - 1, b);               // (32, 10, 6, 1) halo box
             tma_load_4d(st + W32_IN_BYTES, &tmG, &bar_full[s], 0, x0, y0, b);         // (32, 8, 4, 1)
         }
-    } else if (t == 32) {
+    } else if (warp == 1) {
+        // MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist)
         for (int i = 0; i < nst; i++) {
             const int s = i % STAGES, u = i / STAGES;
             mbar_wait(&bar_full[s], (uint32_t)(u & 1));
@@ -1370,17 +1446,20 @@ __global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CU
             const uint32_t abase = smem_base + (uint32_t)(s * W32_STAGE);
             const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 128u);                 // M block j = the tile shifted by j pixel rows
             const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W32_IN_BYTES, (uint32_t)WG_BLOCK);
+            if (elect_one_sync()) {
 #pragma unroll
-            for (int ky = 0; ky < 3; ky++)
+                for (int ky = 0; ky < 3; ky++)
 #pragma unroll
-                for (int h = 0; h < 4; h++) {
-                    const uint64_t da = da0 + (uint64_t)(((ky + h) * 10 * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
-                    if (h == 0) umma_tf32(tmem_d + (uint32_t)(ky * 32), da, db, IDESC, i != 0 ? 1u : 0u);
-                    else umma_tf32_acc(tmem_d + (uint32_t)(ky * 32), da, db, IDESC);
-                }
-            umma_commit(&bar_empty[s]);
+                    for (int h = 0; h < 4; h++) {
+                        const uint64_t da = da0 + (uint64_t)(((ky + h) * 10 * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
+                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(ky * 32), da, db, IDESC, i != 0 ? 1u : 0u);
+                        else umma_tf32_acc(tmem_d + (uint32_t)(ky * 32), da, db, IDESC);
+                    }
+                umma_commit(&bar_empty[s]);
+                if (i == nst - 1) umma_commit(&bar_done);
+            }
+            __syncwarp();
         }
-        umma_commit(&bar_done);
     }
     __syncwarp();
     float* out = p.partial + (size_t)split * 9 * 32 * 32;
@@ -1625,7 +1704,9 @@ int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list) {
     int blocks = 0;
     for (int e = 0; e < list.count; e++) {
         list.blk_start[e] = blocks;
-        blocks += (int)dc_cdiv(list.e[e].n, list.e[e].n <= 512 ? 8 : 32);
+        DC_REQUIRE(list.e[e].n % 4 == 0 && ((uintptr_t)list.e[e].part & 15) == 0 && ((uintptr_t)list.e[e].dst & 15) == 0, DINCAE_EINVAL,
+                   "k2_reduce_batched: entry %d is not float4-aligned (n=%lld)", e, (long long)list.e[e].n);
+        blocks += (int)dc_cdiv(list.e[e].n / 4, list.e[e].n <= 512 ? 8 : 32);
     }
     list.blk_start[list.count] = blocks;
     DC_LAUNCH(ctx, reduce_batched_kernel, blocks, 256, 0, list);
