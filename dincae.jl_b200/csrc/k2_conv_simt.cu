@@ -377,31 +377,43 @@ __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restric
     }
 }
 
-__global__ void pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x, int rnd) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    int C4 = Cp >> 2;
-    int64_t total = (int64_t)B * H2 * W2 * C4;
-    if (i >= total) return;
-    int c4 = (int)(i % C4);
-    int64_t p = i / C4;
-    int x2 = (int)(p % W2);
-    p /= W2;
-    int y2 = (int)(p % H2);
-    int b = (int)(p / H2);
-    int oh = H & 1, ow = W & 1;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int dy = 0; dy < 2; dy++)
-#pragma unroll
-        for (int dx = 0; dx < 2; dx++) {
-            int yy = 2 * y2 + dy - oh, xx = 2 * x2 + dx - ow;
-            if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-                float4 v = ldg4(a + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
-                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+// The element-wise level kernels below share one indexing scheme: a block walks whole pixel rows (row = b * H + y, one 32-bit
+// division per row), a thread owns the float4 column group c4 = t % CW for good and steps through the row PL = 256 / CW
+// pixels at a time.  No per-element 64-bit div/mod, so the kernels are limited by HBM rather than by index arithmetic.
+struct RowThread {
+    int CW, PL, c4, lane;
+    __device__ __forceinline__ RowThread(int C4) {
+        CW = C4 < 256 ? C4 : 256;
+        PL = 256 / CW;
+        c4 = (int)threadIdx.x % CW;
+        lane = (int)threadIdx.x / CW;       // >= PL for the (256 - PL * CW) threads without work
+    }
+};
+
+__global__ void __launch_bounds__(256) pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x, int rnd) {
+    const int C4 = Cp >> 2;
+    const RowThread rt(C4);
+    if (rt.lane >= rt.PL) return;
+    const int oh = H & 1, ow = W & 1;
+    for (int row = blockIdx.x; row < B * H2; row += gridDim.x) {
+        const int b = row / H2, y2 = row - b * H2;
+        const int ya = 2 * y2 - oh, yb = ya + 1;                        // ya may be -1 (odd H: the pad row), yb < H always
+        const float* ra = a + ((size_t)b * H + (ya < 0 ? 0 : ya)) * W * Cp;
+        const float* rb = a + ((size_t)b * H + yb) * W * Cp;
+        float* ro = x + (size_t)row * W2 * Cp;
+        for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
+            for (int x2 = rt.lane; x2 < W2; x2 += rt.PL) {
+                const int xa = 2 * x2 - ow, xb = xa + 1;
+                float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+                // same accumulation order as the reference loop: (dy,dx) = (0,0), (0,1), (1,0), (1,1)
+                if (ya >= 0 && xa >= 0) { float4 v = ldg4(ra + (size_t)xa * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+                if (ya >= 0) { float4 v = ldg4(ra + (size_t)xb * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+                if (xa >= 0) { float4 v = ldg4(rb + (size_t)xa * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+                { float4 v = ldg4(rb + (size_t)xb * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+                s.x *= 0.25f; s.y *= 0.25f; s.z *= 0.25f; s.w *= 0.25f;
+                *reinterpret_cast<float4*>(ro + (size_t)x2 * Cp + c4 * 4) = round_tf32(s, rnd);
             }
-        }
-    s.x *= 0.25f; s.y *= 0.25f; s.z *= 0.25f; s.w *= 0.25f;
-    *reinterpret_cast<float4*>(x + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4) = round_tf32(s, rnd);
+    }
 }
 
 // block-level column partial sums of the float4 each thread accumulated for ITS column group (requires 256 % C4 == 0 and a
@@ -421,37 +433,37 @@ __device__ __forceinline__ void block_colpart(float4 acc, int C4, int Cp, float*
 __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
                                                     const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd,
                                                     float* __restrict__ colpart) {
-    int C4 = Cp >> 2;
-    int64_t total = (int64_t)B * Hs * Ws * C4;
+    const int C4 = Cp >> 2;
+    const RowThread rt(C4);
     float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c4 = (int)(i % C4);
-        int64_t p = i / C4;
-        int xs = (int)(p % Ws);
-        p /= Ws;
-        int ys = (int)(p % Hs);
-        int b = (int)(p / Hs);
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-        for (int dy = 0; dy < 2; dy++)
-#pragma unroll
-            for (int dx = 0; dx < 2; dx++) {
-                int yy = 2 * ys + dy, xx = 2 * xs + dx;
-                if (yy < H && xx < W) {
-                    float4 v = ldg4(gu + (((size_t)b * H + yy) * W + xx) * Cp + c4 * 4);
-                    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    if (rt.lane < rt.PL) {
+        for (int row = blockIdx.x; row < B * Hs; row += gridDim.x) {
+            const int b = row / Hs, ys = row - b * Hs;
+            const int ya = 2 * ys, yb = ya + 1;
+            const float* ra = gu + ((size_t)b * H + ya) * W * Cp;
+            const float* rb = gu + ((size_t)b * H + (yb < H ? yb : ya)) * W * Cp;
+            const size_t ro = (size_t)row * Ws * Cp;
+            for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
+                for (int xs = rt.lane; xs < Ws; xs += rt.PL) {
+                    const int xa = 2 * xs, xb = xa + 1;
+                    float4 s = ldg4(ra + (size_t)xa * Cp + c4 * 4);
+                    if (xb < W) { float4 v = ldg4(ra + (size_t)xb * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+                    if (yb < H) {
+                        float4 v = ldg4(rb + (size_t)xa * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+                        if (xb < W) { float4 u = ldg4(rb + (size_t)xb * Cp + c4 * 4); s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w; }
+                    }
+                    const size_t off = ro + (size_t)xs * Cp + c4 * 4;
+                    if (G) *reinterpret_cast<float4*>(G + off) = s;
+                    if (gd) {
+                        if (r) {
+                            float4 rv = ldg4(r + off);
+                            s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
+                        }
+                        s = round_tf32(s, rnd);
+                        *reinterpret_cast<float4*>(gd + off) = s;
+                        cacc.x += s.x; cacc.y += s.y; cacc.z += s.z; cacc.w += s.w;
+                    }
                 }
-            }
-        size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + c4 * 4;
-        if (G) *reinterpret_cast<float4*>(G + off) = s;
-        if (gd) {
-            if (r) {
-                float4 rv = ldg4(r + off);
-                s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
-            }
-            s = round_tf32(s, rnd);
-            *reinterpret_cast<float4*>(gd + off) = s;
-            cacc.x += s.x; cacc.y += s.y; cacc.z += s.z; cacc.w += s.w;
         }
     }
     if (colpart) block_colpart(cacc, C4, Cp, colpart);
@@ -459,25 +471,27 @@ __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu
 
 __global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
                                                       int H2, int W2, float slope, float* __restrict__ gc, int rnd, float* __restrict__ colpart) {
-    int C4 = Cp >> 2;
-    int64_t total = (int64_t)B * H * W * C4;
+    const int C4 = Cp >> 2;
+    const RowThread rt(C4);
     float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        int c4 = (int)(i % C4);
-        int64_t p = i / C4;
-        int x = (int)(p % W);
-        p /= W;
-        int y = (int)(p % H);
-        int b = (int)(p / H);
-        int y2 = (y + (H & 1)) >> 1, x2 = (x + (W & 1)) >> 1;
-        float4 g = ldg4(xg + (((size_t)b * H2 + y2) * W2 + x2) * Cp + c4 * 4);
-        size_t off = (((size_t)b * H + y) * W + x) * Cp + c4 * 4;
-        float4 av = ldg4(a + off);
-        g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
-        g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
-        g = round_tf32(g, rnd);
-        *reinterpret_cast<float4*>(gc + off) = g;
-        cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
+    if (rt.lane < rt.PL) {
+        const int oh = H & 1, ow = W & 1;
+        for (int row = blockIdx.x; row < B * H; row += gridDim.x) {
+            const int b = row / H, y = row - b * H;
+            const float* rx = xg + ((size_t)b * H2 + ((y + oh) >> 1)) * W2 * Cp;
+            const size_t ro = (size_t)row * W * Cp;
+            for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
+                for (int x = rt.lane; x < W; x += rt.PL) {
+                    float4 g = ldg4(rx + (size_t)((x + ow) >> 1) * Cp + c4 * 4);
+                    const size_t off = ro + (size_t)x * Cp + c4 * 4;
+                    const float4 av = ldg4(a + off);
+                    g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
+                    g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+                    g = round_tf32(g, rnd);
+                    *reinterpret_cast<float4*>(gc + off) = g;
+                    cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
+                }
+        }
     }
     if (colpart) block_colpart(cacc, C4, Cp, colpart);
 }
@@ -521,22 +535,35 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
     o.w = w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w;
     *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(o, rnd);
 }
-__global__ void up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
-                                  int H, int W, float* __restrict__ dst, int rnd) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    int C4 = Cp >> 2;
-    int64_t total = (int64_t)B * H * W * C4;
-    if (i >= total) return;
-    int c4 = (int)(i % C4);
-    int64_t p = i / C4;
-    int x = (int)(p % W);
-    p /= W;
-    int y = (int)(p % H);
-    int b = (int)(p / H);
-    size_t off = (((size_t)b * Hs + (y >> 1)) * Ws + (x >> 1)) * Cp + c4 * 4;
-    float4 v = ldg4(s0 + off);
-    if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
-    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(v, rnd);
+// one thread per SOURCE cell: the (optionally summed) value is read once and written to its 2 x 2 (cropped) destination cells
+__global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
+                                                         int H, int W, float* __restrict__ dst, int rnd) {
+    const int C4 = Cp >> 2;
+    const RowThread rt(C4);
+    if (rt.lane >= rt.PL) return;
+    for (int row = blockIdx.x; row < B * Hs; row += gridDim.x) {
+        const int b = row / Hs, ys = row - b * Hs;
+        const int ya = 2 * ys, yb = ya + 1;
+        if (ya >= H) continue;
+        const size_t rs = (size_t)row * Ws * Cp;
+        float* da = dst + ((size_t)b * H + ya) * W * Cp;
+        float* db = yb < H ? dst + ((size_t)b * H + yb) * W * Cp : nullptr;
+        for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
+            for (int xs = rt.lane; xs < Ws; xs += rt.PL) {
+                const int xa = 2 * xs, xb = xa + 1;
+                if (xa >= W) continue;
+                const size_t off = rs + (size_t)xs * Cp + c4 * 4;
+                float4 v = ldg4(s0 + off);
+                if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+                v = round_tf32(v, rnd);
+                *reinterpret_cast<float4*>(da + (size_t)xa * Cp + c4 * 4) = v;
+                if (xb < W) *reinterpret_cast<float4*>(da + (size_t)xb * Cp + c4 * 4) = v;
+                if (db) {
+                    *reinterpret_cast<float4*>(db + (size_t)xa * Cp + c4 * 4) = v;
+                    if (xb < W) *reinterpret_cast<float4*>(db + (size_t)xb * Cp + c4 * 4) = v;
+                }
+            }
+    }
 }
 // transpose: each low-res cell gathers from the high-res cells whose stencil touches it (deterministic)
 __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
@@ -715,6 +742,13 @@ int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, siz
     return DINCAE_OK;
 }
 
+// grid of the row-walking level kernels: one block per pixel row, capped at 8 resident blocks per SM
+static int k2_row_blocks(dincae_ctx* ctx, int64_t rows, int64_t n_elems4) {
+    (void)n_elems4;
+    int64_t cap = 8 * (int64_t)ctx->num_sms;
+    return (int)(rows < cap ? rows : cap);
+}
+
 int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
     int64_t M = (int64_t)B * H * W;
     if (M == 0) return DINCAE_OK;
@@ -727,7 +761,7 @@ int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, fl
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H2 * W2 * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pool_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
+    DC_LAUNCH(ctx, pool_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * H2, n), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -745,7 +779,7 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
     int Hs = H / 2 + H % 2, Ws = W / 2 + W % 2;
     int64_t n = (int64_t)B * Hs * Ws * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : (int)dc_cdiv(n, 256);
+    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * Hs, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_upbwd: column partials not supported for %d channels", Cp);
     DC_LAUNCH(ctx, upbwd_kernel, nb, 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
@@ -756,7 +790,7 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : (int)dc_cdiv(n, 256);
+    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * H, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd: column partials not supported for %d channels", Cp);
     DC_LAUNCH(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
@@ -774,7 +808,7 @@ int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, in
 int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, up_nearest_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
+    DC_LAUNCH(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
