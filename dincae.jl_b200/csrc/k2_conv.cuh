@@ -40,6 +40,7 @@ struct ConvArgs {
     float* planar_out;    // optional planar (Julia WHCN) output [B][planar_C][H][W] of the first planar_C channels (TMA kernel only)
     int planar_C;
     int planar_accumulate;   // 1: planar_out += value
+    float* pool_dst;         // optional: MeanPool((2,2)) of the output, only when k2_conv_fuses_pool(args) is true
     double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
     double work_bytes;    // algorithmic HBM bytes (input + output + weights, REAL channel counts)
 };
@@ -96,6 +97,7 @@ int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);        // dispatches to the
 bool k2_conv_tc_eligible(const ConvArgs& a);
 int32_t k2_conv_tc(dincae_ctx* ctx, const ConvArgs& a);
 bool k2_conv_tma_eligible(const ConvArgs& a);
+bool k2_conv_fuses_pool(const ConvArgs& a);            // k2_conv(a) can also write MeanPool((2,2)) of its output to a.pool_dst
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a);
 size_t k2_wgrad_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, int Cout_p);
 int32_t k2_wgrad(dincae_ctx* ctx, WgradArgs a, void* scratch, size_t scratch_bytes);   // dispatches to the tcgen05 kernel when eligible

@@ -26,6 +26,8 @@ struct TmaConvArgs {
     float* dst;
     float* planar_out;
     int planar_C, planar_accumulate;
+    float* pool_dst;           // persistent kernel, even H and W: also writes MeanPool((2,2)) of the output, [B][H/2][W/2][Cout_p]
+    int pool_rnd;              // round the pooled values to TF32 (they feed the next tensor-core conv)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -478,13 +480,19 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* map, const void*
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ float rna_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, float4 v) {
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w));
 }
 // One 32-column slab of one accumulator row: bias, leaky ReLU as max(v, v * slope) (0 <= slope <= 1), optional addend, then
 // eight 16 B shared-memory stores at the 128B-swizzled chunk positions of this row.
-template <bool ADD>
-__device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* bs, float slope, const float* addp, uint32_t st_row, int sw) {
+template <bool ADD, bool POOL>
+__device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* bs, float slope, const float* addp, uint32_t st_row, int sw,
+                                         float* poolp, int pool_rnd) {
     float4 av[ADD ? 8 : 1];
     if (ADD) {
 #pragma unroll
@@ -505,8 +513,23 @@ __device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* b
     }
 #pragma unroll
     for (int k = 0; k < 8; k++) st_shared_v4(st_row + (uint32_t)((k ^ sw) << 4), o[k]);
+    if (POOL) {
+        // MeanPool((2,2)): tile row = h * 8 + w, so the 2 x 2 window of an even (h, w) is lanes {l, l^1, l^8, l^9} of this warp
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            float4 s = o[k];
+            s.x += __shfl_xor_sync(0xffffffffu, s.x, 1); s.y += __shfl_xor_sync(0xffffffffu, s.y, 1);
+            s.z += __shfl_xor_sync(0xffffffffu, s.z, 1); s.w += __shfl_xor_sync(0xffffffffu, s.w, 1);
+            s.x += __shfl_xor_sync(0xffffffffu, s.x, 8); s.y += __shfl_xor_sync(0xffffffffu, s.y, 8);
+            s.z += __shfl_xor_sync(0xffffffffu, s.z, 8); s.w += __shfl_xor_sync(0xffffffffu, s.w, 8);
+            if (poolp) {
+                s.x *= 0.25f; s.y *= 0.25f; s.z *= 0.25f; s.w *= 0.25f;
+                if (pool_rnd) { s.x = rna_tf32(s.x); s.y = rna_tf32(s.y); s.z = rna_tf32(s.z); s.w = rna_tf32(s.w); }
+                *reinterpret_cast<float4*>(poolp + 4 * k) = s;
+            }
+        }
+    }
 }
-
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -694,6 +717,8 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
             }
             if (p.dst) {
                 const float* addp = (p.addend && pv) ? p.addend + m * p.Cout_p + n0 : nullptr;
+                float* poolp = (p.pool_dst && pv && (lane & 9) == 0)
+                                   ? p.pool_dst + ((((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * p.Cout_p + n0) : nullptr;
                 uint32_t r[32];
                 tmem_ld16(lane_addr, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
                 tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
@@ -709,8 +734,9 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
                     const uint32_t st_row = smemO_u + (uint32_t)(obuf * 16384 + row * 128);
                     const float* bs = &bias_s[n0 + nl];
                     if (act_mode != 2) {
-                        if (p.addend) epi_slab<true>(r, bs, slope_eff, addp ? addp + nl : nullptr, st_row, row & 7);
-                        else epi_slab<false>(r, bs, slope_eff, nullptr, st_row, row & 7);
+                        if (p.pool_dst) epi_slab<false, true>(r, bs, slope_eff, nullptr, st_row, row & 7, poolp ? poolp + nl : nullptr, p.pool_rnd);
+                        else if (p.addend) epi_slab<true, false>(r, bs, slope_eff, addp ? addp + nl : nullptr, st_row, row & 7, nullptr, 0);
+                        else epi_slab<false, false>(r, bs, slope_eff, nullptr, st_row, row & 7, nullptr, 0);
                     } else {                                 // slopes outside [0, 1): the select form
 #pragma unroll
                         for (int k = 0; k < 8; k++) {
@@ -791,6 +817,8 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.pool_dst = a.pool_dst; p.pool_rnd = ctx->tf32_acts ? 1 : 0;
+    DC_REQUIRE(!a.pool_dst || k2_conv_fuses_pool(a), DINCAE_EINVAL, "conv3x3_persist: pool fusion needs even H, W, a leaky slope in [0,1) and no addend");
     int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
     static const int tune_bn = dc_env_int("DINCAE_TUNE_BN", 0), tune_bs = dc_env_int("DINCAE_TUNE_BSTAGES", 0),
                      tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
@@ -880,6 +908,7 @@ static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
     if (a.Cout_p % 256 == 0) HALO_LAUNCH(256, 2, 3);
@@ -905,6 +934,18 @@ static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
         return DINCAE_OK;                                                                                                  \
     } while (0)
 
+static bool persist_selected(const ConvArgs& a) {
+    static int halo_mode = -1;
+    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
+    return halo_mode == 3 && (a.planar_out == nullptr || a.planar_C <= 16) && a.Cout_p <= 512;
+}
+// true when k2_conv() on these arguments can also emit MeanPool((2,2)) of its output into a.pool_dst (the persistent tcgen05 kernel,
+// even H and W so that no window straddles the padding, activation in the max(v, v*slope) form, NHWC output present)
+bool k2_conv_fuses_pool(const ConvArgs& a) {
+    static const int off = dc_env_int("DINCAE_NO_POOL_FUSION", 0);
+    return !off && k2_conv_tma_eligible(a) && persist_selected(a) && a.dst != nullptr && a.addend == nullptr && (a.H % 2) == 0 && (a.W % 2) == 0 &&
+           a.B * a.H * a.W > 0 && (a.act != ACT_RELU || (a.slope >= 0.f && a.slope < 1.f));
+}
 bool k2_conv_tma_eligible(const ConvArgs& a) {
     return a.wgtK != nullptr && a.in.mode == SRC_DIRECT && a.in.src1 == nullptr && (a.in.C % TM_KC) == 0 && (a.Cout_p % 32) == 0 &&
            a.in_is_tf32 && get_encode() != nullptr;
@@ -915,7 +956,8 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     // DINCAE_CONV_KERNEL: 0 = one activation box per tap; 1 = halo tile with shifted descriptors; 3 = persistent warp-specialised halo kernel (default)
     static int halo_mode = -1;
     if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
-    if (halo_mode == 3 && (a.planar_out == nullptr || a.planar_C <= 16) && a.Cout_p <= 512) return k2_conv_persist(ctx, a);
+    if (persist_selected(a)) return k2_conv_persist(ctx, a);
+    DC_REQUIRE(a.pool_dst == nullptr, DINCAE_EINVAL, "k2_conv_tma: pool fusion is only available in the persistent kernel");
     if (halo_mode > 0) return k2_conv_halo(ctx, a, 1);
     TmaConvArgs p;
     p.B = a.B; p.H = a.H; p.W = a.W;
@@ -925,6 +967,7 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
     if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
@@ -1689,6 +1732,7 @@ extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const f
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0;
+    p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
     if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);

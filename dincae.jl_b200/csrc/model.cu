@@ -77,8 +77,10 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
+        const bool fuse_pool = k2_conv_fuses_pool(a);                             // even H, W on the tcgen05 path: the conv epilogue pools
+        a.pool_dst = fuse_pool ? cb.X[l + 1] : nullptr;
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
-        DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
+        if (!fuse_pool) DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
     }
     for (int l = L - 1; l >= 0; l--) {
         const LayerInfo& d = M->dec[c][l];
