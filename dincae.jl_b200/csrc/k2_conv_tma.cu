@@ -459,7 +459,7 @@ constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; 
 // activation halo per tile and K chunk crosses L2 -> SM.
 namespace {
 
-constexpr int PS_MAX_A = 4, PS_MAX_B = 8, PS_MAX_COUT = 512, PS_MAX_O = 2, PS_THREADS = 384;
+constexpr int PS_MAX_A = 4, PS_MAX_B = 16, PS_MAX_COUT = 512, PS_MAX_O = 2, PS_THREADS = 384;
 
 struct PersistArgs {
     int num_tiles, ntiles_n;
@@ -532,6 +532,91 @@ __device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* b
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Epilogue of one 128-pixel x BN-channel accumulator, run by the 128 threads of one epilogue group (thread = tile row = TMEM lane).
+// Planar output (<= 16 channels) is written directly; NHWC output goes slab by slab (32 channels) through the group's
+// swizzled staging buffers to its store issuer.  `tempty` gets one arrival per thread once the accumulator has been read.
+struct EpiCtx {
+    const float* bias_s;       // shared: the layer bias
+    uint32_t smemO_u;          // shared address of this group's staging slabs
+    uint64_t *ofull, *oempty;  // this group's hand-off barriers [o_stages]
+    int o_stages, obuf, ouse;
+    int row, lane;
+    int act_mode;
+    float slope, slope_eff;
+};
+template <int BN>
+__device__ __forceinline__ void epi_tile(const TmaConvArgs& p, EpiCtx& e, uint32_t lane_addr, uint64_t* tempty, int b, int y0, int x0, int n0) {
+    const int h = e.row / HL_PW, w = e.row - h * HL_PW;
+    const int y = y0 + h, x = x0 + w;
+    const bool pv = b < p.B && y < p.H && x < p.W;
+    const size_t m = ((size_t)b * p.H + y) * p.W + x;
+    if (p.planar_out) {
+        uint32_t r[16];
+        tmem_ld16(lane_addr, r);
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (pv && n0 == 0) {
+#pragma unroll
+            for (int k = 0; k < 16; k++) {
+                if (k < p.planar_C) {
+                    float v = __uint_as_float(r[k]) + e.bias_s[k];
+                    v = act_apply(v, p.act, p.slope);
+                    const size_t po = (((size_t)b * p.planar_C + k) * p.H + y) * p.W + x;
+                    p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
+                }
+            }
+        }
+    }
+    if (p.dst) {
+        const float* addp = (p.addend && pv) ? p.addend + m * p.Cout_p + n0 : nullptr;
+        float* poolp = (p.pool_dst && pv && (e.lane & 9) == 0)
+                           ? p.pool_dst + ((((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * p.Cout_p + n0) : nullptr;
+        uint32_t r[32];
+        tmem_ld16(lane_addr, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+        tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+#pragma unroll 1
+        for (int sl = 0; sl < BN / 32; sl++) {
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (sl == BN / 32 - 1) {                 // accumulator drained: the MMA warp may reuse it
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                mbar_arrive(tempty);
+            }
+            if (e.ouse > 0) mbar_wait(&e.oempty[e.obuf], (uint32_t)((e.ouse - 1) & 1));   // the store that last used this slab has been read out
+            const int nl = sl * 32;                  // column of this slab inside the tile
+            const uint32_t st_row = e.smemO_u + (uint32_t)(e.obuf * 16384 + e.row * 128);
+            const float* bs = &e.bias_s[n0 + nl];
+            if (e.act_mode != 2) {
+                if (p.pool_dst) epi_slab<false, true>(r, bs, e.slope_eff, nullptr, st_row, e.row & 7, poolp ? poolp + nl : nullptr, p.pool_rnd);
+                else if (p.addend) epi_slab<true, false>(r, bs, e.slope_eff, addp ? addp + nl : nullptr, st_row, e.row & 7, nullptr, 0);
+                else epi_slab<false, false>(r, bs, e.slope_eff, nullptr, st_row, e.row & 7, nullptr, 0);
+            } else {                                 // slopes outside [0, 1): the select form
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    float4 o;
+                    o.x = act_apply(__uint_as_float(r[4 * k + 0]) + bs[4 * k + 0], ACT_RELU, e.slope);
+                    o.y = act_apply(__uint_as_float(r[4 * k + 1]) + bs[4 * k + 1], ACT_RELU, e.slope);
+                    o.z = act_apply(__uint_as_float(r[4 * k + 2]) + bs[4 * k + 2], ACT_RELU, e.slope);
+                    o.w = act_apply(__uint_as_float(r[4 * k + 3]) + bs[4 * k + 3], ACT_RELU, e.slope);
+                    if (addp) {
+                        const float4 av = __ldg(reinterpret_cast<const float4*>(addp + nl + 4 * k));
+                        o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
+                    }
+                    st_shared_v4(st_row + (uint32_t)((k ^ (e.row & 7)) << 4), o);
+                }
+            }
+            if (sl + 1 < BN / 32) {                  // next slab's TMEM read overlaps the hand-off below
+                tmem_ld16(lane_addr + (uint32_t)(nl + 32), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                tmem_ld16(lane_addr + (uint32_t)(nl + 48), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the TMA store
+            mbar_arrive(&e.ofull[e.obuf]);
+            if (++e.obuf == e.o_stages) { e.obuf = 0; e.ouse++; }
+        }
+    } else {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(tempty);
+    }
 }
 
 template <int BN>
@@ -678,92 +763,27 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
         // store also clips the pixels of edge patches that fall outside the image.  Planar output (<= 16 channels) is
         // written directly.
         const int g = (warp - 4) >> 2;
-        const int row = (warp & 3) * 32 + lane;              // tile row = TMEM lane
-        const int h = row / HL_PW, w = row - h * HL_PW;
-        const float slope = p.slope;
-        const int act_mode = p.act != ACT_RELU ? 0 : ((slope >= 0.f && slope < 1.f) ? 1 : 2);
-        const float slope_eff = act_mode == 0 ? 1.f : slope;     // max(v, v * 1) = v: no activation
-        const uint32_t smemO_u = smem_u32(smemO) + (uint32_t)(g * q.o_stages * 16384);
+        EpiCtx e;
+        e.bias_s = bias_s;
+        e.smemO_u = smem_u32(smemO) + (uint32_t)(g * q.o_stages * 16384);
+        e.ofull = bar_ofull[g]; e.oempty = bar_oempty[g];
+        e.o_stages = q.o_stages; e.obuf = 0; e.ouse = 0;
+        e.row = (warp & 3) * 32 + lane; e.lane = lane;           // tile row = TMEM lane
+        e.slope = p.slope;
+        e.act_mode = p.act != ACT_RELU ? 0 : ((p.slope >= 0.f && p.slope < 1.f) ? 1 : 2);
+        e.slope_eff = e.act_mode == 0 ? 1.f : p.slope;           // max(v, v * 1) = v: no activation
         const bool tr0 = (t == 128);
-        int obuf = 0, ouse = 0;
         for (int tile = blockIdx.x + g * gridDim.x, it = g; tile < q.num_tiles; tile += q.groups * gridDim.x, it += q.groups) {
             const int acc = it & 1, ut = it >> 1;
             const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
             const int b = pi / patches, pr = pi - b * patches;
             const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
-            const int y = y0 + h, x = x0 + w;
-            const bool pv = y < p.H && x < p.W;
-            const size_t m = ((size_t)b * p.H + y) * p.W + x;
             if (tr0) PS_TRACE(2, 2 * (it / q.groups));
             mbar_wait(&bar_tfull[acc], (uint32_t)(ut & 1));
             if (tr0) PS_TRACE(2, 1 + 2 * (it / q.groups));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t lane_addr = tmem_d + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(acc * BN);
-            if (p.planar_out) {
-                uint32_t r[16];
-                tmem_ld16(lane_addr, r);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (pv && n0 == 0) {
-#pragma unroll
-                    for (int k = 0; k < 16; k++) {
-                        if (k < p.planar_C) {
-                            float v = __uint_as_float(r[k]) + bias_s[k];
-                            v = act_apply(v, p.act, p.slope);
-                            const size_t po = (((size_t)b * p.planar_C + k) * p.H + y) * p.W + x;
-                            p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
-                        }
-                    }
-                }
-            }
-            if (p.dst) {
-                const float* addp = (p.addend && pv) ? p.addend + m * p.Cout_p + n0 : nullptr;
-                float* poolp = (p.pool_dst && pv && (lane & 9) == 0)
-                                   ? p.pool_dst + ((((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * p.Cout_p + n0) : nullptr;
-                uint32_t r[32];
-                tmem_ld16(lane_addr, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
-                tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
-#pragma unroll 1
-                for (int sl = 0; sl < BN / 32; sl++) {
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    if (sl == BN / 32 - 1) {                 // accumulator drained: the MMA warp may start tile it+2
-                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                        mbar_arrive(&bar_tempty[acc]);
-                    }
-                    if (ouse > 0) mbar_wait(&bar_oempty[g][obuf], (uint32_t)((ouse - 1) & 1));   // the store that last used this slab has been read out
-                    const int nl = sl * 32;                  // column of this slab inside the tile
-                    const uint32_t st_row = smemO_u + (uint32_t)(obuf * 16384 + row * 128);
-                    const float* bs = &bias_s[n0 + nl];
-                    if (act_mode != 2) {
-                        if (p.pool_dst) epi_slab<false, true>(r, bs, slope_eff, nullptr, st_row, row & 7, poolp ? poolp + nl : nullptr, p.pool_rnd);
-                        else if (p.addend) epi_slab<true, false>(r, bs, slope_eff, addp ? addp + nl : nullptr, st_row, row & 7, nullptr, 0);
-                        else epi_slab<false, false>(r, bs, slope_eff, nullptr, st_row, row & 7, nullptr, 0);
-                    } else {                                 // slopes outside [0, 1): the select form
-#pragma unroll
-                        for (int k = 0; k < 8; k++) {
-                            float4 o;
-                            o.x = act_apply(__uint_as_float(r[4 * k + 0]) + bs[4 * k + 0], ACT_RELU, slope);
-                            o.y = act_apply(__uint_as_float(r[4 * k + 1]) + bs[4 * k + 1], ACT_RELU, slope);
-                            o.z = act_apply(__uint_as_float(r[4 * k + 2]) + bs[4 * k + 2], ACT_RELU, slope);
-                            o.w = act_apply(__uint_as_float(r[4 * k + 3]) + bs[4 * k + 3], ACT_RELU, slope);
-                            if (addp) {
-                                const float4 av = __ldg(reinterpret_cast<const float4*>(addp + nl + 4 * k));
-                                o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
-                            }
-                            st_shared_v4(st_row + (uint32_t)((k ^ (row & 7)) << 4), o);
-                        }
-                    }
-                    if (sl + 1 < BN / 32) {                  // next slab's TMEM read overlaps the hand-off below
-                        tmem_ld16(lane_addr + (uint32_t)(nl + 32), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
-                        tmem_ld16(lane_addr + (uint32_t)(nl + 48), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
-                    }
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the TMA store
-                    mbar_arrive(&bar_ofull[g][obuf]);
-                    if (++obuf == q.o_stages) { obuf = 0; ouse++; }
-                }
-            } else {
-                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                mbar_arrive(&bar_tempty[acc]);               // 128 arrivals free the accumulator for tile it+2
-            }
+            epi_tile<BN>(p, e, lane_addr, &bar_tempty[acc], b, y0, x0, n0);
         }
     } else if (lane == 0 && p.dst && warp - 2 < q.groups) {
         // ===== store issuer of group g: one TMA store per staged slab, then hand the slab back once it has been read =====
@@ -790,6 +810,174 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
 }
 
+
+// Paired-tile form for layers whose weights do not stay resident (deep levels: few pixels, wide channels).  There the
+// L2 -> SM weight stream is the limit: every 128-pixel tile re-reads the whole 9 * Cin * BN weight slab.  This kernel gives one
+// CTA TWO pixel tiles of the same channel block at a time: each weight stage that lands in shared memory feeds the MMAs of both
+// tiles (two accumulators), which halves the weight traffic per output.  Epilogue group g drains tile g of every pair, the pair
+// of accumulators is double-buffered (4 x BN TMEM columns), everything else is as in conv3x3_persist.
+template <int BN>
+__global__ void __launch_bounds__(PS_THREADS) conv3x3_pair(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmO,
+                                                    TmaConvArgs p, PersistArgs q) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int B_BYTES = BN * 128;
+    constexpr int TCOLS = 4 * BN;
+    static_assert(TCOLS <= 512, "two double-buffered accumulator pairs must fit TMEM");
+    __shared__ uint64_t bar_fullA[PS_MAX_A], bar_emptyA[PS_MAX_A], bar_fullB[PS_MAX_B], bar_emptyB[PS_MAX_B];
+    __shared__ uint64_t bar_tfull[2], bar_tempty[2];
+    __shared__ uint64_t bar_ofull[2][PS_MAX_O], bar_oempty[2][PS_MAX_O];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ __align__(16) float bias_s[PS_MAX_COUT];
+
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    constexpr int A_PAIR = 2 * HL_A_STRIDE;                                  // one activation stage = the halos of both tiles
+    uint8_t* smemB = smem + q.a_stages * A_PAIR;
+    uint8_t* smemO = smemB + q.b_stages * B_BYTES;
+    const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int patches = p.ptx * p.pty;
+    const int nkc = p.Cin_p / TM_KC;
+    const int num_units = q.num_tiles;                                       // (pixel-tile pair, channel block)
+
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+        if (p.dst) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmO)) : "memory");
+        for (int s = 0; s < PS_MAX_A; s++) { mbar_init(&bar_fullA[s], 1); mbar_init(&bar_emptyA[s], 1); }
+        for (int s = 0; s < PS_MAX_B; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
+        for (int s = 0; s < 2; s++) { mbar_init(&bar_tfull[s], 1); mbar_init(&bar_tempty[s], 256); }
+        for (int g = 0; g < 2; g++)
+            for (int s = 0; s < PS_MAX_O; s++) { mbar_init(&bar_ofull[g][s], 128); mbar_init(&bar_oempty[g][s], 1); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
+
+    // unit -> pixel tiles 2*pp and 2*pp+1 (the second may lie past the last image: TMA then reads zeros and stores nothing)
+    auto tile_coords = [&](int pi, int& b, int& y0, int& x0) {
+        b = pi / patches;
+        const int pr = pi - b * patches;
+        y0 = (pr / p.ptx) * HL_PH; x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+    };
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ===== TMA producer =====
+            int ia = 0, ib = 0;
+            for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+                const int pp = unit / q.ntiles_n, n0 = (unit - pp * q.ntiles_n) * BN;
+                int b0, y00, x00, b1, y01, x01;
+                tile_coords(2 * pp, b0, y00, x00);
+                tile_coords(2 * pp + 1, b1, y01, x01);
+                for (int kc = 0; kc < nkc; kc++, ia++) {
+                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                    if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+                    mbar_expect_tx(&bar_fullA[sa], (uint32_t)(2 * HL_A_BYTES));
+                    tma_load_4d(smem + (size_t)sa * A_PAIR, &tmA, &bar_fullA[sa], kc * TM_KC, x00 - 1, y00 - 1, b0);
+                    tma_load_4d(smem + (size_t)sa * A_PAIR + HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x01 - 1, y01 - 1, b1);
+                    for (int tap = 0; tap < 9; tap++, ib++) {
+                        const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                        if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
+                        mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
+                        tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (warp-uniform loop, one elected lane issues) =====
+        int ia = 0, ib = 0, iu = 0;
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, iu++) {
+            const int ubuf = iu & 1, ut = iu >> 1;
+            if (ut > 0) mbar_wait(&bar_tempty[ubuf], (uint32_t)((ut - 1) & 1));     // both epilogue groups have drained this accumulator pair
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t dcol0 = tmem_d + (uint32_t)(ubuf * 2 * BN), dcol1 = dcol0 + (uint32_t)BN;
+            for (int kc = 0; kc < nkc; kc++, ia++) {
+                const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t da00 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * A_PAIR), 0);
+                const uint64_t da10 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * A_PAIR + HL_A_STRIDE), 0);
+#pragma unroll 1
+                for (int tap = 0; tap < 9; tap++, ib++) {
+                    const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                    mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
+                    const uint64_t toff = (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                    if (elect_one_sync()) {
+                        if (tap == 0) { umma_tf32(dcol0, da00 + toff, db0, IDESC, kc != 0 ? 1u : 0u); umma_tf32(dcol1, da10 + toff, db0, IDESC, kc != 0 ? 1u : 0u); }
+                        else { umma_tf32_acc(dcol0, da00 + toff, db0, IDESC); umma_tf32_acc(dcol1, da10 + toff, db0, IDESC); }
+#pragma unroll
+                        for (int k = 1; k < TM_KC / 8; k++) {
+                            umma_tf32_acc(dcol0, da00 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                            umma_tf32_acc(dcol1, da10 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                        }
+                        umma_commit(&bar_emptyB[sb]);
+                        if (tap == 8) {
+                            umma_commit(&bar_emptyA[sa]);
+                            if (kc == nkc - 1) umma_commit(&bar_tfull[ubuf]);
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue: group g drains tile g of every pair =====
+        const int g = (warp - 4) >> 2;
+        EpiCtx e;
+        e.bias_s = bias_s;
+        e.smemO_u = smem_u32(smemO) + (uint32_t)(g * q.o_stages * 16384);
+        e.ofull = bar_ofull[g]; e.oempty = bar_oempty[g];
+        e.o_stages = q.o_stages; e.obuf = 0; e.ouse = 0;
+        e.row = (warp & 3) * 32 + lane; e.lane = lane;
+        e.slope = p.slope;
+        e.act_mode = p.act != ACT_RELU ? 0 : ((p.slope >= 0.f && p.slope < 1.f) ? 1 : 2);
+        e.slope_eff = e.act_mode == 0 ? 1.f : p.slope;
+        int iu = 0;
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x, iu++) {
+            const int ubuf = iu & 1, ut = iu >> 1;
+            const int pp = unit / q.ntiles_n, n0 = (unit - pp * q.ntiles_n) * BN;
+            int b, y0, x0;
+            tile_coords(2 * pp + g, b, y0, x0);
+            mbar_wait(&bar_tfull[ubuf], (uint32_t)(ut & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t lane_addr = tmem_d + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((ubuf * 2 + g) * BN);
+            epi_tile<BN>(p, e, lane_addr, &bar_tempty[ubuf], b, y0, x0, n0);
+        }
+    } else if (lane == 0 && p.dst) {
+        // ===== store issuer of group g =====
+        const int g = warp - 2;
+        int obuf = 0, ouse = 0;
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+            const int pp = unit / q.ntiles_n, n0 = (unit - pp * q.ntiles_n) * BN;
+            int b, y0, x0;
+            tile_coords(2 * pp + g, b, y0, x0);
+            for (int sl = 0; sl < BN / 32; sl++) {
+                mbar_wait(&bar_ofull[g][obuf], (uint32_t)(ouse & 1));
+                tma_store_4d(&tmO, smemO + (size_t)(g * q.o_stages + obuf) * 16384, n0 + sl * 32, x0, y0, b);
+                tma_store_commit();
+                tma_store_wait_read<0>();
+                mbar_arrive(&bar_oempty[g][obuf]);
+                if (++obuf == q.o_stages) { obuf = 0; ouse++; }
+            }
+        }
+    }
+    __syncwarp();
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
+}
+
 }  // namespace
 
 static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_trace only
@@ -805,6 +993,21 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
         DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
         DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, q.groups == 2 ? PS_THREADS : 256, smem, tmA, tmB, tmO, p, q);                                         \
+        DC_CHECK_LAUNCH();                                                                                                 \
+        return DINCAE_OK;                                                                                                  \
+    } while (0)
+
+#define PAIR_LAUNCH(BN_)                                                                                                   \
+    do {                                                                                                                   \
+        auto conv3x3_pair_bn##BN_ = conv3x3_pair<BN_>;                                                                     \
+        static int attr_smem = 0;                                                                                          \
+        if (smem > attr_smem) {                                                                                            \
+            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_pair_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));  \
+            attr_smem = smem;                                                                                              \
+        }                                                                                                                  \
+        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
+        DC_LAUNCH(ctx, conv3x3_pair_bn##BN_, grid, PS_THREADS, smem, tmA, tmB, tmO, p, q);                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
     } while (0)
@@ -869,6 +1072,32 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
         if (tune_as > 0 && tune_as < q.a_stages) q.a_stages = tune_as;
         smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 2 * q.o_stages * 16384 + 1024;
         per_sm = 1;
+    }
+    // paired tiles: streamed weights (deep levels), two pixel tiles per CTA share every weight stage
+    static const int tune_pair = dc_env_int("DINCAE_TUNE_PAIR", 1);
+    if (tune_pair && q.groups == 2 && !q.b_resident && bn <= 128 && m_tiles >= 2 && (tune_pair == 2 || (int)dc_cdiv(m_tiles, 2) * q.ntiles_n >= (ctx->num_sms * 3) / 4)) {
+        const int budget = 227 * 1024 - static_smem - 1024;
+        q.o_stages = a.dst ? ((tune_os > 0) ? (tune_os > PS_MAX_O ? PS_MAX_O : tune_os) : 1) : 0;
+        int left = budget - 2 * q.o_stages * 16384 - 2 * (2 * HL_A_STRIDE);
+        int bs = left / bbytes;
+        if (bs > PS_MAX_B) bs = PS_MAX_B;
+        if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
+        if (bs >= 3) {
+            q.b_stages = bs; q.a_stages = 2;
+            left -= bs * bbytes;
+            if (left >= 2 * HL_A_STRIDE) q.a_stages = 3;
+            smem = q.a_stages * 2 * HL_A_STRIDE + q.b_stages * bbytes + 2 * q.o_stages * 16384 + 1024;
+            q.num_tiles = (int)dc_cdiv(m_tiles, 2) * q.ntiles_n;          // units
+            int ctas = ctx->num_sms < q.num_tiles ? ctx->num_sms : q.num_tiles;
+            dim3 grid((unsigned)ctas);
+            alignas(64) CUtensorMap tmA, tmB, tmO;
+            DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
+            if (a.dst) DC_TRY(make_tmap_act(&tmO, a.dst, a.Cout_p, a.W, a.H, a.B, HL_PW, HL_PH));
+            else tmO = tmA;
+            if (bn == 128) PAIR_LAUNCH(128);
+            if (bn == 64) PAIR_LAUNCH(64);
+            PAIR_LAUNCH(32);
+        }
     }
     int ctas = ctx->num_sms * per_sm;                 // persistent
     if (ctas > q.num_tiles) ctas = q.num_tiles;
