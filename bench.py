@@ -360,7 +360,7 @@ def main():
         common = {"kernel": top["kernel"], "share_of_step": top["share"], "launches_per_step": top["launches"] / nprof,
                   "algorithmic_flops_per_launch": top["flops"] / top["launches"], "algorithmic_bytes_per_launch": top["bytes"] / top["launches"],
                   "avg_launch_us": 1e3 * top["ms"] / top["launches"], "traffic": tr_val,
-                  "traffic_note": "dram read+write bytes of the largest launch of this kernel in profiles/r01_ncu_full_top_kernels.csv (ncu --set full)" if tr else None,
+                  "traffic_note": "dram read+write bytes of the largest launch of this kernel in profiles/r01_final_ncu_full_top_kernels.csv (ncu --set full)" if tr else None,
                   "note": "achieved = algorithmic work of all launches of this kernel in %d steps / their CUDA-event time (library per-launch profile)" % nprof}
         if t_bytes >= t_flops:
             ach = top["bytes"] / t_s / 1e9
