@@ -1764,6 +1764,157 @@ __global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CU
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u));
 }
 
+// Weight gradient with a 32-channel operand on one side and 32 or 64 channels on the other (the full- and half-resolution
+// layers): ALL nine taps come out of every MMA.  Per 8x4 pixel patch the 32-channel operand is loaded as a (10 x 4) box and the
+// three dx shifts are stacked in the MMA M dimension (MN-major descriptor with a leading-dimension offset of one pixel =
+// 128 B, 4th block = padding); the other operand is loaded as an (8 x 6) box per 32-channel block and the three dy shifts are
+// stacked in the N dimension the same way (leading-dimension offset of one box row = 1024 B).  So one M=128, N=96, K=8 MMA per
+// box row and channel block replaces nine N=32 MMAs: (128+96)*32 B instead of 9*(128+32)*32 B of shared-memory operand reads,
+// which is what bounds these small-N MMAs.
+//   in_is_m = 1:  M = in  (dx = block i),      N = g  (dy = 2 - block j)
+//   in_is_m = 0:  M = g   (dx = 2 - block i),  N = in (dy = block j)
+constexpr int W9_REGION = 6144;                    // bytes: (10 x 4) box = 5120 + 1 KB of zeroed overrun for the padding block; (8 x 6) box = 6144
+
+template <int NB, int STAGES>
+__global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__ CUtensorMap tmN, WgradTmaArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    constexpr int NCB = NB / 32;                   // 32-channel blocks of the N operand
+    constexpr int STAGE = W9_REGION * (1 + NCB);
+    constexpr uint32_t TCOLS = NCB == 1 ? 128u : 256u;
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int split = blockIdx.x;
+    const int64_t p_lo = (int64_t)split * p.patches_per_split;
+    int64_t p_hi = p_lo + p.patches_per_split;
+    if (p_hi > p.npatches) p_hi = p.npatches;
+    const int nst = (int)(p_hi - p_lo);
+
+    // the overrun of the (discarded) 4th M block must stay finite
+    for (int s = 0; s < STAGES; s++)
+        for (int i = t; i < 1024 / 16; i += 128)
+            reinterpret_cast<float4*>(smem + (size_t)s * STAGE + 5120)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmM)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmN)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TCOLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(96 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+    if (t == 0) {
+        const int per_img = p.ptx * p.pty;
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int64_t pp = p_lo + i;
+            const int b = (int)(pp / per_img);
+            const int r = (int)(pp - (int64_t)b * per_img);
+            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            uint8_t* st = smem + (size_t)s * STAGE;
+            mbar_expect_tx(&bar_full[s], (uint32_t)(5120 + NCB * 6144));
+            tma_load_4d(st, &tmM, &bar_full[s], 0, x0 - 1, y0, b);                                // (32, 10, 4, 1)
+#pragma unroll
+            for (int cb = 0; cb < NCB; cb++)
+                tma_load_4d(st + (1 + cb) * W9_REGION, &tmN, &bar_full[s], cb * 32, x0, y0 - 1, b);   // (32, 8, 6, 1)
+        }
+    } else if (warp == 1) {
+        // MMA issuer: warp-uniform loop, one elected lane issues
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t abase = smem_base + (uint32_t)(s * STAGE);
+            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 128u);                       // M block i = the box shifted by i pixels
+            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W9_REGION, 1024u);  // N block j = the box shifted by j rows
+            if (elect_one_sync()) {
+#pragma unroll
+                for (int h = 0; h < 4; h++) {                                               // one k-step = the 8 pixels of box row h
+#pragma unroll
+                    for (int cb = 0; cb < NCB; cb++) {
+                        const uint64_t da = da0 + (uint64_t)((h * 10 * 128) >> 4), db = db0 + (uint64_t)((cb * W9_REGION + h * 1024) >> 4);
+                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(cb * 96), da, db, IDESC, i != 0 ? 1u : 0u);
+                        else umma_tf32_acc(tmem_d + (uint32_t)(cb * 96), da, db, IDESC);
+                    }
+                }
+                umma_commit(&bar_empty[s]);
+                if (i == nst - 1) umma_commit(&bar_done);
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
+    if (nst > 0) {
+        mbar_wait(&bar_done, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+    const int bi = t >> 5, cm = t & 31;            // M block (warp) and channel of the 32-channel operand
+#pragma unroll 1
+    for (int cb = 0; cb < NCB; cb++) {
+#pragma unroll 1
+        for (int j = 0; j < 3; j++) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < 32; c0 += 16) {
+                uint32_t r[16];
+                if (nst > 0) {
+                    tmem_ld16(lane_addr + (uint32_t)(cb * 96 + j * 32 + c0), r);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 16; k++) r[k] = 0u;
+                }
+                if (bi < 3) {
+                    if (p.in_is_m) {               // thread = ci, 16 consecutive co
+                        const int tap = (2 - j) * 3 + bi;
+                        float* o = out + ((size_t)tap * p.Cin_p + cm) * p.Cout_p + cb * 32 + c0;
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            *reinterpret_cast<float4*>(o + 4 * k) = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
+                    } else {                       // thread = co (lanes coalesce), column = ci
+                        const int tap = j * 3 + (2 - bi);
+#pragma unroll
+                        for (int k = 0; k < 16; k++)
+                            out[((size_t)tap * p.Cin_p + cb * 32 + c0 + k) * p.Cout_p + cm] = __uint_as_float(r[k]);
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TCOLS));
+}
+
+int32_t make_tmap_box(CUtensorMap* m, const float* ptr, int C, int W, int H, int B, int bw, int bh) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(box %dx%d C=%d W=%d H=%d B=%d) failed: %d", bw, bh, C, W, H, B, (int)r);
+    return DINCAE_OK;
+}
+
 int32_t make_tmap_in32(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
     EncodeTiledFn enc = get_encode();
     DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
@@ -1793,6 +1944,11 @@ int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, i
 template <int BN, int STAGES>
 constexpr int wg_smem_bytes() { return STAGES * (4 * WG_BLOCK + (BN / 32) * WG_BLOCK) + 1024; }
 
+static bool wgrad9_selected(int Cin_p, int Cout_p) {
+    static const int on = dc_env_int("DINCAE_WGRAD9", 1);
+    return on && ((Cin_p == 32 && (Cout_p == 32 || Cout_p == 64)) || (Cin_p == 64 && Cout_p == 32));
+}
+
 void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64_t& npatches, int64_t& pps, int& in_is_m) {
     const int Cin_p = a.in.C, Cout_p = a.Cout_p;
     in_is_m = Cin_p >= Cout_p;
@@ -1802,7 +1958,9 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
     npatches = (int64_t)a.B * dc_cdiv(a.H, 4) * dc_cdiv(a.W, 8);
     int tiles = mtiles * ntiles * (bn == 32 ? 3 : 9);     // three taps per CTA in the halo variant (narrow N only)
     if (Cin_p == 32 && Cout_p == 32) tiles = 1;           // wgrad32_kernel: all nine taps in one CTA
-    splits = ((bn == 32 ? 3 : 2) * num_sms + tiles - 1) / tiles;
+    const bool w9 = wgrad9_selected(Cin_p, Cout_p);
+    if (w9) { tiles = 1; in_is_m = Cin_p == 32; }          // wgrad9_kernel: all nine taps in every MMA; M = the 32-channel side
+    splits = (((bn == 32 && !w9) || (w9 && Cin_p == 32 && Cout_p == 32) ? 3 : 2) * num_sms + tiles - 1) / tiles;   // CTAs per SM the kernels fit (smem, TMEM)
     int64_t maxs = dc_cdiv(npatches, 4);
     if (splits > maxs) splits = (int)maxs;
     // the split partials are written and re-read once: keep them below ~16 MB per layer
@@ -1875,7 +2033,26 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     alignas(64) CUtensorMap tmIn, tmG;
     DC_TRY(make_tmap_patch(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
     DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
-    if (Cin_p == 32 && Cout_p == 32) {
+    if (wgrad9_selected(Cin_p, Cout_p)) {
+        alignas(64) CUtensorMap tmM, tmN;
+        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, 32, a.W, a.H, a.B, 10, 4));
+        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, 6));
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * Cin_p * Cout_p * (double)a.B * a.H * a.W, a.work_bytes);
+        if (p.n_ch == 32) {
+            auto wgrad9_n32 = wgrad9_kernel<32, 6>;
+            constexpr int smem = 6 * W9_REGION * 2 + 1024;
+            static bool attr_set = false;
+            if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad9_n32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
+            DC_LAUNCH(ctx, wgrad9_n32, (unsigned)splits, 128, smem, tmM, tmN, p);
+        } else {
+            auto wgrad9_n64 = wgrad9_kernel<64, 6>;
+            constexpr int smem = 6 * W9_REGION * 3 + 1024;
+            static bool attr_set = false;
+            if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad9_n64, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
+            DC_LAUNCH(ctx, wgrad9_n64, (unsigned)splits, 128, smem, tmM, tmN, p);
+        }
+        DC_CHECK_LAUNCH();
+    } else if (Cin_p == 32 && Cout_p == 32) {
         DC_TRY(make_tmap_in32(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
         auto wgrad32 = wgrad32_kernel<6>;
         constexpr int smem = 6 * W32_STAGE + 1024;
