@@ -1902,6 +1902,132 @@ __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUt
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TCOLS));
 }
 
+// The same idea for wide layers: M = 128 channels of the wider operand (four 32-channel boxes of the (10 x 4) patch halo), N = 32
+// channels of the other operand with the three dy shifts stacked (one (8 x 6) box), and the three dx shifts as three start
+// offsets of the M descriptor into three accumulators (3 x 96 TMEM columns).  One CTA = one (128-channel, 32-channel) block of
+// all nine taps; per 32 pixels it loads 26 KB where the one-tap-per-CTA kernel loads 9 x (16 + 4*BN/32) KB -- the deep levels
+// are bound by exactly this L2 -> SM stream.
+//   in_is_m = 1:  M = in  (offset dx),      N = g  (dy = 2 - block j)
+//   in_is_m = 0:  M = g   (offset 2 - dx),  N = in (dy = block j)
+constexpr int WM_MREGION = 4 * 5120, WM_STAGE = WM_MREGION + W9_REGION;      // 26 KB
+
+template <int STAGES>
+__global__ void __launch_bounds__(128) wgradm_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__ CUtensorMap tmN, WgradTmaArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ uint64_t bar_full[STAGES];
+    __shared__ uint64_t bar_empty[STAGES];
+    __shared__ uint64_t bar_done;
+    __shared__ uint32_t tmem_base_s;
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const uint32_t smem_base = smem_u32(smem);
+    const int t = threadIdx.x, warp = t >> 5;
+    const int split = blockIdx.x, m0 = blockIdx.y * 128, n0 = blockIdx.z * 32;
+    const int64_t p_lo = (int64_t)split * p.patches_per_split;
+    int64_t p_hi = p_lo + p.patches_per_split;
+    if (p_hi > p.npatches) p_hi = p.npatches;
+    const int nst = (int)(p_hi - p_lo);
+
+    if (t == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmM)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmN)) : "memory");
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
+        mbar_init(&bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512u));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_d = tmem_base_s;
+    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(96 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+    if (t == 0) {
+        const int per_img = p.ptx * p.pty;
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
+            const int64_t pp = p_lo + i;
+            const int b = (int)(pp / per_img);
+            const int r = (int)(pp - (int64_t)b * per_img);
+            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            uint8_t* st = smem + (size_t)s * WM_STAGE;
+            mbar_expect_tx(&bar_full[s], (uint32_t)WM_STAGE);
+#pragma unroll
+            for (int j = 0; j < 4; j++) tma_load_4d(st + j * 5120, &tmM, &bar_full[s], m0 + j * 32, x0 - 1, y0, b);   // channels past the tensor read zeros
+            tma_load_4d(st + WM_MREGION, &tmN, &bar_full[s], n0, x0, y0 - 1, b);
+        }
+    } else if (warp == 1) {
+        for (int i = 0; i < nst; i++) {
+            const int s = i % STAGES, u = i / STAGES;
+            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t abase = smem_base + (uint32_t)(s * WM_STAGE);
+            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 5120u);                          // M block = next 32-channel box
+            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)WM_MREGION, 1024u);   // N block j = the box shifted by j rows
+            if (elect_one_sync()) {
+#pragma unroll
+                for (int h = 0; h < 4; h++) {
+#pragma unroll
+                    for (int dx = 0; dx < 3; dx++) {
+                        const uint64_t da = da0 + (uint64_t)((h * 1280 + dx * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
+                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(dx * 96), da, db, IDESC, i != 0 ? 1u : 0u);
+                        else umma_tf32_acc(tmem_d + (uint32_t)(dx * 96), da, db, IDESC);
+                    }
+                }
+                umma_commit(&bar_empty[s]);
+                if (i == nst - 1) umma_commit(&bar_done);
+            }
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
+    if (nst > 0) {
+        mbar_wait(&bar_done, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
+    const int mch = m0 + t;
+#pragma unroll 1
+    for (int o = 0; o < 3; o++) {                  // descriptor offset o: dx = o (in_is_m) or 2 - o
+#pragma unroll 1
+        for (int j = 0; j < 3; j++) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < 32; c0 += 16) {
+                uint32_t r[16];
+                if (nst > 0) {
+                    tmem_ld16(lane_addr + (uint32_t)(o * 96 + j * 32 + c0), r);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 16; k++) r[k] = 0u;
+                }
+                if (mch < p.m_ch) {
+                    if (p.in_is_m) {               // thread = ci, 16 consecutive co
+                        const int tap = (2 - j) * 3 + o;
+                        float* dst = out + ((size_t)tap * p.Cin_p + mch) * p.Cout_p + n0 + c0;
+#pragma unroll
+                        for (int k = 0; k < 4; k++)
+                            *reinterpret_cast<float4*>(dst + 4 * k) = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
+                    } else {                       // thread = co (lanes coalesce), column = ci
+                        const int tap = j * 3 + (2 - o);
+#pragma unroll
+                        for (int k = 0; k < 16; k++)
+                            out[((size_t)tap * p.Cin_p + n0 + c0 + k) * p.Cout_p + mch] = __uint_as_float(r[k]);
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(512u));
+}
+
 int32_t make_tmap_box(CUtensorMap* m, const float* ptr, int C, int W, int H, int B, int bw, int bh) {
     EncodeTiledFn enc = get_encode();
     DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
@@ -1944,6 +2070,10 @@ int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, i
 template <int BN, int STAGES>
 constexpr int wg_smem_bytes() { return STAGES * (4 * WG_BLOCK + (BN / 32) * WG_BLOCK) + 1024; }
 
+static bool wgradm_selected() {
+    static const int on = dc_env_int("DINCAE_WGRADM", 1);
+    return on != 0;
+}
 static bool wgrad9_selected(int Cin_p, int Cout_p) {
     static const int on = dc_env_int("DINCAE_WGRAD9", 1);
     return on && ((Cin_p == 32 && (Cout_p == 32 || Cout_p == 64)) || (Cin_p == 64 && Cout_p == 32));
@@ -1960,6 +2090,11 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
     if (Cin_p == 32 && Cout_p == 32) tiles = 1;           // wgrad32_kernel: all nine taps in one CTA
     const bool w9 = wgrad9_selected(Cin_p, Cout_p);
     if (w9) { tiles = 1; in_is_m = Cin_p == 32; }          // wgrad9_kernel: all nine taps in every MMA; M = the 32-channel side
+    const bool wm = !w9 && wgradm_selected();
+    if (wm) {                                              // wgradm_kernel: one CTA per SM, (128-channel, 32-channel) blocks of all nine taps
+        tiles = mtiles * (n_ch / 32);
+        splits = (num_sms + tiles - 1) / tiles;
+    } else
     splits = (((bn == 32 && !w9) || (w9 && Cin_p == 32 && Cout_p == 32) ? 3 : 2) * num_sms + tiles - 1) / tiles;   // CTAs per SM the kernels fit (smem, TMEM)
     int64_t maxs = dc_cdiv(npatches, 4);
     if (splits > maxs) splits = (int)maxs;
@@ -2051,6 +2186,18 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
             if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad9_n64, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
             DC_LAUNCH(ctx, wgrad9_n64, (unsigned)splits, 128, smem, tmM, tmN, p);
         }
+        DC_CHECK_LAUNCH();
+    } else if (wgradm_selected()) {
+        alignas(64) CUtensorMap tmM, tmN;
+        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, p.m_ch, a.W, a.H, a.B, 10, 4));
+        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, 6));
+        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * Cin_p * Cout_p * (double)a.B * a.H * a.W, a.work_bytes);
+        auto wgradm = wgradm_kernel<7>;
+        constexpr int smem = 7 * WM_STAGE + 1024;
+        static bool attr_set = false;
+        if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgradm, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
+        dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(p.n_ch / 32));
+        DC_LAUNCH(ctx, wgradm, grid, 128, smem, tmM, tmN, p);
         DC_CHECK_LAUNCH();
     } else if (Cin_p == 32 && Cout_p == 32) {
         DC_TRY(make_tmap_in32(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
