@@ -31,6 +31,8 @@ struct ConvArgs {
     const float* wgtK;    // tensor-core path: K-major copy [Cout_p][ldk] (values pre-rounded to TF32), or NULL
     int ldk;              // 9*Cin_p
     int in_is_tf32;       // the input tensor already holds TF32-representable values (TMA path needs no producer math)
+    int in_real_C;        // 0 or the number of leading input channels that can be non-zero (the rest is zero padding): the persistent
+                          // tensor-core kernel then skips the K = 8 steps that would only multiply zeros
     const float* bias;    // [Cout_p] or NULL
     int Cout_p;
     int act;

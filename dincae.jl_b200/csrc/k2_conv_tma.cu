@@ -467,6 +467,7 @@ struct PersistArgs {
     int b_resident;
     int o_stages;              // 16 KB output staging slabs per epilogue group (1 or 2)
     int groups;                // epilogue groups (1: 256 threads, 2: 384 threads)
+    int ksteps;                // K = 8 steps over the input channels that are not zero padding (= Cin_p / 8 when unknown)
     long long* trace;          // tuning aid (dincae_debug_conv): clock64 stamps of CTA 0, 3 roles x 64 slots; nullptr in production
 };
 
@@ -717,6 +718,7 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
                 const uint64_t da0 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * HL_A_STRIDE), 0);
                 if (q.b_resident) {
                     const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(kc * 9 * B_BYTES));
+                    const int ks = q.ksteps - kc * (TM_KC / 8);           // >= 1: steps of this chunk that are not zero padding
                     if (elect_one_sync()) {
 #pragma unroll
                         for (int tap = 0; tap < 9; tap++) {
@@ -725,7 +727,7 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
                                 const uint64_t da = da0 + (uint64_t)((((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4) + 2 * k);
                                 const uint64_t db = db0 + (uint64_t)((tap * B_BYTES >> 4) + 2 * k);
                                 if (tap == 0 && k == 0) umma_tf32(dcol, da, db, IDESC, kc != 0 ? 1u : 0u);
-                                else umma_tf32_acc(dcol, da, db, IDESC);
+                                else if (k < ks) umma_tf32_acc(dcol, da, db, IDESC);
                             }
                         }
                         umma_commit(&bar_emptyA[sa]);
@@ -1033,6 +1035,8 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     q.ntiles_n = a.Cout_p / bn;
     q.num_tiles = m_tiles * q.ntiles_n;
     q.trace = g_persist_trace;
+    q.ksteps = a.in.C / 8;
+    if (a.in_real_C > 0 && a.in_real_C < a.in.C) q.ksteps = (int)dc_cdiv(a.in_real_C, 8);
     const int bbytes = bn * 128;
     const int resident_bytes = nkc * 9 * bbytes;
     // shared-memory plan.  Narrow resident layers: two CTAs per SM, each with one epilogue group, two activation stages and

@@ -74,6 +74,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
         a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = 1;     // X[0] from pack, X[l>=1] from pool_kernel (both rounded on store)
+        a.in_real_C = e.Cin;                                                               // channels past Cin are zero padding
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
@@ -187,6 +188,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
         a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = 1;   // GD[l>=1] from upbwd, GD0 from pack (both rounded on store)
+        a.in_real_C = d.Cout;                                                               // the gradient tensor's channels past Cout are zero
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         a.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
