@@ -344,7 +344,7 @@ __global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits
 // planar (WHCN) -> NHWC: a warp moves 32 consecutive pixels; reads are coalesced along pixels (one channel plane at a time),
 // a padded smem tile transposes, writes are coalesced along channels (4 pixels x 128 B per store instruction)
 __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
-                                                          int B, int HW, float* __restrict__ dst, int Cp, int rnd) {
+                                                          int B, int HW, float* __restrict__ dst, int Cp, int Cw, int rnd) {
     __shared__ float tile[8][32][33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t total = (int64_t)B * HW;
@@ -353,8 +353,8 @@ __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restric
     const int64_t m = m0 + lane;
     const bool pv = m < total;
     const int b = pv ? (int)(m / HW) : 0, r = pv ? (int)(m - (int64_t)b * HW) : 0;
-    for (int cg = 0; cg < Cp; cg += 32) {
-        const int nc = Cp - cg < 32 ? Cp - cg : 32;
+    for (int cg = 0; cg < Cw; cg += 32) {                  // channels >= Cw are zero padding and stay as the buffer was created (zeros)
+        const int nc = Cw - cg < 32 ? Cw - cg : 32;
         for (int c = 0; c < nc; c++) {
             const int cc = cg + c;
             float v = 0.f;
@@ -606,26 +606,26 @@ __global__ void up_bilinear_bwd_kernel(const float* __restrict__ gu, int B, int 
     }
 }
 
-__global__ void make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, float* __restrict__ wK, float* __restrict__ wTK,
-                               const WLayerDesc* __restrict__ tab, int nlayers, int64_t total) {
-    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    int l = 0;
-    int64_t base = 0;
-    while (l < nlayers - 1 && i >= base + tab[l].n) { base += tab[l].n; l++; }
-    int64_t j = i - base;                       // index into wT of layer l: (tapT*Cout_p + co)*Cin_p + ci
-    int Cin_p = tab[l].Cin_p, Cout_p = tab[l].Cout_p;
-    int ci = (int)(j % Cin_p);
-    int64_t t = j / Cin_p;
-    int co = (int)(t % Cout_p);
-    int tapT = (int)(t / Cout_p);
-    float v = w[tab[l].w_off + ((size_t)(8 - tapT) * Cin_p + ci) * Cout_p + co];
-    wT[tab[l].wT_off + j] = v;
-    if (wK) {
-        float r = round_tf32(v);
-        int tap = 8 - tapT;
-        wK[tab[l].wk_off + (size_t)co * (9 * Cin_p) + (size_t)tap * Cin_p + ci] = r;
-        wTK[tab[l].wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = r;
+// derived weight copies, one layer per blockIdx.y.  Pass A walks the wT index (ci fastest): wT and wK are written coalesced,
+// the strided reads of w hit L2.  Pass B walks the wTK index (co fastest): read and write are both coalesced.
+__global__ void __launch_bounds__(256) make_wT_kernel(const float* __restrict__ w, float* __restrict__ wT, float* __restrict__ wK, float* __restrict__ wTK,
+                                                      const WLayerDesc* __restrict__ tab, int nlayers) {
+    const WLayerDesc L = tab[blockIdx.y];
+    const unsigned Cin_p = (unsigned)L.Cin_p, Cout_p = (unsigned)L.Cout_p, n = (unsigned)L.n;
+    const float* wl = w + L.w_off;
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        // j = (tapT*Cout_p + co)*Cin_p + ci
+        const unsigned ci = j % Cin_p, t = j / Cin_p, co = t % Cout_p, tapT = t / Cout_p, tap = 8u - tapT;
+        const float v = wl[((size_t)tap * Cin_p + ci) * Cout_p + co];
+        wT[L.wT_off + j] = v;
+        if (wK) wK[L.wk_off + (size_t)co * (9 * Cin_p) + (size_t)tap * Cin_p + ci] = round_tf32(v);
+    }
+    if (wTK) {
+        for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+            // j = (tap*Cin_p + ci)*Cout_p + co  (the layout of w itself)
+            const unsigned co = j % Cout_p, t = j / Cout_p, ci = t % Cin_p, tap = t / Cin_p, tapT = 8u - tap;
+            wTK[L.wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(wl[j]);
+        }
     }
 }
 
@@ -752,7 +752,9 @@ static int k2_row_blocks(dincae_ctx* ctx, int64_t rows, int64_t n_elems4) {
 int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
     int64_t M = (int64_t)B * H * W;
     if (M == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
+    int Cw = (int)dc_round_up(C0 + C1, 8);                  // whole 32-byte sectors; the rest of the row is never written (zero since allocation)
+    if (Cw > Cp) Cw = Cp;
+    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -823,8 +825,9 @@ int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W
 }
 
 int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, float* wK, float* wTK, const WLayerDesc* d_table, int nlayers, int64_t total) {
-    if (total == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, make_wT_kernel, (unsigned)dc_cdiv(total, 256), 256, 0, w, wT, wK, wTK, d_table, nlayers, total);
+    if (total == 0 || nlayers == 0) return DINCAE_OK;
+    dim3 grid(48u, (unsigned)nlayers);                      // layers differ in size; 48 x 256 threads stride over each
+    DC_LAUNCH(ctx, make_wT_kernel, grid, 256, 0, w, wT, wK, wTK, d_table, nlayers);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
