@@ -1777,13 +1777,18 @@ __global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CU
 // which is what bounds these small-N MMAs.
 //   in_is_m = 1:  M = in  (dx = block i),      N = g  (dy = 2 - block j)
 //   in_is_m = 0:  M = g   (dx = 2 - block i),  N = in (dy = block j)
-constexpr int W9_REGION = 6144;                    // bytes: (10 x 4) box = 5120 + 1 KB of zeroed overrun for the padding block; (8 x 6) box = 6144
+// Patches are 8 pixels wide and W9_PR rows high.  tcgen05.commit costs a pipeline drain (~250 cycles measured), so one commit
+// (= one stage) should cover many MMAs: 8 rows = 8 k-steps per stage.
+constexpr int W9_PR = 8;
+constexpr int W9_MBOX = 10 * W9_PR * 128;          // (10 x PR) box of the 32-channel operand
+constexpr int W9_MREGION = W9_MBOX + 1024;         // + zeroed overrun read by the (discarded) padding block
+constexpr int W9_NBOX = 8 * (W9_PR + 2) * 128;     // (8 x (PR+2)) box per 32-channel block of the other operand (multiple of 1024)
 
 template <int NB, int STAGES>
 __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__ CUtensorMap tmN, WgradTmaArgs p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     constexpr int NCB = NB / 32;                   // 32-channel blocks of the N operand
-    constexpr int STAGE = W9_REGION * (1 + NCB);
+    constexpr int STAGE = W9_MREGION + NCB * W9_NBOX;
     constexpr uint32_t TCOLS = NCB == 1 ? 128u : 256u;
     __shared__ uint64_t bar_full[STAGES];
     __shared__ uint64_t bar_empty[STAGES];
@@ -1801,7 +1806,7 @@ __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUt
     // the overrun of the (discarded) 4th M block must stay finite
     for (int s = 0; s < STAGES; s++)
         for (int i = t; i < 1024 / 16; i += 128)
-            reinterpret_cast<float4*>(smem + (size_t)s * STAGE + 5120)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            reinterpret_cast<float4*>(smem + (size_t)s * STAGE + W9_MBOX)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     if (t == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmM)) : "memory");
@@ -1829,13 +1834,13 @@ __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUt
             const int64_t pp = p_lo + i;
             const int b = (int)(pp / per_img);
             const int r = (int)(pp - (int64_t)b * per_img);
-            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            const int y0 = (r / p.ptx) * W9_PR, x0 = (r - (r / p.ptx) * p.ptx) * 8;
             uint8_t* st = smem + (size_t)s * STAGE;
-            mbar_expect_tx(&bar_full[s], (uint32_t)(5120 + NCB * 6144));
-            tma_load_4d(st, &tmM, &bar_full[s], 0, x0 - 1, y0, b);                                // (32, 10, 4, 1)
+            mbar_expect_tx(&bar_full[s], (uint32_t)(W9_MBOX + NCB * W9_NBOX));
+            tma_load_4d(st, &tmM, &bar_full[s], 0, x0 - 1, y0, b);                                // (32, 10, PR, 1)
 #pragma unroll
             for (int cb = 0; cb < NCB; cb++)
-                tma_load_4d(st + (1 + cb) * W9_REGION, &tmN, &bar_full[s], cb * 32, x0, y0 - 1, b);   // (32, 8, 6, 1)
+                tma_load_4d(st + W9_MREGION + cb * W9_NBOX, &tmN, &bar_full[s], cb * 32, x0, y0 - 1, b);   // (32, 8, PR+2, 1)
         }
     } else if (warp == 1) {
         // MMA issuer: warp-uniform loop, one elected lane issues
@@ -1845,13 +1850,13 @@ __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUt
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t abase = smem_base + (uint32_t)(s * STAGE);
             const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 128u);                       // M block i = the box shifted by i pixels
-            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W9_REGION, 1024u);  // N block j = the box shifted by j rows
+            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W9_MREGION, 1024u);  // N block j = the box shifted by j rows
             if (elect_one_sync()) {
 #pragma unroll
-                for (int h = 0; h < 4; h++) {                                               // one k-step = the 8 pixels of box row h
+                for (int h = 0; h < W9_PR; h++) {                                           // one k-step = the 8 pixels of box row h
 #pragma unroll
                     for (int cb = 0; cb < NCB; cb++) {
-                        const uint64_t da = da0 + (uint64_t)((h * 10 * 128) >> 4), db = db0 + (uint64_t)((cb * W9_REGION + h * 1024) >> 4);
+                        const uint64_t da = da0 + (uint64_t)((h * 10 * 128) >> 4), db = db0 + (uint64_t)((cb * W9_NBOX + h * 1024) >> 4);
                         if (h == 0) umma_tf32(tmem_d + (uint32_t)(cb * 96), da, db, IDESC, i != 0 ? 1u : 0u);
                         else umma_tf32_acc(tmem_d + (uint32_t)(cb * 96), da, db, IDESC);
                     }
@@ -1913,7 +1918,7 @@ __global__ void __launch_bounds__(128) wgrad9_kernel(const __grid_constant__ CUt
 // are bound by exactly this L2 -> SM stream.
 //   in_is_m = 1:  M = in  (offset dx),      N = g  (dy = 2 - block j)
 //   in_is_m = 0:  M = g   (offset 2 - dx),  N = in (dy = block j)
-constexpr int WM_MREGION = 4 * 5120, WM_STAGE = WM_MREGION + W9_REGION;      // 26 KB
+constexpr int WM_MREGION = 4 * W9_MBOX, WM_STAGE = WM_MREGION + W9_NBOX;      // 50 KB
 
 template <int STAGES>
 __global__ void __launch_bounds__(128) wgradm_kernel(const __grid_constant__ CUtensorMap tmM, const __grid_constant__ CUtensorMap tmN, WgradTmaArgs p) {
@@ -1957,11 +1962,11 @@ __global__ void __launch_bounds__(128) wgradm_kernel(const __grid_constant__ CUt
             const int64_t pp = p_lo + i;
             const int b = (int)(pp / per_img);
             const int r = (int)(pp - (int64_t)b * per_img);
-            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
+            const int y0 = (r / p.ptx) * W9_PR, x0 = (r - (r / p.ptx) * p.ptx) * 8;
             uint8_t* st = smem + (size_t)s * WM_STAGE;
             mbar_expect_tx(&bar_full[s], (uint32_t)WM_STAGE);
 #pragma unroll
-            for (int j = 0; j < 4; j++) tma_load_4d(st + j * 5120, &tmM, &bar_full[s], m0 + j * 32, x0 - 1, y0, b);   // channels past the tensor read zeros
+            for (int j = 0; j < 4; j++) tma_load_4d(st + j * W9_MBOX, &tmM, &bar_full[s], m0 + j * 32, x0 - 1, y0, b);   // channels past the tensor read zeros
             tma_load_4d(st + WM_MREGION, &tmN, &bar_full[s], n0, x0, y0 - 1, b);
         }
     } else if (warp == 1) {
@@ -1970,11 +1975,11 @@ __global__ void __launch_bounds__(128) wgradm_kernel(const __grid_constant__ CUt
             mbar_wait(&bar_full[s], (uint32_t)(u & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t abase = smem_base + (uint32_t)(s * WM_STAGE);
-            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 5120u);                          // M block = next 32-channel box
+            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, (uint32_t)W9_MBOX);                // M block = next 32-channel box
             const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)WM_MREGION, 1024u);   // N block j = the box shifted by j rows
             if (elect_one_sync()) {
 #pragma unroll
-                for (int h = 0; h < 4; h++) {
+                for (int h = 0; h < W9_PR; h++) {
 #pragma unroll
                     for (int dx = 0; dx < 3; dx++) {
                         const uint64_t da = da0 + (uint64_t)((h * 1280 + dx * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
@@ -2083,13 +2088,15 @@ static bool wgrad9_selected(int Cin_p, int Cout_p) {
     return on && ((Cin_p == 32 && (Cout_p == 32 || Cout_p == 64)) || (Cin_p == 64 && Cout_p == 32));
 }
 
+static int wgrad_patch_rows(int Cin_p, int Cout_p) { return (wgrad9_selected(Cin_p, Cout_p) || wgradm_selected()) ? 8 : 4; }
+
 void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64_t& npatches, int64_t& pps, int& in_is_m) {
     const int Cin_p = a.in.C, Cout_p = a.Cout_p;
     in_is_m = Cin_p >= Cout_p;
     const int m_ch = in_is_m ? Cin_p : Cout_p, n_ch = in_is_m ? Cout_p : Cin_p;
     bn = n_ch % 256 == 0 ? 256 : (n_ch % 128 == 0 ? 128 : (n_ch % 64 == 0 ? 64 : 32));
     const int mtiles = (m_ch + 127) / 128, ntiles = n_ch / bn;
-    npatches = (int64_t)a.B * dc_cdiv(a.H, 4) * dc_cdiv(a.W, 8);
+    npatches = (int64_t)a.B * dc_cdiv(a.H, wgrad_patch_rows(Cin_p, Cout_p)) * dc_cdiv(a.W, 8);
     int tiles = mtiles * ntiles * (bn == 32 ? 3 : 9);     // three taps per CTA in the halo variant (narrow N only)
     if (Cin_p == 32 && Cout_p == 32) tiles = 1;           // wgrad32_kernel: all nine taps in one CTA
     const bool w9 = wgrad9_selected(Cin_p, Cout_p);
@@ -2100,7 +2107,7 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
         splits = (num_sms + tiles - 1) / tiles;
     } else
     splits = (((bn == 32 && !w9) || (w9 && Cin_p == 32 && Cout_p == 32) ? 3 : 2) * num_sms + tiles - 1) / tiles;   // CTAs per SM the kernels fit (smem, TMEM)
-    int64_t maxs = dc_cdiv(npatches, 4);
+    int64_t maxs = dc_cdiv(npatches, wgrad_patch_rows(Cin_p, Cout_p) == 8 ? 2 : 4);
     if (splits > maxs) splits = (int)maxs;
     // the split partials are written and re-read once: keep them below ~16 MB per layer
     int64_t cap = (int64_t)(16 << 20) / ((int64_t)9 * Cin_p * Cout_p * 4);
@@ -2165,7 +2172,7 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     const int cs_blocks = (int)(M < (int64_t)4 * ctx->num_sms * 32 ? dc_cdiv(M, 32) : 4 * ctx->num_sms);
     DC_REQUIRE(scratch_bytes >= ((size_t)splits * nW + (size_t)cs_blocks * Cout_p) * sizeof(float), DINCAE_ESIZE, "k2_wgrad_tma: scratch too small");
     WgradTmaArgs p;
-    p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, 4);
+    p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, wgrad_patch_rows(Cin_p, Cout_p));
     p.Cin_p = Cin_p; p.Cout_p = Cout_p; p.in_is_m = in_is_m;
     p.m_ch = in_is_m ? Cin_p : Cout_p; p.n_ch = in_is_m ? Cout_p : Cin_p;
     p.npatches = np; p.patches_per_split = pps; p.partial = (float*)scratch;
@@ -2174,18 +2181,18 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
     if (wgrad9_selected(Cin_p, Cout_p)) {
         alignas(64) CUtensorMap tmM, tmN;
-        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, 32, a.W, a.H, a.B, 10, 4));
-        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, 6));
+        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, 32, a.W, a.H, a.B, 10, W9_PR));
+        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, W9_PR + 2));
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * Cin_p * Cout_p * (double)a.B * a.H * a.W, a.work_bytes);
         if (p.n_ch == 32) {
-            auto wgrad9_n32 = wgrad9_kernel<32, 6>;
-            constexpr int smem = 6 * W9_REGION * 2 + 1024;
+            auto wgrad9_n32 = wgrad9_kernel<32, 3>;
+            constexpr int smem = 3 * (W9_MREGION + W9_NBOX) + 1024;
             static bool attr_set = false;
             if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad9_n32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
             DC_LAUNCH(ctx, wgrad9_n32, (unsigned)splits, 128, smem, tmM, tmN, p);
         } else {
-            auto wgrad9_n64 = wgrad9_kernel<64, 6>;
-            constexpr int smem = 6 * W9_REGION * 3 + 1024;
+            auto wgrad9_n64 = wgrad9_kernel<64, 3>;
+            constexpr int smem = 3 * (W9_MREGION + 2 * W9_NBOX) + 1024;
             static bool attr_set = false;
             if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad9_n64, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
             DC_LAUNCH(ctx, wgrad9_n64, (unsigned)splits, 128, smem, tmM, tmN, p);
@@ -2193,11 +2200,11 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
         DC_CHECK_LAUNCH();
     } else if (wgradm_selected()) {
         alignas(64) CUtensorMap tmM, tmN;
-        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, p.m_ch, a.W, a.H, a.B, 10, 4));
-        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, 6));
+        DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, p.m_ch, a.W, a.H, a.B, 10, W9_PR));
+        DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, W9_PR + 2));
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * Cin_p * Cout_p * (double)a.B * a.H * a.W, a.work_bytes);
-        auto wgradm = wgradm_kernel<7>;
-        constexpr int smem = 7 * WM_STAGE + 1024;
+        auto wgradm = wgradm_kernel<4>;
+        constexpr int smem = 4 * WM_STAGE + 1024;
         static bool attr_set = false;
         if (!attr_set) { DC_CHECK_CUDA(cudaFuncSetAttribute(wgradm, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr_set = true; }
         dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(p.n_ch / 32));

@@ -42,7 +42,7 @@ for (S, ci, co) in shapes:
 if os.environ.get("TRACE"):
     tr = lib.dincae_debug_conv_trace
     tr.argtypes = [ctypes.c_void_p]; tr.restype = ctypes.c_int32
-    for (S, ci, co) in shapes[:4]:
+    for (S, ci, co) in shapes[:int(os.environ.get('NTRACE', '4'))]:
         x = torch.randn(B, S, S, ci, device="cuda"); w = torch.randn(9 * ci * co, device="cuda") * 0.05
         wK = torch.randn(co * 9 * ci, device="cuda") * 0.05; bias = torch.randn(co, device="cuda")
         out = torch.empty(B, S, S, co, device="cuda")
