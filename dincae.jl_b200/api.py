@@ -223,6 +223,39 @@ class Model:
         m = np.ascontiguousarray(m, np.float32); v = np.ascontiguousarray(v, np.float32)
         L.check(self._lib.dincae_model_set_opt_state(self.handle, L.ptr(m), L.ptr(v), m.size, int(t)))
 
+    # -- checkpoint (SURVEY N1): weights in Flux.trainables order as Flux.state/loadmodel! walk them (src/model.jl:366-399,
+    #    :599-620), plus the Adam state the reference does not save (so a run can really be resumed)
+    def flux_layout(self):
+        """[(name, shape, offset)] of the flat parameter vector: per chain enc1..encL then decL..dec1, W as (3,3,cin,cout)
+        column-major (kw fastest, Flux's true-convolution kernel) followed by b (cout)."""
+        nf = list(self.cfg.enc_nfilter_internal)
+        out, off = [], 0
+        for c in range(len(self.cfg.loss_weights_refine)):
+            cin0 = self.cfg.ninput + (2 * self.cfg.noutput if c > 0 else 0)
+            enc = [cin0] + nf
+            dec = [2 * self.cfg.noutput] + nf
+            layers = [("chain%d.enc%d" % (c + 1, l + 1), enc[l], enc[l + 1]) for l in range(len(nf))]
+            layers += [("chain%d.dec%d" % (c + 1, l + 1), dec[l + 1], dec[l]) for l in reversed(range(len(nf)))]
+            for name, ci, co in layers:
+                out.append((name + ".weight", (3, 3, ci, co), off)); off += 9 * ci * co
+                out.append((name + ".bias", (co,), off)); off += co
+        assert off == self.num_params, (off, self.num_params)
+        return out
+
+    def save_checkpoint(self, path, **extra):
+        m, v, t = self.get_opt_state()
+        cfg = {k: (list(val) if isinstance(val, (tuple, list)) else val) for k, val in self.cfg.__dict__.items()}
+        np.savez(path, params=self.get_params(), adam_m=m, adam_v=v, adam_t=np.int64(t),
+                 config=np.array(repr(cfg)), layout=np.array(repr(self.flux_layout())), **extra)
+
+    def load_checkpoint(self, path, load_optimizer=True):
+        with np.load(path, allow_pickle=False) as z:
+            if z["params"].size != self.num_params:
+                raise ValueError("checkpoint holds %d parameters, the model has %d" % (z["params"].size, self.num_params))
+            self.set_params(z["params"])
+            if load_optimizer and "adam_m" in z:
+                self.set_opt_state(z["adam_m"], z["adam_v"], int(z["adam_t"]))
+
     # -- calls; x may be numpy (host) or an int / torch tensor (device)
     @staticmethod
     def _loc(a):
@@ -383,6 +416,7 @@ class GriddedDataset:
         tc, ts = time_cos_sin(days, cycle_periods[0])
         lm = None if mask is None else np.asfortranarray(mask, np.uint8)
         md = None if mean_data is None else _f32(mean_data)
+        self.lon, self.lat = np.asarray(lon, np.float64), np.asarray(lat, np.float64)
         self.lon_scaled, self.lat_scaled = scale_pm1(lon), scale_pm1(lat)
         h = C.c_void_p()
         L.check(self._lib.dincae_gridded_create(ctx.handle, L.ptr(data_full), W, H, V, N, L.ptr(oes), L.ptr(js), L.ptr(iso),
@@ -549,6 +583,20 @@ def _device_batch_buffers(ds, batch_size):
     return xin, xtrue
 
 
+def _load_entry(d):
+    """One variable of data_all: either in-memory arrays or the reference's (filename, varname, errvarname) form."""
+    if "data" in d:
+        return d
+    from . import ncio
+    lon, lat, time, data, err, _, mask = ncio.load_gridded_nc(d["filename"], d["varname"], d.get("errvarname"),
+                                                              obs_err_std=d.get("obs_err_std", 1.0))
+    if d.get("errvarname") is not None:
+        raise L.DincaeError(L.EUNSUPPORTED, "per-pixel observation error fields (errvarname) are not supported: obs_err_std is one value per variable")
+    out = dict(d)
+    out.update(lon=lon, lat=lat, time=time, data=data, mask=mask)
+    return out
+
+
 def reconstruct(ctx, data_all, fnames_rec=None, *,
                 epochs=1000, batch_size=50, truth_uncertain=False, enc_nfilter_internal=(16, 24, 36, 54),
                 skipconnections=None, clip_grad=5.0, regularization_L1_beta=0, regularization_L2_beta=0,
@@ -575,6 +623,7 @@ def reconstruct(ctx, data_all, fnames_rec=None, *,
         raise L.DincaeError(L.EUNSUPPORTED, "is3D=true / output_ndims=2 / direction_obs are outside the hot path (SURVEY section 8f N4)")
 
     def make(dlist, train, mean_data=None):
+        dlist = [_load_entry(d) for d in dlist]                                          # {filename, varname} -> arrays (src/data.jl:88-110)
         d0 = dlist[0]
         data = np.stack([np.asarray(d["data"], np.float32) for d in dlist], axis=2)      # (W,H,V,N)
         return GriddedDataset(ctx, d0["lon"], d0["lat"], d0["time"], data, train=train,
@@ -611,8 +660,15 @@ def reconstruct(ctx, data_all, fnames_rec=None, *,
                 res["mean"], res["sigma"] = reconstruct_range(model, ds_, 0, len(ds_), res["count"], -9999.0, res["mean"], res["sigma"])
         train.shuffle_()                                               # src/model.jl:650
     if fnames_rec is not None:
-        for fn, res in zip(fnames_rec, results):
-            np.savez(fn, **{k: v for k, v in res.items() if v is not None})
+        for fn, res, dl, ds_ in zip(fnames_rec, results, data_all[1:], tests):
+            if str(fn).endswith(".nc"):                                # the reference's output file (src/data.jl:712-769)
+                from . import ncio
+                names = [d.get("varname", "var%d" % (i + 1)) for i, d in enumerate(dl) if d.get("isoutput", i == 0)]
+                nv = res["mean"].shape[3]                               # results are (W, H, N, noutput)
+                ncio.write_reconstruction(fn, names[:nv], ds_.lon, ds_.lat, np.asarray(train_mean)[:, :, np.flatnonzero(train_data.isoutput)[:nv]],
+                                          [res["mean"][:, :, :, i] for i in range(nv)], [res["sigma"][:, :, :, i] for i in range(nv)], res["count"])
+            else:
+                np.savez(fn, **{k: v for k, v in res.items() if v is not None})
     if paramfile is not None:
         np.savez(paramfile, losses=np.asarray(losses), epochs=epochs, batch_size=batch_size)
     reconstruct.last_model = model
