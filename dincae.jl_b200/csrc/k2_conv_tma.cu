@@ -53,6 +53,10 @@ __device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, u
     asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
@@ -271,6 +275,22 @@ int32_t make_tmap_w(CUtensorMap* m, const float* ptr, int ldk, int rows, int BN)
     return DINCAE_OK;
 }
 
+// the same K-major weight matrix seen as [tap][row][ci]: one box = (32 ci, BN rows, `taps` taps) -> `taps` consecutive K-major
+// SW128 tiles in shared memory from ONE TMA instruction (the L2 -> SM stream is latency x bytes-in-flight bound: ~2100 cycles
+// per bulk load measured, so few large loads beat many small ones)
+int32_t make_tmap_w3(CUtensorMap* m, const float* ptr, int Cin_p, int rows, int BN, int taps) {
+    EncodeTiledFn enc = get_encode();
+    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+    cuuint64_t gdim[3] = {(cuuint64_t)Cin_p, (cuuint64_t)rows, 9};
+    cuuint64_t gstr[2] = {(cuuint64_t)9 * Cin_p * 4, (cuuint64_t)Cin_p * 4};
+    cuuint32_t box[3] = {32, (cuuint32_t)BN, (cuuint32_t)taps};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(weights3 Cin_p=%d rows=%d taps=%d) failed: %d", Cin_p, rows, taps, (int)r);
+    return DINCAE_OK;
+}
+
 template <int BN, int STAGES>
 constexpr int tm_smem_bytes() { return STAGES * (TM_BM * 128 + BN * 128) + 1024; }
 
@@ -467,6 +487,7 @@ struct PersistArgs {
     int b_resident;
     int o_stages;              // 16 KB output staging slabs per epilogue group (1 or 2)
     int groups;                // epilogue groups (1: 256 threads, 2: 384 threads)
+    int tps;                   // streamed weights: taps per weight stage (3 = one kernel row per TMA load, 1 when shared memory is short)
     int ksteps;                // K = 8 steps over the input channels that are not zero padding (= Cin_p / 8 when unknown)
     long long* trace;          // tuning aid (dincae_debug_conv): clock64 stamps of CTA 0, 3 roles x 64 slots; nullptr in production
 };
@@ -634,7 +655,7 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
 
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* smemB = smem + q.a_stages * HL_A_STRIDE;
-    uint8_t* smemO = smemB + (q.b_resident ? (p.Cin_p / TM_KC) * 9 : q.b_stages) * B_BYTES;     // 1024-aligned: B_BYTES is a multiple of 4 KB
+    uint8_t* smemO = smemB + (q.b_resident ? (p.Cin_p / TM_KC) * 9 : q.b_stages * q.tps) * B_BYTES;     // 1024-aligned: B_BYTES is a multiple of 4 KB
     const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int patches = p.ptx * p.pty;
@@ -666,33 +687,39 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
     constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== TMA producer =====
-            if (q.b_resident) {
-                mbar_expect_tx(&bar_bres, (uint32_t)(nkc * 9 * B_BYTES));
-                for (int kc = 0; kc < nkc; kc++)
-                    for (int tap = 0; tap < 9; tap++)
-                        tma_load_2d(smemB + (size_t)(kc * 9 + tap) * B_BYTES, &tmB, &bar_bres, tap * p.Cin_p + kc * TM_KC, 0);
-            }
-            int ia = 0, ib = 0;
-            PS_TRACE(0, 0);
-            for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x) {
-                const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
-                const int b = pi / patches, pr = pi - b * patches;
-                const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
-                for (int kc = 0; kc < nkc; kc++, ia++) {
-                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
-                    if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
-                    PS_TRACE(0, 1 + ia);
+        // ===== TMA producer: warp-uniform loop, one elected lane issues (a divergent lane-0 branch costs ~50 cycles per TMA issue) =====
+        if (q.b_resident && elect_one_sync()) {
+            mbar_expect_tx(&bar_bres, (uint32_t)(nkc * 9 * B_BYTES));
+            for (int kc = 0; kc < nkc; kc++)
+                for (int tap = 0; tap < 9; tap++)
+                    tma_load_2d(smemB + (size_t)(kc * 9 + tap) * B_BYTES, &tmB, &bar_bres, tap * p.Cin_p + kc * TM_KC, 0);
+        }
+        __syncwarp();
+        int ia = 0, ib = 0;
+        if (lane == 0) PS_TRACE(0, 0);
+        const uint32_t stage_b = (uint32_t)(q.tps * B_BYTES);
+        for (int tile = blockIdx.x; tile < q.num_tiles; tile += gridDim.x) {
+            const int pi = tile / q.ntiles_n, n0 = (tile - pi * q.ntiles_n) * BN;
+            const int b = pi / patches, pr = pi - b * patches;
+            const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
+            for (int kc = 0; kc < nkc; kc++, ia++) {
+                const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+                if (lane == 0) PS_TRACE(0, 1 + ia);
+                if (elect_one_sync()) {
                     mbar_expect_tx(&bar_fullA[sa], (uint32_t)HL_A_BYTES);
                     tma_load_4d(smem + (size_t)sa * HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x0 - 1, y0 - 1, b);
-                    if (!q.b_resident) {
-                        for (int tap = 0; tap < 9; tap++, ib++) {
-                            const int sb = ib % q.b_stages, ub = ib / q.b_stages;
-                            if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
-                            mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
-                            tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
+                }
+                __syncwarp();
+                if (!q.b_resident) {
+                    for (int t0 = 0; t0 < 9; t0 += q.tps, ib++) {           // one weight stage = q.tps taps from one 3-D box
+                        const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                        if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
+                        if (elect_one_sync()) {
+                            mbar_expect_tx(&bar_fullB[sb], stage_b);
+                            tma_load_3d(smemB + (size_t)sb * stage_b, &tmB, &bar_fullB[sb], kc * TM_KC, n0, t0);
                         }
+                        __syncwarp();
                     }
                 }
             }
@@ -735,19 +762,23 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
                     }
                 } else {
 #pragma unroll 1
-                    for (int tap = 0; tap < 9; tap++, ib++) {
+                    for (int t0 = 0; t0 < 9; t0 += q.tps, ib++) {
                         const int sb = ib % q.b_stages, ub = ib / q.b_stages;
                         mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
                         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
-                        const uint64_t dat = da0 + (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                        const uint64_t dbs = make_desc_k_sw128(smemB_u + (uint32_t)(sb * q.tps * B_BYTES));
                         if (elect_one_sync()) {
-                            if (tap == 0) umma_tf32(dcol, dat, db0, IDESC, kc != 0 ? 1u : 0u);
-                            else umma_tf32_acc(dcol, dat, db0, IDESC);
+                            for (int tl = 0; tl < q.tps; tl++) {
+                                const int tap = t0 + tl;
+                                const uint64_t db0 = dbs + (uint64_t)((tl * B_BYTES) >> 4);
+                                const uint64_t dat = da0 + (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                                if (tap == 0) umma_tf32(dcol, dat, db0, IDESC, kc != 0 ? 1u : 0u);
+                                else umma_tf32_acc(dcol, dat, db0, IDESC);
 #pragma unroll
-                            for (int k = 1; k < TM_KC / 8; k++) umma_tf32_acc(dcol, dat + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                                for (int k = 1; k < TM_KC / 8; k++) umma_tf32_acc(dcol, dat + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                            }
                             umma_commit(&bar_emptyB[sb]);
-                            if (tap == 8) {
+                            if (t0 + q.tps >= 9) {
                                 umma_commit(&bar_emptyA[sa]);
                                 if (kc == nkc - 1) umma_commit(&bar_tfull[acc]);
                             }
@@ -834,7 +865,7 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_pair(const __grid_constant
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     constexpr int A_PAIR = 2 * HL_A_STRIDE;                                  // one activation stage = the halos of both tiles
     uint8_t* smemB = smem + q.a_stages * A_PAIR;
-    uint8_t* smemO = smemB + q.b_stages * B_BYTES;
+    uint8_t* smemO = smemB + q.b_stages * q.tps * B_BYTES;
     const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int patches = p.ptx * p.pty;
@@ -871,26 +902,31 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_pair(const __grid_constant
     };
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ===== TMA producer =====
-            int ia = 0, ib = 0;
-            for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
-                const int pp = unit / q.ntiles_n, n0 = (unit - pp * q.ntiles_n) * BN;
-                int b0, y00, x00, b1, y01, x01;
-                tile_coords(2 * pp, b0, y00, x00);
-                tile_coords(2 * pp + 1, b1, y01, x01);
-                for (int kc = 0; kc < nkc; kc++, ia++) {
-                    const int sa = ia % q.a_stages, ua = ia / q.a_stages;
-                    if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+        // ===== TMA producer (warp-uniform loop, one elected lane issues) =====
+        int ia = 0, ib = 0;
+        const uint32_t stage_b = (uint32_t)(q.tps * B_BYTES);
+        for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+            const int pp = unit / q.ntiles_n, n0 = (unit - pp * q.ntiles_n) * BN;
+            int b0, y00, x00, b1, y01, x01;
+            tile_coords(2 * pp, b0, y00, x00);
+            tile_coords(2 * pp + 1, b1, y01, x01);
+            for (int kc = 0; kc < nkc; kc++, ia++) {
+                const int sa = ia % q.a_stages, ua = ia / q.a_stages;
+                if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
+                if (elect_one_sync()) {
                     mbar_expect_tx(&bar_fullA[sa], (uint32_t)(2 * HL_A_BYTES));
                     tma_load_4d(smem + (size_t)sa * A_PAIR, &tmA, &bar_fullA[sa], kc * TM_KC, x00 - 1, y00 - 1, b0);
                     tma_load_4d(smem + (size_t)sa * A_PAIR + HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x01 - 1, y01 - 1, b1);
-                    for (int tap = 0; tap < 9; tap++, ib++) {
-                        const int sb = ib % q.b_stages, ub = ib / q.b_stages;
-                        if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
-                        mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
-                        tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
+                }
+                __syncwarp();
+                for (int t0 = 0; t0 < 9; t0 += q.tps, ib++) {               // one weight stage = q.tps taps from one 3-D box
+                    const int sb = ib % q.b_stages, ub = ib / q.b_stages;
+                    if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
+                    if (elect_one_sync()) {
+                        mbar_expect_tx(&bar_fullB[sb], stage_b);
+                        tma_load_3d(smemB + (size_t)sb * stage_b, &tmB, &bar_fullB[sb], kc * TM_KC, n0, t0);
                     }
+                    __syncwarp();
                 }
             }
         }
@@ -909,22 +945,26 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_pair(const __grid_constant
                 const uint64_t da00 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * A_PAIR), 0);
                 const uint64_t da10 = make_desc_k_sw128_halo(smemA_u + (uint32_t)(sa * A_PAIR + HL_A_STRIDE), 0);
 #pragma unroll 1
-                for (int tap = 0; tap < 9; tap++, ib++) {
+                for (int t0 = 0; t0 < 9; t0 += q.tps, ib++) {
                     const int sb = ib % q.b_stages, ub = ib / q.b_stages;
                     mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint64_t db0 = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
-                    const uint64_t toff = (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                    const uint64_t dbs = make_desc_k_sw128(smemB_u + (uint32_t)(sb * q.tps * B_BYTES));
                     if (elect_one_sync()) {
-                        if (tap == 0) { umma_tf32(dcol0, da00 + toff, db0, IDESC, kc != 0 ? 1u : 0u); umma_tf32(dcol1, da10 + toff, db0, IDESC, kc != 0 ? 1u : 0u); }
-                        else { umma_tf32_acc(dcol0, da00 + toff, db0, IDESC); umma_tf32_acc(dcol1, da10 + toff, db0, IDESC); }
+                        for (int tl = 0; tl < q.tps; tl++) {
+                            const int tap = t0 + tl;
+                            const uint64_t db0 = dbs + (uint64_t)((tl * B_BYTES) >> 4);
+                            const uint64_t toff = (uint64_t)(((tap / 3) * HL_HW + (tap % 3)) * 128 >> 4);
+                            if (tap == 0) { umma_tf32(dcol0, da00 + toff, db0, IDESC, kc != 0 ? 1u : 0u); umma_tf32(dcol1, da10 + toff, db0, IDESC, kc != 0 ? 1u : 0u); }
+                            else { umma_tf32_acc(dcol0, da00 + toff, db0, IDESC); umma_tf32_acc(dcol1, da10 + toff, db0, IDESC); }
 #pragma unroll
-                        for (int k = 1; k < TM_KC / 8; k++) {
-                            umma_tf32_acc(dcol0, da00 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
-                            umma_tf32_acc(dcol1, da10 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                            for (int k = 1; k < TM_KC / 8; k++) {
+                                umma_tf32_acc(dcol0, da00 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                                umma_tf32_acc(dcol1, da10 + toff + (uint64_t)(2 * k), db0 + (uint64_t)(2 * k), IDESC);
+                            }
                         }
                         umma_commit(&bar_emptyB[sb]);
-                        if (tap == 8) {
+                        if (t0 + q.tps >= 9) {
                             umma_commit(&bar_emptyA[sa]);
                             if (kc == nkc - 1) umma_commit(&bar_tfull[ubuf]);
                         }
@@ -992,7 +1032,8 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
             DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_persist_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); \
             attr_smem = smem;                                                                                              \
         }                                                                                                                  \
-        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        if (q.b_resident) DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                         \
+        else DC_TRY(make_tmap_w3(&tmB, a.wgtK, a.in.C, a.Cout_p, BN_, q.tps));                                             \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
         DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, q.groups == 2 ? PS_THREADS : 256, smem, tmA, tmB, tmO, p, q);                                         \
         DC_CHECK_LAUNCH();                                                                                                 \
@@ -1007,7 +1048,8 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
             DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_pair_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));  \
             attr_smem = smem;                                                                                              \
         }                                                                                                                  \
-        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
+        if (q.b_resident) DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                         \
+        else DC_TRY(make_tmap_w3(&tmB, a.wgtK, a.in.C, a.Cout_p, BN_, q.tps));                                             \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
         DC_LAUNCH(ctx, conv3x3_pair_bn##BN_, grid, PS_THREADS, smem, tmA, tmB, tmO, p, q);                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
@@ -1043,7 +1085,8 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     // one staging slab (the second CTA hides the bubbles between tiles).  Everything else: one CTA per SM with two epilogue
     // groups; resident weights if they fit beside two activation stages, else a ring of weight stages; whatever is left
     // deepens the activation ring (TMA latency is 2-3k cycles).
-    static const int tune_groups = dc_env_int("DINCAE_TUNE_GROUPS", 0);
+    static const int tune_groups = dc_env_int("DINCAE_TUNE_GROUPS", 0), tune_tps = dc_env_int("DINCAE_TUNE_TPS", 0);
+    q.tps = 1;
     const int static_smem = 5120;                     // barriers + bias (~3.2 KB) and the 1 KB alignment slack, rounded up
     const int small_plan = 2 * HL_A_STRIDE + resident_bytes + (a.dst ? 16384 : 0) + 1024;
     const bool two_per_sm = q.ntiles_n == 1 && 2 * (small_plan + static_smem) <= 227 * 1024 && 4 * bn <= 512 && tune_groups != 2;
@@ -1064,17 +1107,19 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
             q.b_stages = 0;
             left -= resident_bytes;
         } else {
-            int bs = (left - 2 * HL_A_STRIDE) / bbytes;
+            q.tps = tune_tps > 0 ? tune_tps : 3;                 // one kernel row of taps per weight stage ...
+            int bs = (left - 2 * HL_A_STRIDE) / (q.tps * bbytes);
+            if (bs < 2) { q.tps = 1; bs = (left - 2 * HL_A_STRIDE) / bbytes; }      // ... unless two such stages do not fit
             if (bs > PS_MAX_B) bs = PS_MAX_B;
             if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
             DC_REQUIRE(bs >= 2, DINCAE_EUNSUPPORTED, "conv3x3_persist: no room for two weight stages (BN=%d)", bn);
             q.b_stages = bs;
-            left -= bs * bbytes;
+            left -= bs * q.tps * bbytes;
         }
         q.a_stages = left / HL_A_STRIDE;
         if (q.a_stages > PS_MAX_A) q.a_stages = PS_MAX_A;
         if (tune_as > 0 && tune_as < q.a_stages) q.a_stages = tune_as;
-        smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * bbytes) + 2 * q.o_stages * 16384 + 1024;
+        smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * q.tps * bbytes) + 2 * q.o_stages * 16384 + 1024;
         per_sm = 1;
     }
     // paired tiles: streamed weights (deep levels), two pixel tiles per CTA share every weight stage
@@ -1083,14 +1128,16 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
         const int budget = 227 * 1024 - static_smem - 1024;
         q.o_stages = a.dst ? ((tune_os > 0) ? (tune_os > PS_MAX_O ? PS_MAX_O : tune_os) : 1) : 0;
         int left = budget - 2 * q.o_stages * 16384 - 2 * (2 * HL_A_STRIDE);
-        int bs = left / bbytes;
+        q.tps = tune_tps > 0 ? tune_tps : 3;
+        int bs = left / (q.tps * bbytes);
+        if (bs < 2) { q.tps = 1; bs = left / bbytes; }
         if (bs > PS_MAX_B) bs = PS_MAX_B;
         if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
-        if (bs >= 3) {
+        if (bs >= 2) {
             q.b_stages = bs; q.a_stages = 2;
-            left -= bs * bbytes;
+            left -= bs * q.tps * bbytes;
             if (left >= 2 * HL_A_STRIDE) q.a_stages = 3;
-            smem = q.a_stages * 2 * HL_A_STRIDE + q.b_stages * bbytes + 2 * q.o_stages * 16384 + 1024;
+            smem = q.a_stages * 2 * HL_A_STRIDE + q.b_stages * q.tps * bbytes + 2 * q.o_stages * 16384 + 1024;
             q.num_tiles = (int)dc_cdiv(m_tiles, 2) * q.ntiles_n;          // units
             int ctas = ctx->num_sms < q.num_tiles ? ctx->num_sms : q.num_tiles;
             dim3 grid((unsigned)ctas);
