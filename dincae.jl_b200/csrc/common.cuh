@@ -23,6 +23,10 @@ struct dincae_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    // side stream for work that is independent of the main dependency chain (weight gradients during the backward pass);
+    // created on first use, fenced against `stream` with the two events
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int64_t launches = 0;
     int num_sms = 148;
     // reusable device scratch (grown on demand, never shrunk)

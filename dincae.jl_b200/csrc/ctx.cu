@@ -46,6 +46,9 @@ extern "C" int32_t dincae_ctx_destroy(dincae_ctx* c) {
     cudaStreamSynchronize(c->stream);
     if (c->scratch) cudaFree(c->scratch);
     if (c->pinned) cudaFreeHost(c->pinned);
+    if (c->side) { cudaStreamSynchronize(c->side); cudaStreamDestroy(c->side); c->side = nullptr; }
+    if (c->ev_fork) { cudaEventDestroy(c->ev_fork); c->ev_fork = nullptr; }
+    if (c->ev_join) { cudaEventDestroy(c->ev_join); c->ev_join = nullptr; }
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
     return DINCAE_OK;

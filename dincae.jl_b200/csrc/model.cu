@@ -140,13 +140,48 @@ float* colpart_alloc(dincae_model* M, int64_t n_elems4, int Cp, int* nblocks) {
     return p;
 }
 
+// The weight gradients hang off the backward chain (nothing downstream reads them before the final reduction), so in TF32 mode
+// they are issued on the context's side stream: each one forks after its g tensor has been produced and runs beside the
+// data-gradient / level kernels of the main stream; wgrad_join() makes the main stream wait before buffers are reused.
+static bool side_stream_on() {
+    static const int on = dc_env_int("DINCAE_SIDE_STREAM", 1);
+    return on != 0;
+}
+static int32_t wgrad_fork(dincae_ctx* ctx) {
+    if (!ctx->side) {
+        DC_CHECK_CUDA(cudaStreamCreateWithFlags(&ctx->side, cudaStreamNonBlocking));
+        DC_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+        DC_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    }
+    DC_CHECK_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->side, ctx->ev_fork, 0));
+    return DINCAE_OK;
+}
+int32_t wgrad_join(dincae_model* M) {
+    dincae_ctx* ctx = M->ctx;
+    if (!M->side_pending) return DINCAE_OK;
+    DC_CHECK_CUDA(cudaEventRecord(ctx->ev_join, ctx->side));
+    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+    M->side_pending = false;
+    return DINCAE_OK;
+}
+
 // weight gradient with its own scratch slice; in TF32 mode the second-stage reductions are queued in M->red
 int32_t run_wgrad(dincae_model* M, WgradArgs& wa) {
     if (!M->wK) return k2_wgrad(M->ctx, wa, M->wg_scratch, M->wg_scratch_bytes);
     size_t need = (k2_wgrad_tma_scratch_bytes(M->ctx->num_sms, wa.B, wa.H, wa.W, wa.in.C, wa.Cout_p) + 255) / 256 * 256;
     DC_REQUIRE(M->wg_off + need <= M->wg_scratch_bytes, DINCAE_ESIZE, "weight-gradient scratch arena exhausted");
     wa.defer = &M->red;
-    int32_t st = k2_wgrad(M->ctx, wa, (char*)M->wg_scratch + M->wg_off, need);
+    dincae_ctx* ctx = M->ctx;
+    const bool side = side_stream_on() && !ctx->prof;          // the per-kernel profile times kernels one after the other
+    cudaStream_t main_stream = ctx->stream;
+    if (side) {
+        DC_TRY(wgrad_fork(ctx));
+        ctx->stream = ctx->side;
+        M->side_pending = true;
+    }
+    int32_t st = k2_wgrad(ctx, wa, (char*)M->wg_scratch + M->wg_off, need);
+    ctx->stream = main_stream;
     M->wg_off += need;
     return st;
 }
@@ -246,6 +281,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             DC_TRY(k2_conv_small(ctx, a, M->nco));
         }
     }
+    DC_TRY(wgrad_join(M));       // the next chain (or step) reuses the gradient workspace the side-stream kernels read
     return DINCAE_OK;
 }
 

@@ -26,6 +26,8 @@ struct ChainBufs {
 };
 
 struct dincae_model {
+    bool side_pending = false;   // weight gradients in flight on the context's side stream
+
     dincae_ctx* ctx = nullptr;
     dincae_config cfg;
     int L = 0, nchains = 0, O = 0, nco = 4, maxB = 0;
