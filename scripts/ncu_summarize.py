@@ -56,6 +56,10 @@ with open(os.path.join(prof, tag + "_ncu_full_top_kernels.csv"), "w") as f:
         key = "%s_bn%s" % (m.group(1), m.group(2)) if m else name
         if key.startswith("wgrad32_kernel"):
             key = "wgrad32"
+        elif key.startswith("wgrad9_kernel_bn"):
+            key = "wgrad9_n" + key[len("wgrad9_kernel_bn"):]
+        elif key.startswith("wgradm_kernel"):
+            key = "wgradm"
         def num(col):
             i = hdr.index(col); v = float(r[i].replace(",", "")); u = units[i]
             return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
