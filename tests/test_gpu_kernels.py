@@ -78,3 +78,30 @@ def test_wgrad_kernel_families_bit_exact(env, B, H, W, Ci, Co):
     torch.nn.functional.conv2d(xt, wt, padding=1).backward(gout.cpu().permute(0, 3, 1, 2))
     ref = wt.grad.permute(2, 3, 1, 0).reshape(9, Ci, Co)                      # [tap=(ky,kx)][ci][co]
     assert torch.equal(res[0][0].reshape(9, Ci, Co), ref)
+
+
+@pytest.mark.parametrize("B,H,W,Ci,Co", [(2, 9, 13, 32, 64), (3, 14, 14, 128, 256), (1, 20, 10, 32, 32)])
+def test_persistent_conv_writes_only_its_output(env, B, H, W, Ci, Co):
+    """Canaries around the output tensor: the TMA-store epilogue (edge patches are clipped by the unit) and the paired-tile kernel
+    (phantom second tile of an odd tile count) must not touch a byte outside [B,H,W,Co]."""
+    pkg, lib, ctx = env
+    dev = torch.device("cuda")
+    g = torch.Generator(device="cpu").manual_seed(7)
+    x = torch.randint(-3, 4, (B, H, W, Ci), generator=g).float().to(dev)
+    w = torch.randint(-2, 3, (9, Ci, Co), generator=g).float()
+    kpad = (9 * Ci + 15) // 16 * 16
+    w_fwd = torch.zeros(kpad, Co); w_fwd[:9 * Ci] = w.reshape(9 * Ci, Co)
+    w_k = w.reshape(9 * Ci, Co).t().contiguous()
+    bias = torch.zeros(Co)
+    w_fwd, w_k, bias = w_fwd.to(dev), w_k.to(dev), bias.to(dev)
+    n = B * H * W * Co
+    pad = 1 << 16
+    buf = torch.full((pad + n + pad,), -123.0, device=dev)
+    out = buf[pad:pad + n]
+    torch.cuda.synchronize()
+    pkg.lib.check(lib.dincae_debug_conv(ctx.handle, x.data_ptr(), w_fwd.data_ptr(), w_k.data_ptr(), bias.data_ptr(),
+                                        B, H, W, Ci, Co, 0, out.data_ptr(), 4))
+    ctx.sync()
+    assert torch.all(buf[:pad] == -123.0) and torch.all(buf[pad + n:] == -123.0)
+    ref = torch.nn.functional.conv2d(x.cpu().permute(0, 3, 1, 2), w.reshape(3, 3, Ci, Co).permute(3, 2, 0, 1), None, padding=1).permute(0, 2, 3, 1)
+    assert torch.equal(out.cpu().reshape(B, H, W, Co), ref)
