@@ -298,8 +298,7 @@ def main():
     assert xin_np.flags.f_contiguous and xt_np.flags.f_contiguous
 
     e2e_slot = [0]
-    if world == 1:
-        model.upload(0, xin_np, xt_np)
+    model.upload(0, xin_np, xt_np)
 
     def step_e2e():
         if world == 1:
@@ -311,7 +310,10 @@ def main():
             e2e_slot[0] = s_ ^ 1
             return loss
         nglob = np.array([counts[idx].sum()], np.int64)
-        model.grad_step(xin_np, xt_np, n_valid_global=nglob)                      # H2D inside
+        s_ = e2e_slot[0]
+        model.upload(s_ ^ 1, xin_np, xt_np)                                        # next shard's H2D overlaps this step, as above
+        model.grad_step_slot(s_, B, nglob)
+        e2e_slot[0] = s_ ^ 1
         with torch.cuda.stream(stream):
             dist.all_reduce(gview)
         return model.apply_step(wl["lr"], want_loss=True)

@@ -308,6 +308,10 @@ class Model:
         L.check(self._lib.dincae_train_step_slot(self.handle, slot, B, lr, C.byref(out) if want_loss else None))
         return out.value if want_loss else None
 
+    def grad_step_slot(self, slot, B, n_valid_global):
+        nv = np.ascontiguousarray(n_valid_global, np.int64)
+        L.check(self._lib.dincae_grad_step_slot(self.handle, slot, B, L.ptr(nv)))
+
     def grad_step(self, xin, xtrue, B=None, n_valid_global=None):
         xin, B = self._batch(xin, B)
         if isinstance(xtrue, np.ndarray):

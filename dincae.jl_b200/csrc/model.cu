@@ -8,6 +8,12 @@
 
 namespace {
 
+// valid-pixel counts handed over BY VALUE (kernel parameter): no host->device copy of a stack variable, hence no stream
+// synchronisation in the data-parallel step
+struct NValidArg { unsigned long long v[16]; };
+__global__ void set_nvalid_kernel(NValidArg a, int nout, unsigned long long* __restrict__ n) {
+    if ((int)threadIdx.x < nout) n[threadIdx.x] = a.v[threadIdx.x];
+}
 __global__ void inv_n_kernel(const unsigned long long* __restrict__ n, int nout, float* __restrict__ inv_n) {
     int v = threadIdx.x;
     if (v < nout) inv_n[v] = 1.0f / (float)n[v];     // "/ n_noncloud", src/model.jl:86,92 (Inf for n = 0, as the reference)
@@ -314,10 +320,11 @@ int32_t gridded_loss(dincae_model* M, const float* d_xtrue, int B, const int64_t
     dincae_ctx* ctx = M->ctx;
     const int64_t npix = (int64_t)M->cfg.W * M->cfg.H;
     if (n_valid_global) {
-        unsigned long long tmp[16];
-        for (int v = 0; v < M->O; v++) tmp[v] = (unsigned long long)n_valid_global[v];
-        DC_CHECK_CUDA(cudaMemcpyAsync(M->d_nvalid, tmp, sizeof(unsigned long long) * M->O, cudaMemcpyHostToDevice, ctx->stream));
-        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));     // tmp is a stack buffer
+        NValidArg nv{};
+        DC_REQUIRE(M->O <= 16, DINCAE_EUNSUPPORTED, "at most 16 output variables");
+        for (int v = 0; v < M->O; v++) nv.v[v] = (unsigned long long)n_valid_global[v];
+        DC_LAUNCH(ctx, set_nvalid_kernel, 1, 32, 0, nv, M->O, M->d_nvalid);
+        DC_CHECK_LAUNCH();
     } else {
         DC_TRY(k3_count_valid(ctx, d_xtrue, B, M->O, npix, M->d_nvalid));
     }
@@ -387,9 +394,10 @@ int32_t points_loss(dincae_model* M, PointTruth& pt, int B, int64_t n_valid_glob
     float* mv = M->pt_buf;
     float* gms = M->pt_buf + 2 * M->pt_cap;
     if (n_valid_global >= 0) {
-        unsigned long long tmp = (unsigned long long)n_valid_global;
-        DC_CHECK_CUDA(cudaMemcpyAsync(M->d_nvalid, &tmp, sizeof(tmp), cudaMemcpyHostToDevice, ctx->stream));
-        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+        NValidArg nv{};
+        nv.v[0] = (unsigned long long)n_valid_global;
+        DC_LAUNCH(ctx, set_nvalid_kernel, 1, 32, 0, nv, 1, M->d_nvalid);
+        DC_CHECK_LAUNCH();
     } else {
         DC_CHECK_CUDA(cudaMemsetAsync(M->d_nvalid, 0, sizeof(unsigned long long), ctx->stream));
         if (P > 0) {
@@ -876,6 +884,19 @@ extern "C" int32_t dincae_train_step_slot(dincae_model* M, int32_t slot, int32_t
     DC_CHECK_CUDA(cudaEventRecord(M->slot_free[slot], ctx->stream));
     M->slot_used[slot] = true;
     return dincae_apply_step(M, lr, loss);
+}
+
+extern "C" int32_t dincae_grad_step_slot(dincae_model* M, int32_t slot, int32_t B, const int64_t* n_valid_global) {
+    DC_TRY(check_batch(M, B, "dincae_grad_step_slot"));
+    DC_REQUIRE((slot == 0 || slot == 1) && M->copy_stream, DINCAE_EINVAL, "dincae_grad_step_slot: nothing was uploaded to slot %d", slot);
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const size_t nx = (size_t)M->cfg.W * M->cfg.H * M->cfg.ninput * M->maxB;
+    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, M->up_done[slot], 0));
+    DC_TRY(dincae_grad_step(M, M->up_buf[slot], M->up_buf[slot] + nx, B, n_valid_global, DINCAE_DEVICE));
+    DC_CHECK_CUDA(cudaEventRecord(M->slot_free[slot], ctx->stream));
+    M->slot_used[slot] = true;
+    return DINCAE_OK;
 }
 
 extern "C" int32_t dincae_loss_points(dincae_model* M, const float* xin, const float* pos, const float* x,

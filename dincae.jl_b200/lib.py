@@ -62,6 +62,7 @@ SIGNATURES = {
     "dincae_train_step": (i32, [vp, vp, vp, i32, f32, i32, C.POINTER(f32)]),
     "dincae_batch_upload": (i32, [vp, i32, vp, vp, i32]),
     "dincae_train_step_slot": (i32, [vp, i32, i32, f32, C.POINTER(f32)]),
+    "dincae_grad_step_slot": (i32, [vp, i32, i32, vp]),
     "dincae_loss_points": (i32, [vp, vp, vp, vp, vp, i32, i32, C.POINTER(C.c_double)]),
     "dincae_train_step_points": (i32, [vp, vp, vp, vp, vp, i32, f32, i32, C.POINTER(f32)]),
     "dincae_grad_step": (i32, [vp, vp, vp, i32, vp, i32]),

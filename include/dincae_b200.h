@@ -122,6 +122,9 @@ int32_t dincae_train_step(dincae_model* m, const float* xin, const float* xtrue,
  * dincae_train_step_slot returns. */
 int32_t dincae_batch_upload(dincae_model* m, int32_t slot, const float* xin_host, const float* xtrue_host, int32_t B);
 int32_t dincae_train_step_slot(dincae_model* m, int32_t slot, int32_t B, float lr, float* loss);
+/* data-parallel form of the same: gradient sums of the uploaded shard, normalised by the GLOBAL valid counts (see dincae_grad_step);
+ * the caller all-reduces dincae_grad_buffer and calls dincae_apply_step */
+int32_t dincae_grad_step_slot(dincae_model* m, int32_t slot, int32_t B, const int64_t* n_valid_global);
 /* point-cloud truth (src/points.jl:354-426): pos (sumP,2), x (sumP,2) = (value, 1/err var), offsets (B+1) int64 */
 int32_t dincae_loss_points(dincae_model* m, const float* xin, const float* pos, const float* x,
                            const int64_t* offsets, int32_t B, int32_t loc, double* loss);
