@@ -62,6 +62,7 @@ void dincae_set_error(const char* fmt, ...);
         if (_s != DINCAE_OK) return _s; \
     } while (0)
 
+static inline int dc_env_int_early(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 // every kernel launch of the library goes through this so that gpu_launches is a count, not a guess
 #define DC_LAUNCH(ctx, kernel, grid, block, smem, ...)                        \
     do {                                                                      \
@@ -72,6 +73,30 @@ void dincae_set_error(const char* fmt, ...);
         (ctx)->cur_bytes = 0.0;                                               \
         (ctx)->launches++;                                                    \
     } while (0)
+// Programmatic dependent launch: the kernel may start while its predecessor in the stream drains (its CTAs take over SMs as they
+// free up and run their prologue), and must execute dc_pdl_wait() before it touches global memory.  Only kernels that contain
+// dc_pdl_wait() may be launched through this macro.
+static inline bool dc_pdl_on() { static const int on = dc_env_int_early("DINCAE_PDL", 1); return on != 0; }
+#define DC_LAUNCH_PDL(ctx, kernel, grid, block, smem, ...)                                         \
+    do {                                                                                           \
+        if ((ctx)->prof) dc_prof_begin((ctx), #kernel);                                            \
+        cudaLaunchConfig_t _cfg = {};                                                              \
+        _cfg.gridDim = dim3(grid); _cfg.blockDim = dim3(block);                                    \
+        _cfg.dynamicSmemBytes = (size_t)(smem); _cfg.stream = (ctx)->stream;                       \
+        cudaLaunchAttribute _at[1];                                                                \
+        _at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                            \
+        _at[0].val.programmaticStreamSerializationAllowed = 1;                                     \
+        _cfg.attrs = _at; _cfg.numAttrs = (dc_pdl_on() && !(ctx)->prof) ? 1 : 0;                   \
+        cudaLaunchKernelEx(&_cfg, kernel, __VA_ARGS__);                                            \
+        if ((ctx)->prof) dc_prof_end((ctx));                                                       \
+        (ctx)->cur_flops = 0.0;                                                                    \
+        (ctx)->cur_bytes = 0.0;                                                                    \
+        (ctx)->launches++;                                                                         \
+    } while (0)
+#ifdef __CUDACC__
+__device__ __forceinline__ void dc_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void dc_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
 // algorithmic FLOPs / bytes of the next launch (reported by dincae_profile_end, used for rooflines)
 #define DC_WORK(ctx, fl, by)        \
     do {                            \

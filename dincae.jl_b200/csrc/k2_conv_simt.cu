@@ -345,6 +345,8 @@ __global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits
 // a padded smem tile transposes, writes are coalesced along channels (4 pixels x 128 B per store instruction)
 __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
                                                           int B, int HW, float* __restrict__ dst, int Cp, int Cw, int rnd) {
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
     __shared__ float tile[8][32][33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t total = (int64_t)B * HW;
@@ -391,6 +393,8 @@ struct RowThread {
 };
 
 __global__ void __launch_bounds__(256) pool_kernel(const float* __restrict__ a, int B, int H, int W, int Cp, int H2, int W2, float* __restrict__ x, int rnd) {
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
     const int C4 = Cp >> 2;
     const RowThread rt(C4);
     if (rt.lane >= rt.PL) return;
@@ -433,6 +437,8 @@ __device__ __forceinline__ void block_colpart(float4 acc, int C4, int Cp, float*
 __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
                                                     const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd,
                                                     float* __restrict__ colpart) {
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
     const int C4 = Cp >> 2;
     const RowThread rt(C4);
     float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -471,6 +477,8 @@ __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu
 
 __global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
                                                       int H2, int W2, float slope, float* __restrict__ gc, int rnd, float* __restrict__ colpart) {
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
     const int C4 = Cp >> 2;
     const RowThread rt(C4);
     float4 cacc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -538,6 +546,8 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
 // one thread per SOURCE cell: the (optionally summed) value is read once and written to its 2 x 2 (cropped) destination cells
 __global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
                                                          int H, int W, float* __restrict__ dst, int rnd) {
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
     const int C4 = Cp >> 2;
     const RowThread rt(C4);
     if (rt.lane >= rt.PL) return;
@@ -754,7 +764,7 @@ int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, i
     if (M == 0) return DINCAE_OK;
     int Cw = (int)dc_round_up(C0 + C1, 8);                  // whole 32-byte sectors; the rest of the row is never written (zero since allocation)
     if (Cw > Cp) Cw = Cp;
-    DC_LAUNCH(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
+    DC_LAUNCH_PDL(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -763,7 +773,7 @@ int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, fl
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H2 * W2 * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, pool_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * H2, n), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
+    DC_LAUNCH_PDL(ctx, pool_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * H2, n), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -783,7 +793,7 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
     if (n == 0) return DINCAE_OK;
     int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * Hs, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_upbwd: column partials not supported for %d channels", Cp);
-    DC_LAUNCH(ctx, upbwd_kernel, nb, 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts, colpart);
+    DC_LAUNCH_PDL(ctx, upbwd_kernel, nb, 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -794,7 +804,7 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     if (n == 0) return DINCAE_OK;
     int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * H, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd: column partials not supported for %d channels", Cp);
-    DC_LAUNCH(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
+    DC_LAUNCH_PDL(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -810,7 +820,7 @@ int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, in
 int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
+    DC_LAUNCH_PDL(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

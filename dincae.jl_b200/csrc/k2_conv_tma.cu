@@ -674,11 +674,13 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_persist(const __grid_const
             for (int s = 0; s < PS_MAX_O; s++) { mbar_init(&bar_ofull[g][s], 128); mbar_init(&bar_oempty[g][s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
+    dc_pdl_launch_dependents();
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
+    dc_pdl_wait();                 // everything above overlaps the tail of the previous kernel; global memory only from here on
+    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -883,11 +885,13 @@ __global__ void __launch_bounds__(PS_THREADS) conv3x3_pair(const __grid_constant
             for (int s = 0; s < PS_MAX_O; s++) { mbar_init(&bar_ofull[g][s], 128); mbar_init(&bar_oempty[g][s], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
+    dc_pdl_launch_dependents();
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
+    dc_pdl_wait();                 // everything above overlaps the tail of the previous kernel; global memory only from here on
+    for (int i = t; i < p.Cout_p; i += (int)blockDim.x) bias_s[i] = p.bias ? __ldg(p.bias + i) : 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -1035,7 +1039,7 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
         if (q.b_resident) DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                         \
         else DC_TRY(make_tmap_w3(&tmB, a.wgtK, a.in.C, a.Cout_p, BN_, q.tps));                                             \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
-        DC_LAUNCH(ctx, conv3x3_persist_bn##BN_, grid, q.groups == 2 ? PS_THREADS : 256, smem, tmA, tmB, tmO, p, q);                                         \
+        DC_LAUNCH_PDL(ctx, conv3x3_persist_bn##BN_, grid, q.groups == 2 ? PS_THREADS : 256, smem, tmA, tmB, tmO, p, q);                                         \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
     } while (0)
@@ -1051,7 +1055,7 @@ static long long* g_persist_trace = nullptr;     // set by dincae_debug_conv_tra
         if (q.b_resident) DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                         \
         else DC_TRY(make_tmap_w3(&tmB, a.wgtK, a.in.C, a.Cout_p, BN_, q.tps));                                             \
         DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes); \
-        DC_LAUNCH(ctx, conv3x3_pair_bn##BN_, grid, PS_THREADS, smem, tmA, tmB, tmO, p, q);                                 \
+        DC_LAUNCH_PDL(ctx, conv3x3_pair_bn##BN_, grid, PS_THREADS, smem, tmA, tmB, tmO, p, q);                                 \
         DC_CHECK_LAUNCH();                                                                                                 \
         return DINCAE_OK;                                                                                                  \
     } while (0)
