@@ -639,6 +639,41 @@ __global__ void __launch_bounds__(256) make_wT_kernel(const float* __restrict__ 
     }
 }
 
+// TF32 mode (all channel counts are multiples of 32): one block = one 32 (ci) x 32 (co) tile of one (layer, tap).  The tile is
+// read once, coalesced along co; wTK (co fastest) is written straight from it, wT and wK (ci fastest) from its shared-memory
+// transpose: every global access is a full 128-byte line.
+__global__ void __launch_bounds__(256) make_wT_tiled_kernel(const float* __restrict__ w, float* __restrict__ wT, float* __restrict__ wK,
+                                                            float* __restrict__ wTK, const WLayerDesc* __restrict__ tab, int nlayers) {
+    __shared__ float tile[32][33];
+    int l = 0, rem = (int)blockIdx.x;
+    for (; l < nlayers - 1; l++) {
+        const int nt = 9 * (tab[l].Cin_p >> 5) * (tab[l].Cout_p >> 5);
+        if (rem < nt) break;
+        rem -= nt;
+    }
+    const WLayerDesc L = tab[l];
+    const int Cin_p = L.Cin_p, Cout_p = L.Cout_p, nco = Cout_p >> 5, nci = Cin_p >> 5;
+    const int tap = rem / (nci * nco), r2 = rem - tap * (nci * nco), ci0 = (r2 / nco) * 32, co0 = (r2 - (r2 / nco) * nco) * 32;
+    const int tapT = 8 - tap;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;        // 8 rows per pass
+    const float* wl = w + L.w_off;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int ci = ci0 + ty + 8 * k, co = co0 + tx;
+        const float v = wl[((size_t)tap * Cin_p + ci) * Cout_p + co];
+        tile[ty + 8 * k][tx] = v;
+        wTK[L.wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(v);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int co = co0 + ty + 8 * k, ci = ci0 + tx;
+        const float v = tile[tx][ty + 8 * k];
+        wT[L.wT_off + ((size_t)tapT * Cout_p + co) * Cin_p + ci] = v;
+        wK[L.wk_off + (size_t)co * (9 * Cin_p) + (size_t)tap * Cin_p + ci] = round_tf32(v);
+    }
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -836,6 +871,11 @@ int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W
 
 int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, float* wK, float* wTK, const WLayerDesc* d_table, int nlayers, int64_t total) {
     if (total == 0 || nlayers == 0) return DINCAE_OK;
+    if (wK && wTK && (total % 1024) == 0) {                 // TF32 mode: every layer is padded to multiples of 32 channels
+        DC_LAUNCH(ctx, make_wT_tiled_kernel, (unsigned)(total / 1024), 256, 0, w, wT, wK, wTK, d_table, nlayers);
+        DC_CHECK_LAUNCH();
+        return DINCAE_OK;
+    }
     dim3 grid(48u, (unsigned)nlayers);                      // layers differ in size; 48 x 256 threads stride over each
     DC_LAUNCH(ctx, make_wT_kernel, grid, 256, 0, w, wT, wK, wTK, d_table, nlayers);
     DC_CHECK_LAUNCH();
