@@ -22,7 +22,8 @@ def env(pkg):
     return pkg, lib, pkg.Context(0)
 
 
-CONV_SHAPES = [(1, 16, 8, 32, 32), (2, 9, 13, 32, 64), (3, 14, 14, 64, 128), (2, 28, 28, 128, 256), (2, 7, 5, 256, 32), (4, 56, 56, 32, 32)]
+CONV_SHAPES = [(1, 16, 8, 32, 32), (2, 9, 13, 32, 64), (3, 14, 14, 64, 128), (2, 28, 28, 128, 256), (2, 7, 5, 256, 32), (4, 56, 56, 32, 32),
+               (2, 12, 15, 192, 96), (3, 6, 4, 96, 192), (2, 23, 15, 64, 64)]       # channel counts that are not powers of two
 
 
 @pytest.mark.parametrize("B,H,W,Ci,Co", CONV_SHAPES)
@@ -53,7 +54,8 @@ def test_conv_kernel_families_bit_exact(env, B, H, W, Ci, Co):
 
 
 WGRAD_SHAPES = [(1, 4, 8, 32, 32), (3, 9, 13, 32, 32), (2, 112, 112, 32, 32), (1, 4, 8, 128, 32), (2, 9, 13, 64, 32), (2, 9, 13, 32, 64),
-                (4, 28, 28, 64, 128), (2, 14, 14, 256, 128), (2, 14, 14, 128, 256), (1, 6, 7, 512, 256)]
+                (4, 28, 28, 64, 128), (2, 14, 14, 256, 128), (2, 14, 14, 128, 256), (1, 6, 7, 512, 256),
+                (2, 12, 15, 192, 96), (3, 6, 4, 96, 192), (2, 23, 15, 64, 64), (2, 5, 3, 160, 32)]
 
 
 @pytest.mark.parametrize("B,H,W,Ci,Co", WGRAD_SHAPES)
