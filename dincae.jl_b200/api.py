@@ -362,12 +362,15 @@ class Model:
         L.check(self._lib.dincae_loss_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, L.HOST, C.byref(out)))
         return out.value
 
-    def train_step_points(self, xin, point_truth, lr):
-        xin, B = self._batch(xin, None)
+    def train_step_points(self, xin, point_truth, lr, want_loss=True):
+        """xin: host array, or a device buffer (e.g. filled by PointDataset.assemble(..., xin=buf)); the point truth stays on the host."""
+        xin, B = self._batch(xin, len(point_truth))
         pos, x, offs = self._pack_points(point_truth)
         out = C.c_float()
-        L.check(self._lib.dincae_train_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, lr, L.HOST, C.byref(out)))
-        return out.value
+        loc = L.HOST if isinstance(xin, np.ndarray) else L.DEVICE_XIN
+        L.check(self._lib.dincae_train_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, lr, loc,
+                                                   C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
 
     def grad_step_points(self, xin, point_truth, n_valid_global=-1):
         xin, B = self._batch(xin, None)
@@ -733,7 +736,7 @@ class PointDataset:
             sel[ids == uniq[rng.integers(0, len(uniq))]] = True                    # at least one track
         return sel
 
-    def assemble(self, time_idx, seed=0, sample_ctr0=0, keep=None, perturb=None):
+    def assemble(self, time_idx, seed=0, sample_ctr0=0, keep=None, perturb=None, xin=None):
         time_idx = np.ascontiguousarray(time_idx, np.int64)
         B = len(time_idx)
         perturb = self.train if perturb is None else perturb
@@ -742,9 +745,11 @@ class PointDataset:
             ko = np.zeros(B + 1, np.int64)
             ko[1:] = np.cumsum([len(k) for k in keep])
             kp = np.ascontiguousarray(np.concatenate(keep) if ko[-1] else np.zeros(0), np.uint8)
-        xin = np.zeros(self.sizex() + (B,), np.float32, order="F")
+        loc = L.HOST if xin is None else L.DEVICE                                # device buffer: the batch never visits the host
+        if xin is None:
+            xin = np.zeros(self.sizex() + (B,), np.float32, order="F")
         L.check(self._lib.dincae_points_assemble(self.handle, L.ptr(time_idx), B, int(perturb), seed, sample_ctr0,
-                                                 L.ptr(kp), L.ptr(ko), L.ptr(xin), L.HOST))
+                                                 L.ptr(kp), L.ptr(ko), L.ptr(xin), loc))
         truth = [(self.pos[i], self.x[i]) for i in time_idx]                       # xtrue = (pos[ind], x[ind]), src/points.jl:310
         return xin, truth
 
@@ -798,13 +803,15 @@ def reconstruct_points(ctx, data, grid, fnames_rec=None, *,
     losses = []
     result = dict(mean=None, sigma=None, count=0)
     ctr = 0
+    import torch                                                       # device memory for the gridded mini-batch: it never visits the host
+    xbuf = torch.empty(int(np.prod(train.sizex())) * batch_size, dtype=torch.float32, device="cuda:%d" % ctx.device)
     for e in range(1, epochs + 1):
         lr = learning_rate * 0.5 ** (e / learning_rate_decay_epoch)    # src/points.jl:622
         s, nb = 0.0, 0
         for start in range(0, N, batch_size):
             idx = perm[start:start + batch_size]
             keep = [train.draw_track_keep(int(i), rng) for i in idx]
-            xin, truth = train.assemble(idx, seed, ctr, keep)
+            xin, truth = train.assemble(idx, seed, ctr, keep, xin=xbuf)
             ctr += len(idx)
             s += model.train_step_points(xin, truth, lr)
             nb += 1

@@ -354,7 +354,7 @@ int32_t point_workspace(dincae_model* M, int64_t P) {
     if (M->pt_buf) cudaFree(M->pt_buf);
     M->pt_buf = nullptr;
     M->pt_cap = 0;
-    size_t cap = (size_t)P + (size_t)P / 4 + 1024;
+    size_t cap = ((size_t)P + (size_t)P / 4 + 1024 + 3) & ~(size_t)3;     // multiple of 4 floats: the int64 offsets behind the float arrays stay 8-byte aligned
     // mv[2P] gathered (m,s2); gms[2P] their gradients; plane_of[P]; offsets
     cudaError_t e = cudaMalloc((void**)&M->pt_buf, sizeof(float) * (5 * cap) + sizeof(int64_t) * (M->maxB + 2));
     if (e != cudaSuccess) { dincae_set_error("point workspace allocation failed: %s", cudaGetErrorString(e)); return DINCAE_ENOMEM; }
@@ -906,9 +906,9 @@ extern "C" int32_t dincae_loss_points(dincae_model* M, const float* xin, const f
     dincae_ctx* ctx = M->ctx;
     DC_CHECK_CUDA(cudaSetDevice(ctx->device));
     const float* dx;
-    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc == DINCAE_HOST ? DINCAE_HOST : DINCAE_DEVICE, M->in_xin, &dx));
     PointTruth pt;
-    DC_TRY(stage_points(M, pos, x, offsets, B, loc, &pt));
+    DC_TRY(stage_points(M, pos, x, offsets, B, loc == DINCAE_DEVICE ? DINCAE_DEVICE : DINCAE_HOST, &pt));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
     DC_TRY(model_forward(M, dx, B, false));
     int32_t st = points_loss(M, pt, B, -1, false);
@@ -926,9 +926,9 @@ extern "C" int32_t dincae_grad_step_points(dincae_model* M, const float* xin, co
     dincae_ctx* ctx = M->ctx;
     DC_CHECK_CUDA(cudaSetDevice(ctx->device));
     const float* dx;
-    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc == DINCAE_HOST ? DINCAE_HOST : DINCAE_DEVICE, M->in_xin, &dx));
     PointTruth pt;
-    DC_TRY(stage_points(M, pos, x, offsets, B, loc, &pt));
+    DC_TRY(stage_points(M, pos, x, offsets, B, loc == DINCAE_DEVICE ? DINCAE_DEVICE : DINCAE_HOST, &pt));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
     DC_TRY(model_forward(M, dx, B, true));
     int32_t st = points_loss(M, pt, B, n_valid_global, true);

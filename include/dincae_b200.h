@@ -22,7 +22,8 @@ extern "C" {
 #endif
 
 enum { DINCAE_OK = 0, DINCAE_EINVAL = 1, DINCAE_EUNSUPPORTED = 2, DINCAE_ECUDA = 3, DINCAE_ENOMEM = 4, DINCAE_ESIZE = 5 };
-enum { DINCAE_HOST = 0, DINCAE_DEVICE = 1 };
+enum { DINCAE_HOST = 0, DINCAE_DEVICE = 1,
+       DINCAE_DEVICE_XIN = 2 /* *_points entry points only: xin on the device (e.g. written by dincae_points_assemble), the point truth on the host */ };
 enum { DINCAE_UP_NEAREST = 0, DINCAE_UP_BILINEAR = 1 };
 enum { DINCAE_PREC_FP32 = 0, DINCAE_PREC_TF32 = 1 };   /* conv operand precision; accumulation is always FP32 */
 

@@ -148,3 +148,25 @@ def test_reconstruct_gridded_driver(pkg, ctx):
         assert np.all(res[0]["mean"][~entry["mask"]] == -9999)
     with pytest.raises(pkg.lib.DincaeError):
         pkg.reconstruct(ctx, [[entry], [entry]], epochs=1, save_epochs=[1], is3D=True)
+
+
+def test_point_step_with_odd_point_counts_and_device_batch(pkg, ctx):
+    """Regression: the int64 offsets behind the float point workspace were misaligned for some total point counts.  Also the
+    device-resident batch (assemble(..., xin=device buffer) -> train_step_points) must equal the host-array path bit for bit."""
+    for npts in (7, 50, 51):
+        rng = np.random.default_rng(npts)
+        lon, lat, val, ids = synth_tracks(rng, GRID, 8, ntracks=6, npts=npts)
+        ds = pkg.PointDataset(ctx, GRID, lon, lat, val, ids, 50 + np.arange(8), ntime_win=3, probability_skip_for_training=0.5,
+                              jitter_std_pos=(0.17, 0.17), auxdata=None, train=True)
+        W, H, C = ds.sizex()
+        idx = np.array([0, 3, 5, 6])
+        keep = [ds.draw_track_keep(int(i), rng) for i in idx]
+        cfg = pkg.ModelConfig(W=W, H=H, ninput=C, enc_nfilter_internal=(8, 12), regularization_L2_beta=1e-4, max_batch=4, precision="fp32")
+        xin, truth = ds.assemble(idx, seed=5, sample_ctr0=0, keep=keep)
+        a = pkg.Model(ctx, cfg, seed=2)
+        la = [a.train_step_points(xin, truth, 1e-3) for _ in range(2)]
+        buf = torch.empty(W * H * C * 4, dtype=torch.float32, device="cuda")
+        xdev, truth2 = ds.assemble(idx, seed=5, sample_ctr0=0, keep=keep, xin=buf)
+        b = pkg.Model(ctx, cfg, seed=2)
+        lb = [b.train_step_points(xdev, truth2, 1e-3) for _ in range(2)]
+        assert la == lb and np.isfinite(la).all()
