@@ -66,14 +66,52 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_hist(const uint32_t* __res
     hist[(size_t)threadIdx.x * nblk + blockIdx.x] = sh[threadIdx.x];
 }
 
-// exclusive scan of n values in place by one block (n = 256 * nblk, small)
-__global__ void __launch_bounds__(1024) radix_scan(uint32_t* __restrict__ data, int64_t n) {
+// Exclusive scan of the n = 256 * nblk digit counts in two levels: every block scans one chunk of SCAN_CHUNK values in place
+// (coalesced loads, warp shuffles) and leaves the chunk total; one block then scans the chunk totals.  radix_scatter adds the
+// chunk offset when it reads its 256 bases, so no third pass over the counts is needed.
+constexpr int SCAN_CHUNK = 4096;            // 1024 threads x 4 values
+__global__ void __launch_bounds__(1024) radix_scan_chunks(uint32_t* __restrict__ data, int64_t n, uint32_t* __restrict__ totals) {
+    __shared__ uint32_t wsum[32];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int64_t base = (int64_t)blockIdx.x * SCAN_CHUNK + (int64_t)t * 4;
+    uint32_t v[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) v[k] = base + k < n ? data[base + k] : 0u;
+    const uint32_t mine = v[0] + v[1] + v[2] + v[3];
+    uint32_t inc = mine;                                           // inclusive scan of the per-thread sums inside the warp
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t o = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += o;
+    }
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = wsum[lane], winc = w;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(0xffffffffu, winc, off);
+            if (lane >= off) winc += o;
+        }
+        wsum[lane] = winc - w;                                     // exclusive offset of each warp
+        if (lane == 31) totals[blockIdx.x] = winc;
+    }
+    __syncthreads();
+    uint32_t run = wsum[warp] + inc - mine;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (base + k < n) data[base + k] = run;
+        run += v[k];
+    }
+}
+// exclusive scan of the (few) chunk totals by one block
+__global__ void __launch_bounds__(1024) radix_scan_totals(uint32_t* __restrict__ totals, int nchunks) {
     __shared__ uint32_t part[1024];
-    int t = threadIdx.x;
-    int64_t chunk = (n + 1023) / 1024;
-    int64_t lo = t * chunk, hi = lo + chunk < n ? lo + chunk : n;
+    const int t = threadIdx.x;
+    const int per = (nchunks + 1023) / 1024;
+    const int lo = t * per, hi = lo + per < nchunks ? lo + per : nchunks;
     uint32_t s = 0;
-    for (int64_t i = lo; i < hi; i++) s += data[i];
+    for (int i = lo; i < hi; i++) s += totals[i];
     part[t] = s;
     __syncthreads();
     for (int off = 1; off < 1024; off <<= 1) {
@@ -83,16 +121,17 @@ __global__ void __launch_bounds__(1024) radix_scan(uint32_t* __restrict__ data, 
         __syncthreads();
     }
     uint32_t run = part[t] - s;
-    for (int64_t i = lo; i < hi; i++) {
-        uint32_t v = data[i];
-        data[i] = run;
+    for (int i = lo; i < hi; i++) {
+        uint32_t v = totals[i];
+        totals[i] = run;
         run += v;
     }
 }
 
 __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ idx_in,
                                                               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ idx_out,
-                                                              int64_t E, int shift, const uint32_t* __restrict__ hist, int nblk) {
+                                                              int64_t E, int shift, const uint32_t* __restrict__ hist, int nblk,
+                                                              const uint32_t* __restrict__ chunk_off) {
     __shared__ uint32_t wcount[SORT_THREADS / 32][256];
     __shared__ uint32_t gbase[256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -125,7 +164,8 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
             wcount[w][d] = run;
             run += c;
         }
-        gbase[d] = hist[(size_t)d * nblk + blockIdx.x];
+        const size_t hi_ = (size_t)d * nblk + blockIdx.x;
+        gbase[d] = hist[hi_] + chunk_off[hi_ / SCAN_CHUNK];
     }
     __syncthreads();
 #pragma unroll
@@ -200,7 +240,8 @@ __global__ void k4_cells_kernel(const float* __restrict__ pos, int64_t P, int32_
 struct SortLayout {
     int64_t E;
     int nblk;
-    size_t off_keys[2], off_idx[2], off_hist, total;
+    size_t off_keys[2], off_idx[2], off_hist, off_tot, total;
+    int nchunks;
 };
 SortLayout sort_layout(int64_t P) {
     SortLayout L;
@@ -212,6 +253,9 @@ SortLayout sort_layout(int64_t P) {
     for (int i = 0; i < 2; i++) { L.off_idx[i] = o; o += a; }
     L.off_hist = o;
     o += ((size_t)256 * L.nblk * 4 + 255) / 256 * 256;
+    L.nchunks = (int)dc_cdiv((int64_t)256 * L.nblk, SCAN_CHUNK);
+    L.off_tot = o;
+    o += ((size_t)L.nchunks * 4 + 255) / 256 * 256;
     L.total = o;
     return L;
 }
@@ -245,6 +289,7 @@ int32_t k4_scatter_sorted(dincae_ctx* ctx, const K4Batch& b, const float* vals0,
     uint32_t* keys[2] = {(uint32_t*)(sc + L.off_keys[0]), (uint32_t*)(sc + L.off_keys[1])};
     uint32_t* idx[2] = {(uint32_t*)(sc + L.off_idx[0]), (uint32_t*)(sc + L.off_idx[1])};
     uint32_t* hist = (uint32_t*)(sc + L.off_hist);
+    uint32_t* tot = (uint32_t*)(sc + L.off_tot);
     DC_LAUNCH(ctx, k4_make_keys, (unsigned)dc_cdiv(L.E, 256), 256, 0, b, keys[0], idx[0], L.E);
     // KEY_INVALID has all bits set, so it sorts last as long as every pass that could separate it is run:
     // sort on the bits of (nkeys) where nkeys = planes*W*H; invalid keys differ from valid ones in a sorted bit
@@ -257,8 +302,9 @@ int32_t k4_scatter_sorted(dincae_ctx* ctx, const K4Batch& b, const float* vals0,
     int cur = 0;
     for (int p = 0; p < passes; p++) {
         DC_LAUNCH(ctx, radix_hist, L.nblk, SORT_THREADS, 0, keys[cur], L.E, 8 * p, hist, L.nblk);
-        DC_LAUNCH(ctx, radix_scan, 1, 1024, 0, hist, (int64_t)256 * L.nblk);
-        DC_LAUNCH(ctx, radix_scatter, L.nblk, SORT_THREADS, 0, keys[cur], idx[cur], keys[cur ^ 1], idx[cur ^ 1], L.E, 8 * p, hist, L.nblk);
+        DC_LAUNCH(ctx, radix_scan_chunks, L.nchunks, 1024, 0, hist, (int64_t)256 * L.nblk, tot);
+        DC_LAUNCH(ctx, radix_scan_totals, 1, 1024, 0, tot, L.nchunks);
+        DC_LAUNCH(ctx, radix_scatter, L.nblk, SORT_THREADS, 0, keys[cur], idx[cur], keys[cur ^ 1], idx[cur ^ 1], L.E, 8 * p, hist, L.nblk, tot);
         cur ^= 1;
     }
     if (b.nfields == 1)
@@ -361,7 +407,8 @@ constexpr int64_t NOALLOC_MAX_POINTS = 65536;
 constexpr size_t noalloc_align(size_t v) { return (v + 255) / 256 * 256; }
 constexpr size_t NOALLOC_ENTRIES = 4 * (size_t)NOALLOC_MAX_POINTS;
 constexpr size_t NOALLOC_NBLK = (NOALLOC_ENTRIES + SORT_TILE - 1) / SORT_TILE;
-constexpr size_t NOALLOC_SCRATCH_BYTES = 4 * noalloc_align(NOALLOC_ENTRIES * 4) + noalloc_align(256 * NOALLOC_NBLK * 4);
+constexpr size_t NOALLOC_NCHUNKS = (256 * NOALLOC_NBLK + SCAN_CHUNK - 1) / SCAN_CHUNK;
+constexpr size_t NOALLOC_SCRATCH_BYTES = 4 * noalloc_align(NOALLOC_ENTRIES * 4) + noalloc_align(256 * NOALLOC_NBLK * 4) + noalloc_align(NOALLOC_NCHUNKS * 4);
 }  // namespace
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];

@@ -46,3 +46,28 @@ for prec, DEVICE_BATCH in (("tf32", False), ("tf32", True), ("fp32", True)):
         a, s, loss = step(3 + k); ta += a; ts += s
     print("%s device_batch=%s: Cin=%d, assembly %.2f ms/batch, train step %.2f ms/batch -> %.0f samples/s end to end, loss %.4f"
           % (prec, DEVICE_BATCH, C, ta / n * 1e3, ts / n * 1e3, B * n / (ta + ts), loss))
+
+# per-kernel CUDA-event profile of three TF32 steps (library profile hooks)
+import ctypes, json
+lib = pkg.lib.load()
+cfg = pkg.ModelConfig(W=Wd, H=Hd, ninput=C, enc_nfilter_internal=(25, 50, 75), regularization_L2_beta=1e-4, laplacian_penalty=0.1, max_batch=B, precision="tf32")
+model = pkg.Model(ctx, cfg, seed=1)
+import torch
+xbuf = torch.empty(Wd * Hd * C * B, dtype=torch.float32, device="cuda")
+def one(k):
+    idx = rng.integers(0, N, B)
+    keep = [ds.draw_track_keep(int(i), rng) for i in idx]
+    xin, truth = ds.assemble(idx, seed=3, sample_ctr0=k * B, keep=keep, xin=xbuf)
+    return model.train_step_points(xin, truth, 1e-3)
+one(0)
+pkg.lib.check(lib.dincae_profile_begin(ctx.handle))
+t0 = time.perf_counter()
+for k in range(3): one(1 + k)
+wall = (time.perf_counter() - t0) / 3
+buf = ctypes.create_string_buffer(1 << 16)
+pkg.lib.check(lib.dincae_profile_end(ctx.handle, buf, len(buf)))
+tab = json.loads(buf.value.decode())
+tab.sort(key=lambda k: -k["ms"])
+print("profiled step wall %.2f ms; kernel total %.2f ms/step" % (wall * 1e3, sum(k["ms"] for k in tab) / 3))
+for k in tab[:14]:
+    print("  %-28s %3d launches/step %7.3f ms/step" % (k["kernel"], k["launches"] // 3, k["ms"] / 3))
