@@ -170,3 +170,27 @@ def test_point_step_with_odd_point_counts_and_device_batch(pkg, ctx):
         b = pkg.Model(ctx, cfg, seed=2)
         lb = [b.train_step_points(xdev, truth2, 1e-3) for _ in range(2)]
         assert la == lb and np.isfinite(la).all()
+
+
+def test_point_loss_and_train_step_tf32_vs_oracle(pkg, ctx):
+    """The point-cloud loss through the tensor-core (TF32) model.  Stated tolerance: 1e-3 on the loss; gradients rms 1e-2 relative
+    and 4e-2 of their range at worst (a few hundred observations drive the whole gradient, so TF32 rounding of the activations
+    shows more than in the gridded loss; observed 5e-3 rms, 1.7e-2 worst against the library's own FP32 mode)."""
+    rng = np.random.default_rng(8)
+    ds, od = make(pkg, ctx, rng, N=6, T=3, naux=2, train=True)
+    W, H, C = ds.sizex()
+    idx = np.array([1, 2, 4, 3])
+    keep = [ds.draw_track_keep(int(i), rng) for i in idx]
+    xin, truth = ds.assemble(idx, seed=5, sample_ctr0=0, keep=keep)
+    kw = dict(loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-4)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=C, enc_nfilter_internal=(32, 64), max_batch=4, precision="tf32", **kw)
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=C, nfilter=[32, 64], **kw)
+    model = pkg.Model(ctx, cfg, seed=6)
+    flat = model.get_params()
+    loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, None, point_truth=truth)
+    assert model.loss_points(xin, truth) == pytest.approx(loss_o, rel=1e-3)
+    assert model.train_step_points(xin, truth, 1e-3) == pytest.approx(loss_o, rel=1e-3)
+    m, v, t = model.get_opt_state()
+    gc = np.clip(g_o, -5, 5)
+    d = m * 10 - gc
+    assert np.abs(d).max() < 4e-2 * np.abs(gc).max() and np.sqrt((d ** 2).mean()) < 1e-2 * np.sqrt((gc ** 2).mean())
