@@ -383,3 +383,24 @@ def test_prefetch_slots_equal_plain_train_step(pkg, ctx):
     got = pkg.api.train_epoch_prefetch(b_, batches, 1e-3)
     assert got == pytest.approx(sum(ref) / 3, rel=1e-6)
     assert np.array_equal(a.get_params(), b_.get_params())
+
+
+def test_cuda_path_matches_committed_fixture(pkg, ctx):
+    """CUDA path (through the C-ABI) against the committed oracle outputs in tests/golden/oracle_small.npz."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_small.npz"))
+    ds = pkg.GriddedDataset(ctx, z["grid_lon"], z["grid_lat"], z["grid_days"], z["grid_data"], train=False, ntime_win=int(z["grid_T"]))
+    xin, xtrue = ds.assemble(z["grid_idx"])
+    assert np.array_equal(xin, z["xin"]) and np.array_equal(xtrue, z["xtrue"])                 # integer / select work: bit-exact
+    W, H = xin.shape[:2]
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=xin.shape[2], enc_nfilter_internal=tuple(int(f) for f in z["nfilter"]),
+                          loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3, max_batch=3, precision="fp32")
+    model = pkg.Model(ctx, cfg, seed=None)
+    model.set_params(z["params"])
+    np.testing.assert_allclose(model(xin), z["forward"], rtol=1e-3, atol=1e-5)                 # north_star tolerance; observed 1e-6
+    assert model.loss(xin, xtrue) == pytest.approx(float(z["loss"]), rel=1e-5)
+    assert model.train_step(xin, xtrue, 1e-3) == pytest.approx(float(z["loss"]), rel=1e-5)
+    big = np.abs(z["grad"]) > 1e-5                                                             # first Adam step is lr*sign(g) where g ~ eps
+    assert np.abs(model.get_params() - z["params_after_adam"])[big].max() < 2e-4
+    np.testing.assert_allclose(pkg.interpnd(z["pt_pos"], z["pt_A"], ctx), z["pt_interp"], rtol=1e-6)
+    assert np.array_equal(pkg.interp_adjn(z["pt_pos"], z["pt_vals"], (W, H), ctx), z["pt_adjoint"])     # sorted segments = sequential order

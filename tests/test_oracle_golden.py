@@ -221,3 +221,41 @@ def test_savesample_running_mean():
     np.testing.assert_allclose(s1[2, 2], np.sqrt(xrec[2, 2, 1]), rtol=1e-6)
     m2, s2 = D.savesample_accumulate(m1, s1, 2 * xrec, mean, mask, 2)
     np.testing.assert_allclose(m2[2, 2], (m1[2, 2] + 2 * xrec[2, 2, 0] + mean[2, 2]) / 2, rtol=1e-6)
+
+
+# ---- committed fixtures under tests/golden/ ------------------------------------------------------
+import json
+import os
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_reference_vectors_file_matches_the_oracle():
+    """tests/golden/reference_vectors.json holds the reference's own fixtures (test/test_interp_adjoint.jl:20-47)."""
+    ref = json.load(open(os.path.join(GOLDEN, "reference_vectors.json")))["interp_adjoint"]
+    pos, vals, sz = np.array(ref["pos"], np.float32), np.array(ref["values"], np.float32), tuple(ref["sz"])
+    A_ref = np.zeros(sz, np.float32); dA_ref = np.zeros(sz, np.float32)
+    for i, j, v in ref["A_ref_nonzero"]:
+        A_ref[i - 1, j - 1] = v
+    for i, j, v in ref["dA_ref_nonzero"]:
+        dA_ref[i - 1, j - 1] = v
+    for adj in (P.interp_adjn, cbind.interp_adjn):
+        np.testing.assert_allclose(adj(pos, vals, sz), A_ref, rtol=RTOL_JULIA, atol=1e-7)
+        np.testing.assert_allclose(adj(pos, np.ones(len(vals), np.float32), sz), dA_ref, rtol=RTOL_JULIA, atol=1e-7)
+
+
+def test_oracle_reproduces_committed_fixture():
+    """The oracle must keep producing tests/golden/oracle_small.npz (made by tests/golden/make_fixtures.py)."""
+    z = np.load(os.path.join(GOLDEN, "oracle_small.npz"))
+    od = D.NCData(z["grid_lon"], z["grid_lat"], z["grid_days"], z["grid_data"], train=False, ntime_win=int(z["grid_T"]))
+    xin, xtrue = od.batch(z["grid_idx"])
+    assert np.array_equal(xin, z["xin"]) and np.array_equal(xtrue, z["xtrue"])
+    W, H = xin.shape[:2]
+    cfg = M.ModelConfig(W=W, H=H, ninput=xin.shape[2], nfilter=list(z["nfilter"]), loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3)
+    np.testing.assert_allclose(M.forward(cfg, z["params"], xin), z["forward"], rtol=1e-4, atol=1e-6)
+    loss, g = M.loss_and_grad(cfg, z["params"], xin, xtrue)
+    assert loss == pytest.approx(float(z["loss"]), rel=1e-6)
+    np.testing.assert_allclose(g, z["grad"], rtol=1e-3, atol=1e-6 * np.abs(z["grad"]).max())
+    np.testing.assert_allclose(P.interpnd(z["pt_pos"], z["pt_A"]), z["pt_interp"], rtol=1e-6)
+    assert np.array_equal(P.interp_adjn(z["pt_pos"], z["pt_vals"], (W, H)), z["pt_adjoint"])
+    assert np.array_equal(cbind.interp_adjn(z["pt_pos"], z["pt_vals"], (W, H)), z["pt_adjoint"])
