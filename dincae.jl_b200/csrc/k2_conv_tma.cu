@@ -2161,7 +2161,8 @@ void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64
     int64_t maxs = dc_cdiv(npatches, wgrad_patch_rows(Cin_p, Cout_p) == 8 ? 2 : 4);
     if (splits > maxs) splits = (int)maxs;
     // the split partials are written and re-read once: keep them below ~16 MB per layer
-    int64_t cap = (int64_t)(16 << 20) / ((int64_t)9 * Cin_p * Cout_p * 4);
+    static const int cap_mb = dc_env_int("DINCAE_WGRAD_CAP_MB", 16);
+    int64_t cap = ((int64_t)cap_mb << 20) / ((int64_t)9 * Cin_p * Cout_p * 4);
     if (cap < 1) cap = 1;
     if (splits > cap) splits = (int)cap;
     if (splits < 1) splits = 1;
