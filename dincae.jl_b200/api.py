@@ -184,7 +184,7 @@ class ModelConfig:
         c.clip_grad = float(self.clip_grad) if self.clip_grad is not None else 0.0
         c.adam_beta1, c.adam_beta2, c.adam_eps = self.adam_beta[0], self.adam_beta[1], self.adam_eps
         c.leaky_slope = float(self.leaky_slope)
-        c.precision = {"fp32": L.PREC_FP32, "tf32": L.PREC_TF32}[self.precision]
+        c.precision = {"fp32": L.PREC_FP32, "tf32": L.PREC_TF32, "tf32x1": L.PREC_TF32X1}[self.precision]
         c.max_batch = int(self.max_batch)
         return c
 

@@ -42,6 +42,8 @@ struct ConvArgs {
     float* planar_out;    // optional planar (Julia WHCN) output [B][planar_C][H][W] of the first planar_C channels (TMA kernel only)
     int planar_C;
     int planar_accumulate;   // 1: planar_out += value
+    int planar_fold;         // 1: planar channel k = accumulator column k + column (8 + k): the head conv's low-order weight
+                             // columns (3xTF32 split, see k2_make_wK_split) are summed in the epilogue; needs planar_C <= 8
     float* pool_dst;         // optional: MeanPool((2,2)) of the output, only when k2_conv_fuses_pool(args) is true
     double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
     double work_bytes;    // algorithmic HBM bytes (input + output + weights, REAL channel counts)
@@ -110,8 +112,17 @@ int32_t k2_conv_small(dincae_ctx* ctx, const ConvSmallArgs& a, int nco);
 // weight gradient for gout with NCO (4 or 8) padded channels
 int32_t k2_wgrad_small(dincae_ctx* ctx, WgradArgs a, int nco, void* scratch, size_t scratch_bytes);
 
+// Head conv fused with nearest upsample (+ crop + skip add) of its half-resolution source, exact FP32 (CUDA cores), planar output
+// out[b][o][y][x], o < nout2 = 2*noutput (src/model.jl:270-272, src/flux.jl:4); src NHWC with Cp channels of which Cin are real
+bool k2_head_up_conv_eligible(int Cin, int nout2);
+int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int Cin,
+                        const float* wgt, int Cin_p, int Cout_p, const float* bias, int nout2, int H, int W, float* out,
+                        double work_flops, double work_bytes);
 // planar (Julia WHCN) -> NHWC padded; channels [0,C0) from src0, [C0,C0+C1) from src1 (cat(xout,xin,dims=3), src/model.jl:186)
-int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp);
+// split != 0 (tensor-core mode, first conv of a chain): the C = C0 + C1 real channels are written twice as
+// [tf32(a) | tf32(a - tf32(a))], so that the conv multiplies the unrounded activation (a_hi + a_lo) * tf32(w); the matching
+// weight rows are laid out by k2_make_wK_split (Cp >= 2*C)
+int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp, int split = 0);
 // MeanPool((2,2), pad=odd): count-include-pad (src/model.jl:268)
 int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, float* x);
 // backward of nearest-upsample + crop (+ activation mask of r): G = up^T(gu); gd = G * act'(r)
@@ -122,8 +133,9 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
 int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc, float* colpart = nullptr);
 // bilinear (align_corners=true) upsample+crop of (src0 + src1) and its transpose
 // nearest upsample x2 + crop of (src0 + src1), materialised (TF32 mode: feeds the TMA kernels)
-int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);
-int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst);
+// split != 0: dst has 2*Cp channels per pixel, [tf32(v) | tf32(v - tf32(v))] (input of the 3xTF32 head conv)
+int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst, int split = 0);
+int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst, int split = 0);
 int32_t k2_up_bilinear_bwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, int Hs, int Ws, const float* r, float slope, float* G, float* gd);
 
 // table-driven weight transpose+flip for the data-gradient convs
@@ -131,8 +143,29 @@ struct WLayerDesc {
     int64_t w_off, wT_off;
     int Cin_p, Cout_p;
     int64_t n;   // 9*Cin_p*Cout_p
-    int64_t wk_off;   // offset of this layer in the K-major copies (both have n elements)
+    int64_t wk_off;   // offset of this layer in the forward K-major copy wK
+    int64_t wtk_off;  // offset of this layer in the data-gradient K-major copy wTK
 };
 // wT: transposed + tap-flipped [9*Cout_p][Cin_p] (FP32 path).  If wK/wTK are given also the K-major TF32-rounded copies:
 //   wK [Cout_p][9*Cin_p] for the forward conv, wTK [Cin_p][9*Cout_p] (tap-flipped) for the data gradient.
+// Split-operand layers (DINCAE_PREC_TF32: the first conv and the head conv of every chain, the thin full-resolution layers whose
+// operand rounding dominates the output error): K-major forward weights wK [Cout_p][9*Cin_pe] in the expanded operand layout,
+// and the fold of the expanded weight gradient back onto the master layout.
+//   mode 1 (first conv, C real input channels; 2xTF32 = exact activations): k-slots [0,C) = hi(w), [C,2C) = hi(w), rest 0
+//   mode 2 (head conv, P0 = Cin_p, n2 = real output channels): rows co < n2: slots [0,P0) = hi(w), [P0,2P0) = hi(w);
+//           rows 8 <= co < 8 + n2: slots [0,P0) = lo(w[., co - 8]); everything else 0 (n2 <= 8)
+//   hi(w) = tf32(w), lo(w) = tf32(w - hi(w)).
+struct SplitLayerDesc {
+    int64_t w_off;       // master weights [9*Cin_p][Cout_p] (and the gradient slot of the same layout)
+    int64_t wk_off;      // expanded K-major copy [Cout_p][9*Cin_pe]
+    int64_t gexp_off;    // expanded weight gradient [9*Cin_pe][Cout_p] in the temporary buffer
+    int Cin_p, Cin_pe, Cout_p;
+    int mode, C, n2;
+};
+constexpr int SPLIT_MAX = 2 * DINCAE_MAX_CHAINS;
+struct SplitTable { SplitLayerDesc d[SPLIT_MAX]; int count; };
+int32_t k2_make_wK_split(dincae_ctx* ctx, const float* w, float* wK, const SplitTable& tab);
+// g[(tap*Cin_p + ci)*Cout_p + co] = gexp[(tap*Cin_pe + ci)*Cout_p + co] + gexp[(tap*Cin_pe + lo + ci)*Cout_p + co]  (lo = C | Cin_p),
+// zero for the padding channels: the hi and lo activation slots multiply the same weight
+int32_t k2_fold_split_grad(dincae_ctx* ctx, const float* gexp, float* g, const SplitTable& tab);
 int32_t k2_make_wT(dincae_ctx* ctx, const float* w, float* wT, float* wK, float* wTK, const WLayerDesc* d_table, int nlayers, int64_t total);

@@ -344,7 +344,7 @@ __global__ void wgrad_small_reduce(const float* __restrict__ partial, int splits
 // planar (WHCN) -> NHWC: a warp moves 32 consecutive pixels; reads are coalesced along pixels (one channel plane at a time),
 // a padded smem tile transposes, writes are coalesced along channels (4 pixels x 128 B per store instruction)
 __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restrict__ s0, int C0, const float* __restrict__ s1, int C1,
-                                                          int B, int HW, float* __restrict__ dst, int Cp, int Cw, int rnd) {
+                                                          int B, int HW, float* __restrict__ dst, int Cp, int Cw, int rnd, int split) {
     dc_pdl_launch_dependents();
     dc_pdl_wait();
     __shared__ float tile[8][32][33];
@@ -355,16 +355,27 @@ __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restric
     const int64_t m = m0 + lane;
     const bool pv = m < total;
     const int b = pv ? (int)(m / HW) : 0, r = pv ? (int)(m - (int64_t)b * HW) : 0;
+    const int Ct = C0 + C1;
     for (int cg = 0; cg < Cw; cg += 32) {                  // channels >= Cw are zero padding and stay as the buffer was created (zeros)
         const int nc = Cw - cg < 32 ? Cw - cg : 32;
-        for (int c = 0; c < nc; c++) {
-            const int cc = cg + c;
-            float v = 0.f;
-            if (pv) {
-                if (cc < C0) v = __ldg(s0 + ((size_t)b * C0 + cc) * HW + r);
-                else if (cc < C0 + C1) v = __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r);
+        for (int c8 = 0; c8 < nc; c8 += 8) {               // eight independent loads in flight per thread, then the shared stores
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                int cc = cg + c8 + k;
+                if (split && cc >= Ct) cc = cc < 2 * Ct ? cc - Ct : Ct;         // [hi | lo | zero padding]
+                v[k] = 0.f;
+                if (pv) {
+                    if (cc < C0) v[k] = __ldg(s0 + ((size_t)b * C0 + cc) * HW + r);
+                    else if (cc < Ct) v[k] = __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r);
+                }
             }
-            tile[warp][lane][c] = rnd ? round_tf32(v) : v;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const float hi = rnd ? round_tf32(v[k]) : v[k];
+                const bool lo = split && cg + c8 + k >= Ct;
+                tile[warp][lane][c8 + k] = lo ? round_tf32(v[k] - hi) : hi;
+            }
         }
         __syncwarp();
         const int chunks = nc >> 2;                         // float4 chunks per pixel row in this group
@@ -513,7 +524,7 @@ __device__ __forceinline__ void bil_coord(int o, int nin, int nout_full, int& i0
     f = s - (float)i0;
 }
 __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
-                                   int H, int W, float* __restrict__ dst, int rnd) {
+                                   int H, int W, float* __restrict__ dst, int rnd, int split) {
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     int C4 = Cp >> 2;
     int64_t total = (int64_t)B * H * W * C4;
@@ -541,23 +552,31 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
     o.y = w00 * v00.y + w01 * v01.y + w10 * v10.y + w11 * v11.y;
     o.z = w00 * v00.z + w01 * v01.z + w10 * v10.z + w11 * v11.z;
     o.w = w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w;
-    *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(o, rnd);
+    if (!split) {
+        *reinterpret_cast<float4*>(dst + (((size_t)b * H + y) * W + x) * Cp + c4 * 4) = round_tf32(o, rnd);
+    } else {
+        const float4 hi = round_tf32(o, 1);
+        float* d = dst + (((size_t)b * H + y) * W + x) * (2 * Cp) + c4 * 4;
+        *reinterpret_cast<float4*>(d) = hi;
+        *reinterpret_cast<float4*>(d + Cp) = round_tf32(make_float4(o.x - hi.x, o.y - hi.y, o.z - hi.z, o.w - hi.w), 1);
+    }
 }
 // one thread per SOURCE cell: the (optionally summed) value is read once and written to its 2 x 2 (cropped) destination cells
 __global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
-                                                         int H, int W, float* __restrict__ dst, int rnd) {
+                                                         int H, int W, float* __restrict__ dst, int rnd, int split) {
     dc_pdl_launch_dependents();
     dc_pdl_wait();
     const int C4 = Cp >> 2;
     const RowThread rt(C4);
     if (rt.lane >= rt.PL) return;
+    const int Cd = split ? 2 * Cp : Cp;             // destination channels per pixel
     for (int row = blockIdx.x; row < B * Hs; row += gridDim.x) {
         const int b = row / Hs, ys = row - b * Hs;
         const int ya = 2 * ys, yb = ya + 1;
         if (ya >= H) continue;
         const size_t rs = (size_t)row * Ws * Cp;
-        float* da = dst + ((size_t)b * H + ya) * W * Cp;
-        float* db = yb < H ? dst + ((size_t)b * H + yb) * W * Cp : nullptr;
+        float* da = dst + ((size_t)b * H + ya) * W * Cd;
+        float* db = yb < H ? dst + ((size_t)b * H + yb) * W * Cd : nullptr;
         for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
             for (int xs = rt.lane; xs < Ws; xs += rt.PL) {
                 const int xa = 2 * xs, xb = xa + 1;
@@ -565,12 +584,22 @@ __global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict
                 const size_t off = rs + (size_t)xs * Cp + c4 * 4;
                 float4 v = ldg4(s0 + off);
                 if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+                const float4 full = v;
                 v = round_tf32(v, rnd);
-                *reinterpret_cast<float4*>(da + (size_t)xa * Cp + c4 * 4) = v;
-                if (xb < W) *reinterpret_cast<float4*>(da + (size_t)xb * Cp + c4 * 4) = v;
+                *reinterpret_cast<float4*>(da + (size_t)xa * Cd + c4 * 4) = v;
+                if (xb < W) *reinterpret_cast<float4*>(da + (size_t)xb * Cd + c4 * 4) = v;
                 if (db) {
-                    *reinterpret_cast<float4*>(db + (size_t)xa * Cp + c4 * 4) = v;
-                    if (xb < W) *reinterpret_cast<float4*>(db + (size_t)xb * Cp + c4 * 4) = v;
+                    *reinterpret_cast<float4*>(db + (size_t)xa * Cd + c4 * 4) = v;
+                    if (xb < W) *reinterpret_cast<float4*>(db + (size_t)xb * Cd + c4 * 4) = v;
+                }
+                if (split) {                         // low-order part behind the Cp high-order channels
+                    const float4 lo = round_tf32(make_float4(full.x - v.x, full.y - v.y, full.z - v.z, full.w - v.w), 1);
+                    *reinterpret_cast<float4*>(da + (size_t)xa * Cd + Cp + c4 * 4) = lo;
+                    if (xb < W) *reinterpret_cast<float4*>(da + (size_t)xb * Cd + Cp + c4 * 4) = lo;
+                    if (db) {
+                        *reinterpret_cast<float4*>(db + (size_t)xa * Cd + Cp + c4 * 4) = lo;
+                        if (xb < W) *reinterpret_cast<float4*>(db + (size_t)xb * Cd + Cp + c4 * 4) = lo;
+                    }
                 }
             }
     }
@@ -634,7 +663,7 @@ __global__ void __launch_bounds__(256) make_wT_kernel(const float* __restrict__ 
         for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
             // j = (tap*Cin_p + ci)*Cout_p + co  (the layout of w itself)
             const unsigned co = j % Cout_p, t = j / Cout_p, ci = t % Cin_p, tap = t / Cin_p, tapT = 8u - tap;
-            wTK[L.wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(wl[j]);
+            wTK[L.wtk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(wl[j]);
         }
     }
 }
@@ -662,7 +691,7 @@ __global__ void __launch_bounds__(256) make_wT_tiled_kernel(const float* __restr
         const int ci = ci0 + ty + 8 * k, co = co0 + tx;
         const float v = wl[((size_t)tap * Cin_p + ci) * Cout_p + co];
         tile[ty + 8 * k][tx] = v;
-        wTK[L.wk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(v);
+        wTK[L.wtk_off + (size_t)ci * (9 * Cout_p) + (size_t)tapT * Cout_p + co] = round_tf32(v);
     }
     __syncthreads();
 #pragma unroll
@@ -674,7 +703,195 @@ __global__ void __launch_bounds__(256) make_wT_tiled_kernel(const float* __restr
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Head conv fused with its producer (src/model.jl:270-272 at l = 1 + src/flux.jl:4): raw = Conv3x3(crop(Upsample2x_nearest(s0 + s1)))
+// with NO = 2*noutput output channels, identity activation, planar (WHCN) output.  Exact FP32 on the CUDA cores in every
+// precision mode: the layer has 2*noutput columns (a 32-column MMA would be 94 % padding), is bound by its reads, and its
+// rounding error reaches (m, sigma) undamped, so this is where FP32 operands buy the most accuracy.
+// One thread = one LOW-resolution cell = the 2 x 2 output pixels above it: per input channel nine source values (its 3 x 3
+// low-resolution neighbourhood, shared-memory tile stored channel-major so a warp reads consecutive words) feed the 4 x 9 taps.
+// A tap that leaves the cropped image (odd H or W: output row 2i+1 == H) reads zero, as the conv padding does.
+constexpr int HU_TW = 32, HU_TH = 8;                        // low-resolution cells per block (x, y)
+constexpr int HU_SP = (HU_TW + 2) * (HU_TH + 2) + 1;        // channel stride of the tile (+1: conflict-free transposing fill)
+template <int NO>
+__global__ void __launch_bounds__(256) head_up_conv_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp, int Cin,
+                                                           const float* __restrict__ wgt, int Cin_p, int Cout_p, const float* __restrict__ bias,
+                                                           int H, int W, float* __restrict__ out) {
+    extern __shared__ float hu_smem[];
+    float* S = hu_smem;                                      // [Cin][HU_SP]
+    float* wS = hu_smem + (size_t)Cin * HU_SP;               // [Cin][9][NO]
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
+    const int tilesx = (Ws + HU_TW - 1) / HU_TW, tilesy = (Hs + HU_TH - 1) / HU_TH;
+    int bid = blockIdx.x;
+    const int b = bid / (tilesx * tilesy);
+    bid -= b * tilesx * tilesy;
+    const int ty0 = (bid / tilesx) * HU_TH, tx0 = (bid - (bid / tilesx) * tilesx) * HU_TW;
+    const int t = threadIdx.x;
+    for (int i = t; i < Cin * 9 * NO; i += 256) {
+        const int o = i % NO, r = i / NO, tap = r % 9, ci = r / 9;
+        wS[i] = __ldg(wgt + ((size_t)tap * Cin_p + ci) * Cout_p + o);
+    }
+    {   // tile (with a one-cell halo, zero outside the source image), transposed to channel-major
+        const int C4 = (Cin + 3) >> 2;
+        constexpr int NP = (HU_TW + 2) * (HU_TH + 2);
+        for (int i = t; i < NP * C4; i += 256) {
+            const int c4 = i % C4, pix = i / C4, py = pix / (HU_TW + 2), px = pix - py * (HU_TW + 2);
+            const int ys = ty0 + py - 1, xs = tx0 + px - 1;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ys >= 0 && ys < Hs && xs >= 0 && xs < Ws) {
+                const size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + 4 * c4;
+                v = ldg4(s0 + off);
+                if (s1) { const float4 u = ldg4(s1 + off); v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w; }
+            }
+            const int c = 4 * c4;
+            S[(size_t)c * HU_SP + pix] = v.x;
+            if (c + 1 < Cin) S[(size_t)(c + 1) * HU_SP + pix] = v.y;
+            if (c + 2 < Cin) S[(size_t)(c + 2) * HU_SP + pix] = v.z;
+            if (c + 3 < Cin) S[(size_t)(c + 3) * HU_SP + pix] = v.w;
+        }
+    }
+    __syncthreads();
+    const int ly = t >> 5, lx = t & 31;
+    const int ys = ty0 + ly, xs = tx0 + lx;
+    const bool rowB = 2 * ys + 1 < H, colB = 2 * xs + 1 < W;         // output row 2*ys+1 / column 2*xs+1 exists (not cropped)
+    float acc[2][2][NO];
+#pragma unroll
+    for (int p = 0; p < 2; p++)
+#pragma unroll
+        for (int q = 0; q < 2; q++)
+#pragma unroll
+            for (int o = 0; o < NO; o++) acc[p][q][o] = 0.f;
+    const float* Sp = S + ly * (HU_TW + 2) + lx;
+    for (int ci = 0; ci < Cin; ci++) {
+        // v[a][b]: a, b in {0,1,2} = source cell (ys-1+a, xs-1+b); index 3 = "this cell, seen from the output row/column that the
+        // crop removed" = zero padding
+        float v[4][4];
+#pragma unroll
+        for (int a = 0; a < 3; a++)
+#pragma unroll
+            for (int c = 0; c < 3; c++) v[a][c] = Sp[(size_t)ci * HU_SP + a * (HU_TW + 2) + c];
+#pragma unroll
+        for (int c = 0; c < 3; c++) { v[3][c] = rowB ? v[1][c] : 0.f; v[c][3] = colB ? v[c][1] : 0.f; }
+        v[3][3] = (rowB && colB) ? v[1][1] : 0.f;
+        const float* wc = wS + ci * 9 * NO;
+#pragma unroll
+        for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+            for (int dx = 0; dx < 3; dx++) {
+                float w[NO];
+#pragma unroll
+                for (int o = 0; o < NO; o++) w[o] = wc[(dy * 3 + dx) * NO + o];
+#pragma unroll
+                for (int p = 0; p < 2; p++)
+#pragma unroll
+                    for (int q = 0; q < 2; q++) {
+                        // output row 2*ys+p, tap dy-1 -> high-res row 2*ys+p+dy-1 -> source offset floor((p+dy-1)/2) in {-1,0,+1};
+                        // (p,dy) = (0,2) lands on row 2*ys+1, which may be cropped: slot 3
+                        const int a = (p == 0 && dy == 2) ? 3 : ((p + dy + 1) >> 1);
+                        const int c = (q == 0 && dx == 2) ? 3 : ((q + dx + 1) >> 1);
+                        const float x = v[a][c];
+#pragma unroll
+                        for (int o = 0; o < NO; o++) acc[p][q][o] = fmaf(x, w[o], acc[p][q][o]);
+                    }
+            }
+    }
+    if (ys >= Hs || xs >= Ws) return;
+#pragma unroll
+    for (int o = 0; o < NO; o++) {
+        const float bv = bias ? __ldg(bias + o) : 0.f;
+#pragma unroll
+        for (int p = 0; p < 2; p++) {
+            const int y = 2 * ys + p;
+            if (y >= H) continue;
+            float* dst = out + (((size_t)b * NO + o) * H + y) * W + 2 * xs;
+            dst[0] = acc[p][0][o] + bv;
+            if (colB) dst[1] = acc[p][1][o] + bv;
+        }
+    }
+}
+
+// expanded K-major forward weights of the 3xTF32 layers (layout: SplitLayerDesc in k2_conv.cuh); one layer per blockIdx.y
+__global__ void __launch_bounds__(256) make_wK_split_kernel(const float* __restrict__ w, float* __restrict__ wK, const __grid_constant__ SplitTable tab) {
+    const SplitLayerDesc L = tab.d[blockIdx.y];
+    const int ldk = 9 * L.Cin_pe;
+    const int64_t n = (int64_t)L.Cout_p * ldk;
+    const float* wl = w + L.w_off;
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+        const int co = (int)(j / ldk), k = (int)(j - (int64_t)co * ldk), tap = k / L.Cin_pe, s = k - tap * L.Cin_pe;
+        int ci = -1, cs = co, lo = 0;                   // source channel / output column of the master weight, low-order part?
+        if (L.mode == 1) {
+            if (s < 2 * L.C) ci = s % L.C;
+        } else {
+            if (co < L.n2) { if (s < 2 * L.Cin_p) ci = s % L.Cin_p; }
+            else if (co >= 8 && co < 8 + L.n2 && s < L.Cin_p) { ci = s; cs = co - 8; lo = 1; }
+        }
+        float v = 0.f;
+        if (ci >= 0) {
+            const float x = wl[((size_t)tap * L.Cin_p + ci) * L.Cout_p + cs];
+            const float hi = round_tf32(x);
+            v = lo ? round_tf32(x - hi) : hi;
+        }
+        wK[L.wk_off + j] = v;
+    }
+}
+__global__ void __launch_bounds__(256) fold_split_grad_kernel(const float* __restrict__ gexp, float* __restrict__ g, const __grid_constant__ SplitTable tab) {
+    const SplitLayerDesc L = tab.d[blockIdx.y];
+    const int64_t n = (int64_t)9 * L.Cin_p * L.Cout_p;
+    const int nhi = L.mode == 1 ? L.C : L.Cin_p, lo_off = nhi;
+    const float* ge = gexp + L.gexp_off;
+    for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+        const int co = (int)(j % L.Cout_p);
+        const int64_t t = j / L.Cout_p;
+        const int ci = (int)(t % L.Cin_p), tap = (int)(t / L.Cin_p);
+        float v = 0.f;
+        if (ci < nhi) v = ge[((size_t)tap * L.Cin_pe + ci) * L.Cout_p + co] + ge[((size_t)tap * L.Cin_pe + lo_off + ci) * L.Cout_p + co];
+        g[L.w_off + j] = v;
+    }
+}
+
 }  // namespace
+
+int32_t k2_make_wK_split(dincae_ctx* ctx, const float* w, float* wK, const SplitTable& tab) {
+    if (tab.count == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, make_wK_split_kernel, dim3(32u, (unsigned)tab.count), 256, 0, w, wK, tab);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+int32_t k2_fold_split_grad(dincae_ctx* ctx, const float* gexp, float* g, const SplitTable& tab) {
+    if (tab.count == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, fold_split_grad_kernel, dim3(32u, (unsigned)tab.count), 256, 0, gexp, g, tab);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+bool k2_head_up_conv_eligible(int Cin, int nout2) {
+    return (nout2 == 2 || nout2 == 4 || nout2 == 6 || nout2 == 8) && (size_t)Cin * (HU_SP + 9 * nout2) * sizeof(float) <= 200 * 1024;
+}
+int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int Cin,
+                        const float* wgt, int Cin_p, int Cout_p, const float* bias, int nout2, int H, int W, float* out,
+                        double work_flops, double work_bytes) {
+    if ((int64_t)B * H * W == 0) return DINCAE_OK;
+    DC_REQUIRE(k2_head_up_conv_eligible(Cin, nout2), DINCAE_EUNSUPPORTED, "k2_head_up_conv: %d input / %d output channels not supported", Cin, nout2);
+    DC_REQUIRE(Hs == H / 2 + H % 2 && Ws == W / 2 + W % 2, DINCAE_EINVAL, "k2_head_up_conv: source is not the half-resolution level");
+    const int smem = (int)((size_t)Cin * (HU_SP + 9 * nout2) * sizeof(float));
+    const unsigned grid = (unsigned)(B * ((Ws + HU_TW - 1) / HU_TW) * ((Hs + HU_TH - 1) / HU_TH));
+    DC_WORK(ctx, work_flops, work_bytes);
+#define HU_LAUNCH(NO_)                                                                                                      \
+    do {                                                                                                                    \
+        static int attr = 0;                                                                                                \
+        if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_up_conv_kernel<NO_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
+        DC_LAUNCH_PDL(ctx, head_up_conv_kernel<NO_>, grid, 256, smem, src0, src1, B, Hs, Ws, Cp, Cin, wgt, Cin_p, Cout_p, bias, H, W, out); \
+    } while (0)
+    if (nout2 == 2) HU_LAUNCH(2);
+    else if (nout2 == 4) HU_LAUNCH(4);
+    else if (nout2 == 6) HU_LAUNCH(6);
+    else HU_LAUNCH(8);
+#undef HU_LAUNCH
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
@@ -794,12 +1011,13 @@ static int k2_row_blocks(dincae_ctx* ctx, int64_t rows, int64_t n_elems4) {
     return (int)(rows < cap ? rows : cap);
 }
 
-int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp) {
+int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, int C1, int B, int H, int W, float* dst, int Cp, int split) {
     int64_t M = (int64_t)B * H * W;
     if (M == 0) return DINCAE_OK;
-    int Cw = (int)dc_round_up(C0 + C1, 8);                  // whole 32-byte sectors; the rest of the row is never written (zero since allocation)
+    DC_REQUIRE(!split || (ctx->tf32_acts && 2 * (C0 + C1) <= Cp), DINCAE_EINVAL, "k2_pack: split layout needs TF32 mode and Cp >= 2*C");
+    int Cw = (int)dc_round_up((split ? 2 : 1) * (C0 + C1), 8);                  // whole 32-byte sectors; the rest of the row is never written (zero since allocation)
     if (Cw > Cp) Cw = Cp;
-    DC_LAUNCH_PDL(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts);   // 8 warps x 32 pixels per block
+    DC_LAUNCH_PDL(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts, split);   // 8 warps x 32 pixels per block
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
@@ -844,18 +1062,20 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     return DINCAE_OK;
 }
 
-int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
+int32_t k2_up_bilinear(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst, int split) {
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH(ctx, up_bilinear_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
+    DC_REQUIRE(!split || ctx->tf32_acts, DINCAE_EINVAL, "k2_up_bilinear: split layout needs TF32 mode");
+    DC_LAUNCH(ctx, up_bilinear_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts, split);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
 
-int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst) {
+int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int H, int W, float* dst, int split) {
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
-    DC_LAUNCH_PDL(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts);
+    DC_REQUIRE(!split || ctx->tf32_acts, DINCAE_EINVAL, "k2_up_nearest: split layout needs TF32 mode");
+    DC_LAUNCH_PDL(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts, split);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -25,7 +25,7 @@ struct TmaConvArgs {
     const float* addend;
     float* dst;
     float* planar_out;
-    int planar_C, planar_accumulate;
+    int planar_C, planar_accumulate, planar_fold;
     float* pool_dst;           // persistent kernel, even H and W: also writes MeanPool((2,2)) of the output, [B][H/2][W/2][Cout_p]
     int pool_rnd;              // round the pooled values to TF32 (they feed the next tensor-core conv)
 };
@@ -582,7 +582,9 @@ __device__ __forceinline__ void epi_tile(const TmaConvArgs& p, EpiCtx& e, uint32
 #pragma unroll
             for (int k = 0; k < 16; k++) {
                 if (k < p.planar_C) {
-                    float v = __uint_as_float(r[k]) + e.bias_s[k];
+                    float v = __uint_as_float(r[k]);
+                    if (p.planar_fold) v += __uint_as_float(r[(k + 8) & 15]);     // + the low-order weight column (3xTF32 head), k < planar_C <= 8
+                    v += e.bias_s[k];
                     v = act_apply(v, p.act, p.slope);
                     const size_t po = (((size_t)b * p.planar_C + k) * p.H + y) * p.W + x;
                     p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
@@ -1067,7 +1069,8 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = a.planar_fold;
+    DC_REQUIRE(!a.planar_fold || (a.planar_out && a.planar_C <= 8 && a.Cout_p >= 16), DINCAE_EINVAL, "conv3x3_persist: planar_fold needs a planar output of at most 8 channels");
     p.pool_dst = a.pool_dst; p.pool_rnd = ctx->tf32_acts ? 1 : 0;
     DC_REQUIRE(!a.pool_dst || k2_conv_fuses_pool(a), DINCAE_EINVAL, "conv3x3_persist: pool fusion needs even H, W, a leaky slope in [0,1) and no addend");
     int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
@@ -1191,7 +1194,8 @@ static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
     p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
+    DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
     p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
@@ -1250,7 +1254,8 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate;
+    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
+    DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
     p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
@@ -2347,7 +2352,7 @@ extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const f
     p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0;
+    p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0; p.planar_fold = 0;
     p.pool_dst = nullptr; p.pool_rnd = 0;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));

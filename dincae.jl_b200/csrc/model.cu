@@ -46,22 +46,29 @@ inline double cflops(const LayerInfo& y, int B, int H, int W) { return 2.0 * 9 *
 // algorithmic HBM bytes of one conv / dgrad / wgrad call: both pixel tensors once + the weights (real channel counts)
 inline double cbytes(const LayerInfo& y, int B, int H, int W) { return 4.0 * ((double)(y.Cin + y.Cout) * B * H * W + 9.0 * y.Cin * y.Cout); }
 inline bool has_skip(const dincae_model* M, int l) { return l >= 1 && l < M->L && ((M->cfg.skip_mask >> l) & 1u); }
+// tensor-core modes, nearest upsampling: the head conv runs fused with its upsample + skip-add producer in exact FP32
+// (k2_head_up_conv); U[0] is then only materialised by the backward pass, for the head's weight gradient
+inline bool head_fused(const dincae_model* M) {
+    return M->wK != nullptr && M->cfg.upsampling == DINCAE_UP_NEAREST && k2_head_up_conv_eligible(M->dec[0][0].Cin, 2 * M->O);
+}
 
 // the producer of conv_dec_l: upsample(+crop) of y_{l+1} = R[l+1] (+ X[l+1] when level l+1 has a skip) or X[L]
 int32_t dec_source(dincae_model* M, int c, int l, int B, bool materialise, ConvSrc* s) {
     ChainBufs& cb = M->cb[c];
     const float* src0 = (l + 1 == M->L) ? cb.X[M->L] : cb.R[l + 1];
     const float* src1 = has_skip(M, l + 1) ? cb.X[l + 1] : nullptr;
-    int Cp = M->dec[c][l].Cin_p;
+    const LayerInfo& d = M->dec[c][l];
+    const int Cp = d.Cin_p;                          // channels of the low-resolution source tensors
+    const int split = d.split_mode == 2;             // 3xTF32 head conv: U[0] carries [hi | lo] = 2*Cp channels
     if (M->cfg.upsampling == DINCAE_UP_NEAREST && !M->wK) {
         *s = ConvSrc{src0, src1, SRC_UP_NEAREST, M->Hl[l + 1], M->Wl[l + 1], Cp};       // FP32 path: fused into the conv producer
     } else {
         // bilinear, or TF32 mode: materialise u_l = crop(upsample(y_{l+1})) once (TF32-rounded), it feeds the TMA conv + wgrad
         if (materialise) {
-            if (M->cfg.upsampling == DINCAE_UP_NEAREST) DC_TRY(k2_up_nearest(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
-            else DC_TRY(k2_up_bilinear(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l]));
+            if (M->cfg.upsampling == DINCAE_UP_NEAREST) DC_TRY(k2_up_nearest(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l], split));
+            else DC_TRY(k2_up_bilinear(M->ctx, src0, src1, B, M->Hl[l + 1], M->Wl[l + 1], Cp, M->Hl[l], M->Wl[l], cb.U[l], split));
         }
-        *s = ConvSrc{cb.U[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], Cp};
+        *s = ConvSrc{cb.U[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cin_pe};
     }
     return DINCAE_OK;
 }
@@ -71,16 +78,17 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
     ChainBufs& cb = M->cb[c];
     const int L = M->L;
     const float slope = M->cfg.leaky_slope;
-    if (c == 0) DC_TRY(k2_pack(ctx, d_xin, M->cfg.ninput, nullptr, 0, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_p));
-    else DC_TRY(k2_pack(ctx, M->cb[c - 1].RAW, 2 * M->O, d_xin, M->cfg.ninput, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_p));   // cat(xout,xin), T9
+    const int split0 = M->enc[c][0].split_mode == 1;      // split first conv: X[0] = [hi | lo] of the real channels
+    if (c == 0) DC_TRY(k2_pack(ctx, d_xin, M->cfg.ninput, nullptr, 0, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_pe, split0));
+    else DC_TRY(k2_pack(ctx, M->cb[c - 1].RAW, 2 * M->O, d_xin, M->cfg.ninput, B, M->Hl[0], M->Wl[0], cb.X[0], M->enc[c][0].Cin_pe, split0));   // cat(xout,xin), T9
     for (int l = 0; l < L; l++) {
         const LayerInfo& e = M->enc[c][l];
         ConvArgs a{};
-        a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
+        a.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_pe};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->w + e.w_off; a.bias = M->w + e.b_off; a.Cout_p = e.Cout_p;
-        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_p; a.in_is_tf32 = 1;     // X[0] from pack, X[l>=1] from pool_kernel (both rounded on store)
-        a.in_real_C = e.Cin;                                                               // channels past Cin are zero padding
+        a.wgtK = M->wK ? M->wK + e.wk_off : nullptr; a.ldk = 9 * e.Cin_pe; a.in_is_tf32 = 1;     // X[0] from pack, X[l>=1] from pool_kernel (both rounded on store)
+        a.in_real_C = e.split_mode == 1 ? 2 * e.Cin : e.Cin;                               // channels past this are zero padding
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
@@ -91,6 +99,14 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
     }
     for (int l = L - 1; l >= 0; l--) {
         const LayerInfo& d = M->dec[c][l];
+        if (l == 0 && head_fused(M)) {
+            const float* src0 = (L == 1) ? cb.X[1] : cb.R[1];
+            const float* src1 = has_skip(M, 1) ? cb.X[1] : nullptr;
+            DC_TRY(k2_head_up_conv(ctx, src0, src1, B, M->Hl[1], M->Wl[1], d.Cin_p, d.Cin, M->w + d.w_off, d.Cin_p, d.Cout_p, M->w + d.b_off,
+                                   2 * M->O, M->Hl[0], M->Wl[0], cb.RAW, cflops(d, B, M->Hl[0], M->Wl[0]),
+                                   4.0 * ((double)d.Cin * (has_skip(M, 1) ? 2 : 1) * B * M->Hl[1] * M->Wl[1] + 2.0 * M->O * B * M->Hl[0] * M->Wl[0])));
+            continue;                                                              // Upsample + crop + SumSkip + Conv(identity) in one kernel, :270-272
+        }
         ConvSrc s;
         DC_TRY(dec_source(M, c, l, B, true, &s));                                  // Upsample + croppadding (+ SumSkip below), :270-271
         if (l > 0) {
@@ -107,9 +123,9 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
             ConvArgs a{};
             a.in = s; a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
             a.wgt = M->w + d.w_off; a.bias = M->w + d.b_off; a.Cout_p = d.Cout_p;
-            a.wgtK = M->wK + d.wk_off; a.ldk = 9 * d.Cin_p; a.in_is_tf32 = 1;
+            a.wgtK = M->wK + d.wk_off; a.ldk = 9 * d.Cin_pe; a.in_is_tf32 = 1;
             a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = nullptr;
-            a.planar_out = cb.RAW; a.planar_C = 2 * M->O; a.planar_accumulate = 0;
+            a.planar_out = cb.RAW; a.planar_C = 2 * M->O; a.planar_accumulate = 0; a.planar_fold = d.split_mode == 2;
             a.work_flops = cflops(d, B, M->Hl[0], M->Wl[0]);
             a.work_bytes = cbytes(d, B, M->Hl[0], M->Wl[0]);
             DC_TRY(k2_conv(ctx, a));
@@ -128,6 +144,7 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
 int32_t ensure_wT(dincae_model* M) {
     if (!M->wT_dirty) return DINCAE_OK;
     DC_TRY(k2_make_wT(M->ctx, M->w, M->wT, M->wK, M->wTK, M->d_wtab, M->n_wlayers, M->n_wT_copy));
+    if (M->wK) DC_TRY(k2_make_wK_split(M->ctx, M->w, M->wK, M->split));      // overwrites the forward copies of the 3xTF32 layers
     M->wT_dirty = false;
     return DINCAE_OK;
 }
@@ -214,10 +231,10 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             else DC_TRY(k2_up_bilinear_bwd(ctx, M->GU[l - 1], B, M->Hl[l - 1], M->Wl[l - 1], d.Cout_p, M->Hl[l], M->Wl[l], cb.R[l], slope, M->G[l], M->GD[l]));
         }
         ConvSrc s;
-        DC_TRY(dec_source(M, c, l, B, false, &s));
+        DC_TRY(dec_source(M, c, l, B, l == 0 && head_fused(M), &s));       // fused head: the forward pass did not materialise U[0]
         WgradArgs wa{};
         wa.in = s; wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = gd; wa.Cout_p = d.Cout_p;
-        wa.dW = M->g + d.w_off; wa.db = M->g + d.b_off;
+        wa.dW = d.split_mode ? M->g_exp + d.gexp_off : M->g + d.w_off; wa.db = M->g + d.b_off;     // 3xTF32 layer: expanded gradient, folded after the reductions
         wa.colpart = colpart; wa.colpart_blocks = colblocks;
         wa.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         wa.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
@@ -228,7 +245,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.in = ConvSrc{gd, nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], d.Cout_p};
         a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
         a.wgt = M->wT + d.wT_off; a.bias = nullptr; a.Cout_p = d.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = M->GU[l];
-        a.wgtK = M->wTK ? M->wTK + d.wk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = 1;   // GD[l>=1] from upbwd, GD0 from pack (both rounded on store)
+        a.wgtK = M->wTK ? M->wTK + d.wtk_off : nullptr; a.ldk = 9 * d.Cout_p; a.in_is_tf32 = 1;   // GD[l>=1] from upbwd, GD0 from pack (both rounded on store)
         a.in_real_C = d.Cout;                                                               // the gradient tensor's channels past Cout are zero
         a.work_flops = cflops(d, B, M->Hl[l], M->Wl[l]);
         a.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
@@ -247,9 +264,9 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         float* ecolpart = colpart_alloc(M, (int64_t)B * M->Hl[l] * M->Wl[l] * (e.Cout_p / 4), e.Cout_p, &ecolblocks);
         DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l], ecolpart));
         WgradArgs wa{};
-        wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_p};
+        wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_pe};
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
-        wa.dW = M->g + e.w_off; wa.db = M->g + e.b_off;
+        wa.dW = e.split_mode ? M->g_exp + e.gexp_off : M->g + e.w_off; wa.db = M->g + e.b_off;
         wa.colpart = ecolpart; wa.colpart_blocks = ecolblocks;
         wa.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
         wa.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
@@ -260,7 +277,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.in = ConvSrc{M->GC[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cout_p};
             a.B = B; a.H = M->Hl[l]; a.W = M->Wl[l];
             a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f;
-            a.wgtK = M->wTK ? M->wTK + e.wk_off : nullptr; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;        // GC[l] from poolbwd (rounded)
+            a.wgtK = M->wTK ? M->wTK + e.wtk_off : nullptr; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;        // GC[l] from poolbwd (rounded)
             a.addend = has_skip(M, l) ? M->G[l] : nullptr;       // SumSkip: the level input also feeds the level output
             a.dst = M->XG[l];
             a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
@@ -273,7 +290,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
             a.in = ConvSrc{M->GC[0], nullptr, SRC_DIRECT, M->Hl[0], M->Wl[0], e.Cout_p};
             a.B = B; a.H = M->Hl[0]; a.W = M->Wl[0];
             a.wgt = M->wT + e.wT_off; a.bias = nullptr; a.Cout_p = e.Cin_p; a.act = ACT_NONE; a.slope = 0.f; a.addend = nullptr; a.dst = nullptr;
-            a.wgtK = M->wTK + e.wk_off; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;
+            a.wgtK = M->wTK + e.wtk_off; a.ldk = 9 * e.Cout_p; a.in_is_tf32 = 1;
             a.planar_out = M->cb[c - 1].GRAW; a.planar_C = 2 * M->O; a.planar_accumulate = 1;
             a.work_flops = 2.0 * 9 * 2 * M->O * e.Cout * (double)B * M->Hl[0] * M->Wl[0];
             DC_TRY(k2_conv(ctx, a));
@@ -433,6 +450,7 @@ int32_t backward_all(dincae_model* M, int B) {
     M->red.count = 0;
     for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
     DC_TRY(k2_reduce_batched(M->ctx, M->red));
+    DC_TRY(k2_fold_split_grad(M->ctx, M->g_exp, M->g, M->split));
     DC_LAUNCH(M->ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -528,13 +546,15 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     DC_REQUIRE(cfg->upsampling == DINCAE_UP_NEAREST || cfg->upsampling == DINCAE_UP_BILINEAR, DINCAE_EUNSUPPORTED, "dincae_model_create: unknown upsampling_method %d", cfg->upsampling);
     DC_REQUIRE(!(cfg->skip_mask & 1u), DINCAE_EUNSUPPORTED, "dincae_model_create: a skip connection at level 1 needs ninput == 2*noutput and is not supported");
     DC_REQUIRE(cfg->max_batch >= 1, DINCAE_EINVAL, "dincae_model_create: max_batch < 1");
-    DC_REQUIRE(cfg->precision == DINCAE_PREC_FP32 || cfg->precision == DINCAE_PREC_TF32, DINCAE_EUNSUPPORTED, "dincae_model_create: unknown precision %d", cfg->precision);
+    DC_REQUIRE(cfg->precision == DINCAE_PREC_FP32 || cfg->precision == DINCAE_PREC_TF32 || cfg->precision == DINCAE_PREC_TF32X1, DINCAE_EUNSUPPORTED, "dincae_model_create: unknown precision %d", cfg->precision);
     for (int l = 0; l < cfg->nlevels; l++) DC_REQUIRE(cfg->nfilter[l] >= 1, DINCAE_EINVAL, "dincae_model_create: nfilter[%d] < 1", l);
     DC_CHECK_CUDA(cudaSetDevice(ctx->device));
 
     dincae_model* M = new dincae_model();
     M->ctx = ctx; M->cfg = *cfg; M->L = cfg->nlevels; M->nchains = cfg->nchains; M->O = cfg->noutput; M->maxB = cfg->max_batch;
-    const int cpad = cfg->precision == DINCAE_PREC_TF32 ? 32 : 4;     // TF32 mode: every conv is tensor-core eligible (32-channel K chunks)
+    const bool tc_mode = cfg->precision != DINCAE_PREC_FP32;
+    const bool split3 = cfg->precision == DINCAE_PREC_TF32 && 2 * cfg->noutput <= 8;     // 3xTF32 first + head convs
+    const int cpad = tc_mode ? 32 : 4;     // tensor-core modes: every conv is tensor-core eligible (32-channel K chunks)
     M->nco = dc_round_up(2 * M->O, cpad);
     const int L = M->L;
     M->Hl[0] = cfg->H; M->Wl[0] = cfg->W;
@@ -542,7 +562,8 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
 
     // ---- topology and parameter layout (Flux.trainables order: enc1..encL, decL..dec1 per chain)
     M->enc.resize(M->nchains); M->dec.resize(M->nchains);
-    int64_t off = 0, foff = 0, toff = 0, koff = 0;
+    int64_t off = 0, foff = 0, toff = 0, koff = 0, tkoff = 0, goff = 0;
+    M->split.count = 0;
     std::vector<WLayerDesc> wtab;
     for (int c = 0; c < M->nchains; c++) {
         std::vector<int> encf(L + 1), decf(L + 1);
@@ -550,20 +571,31 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         decf[0] = 2 * M->O;
         for (int l = 0; l < L; l++) { encf[l + 1] = cfg->nfilter[l]; decf[l + 1] = cfg->nfilter[l]; }
         M->enc[c].resize(L); M->dec[c].resize(L);
-        auto fill = [&](LayerInfo& y, int cin, int cout) {
+        auto fill = [&](LayerInfo& y, int cin, int cout, int split_mode) {
             y.Cin = cin; y.Cout = cout; y.Cin_p = dc_round_up(cin, cpad); y.Cout_p = dc_round_up(cout, cpad);
+            y.split_mode = split3 ? split_mode : 0;
+            y.Cin_pe = y.split_mode == 1 ? dc_round_up(2 * cin, cpad) : (y.split_mode == 2 ? 2 * y.Cin_p : y.Cin_p);
+            y.gexp_off = 0;
             y.Kpad = dc_round_up(9 * y.Cin_p, 16); y.KpadT = dc_round_up(9 * y.Cout_p, 16);
             y.w_off = off; off += (int64_t)y.Kpad * y.Cout_p;
             y.b_off = off; off += y.Cout_p;
             y.flux_w_off = foff; foff += (int64_t)9 * cin * cout;
             y.flux_b_off = foff; foff += cout;
             y.wT_off = toff; toff += (int64_t)y.KpadT * y.Cin_p;
-            y.wk_off = koff; koff += (int64_t)9 * y.Cin_p * y.Cout_p;
+            y.wk_off = koff; koff += (int64_t)9 * y.Cin_pe * y.Cout_p;
+            y.wtk_off = tkoff; tkoff += (int64_t)9 * y.Cin_p * y.Cout_p;
+            if (y.split_mode) {
+                y.gexp_off = goff; goff += (int64_t)9 * y.Cin_pe * y.Cout_p;
+                SplitLayerDesc& sd = M->split.d[M->split.count++];
+                sd.w_off = y.w_off; sd.wk_off = y.wk_off; sd.gexp_off = y.gexp_off;
+                sd.Cin_p = y.Cin_p; sd.Cin_pe = y.Cin_pe; sd.Cout_p = y.Cout_p; sd.mode = y.split_mode; sd.C = cin; sd.n2 = cout;
+            }
         };
-        for (int l = 0; l < L; l++) fill(M->enc[c][l], encf[l], encf[l + 1]);
-        for (int l = L - 1; l >= 0; l--) fill(M->dec[c][l], decf[l + 1], decf[l]);
+        for (int l = 0; l < L; l++) fill(M->enc[c][l], encf[l], encf[l + 1], l == 0 ? 1 : 0);
+        const bool fused_head = tc_mode && cfg->upsampling == DINCAE_UP_NEAREST && k2_head_up_conv_eligible(decf[1], decf[0]);
+        for (int l = L - 1; l >= 0; l--) fill(M->dec[c][l], decf[l + 1], decf[l], (l == 0 && !fused_head) ? 2 : 0);
     }
-    M->n_int = off; M->n_flux = foff; M->n_wT = toff; M->n_wk = koff;
+    M->n_int = off; M->n_flux = foff; M->n_wT = toff; M->n_wk = koff; M->n_wtk = tkoff; M->n_gexp = goff;
     // table for the transposed copies, in wT order; each entry copies 9*Cin_p*Cout_p values
     {
         // make_wT walks layers by cumulative n, so wT offsets must be visited in the same order as the table
@@ -575,7 +607,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         int64_t tot = 0;
         for (const LayerInfo* y : order) {
             WLayerDesc d;
-            d.w_off = y->w_off; d.wT_off = y->wT_off; d.Cin_p = y->Cin_p; d.Cout_p = y->Cout_p; d.n = (int64_t)9 * y->Cin_p * y->Cout_p; d.wk_off = y->wk_off;
+            d.w_off = y->w_off; d.wT_off = y->wT_off; d.Cin_p = y->Cin_p; d.Cout_p = y->Cout_p; d.n = (int64_t)9 * y->Cin_p * y->Cout_p; d.wk_off = y->wk_off; d.wtk_off = y->wtk_off;
             wtab.push_back(d);
             tot += d.n;
         }
@@ -594,22 +626,23 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     want((void**)&M->m, sizeof(float) * (M->n_int + 4));
     want((void**)&M->v, sizeof(float) * (M->n_int + 4));
     want((void**)&M->wT, sizeof(float) * (M->n_wT + 4));
-    if (cfg->precision == DINCAE_PREC_TF32) {
+    if (tc_mode) {
         want((void**)&M->wK, sizeof(float) * (M->n_wk + 4));
-        want((void**)&M->wTK, sizeof(float) * (M->n_wk + 4));
+        want((void**)&M->wTK, sizeof(float) * (M->n_wtk + 4));
+        if (M->n_gexp) want((void**)&M->g_exp, sizeof(float) * (M->n_gexp + 4));
     }
     want((void**)&M->d_wtab, sizeof(WLayerDesc) * wtab.size());
     const size_t planar_out = sizeof(float) * Bm * 2 * M->O * cfg->W * cfg->H;
-    const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR || cfg->precision == DINCAE_PREC_TF32;   // U[l] materialised
+    const bool bil = cfg->upsampling == DINCAE_UP_BILINEAR || tc_mode;   // U[l] materialised
     for (int c = 0; c < M->nchains; c++) {
         ChainBufs& cb = M->cb[c];
         memset(&cb, 0, sizeof(cb));
-        want((void**)&cb.X[0], act(0, M->enc[c][0].Cin_p));
+        want((void**)&cb.X[0], act(0, M->enc[c][0].Cin_pe));
         for (int l = 0; l < L; l++) {
             want((void**)&cb.A[l], act(l, M->enc[c][l].Cout_p));
             want((void**)&cb.X[l + 1], act(l + 1, M->enc[c][l].Cout_p));
             if (l >= 1) want((void**)&cb.R[l], act(l, M->dec[c][l].Cout_p));
-            if (bil) want((void**)&cb.U[l], act(l, M->dec[c][l].Cin_p));
+            if (bil) want((void**)&cb.U[l], act(l, M->dec[c][l].Cin_pe));
         }
         want((void**)&cb.RAW, planar_out);
         want((void**)&cb.GRAW, planar_out);
@@ -644,12 +677,12 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             size_t b = k2_wgrad_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
             wgb = a > wgb ? a : wgb;
             wgb = b > wgb ? b : wgb;
-            size_t ta = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_p, M->enc[c][l].Cout_p);
-            size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_p, M->dec[c][l].Cout_p);
+            size_t ta = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->enc[c][l].Cin_pe, M->enc[c][l].Cout_p);
+            size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_pe, M->dec[c][l].Cout_p);
             wg_sum += ((ta + 255) / 256 * 256) + ((tb + 255) / 256 * 256);
             wg_sum += 2 * (((size_t)8 * ctx->num_sms * 512 * sizeof(float) + 255) / 256 * 256);      // bias column partials of both layers
         }
-    if (cfg->precision == DINCAE_PREC_TF32 && wg_sum > wgb) wgb = wg_sum;    // TF32 mode: one slice per layer (second stages are batched)
+    if (tc_mode && wg_sum > wgb) wgb = wg_sum;    // TF32 mode: one slice per layer (second stages are batched)
     M->wg_scratch_bytes = wgb;
     want(&M->wg_scratch, wgb);
     want((void**)&M->in_xin, sizeof(float) * Bm * cfg->ninput * cfg->W * cfg->H);

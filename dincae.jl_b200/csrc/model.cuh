@@ -12,7 +12,12 @@ struct LayerInfo {
     int KpadT;           // round_up(9*Cout_p,16): rows of the transposed matrix used by the data gradient
     int64_t w_off, b_off;    // offsets in the internal flat parameter buffer
     int64_t wT_off;          // offset in the transposed-weight buffer
-    int64_t wk_off;          // offset in the K-major TF32 copies wK / wTK (tensor-core path)
+    int64_t wk_off;          // offset in the K-major TF32 forward copy wK (tensor-core path; expanded layout for 3xTF32 layers)
+    int64_t wtk_off;         // offset in the K-major TF32 data-gradient copy wTK
+    int Cin_pe;              // channels of the conv's INPUT TENSOR on the tensor-core path: Cin_p, or the expanded [hi|lo|hi] /
+                             // [hi|lo] operand layout of a 3xTF32 layer (split_mode 1 = first conv of a chain, 2 = head conv)
+    int split_mode;
+    int64_t gexp_off;        // 3xTF32 layers: offset of the expanded weight gradient in g_exp
     int64_t flux_w_off, flux_b_off;   // offsets in the Flux.trainables order
 };
 
@@ -36,7 +41,10 @@ struct dincae_model {
     int64_t n_flux = 0, n_int = 0, n_wT = 0, n_wT_copy = 0;
     float *w = nullptr, *g = nullptr, *m = nullptr, *v = nullptr, *wT = nullptr;
     float *wK = nullptr, *wTK = nullptr;     // K-major TF32-rounded copies (NULL in FP32 mode)
-    int64_t n_wk = 0;
+    int64_t n_wk = 0, n_wtk = 0;
+    SplitTable split;                        // the 3xTF32 layers (DINCAE_PREC_TF32): first conv and head conv of every chain
+    float* g_exp = nullptr;                  // their weight gradients in the expanded layout, folded into g after the reductions
+    int64_t n_gexp = 0;
     WLayerDesc* d_wtab = nullptr;
     int n_wlayers = 0;
     bool wT_dirty = true;

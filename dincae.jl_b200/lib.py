@@ -11,7 +11,7 @@ HEADER = os.path.join(ROOT, "include", "dincae_b200.h")
 OK, EINVAL, EUNSUPPORTED, ECUDA, ENOMEM, ESIZE = range(6)
 HOST, DEVICE, DEVICE_XIN = 0, 1, 2
 UP_NEAREST, UP_BILINEAR = 0, 1
-PREC_FP32, PREC_TF32 = 0, 1
+PREC_FP32, PREC_TF32, PREC_TF32X1 = 0, 1, 2
 MAX_LEVELS, MAX_CHAINS = 8, 4
 
 

@@ -25,7 +25,13 @@ enum { DINCAE_OK = 0, DINCAE_EINVAL = 1, DINCAE_EUNSUPPORTED = 2, DINCAE_ECUDA =
 enum { DINCAE_HOST = 0, DINCAE_DEVICE = 1,
        DINCAE_DEVICE_XIN = 2 /* *_points entry points only: xin on the device (e.g. written by dincae_points_assemble), the point truth on the host */ };
 enum { DINCAE_UP_NEAREST = 0, DINCAE_UP_BILINEAR = 1 };
-enum { DINCAE_PREC_FP32 = 0, DINCAE_PREC_TF32 = 1 };   /* conv operand precision; accumulation is always FP32 */
+/* conv arithmetic; accumulation is always FP32.
+ *   FP32   : CUDA-core kernels, exact FP32 operands.
+ *   TF32   : tcgen05 tensor cores (default).  Operands rounded to TF32, except the first conv and the 2*noutput-channel head conv
+ *            of every chain (the thin full-resolution layers whose rounding dominates the output error), which run as 3xTF32
+ *            (hi/lo operand split, FP32-grade products): (m, sigma) stay inside 1e-3 of the FP32 reference.
+ *   TF32X1 : single-pass TF32 on every conv (what cuDNN's default math mode does); slightly faster, error ~2.5x larger. */
+enum { DINCAE_PREC_FP32 = 0, DINCAE_PREC_TF32 = 1, DINCAE_PREC_TF32X1 = 2 };
 
 typedef struct dincae_ctx dincae_ctx;
 typedef struct dincae_model dincae_model;

@@ -288,47 +288,108 @@ def test_smoke(pkg, ctx):
     assert r["launches"] > 0
 
 
-# ---------------------------------------------------------------- tensor-core (TF32 operands, FP32 accumulate) mode
+# ---------------------------------------------------------------- tensor-core mode (the default, the benchmarked one)
 TF32_CASES = [
-    (24, 24, 10, 1, (32, 64), "nearest", False, 0.0, 0.0, 3),
-    (21, 17, 10, 1, (32, 64, 128), "nearest", True, 1e-3, 0.0, 4),           # odd sizes, refinement, L2
-    (20, 19, 16, 2, (32, 64), "bilinear", True, 1e-4, 0.0, 2),               # bilinear, two outputs
-    (45, 18, 60, 1, (25, 50, 75), "nearest", False, 1e-4, 0.0, 2),           # cfg4-like channel counts (padded to 32)
-    (112, 112, 10, 1, (32, 64, 128, 256), "nearest", True, 1e-3, 0.0, 4),    # cfg2 shapes
+    # W, H, Cin, O, filters, method, refine, l1, l2, lap, truth_uncertain, B
+    (24, 24, 10, 1, (32, 64), "nearest", False, 0.0, 0.0, 0.0, False, 3),
+    (21, 17, 10, 1, (32, 64, 128), "nearest", True, 0.0, 1e-3, 0.0, False, 4),            # odd sizes, refinement, L2
+    (20, 19, 16, 2, (32, 64), "bilinear", True, 0.0, 1e-4, 0.0, False, 2),                # bilinear (split-operand head conv), two outputs
+    (45, 18, 60, 1, (25, 50, 75), "nearest", False, 0.0, 1e-4, 0.0, False, 2),            # cfg4-like channel counts (padded to 32)
+    (112, 112, 10, 1, (32, 64, 128, 256), "nearest", True, 0.0, 1e-3, 0.0, False, 4),     # cfg2 = the benchmarked model
+    (112, 112, 16, 1, (32, 64, 128, 256), "nearest", True, 0.0, 1e-3, 0.0, False, 2),     # cfg3: V = 2 => 16 / 18 input channels
+    (177, 69, 60, 1, (25, 50, 75), "nearest", False, 0.0, 1e-4, 0.0, False, 2),           # cfg4 at its real grid (T = 27, Appendix B)
+    (28, 26, 10, 1, (32, 64), "nearest", True, 0.0, 1e-4, 0.1, False, 3),                 # Laplacian penalties (src/model.jl:44-52)
+    (23, 19, 16, 2, (32, 64), "nearest", False, 0.0, 0.0, 0.0, True, 2),                  # truth_uncertain (KL form, :79-86), two outputs
+    (24, 20, 10, 1, (32, 64), "nearest", True, 1e-4, 1e-3, 0.0, False, 3),                # L1 + L2 regularisation (:210-219)
 ]
 
 
-@pytest.mark.parametrize("W,H,Cin,O,F,method,refine,l2,lap,B", TF32_CASES)
-def test_tf32_tensor_core_path_vs_oracle(pkg, ctx, W, H, Cin, O, F, method, refine, l2, lap, B):
-    """The default precision: tcgen05 TF32 convs/wgrads (operands rounded to TF32, FP32 accumulation -- what cuDNN does for the
-    reference's CuArray path under CUDA.jl's default math mode).  Stated tolerance: (m, sigma2) rms error <= 1e-3 of their rms and
-    max error <= 2e-3 of their range (observed: rms <= 6e-4, max <= 1.2e-3); loss 1e-3 relative (observed <= 6e-5); gradients 1e-2 of range.
-    precision="fp32" (tests above) is the exact mode: 1e-5."""
+def _msigma_errors(y, y_o, O):
+    """(m, sigma) error measures of one forward pass: worst |dm| / max|m|, rms(dm) / rms(m), worst pointwise |dsigma| / sigma."""
+    e_m = e_rms = e_sig = 0.0
+    for v in range(O):
+        m, m_o = y[:, :, 2 * v].astype(np.float64), y_o[:, :, 2 * v]
+        sg, sg_o = np.sqrt(y[:, :, 2 * v + 1].astype(np.float64)), np.sqrt(y_o[:, :, 2 * v + 1])
+        e_m = max(e_m, np.abs(m - m_o).max() / np.abs(m_o).max())
+        e_rms = max(e_rms, np.sqrt(np.mean((m - m_o) ** 2) / np.mean(m_o ** 2)))
+        e_sig = max(e_sig, (np.abs(sg - sg_o) / sg_o).max())
+    return e_m, e_rms, e_sig
+
+
+@pytest.mark.parametrize("W,H,Cin,O,F,method,refine,l1,l2,lap,tu,B", TF32_CASES)
+def test_tf32_tensor_core_path_vs_oracle(pkg, ctx, W, H, Cin, O, F, method, refine, l1, l2, lap, tu, B):
+    """precision="tf32": tcgen05 convs (TF32 operands, FP32 accumulation) with the two thin full-resolution layers of every chain at
+    FP32-grade precision (first conv: split activations; head conv: exact FP32, or split operands for bilinear).
+    Tolerance (north_star: mean, sigma, loss within 1e-3 of the reference):
+      sigma : |sigma - sigma_ref| <= 1e-3 * sigma_ref at EVERY pixel                       (observed <= 5.5e-4)
+      m     : |m - m_ref| <= 1e-3 * max|m_ref| at every pixel, rms(dm) <= 1e-3 * rms(m)    (observed <= 7.5e-4 / 6.7e-4)
+              (m crosses zero, so a pointwise relative bound is meaningless near its zeros; where |m| >= max|m|/4 the bound
+               above is a pointwise relative 4e-3, observed <= 2.2e-3)
+      loss  : relative 1e-3 (observed <= 1e-4); gradients: 1e-2 of their range (TF32 products in the backward pass)."""
     rng = np.random.default_rng(W + H)
     lw = (0.3, 0.7) if refine else (1.0,)
-    kw = dict(W=W, H=H, ninput=Cin, noutput=O, enc_nfilter_internal=F, upsampling_method=method, loss_weights_refine=lw,
-              regularization_L2_beta=l2, laplacian_penalty=lap, max_batch=B)
-    ocfg = OM.ModelConfig(W=W, H=H, ninput=Cin, noutput=O, nfilter=list(F), upsampling_method=method, loss_weights_refine=lw,
-                          regularization_L2_beta=l2, laplacian_penalty=lap)
-    model = pkg.Model(ctx, pkg.ModelConfig(precision="tf32", **kw), seed=5)
+    kw = dict(W=W, H=H, ninput=Cin, noutput=O, upsampling_method=method, loss_weights_refine=lw, regularization_L1_beta=l1,
+              regularization_L2_beta=l2, laplacian_penalty=lap, truth_uncertain=tu)
+    ocfg = OM.ModelConfig(nfilter=list(F), **kw)
+    # clip_grad off: the first Adam moment is then 0.1 * gradient, compared unclipped (clipping is covered by the FP32 cases)
+    model = pkg.Model(ctx, pkg.ModelConfig(precision="tf32", enc_nfilter_internal=F, max_batch=B, clip_grad=None, **kw), seed=5)
     flat = model.get_params()
     xin, xt = _problem(rng, W, H, Cin, O, B)
     y = model(xin)
     y_o = OM.forward(ocfg, flat, xin)
-    for ch in range(2 * O):
-        err = np.abs(y[:, :, ch] - y_o[:, :, ch]).max() / np.abs(y_o[:, :, ch]).max()
-        rms = np.sqrt(np.mean((y[:, :, ch] - y_o[:, :, ch]) ** 2)) / np.sqrt(np.mean(y_o[:, :, ch] ** 2))
-        assert err < 2e-3 * (2 if lap else 1) and rms < 1e-3 * (2 if lap else 1), (ch, err, rms)
+    e_m, e_rms, e_sig = _msigma_errors(y, y_o, O)
+    assert e_sig <= 1e-3 and e_m <= 1e-3 and e_rms <= 1e-3, (e_sig, e_m, e_rms)
     loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, xt)
     assert model.loss(xin, xt) == pytest.approx(loss_o, rel=1e-3)
     loss = model.train_step(xin, xt, 1e-3)
     assert loss == pytest.approx(loss_o, rel=1e-3)
     m, v, t = model.get_opt_state()
-    gc = np.clip(g_o, -5, 5)
-    assert np.abs(m * 10 - gc).max() < 1e-2 * np.abs(gc).max()
+    assert np.abs(m * 10 - g_o).max() < 1e-2 * np.abs(g_o).max()
     # parameters padded to 32 channels internally still round-trip exactly in Flux order
     model.set_params(flat)
     assert np.array_equal(model.get_params(), flat)
+
+
+def test_tf32x1_single_pass_mode_is_looser(pkg, ctx):
+    """precision="tf32x1" (single-pass TF32 on every conv, cuDNN's default math mode): runs, stays inside 2e-3, and the default mode
+    beats it on the same problem -- the split-operand layers are what buys the 1e-3."""
+    W, H, Cin, O, F, B = 112, 112, 10, 1, (32, 64, 128, 256), 4
+    rng = np.random.default_rng(W + H)
+    kw = dict(W=W, H=H, ninput=Cin, noutput=O, loss_weights_refine=(0.3, 0.7))
+    xin, _ = _problem(rng, W, H, Cin, O, B)
+    errs = {}
+    for prec in ("tf32", "tf32x1"):
+        model = pkg.Model(ctx, pkg.ModelConfig(precision=prec, enc_nfilter_internal=F, max_batch=B, **kw), seed=5)
+        y_o = OM.forward(OM.ModelConfig(nfilter=list(F), **kw), model.get_params(), xin)
+        errs[prec] = _msigma_errors(model(xin), y_o, O)
+    assert max(errs["tf32x1"]) <= 2e-3
+    assert errs["tf32"][1] < errs["tf32x1"][1] and errs["tf32"][2] < errs["tf32x1"][2], errs
+
+
+@pytest.mark.parametrize("prec", ["fp32", "tf32"])
+def test_l1_regularisation(pkg, ctx, prec):
+    """regularization_L1_beta (src/model.jl:210-214): beta * sum(abs, trainables) in the loss and beta * sign(w) in the gradient."""
+    rng = np.random.default_rng(41)
+    W, H, Cin, B = 18, 16, 10, 2
+    F = (32, 64) if prec == "tf32" else (6, 8)
+    kw = dict(W=W, H=H, ninput=Cin, loss_weights_refine=(0.3, 0.7), regularization_L1_beta=1e-2, regularization_L2_beta=1e-3)
+    xin, xt = _problem(rng, W, H, Cin, 1, B)
+    model = pkg.Model(ctx, pkg.ModelConfig(precision=prec, enc_nfilter_internal=F, max_batch=B, **kw), seed=3)
+    plain = pkg.Model(ctx, pkg.ModelConfig(precision=prec, enc_nfilter_internal=F, max_batch=B, **dict(kw, regularization_L1_beta=0.0)), seed=3)
+    flat = model.get_params()
+    ocfg = OM.ModelConfig(nfilter=list(F), **kw)
+    loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, xt)
+    tol = 1e-3 if prec == "tf32" else 1e-4
+    assert model.loss(xin, xt) == pytest.approx(loss_o, rel=tol)
+    assert model.loss(xin, xt) - plain.loss(xin, xt) == pytest.approx(1e-2 * np.abs(flat).sum(), rel=1e-3)    # the L1 term itself
+    assert model.train_step(xin, xt, 1e-3) == pytest.approx(loss_o, rel=tol)
+    plain.train_step(xin, xt, 1e-3)
+    m, _, _ = model.get_opt_state()
+    m0, _, _ = plain.get_opt_state()
+    gc = np.clip(g_o, -5, 5)
+    assert np.abs(m * 10 - gc).max() < (1e-2 if prec == "tf32" else 1e-4) * np.abs(gc).max()
+    nz = flat != 0                                                   # d/dw of beta*|w| = beta*sign(w) on top of the L1-free gradient
+    np.testing.assert_allclose((m - m0)[nz] * 10, 1e-2 * np.sign(flat[nz]), rtol=0, atol=2e-5)
 
 
 def test_tf32_loss_curve_and_determinism(pkg, ctx):

@@ -36,8 +36,11 @@ def synth_tracks(rng, grid, N, ntracks=4, npts=120):
 GRID = (np.arange(-7, 37.001, 1.0), np.arange(29, 46.001, 1.0))          # 45 x 18
 
 
-def make(pkg, ctx, rng, N=7, T=3, naux=2, train=True):
-    lon, lat, val, ids = synth_tracks(rng, GRID, N)
+GRID_FULL = (np.arange(-7, 37.001, 0.25), np.arange(29, 46.001, 0.25))     # 177 x 69: test/test_reconstruct_points.jl:27-31 (cfg4)
+
+
+def make(pkg, ctx, rng, N=7, T=3, naux=2, train=True, GRID=GRID, ntracks=4, npts=120):
+    lon, lat, val, ids = synth_tracks(rng, GRID, N, ntracks, npts)
     W, H = len(GRID[0]), len(GRID[1])
     aux = rng.standard_normal((W, H, naux, N)).astype(np.float32) if naux else None
     doy = 50 + np.arange(N)
@@ -172,25 +175,31 @@ def test_point_step_with_odd_point_counts_and_device_batch(pkg, ctx):
         assert la == lb and np.isfinite(la).all()
 
 
-def test_point_loss_and_train_step_tf32_vs_oracle(pkg, ctx):
-    """The point-cloud loss through the tensor-core (TF32) model.  Stated tolerance: 1e-3 on the loss; gradients rms 1e-2 relative
-    and 4e-2 of their range at worst (a few hundred observations drive the whole gradient, so TF32 rounding of the activations
-    shows more than in the gridded loss; observed 5e-3 rms, 1.7e-2 worst against the library's own FP32 mode)."""
+@pytest.mark.parametrize("full", [False, True])
+def test_point_loss_and_train_step_tf32_vs_oracle(pkg, ctx, full):
+    """The point-cloud loss through the tensor-core model; full=True is BASELINE configs[3] at its real size: 177 x 69 grid,
+    ntime_win = 27 (60 input channels), enc_nfilter_internal = [25, 50, 75], Laplacian penalty.  Stated tolerance: 1e-3 on the loss;
+    gradients rms 1e-2 relative and 4e-2 of their range at worst (a few hundred observations drive the whole gradient, so TF32
+    rounding of the backward products shows more than in the gridded loss)."""
     rng = np.random.default_rng(8)
-    ds, od = make(pkg, ctx, rng, N=6, T=3, naux=2, train=True)
+    if full:
+        ds, od = make(pkg, ctx, rng, N=6, T=27, naux=2, train=True, GRID=GRID_FULL, ntracks=6, npts=400)
+        F, B, idx, lap = (25, 50, 75), 2, np.array([1, 4]), 0.1
+    else:
+        ds, od = make(pkg, ctx, rng, N=6, T=3, naux=2, train=True)
+        F, B, idx, lap = (32, 64), 4, np.array([1, 2, 4, 3]), 0.0
     W, H, C = ds.sizex()
-    idx = np.array([1, 2, 4, 3])
+    assert not full or (W, H, C) == (177, 69, 60)
     keep = [ds.draw_track_keep(int(i), rng) for i in idx]
     xin, truth = ds.assemble(idx, seed=5, sample_ctr0=0, keep=keep)
-    kw = dict(loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-4)
-    cfg = pkg.ModelConfig(W=W, H=H, ninput=C, enc_nfilter_internal=(32, 64), max_batch=4, precision="tf32", **kw)
-    ocfg = OM.ModelConfig(W=W, H=H, ninput=C, nfilter=[32, 64], **kw)
+    kw = dict(loss_weights_refine=(1.0,) if full else (0.3, 0.7), regularization_L2_beta=1e-4, laplacian_penalty=lap)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=C, enc_nfilter_internal=F, max_batch=B, precision="tf32", clip_grad=None, **kw)
+    ocfg = OM.ModelConfig(W=W, H=H, ninput=C, nfilter=list(F), **kw)
     model = pkg.Model(ctx, cfg, seed=6)
     flat = model.get_params()
     loss_o, g_o = OM.loss_and_grad(ocfg, flat, xin, None, point_truth=truth)
     assert model.loss_points(xin, truth) == pytest.approx(loss_o, rel=1e-3)
     assert model.train_step_points(xin, truth, 1e-3) == pytest.approx(loss_o, rel=1e-3)
-    m, v, t = model.get_opt_state()
-    gc = np.clip(g_o, -5, 5)
-    d = m * 10 - gc
-    assert np.abs(d).max() < 4e-2 * np.abs(gc).max() and np.sqrt((d ** 2).mean()) < 1e-2 * np.sqrt((gc ** 2).mean())
+    m, v, t = model.get_opt_state()              # clip_grad off: m = 0.1 * gradient, compared unclipped
+    d = m * 10 - g_o
+    assert np.abs(d).max() < 4e-2 * np.abs(g_o).max() and np.sqrt((d ** 2).mean()) < 1e-2 * np.sqrt((g_o ** 2).mean())
