@@ -11,6 +11,7 @@ pointer handed to the library is the memory a Julia caller would hand over.
 """
 import ctypes as C
 import math
+import os
 from dataclasses import dataclass, field
 from typing import List, Optional, Sequence, Tuple
 
@@ -43,6 +44,27 @@ class Context:
 
     def sync(self):
         L.check(self._lib.dincae_sync(self.handle))
+
+    # -- data-parallel communicator (one process per GPU; the collective lives in the library, NCCL over NVLink)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """Rank 0: the 128-byte NCCL rendezvous id, to be handed to every rank by the host's own means."""
+        buf = C.create_string_buffer(L.COMM_ID_BYTES)
+        L.check(L.load().dincae_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, nranks: int, rank: int, unique_id: bytes):
+        if len(unique_id) != L.COMM_ID_BYTES:
+            raise ValueError("unique_id must be %d bytes" % L.COMM_ID_BYTES)
+        L.check(self._lib.dincae_comm_init_rank(self.handle, nranks, rank, C.c_char_p(unique_id)))
+
+    def comm_info(self):
+        n, r, v = C.c_int32(), C.c_int32(), C.c_int32()
+        L.check(self._lib.dincae_comm_info(self.handle, C.byref(n), C.byref(r), C.byref(v)))
+        return {"nranks": n.value, "rank": r.value, "nccl_version": v.value}
+
+    def allreduce(self, dev_buf, n):
+        L.check(self._lib.dincae_allreduce(self.handle, L.ptr(dev_buf), int(n)))
 
     @property
     def launches(self) -> int:
@@ -319,6 +341,34 @@ class Model:
         nv = None if n_valid_global is None else np.ascontiguousarray(n_valid_global, np.int64)
         L.check(self._lib.dincae_grad_step(self.handle, L.ptr(xin), L.ptr(xtrue), B, L.ptr(nv), self._loc(xin)))
 
+    def allreduce_grads(self):
+        """SUM the flat gradient buffer (+ loss slot) over all ranks of the context's communicator."""
+        L.check(self._lib.dincae_allreduce_grads(self.handle))
+
+    def train_step_dp(self, xin, xtrue, lr, n_valid_global, B=None, want_loss=True):
+        """One data-parallel mini-batch on this rank's shard: backward with the per-chain gradient buckets all-reduced behind it,
+        then the (replica-identical) L2 + ClipGrad + Adam update."""
+        xin, B = self._batch(xin, B)
+        if isinstance(xtrue, np.ndarray):
+            xtrue = _f32(xtrue)
+        nv = np.ascontiguousarray(n_valid_global, np.int64)
+        out = C.c_float()
+        L.check(self._lib.dincae_train_step_dp(self.handle, L.ptr(xin), L.ptr(xtrue), B, L.ptr(nv), lr, self._loc(xin),
+                                               C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
+
+    def train_step_dp_slot(self, slot, B, lr, n_valid_global, want_loss=True):
+        nv = np.ascontiguousarray(n_valid_global, np.int64)
+        out = C.c_float()
+        L.check(self._lib.dincae_train_step_dp_slot(self.handle, slot, B, L.ptr(nv), lr, C.byref(out) if want_loss else None))
+        return out.value if want_loss else None
+
+    def replica_divergence(self):
+        """max |w_rank - w_rank0| over all ranks and parameters (collective); 0.0 = bit-identical replicas."""
+        out = C.c_float()
+        L.check(self._lib.dincae_replica_divergence(self.handle, C.byref(out)))
+        return out.value
+
     def grad_buffer(self):
         p = C.c_void_p(); n = C.c_int64()
         L.check(self._lib.dincae_grad_buffer(self.handle, C.byref(p), C.byref(n)))
@@ -409,14 +459,29 @@ class GriddedDataset:
         if len(cycle_periods) != 1:
             raise NotImplementedError("exactly one cycle period is supported (4 meta channels, src/data.jl:199)")
         self.ctx, self._lib = ctx, ctx._lib
-        data_full = np.asfortranarray(data_full, np.float32)
-        if data_full.ndim != 4:
-            raise ValueError("data_full must be (W,H,V,N)")
-        W, H, V, N = data_full.shape
+        if hasattr(data_full, "data_ptr"):
+            # a cube that already lives on the device: a contiguous float32 torch tensor of shape (N,V,H,W), i.e. the memory of
+            # a Julia (W,H,V,N) array
+            if data_full.dim() != 4 or not data_full.is_contiguous() or str(data_full.dtype) != "torch.float32" or not data_full.is_cuda:
+                raise ValueError("device cube must be a contiguous float32 CUDA tensor of shape (N,V,H,W)")
+            N, V, H, W = data_full.shape
+            cube_loc = L.DEVICE
+        else:
+            data_full = np.asfortranarray(data_full, np.float32)
+            if data_full.ndim != 4:
+                raise ValueError("data_full must be (W,H,V,N)")
+            W, H, V, N = data_full.shape
+            cube_loc = L.HOST
         self.shape = (W, H, V, N)
         self.train, self.ntime_win = train, ntime_win
         self.isoutput = (np.arange(V) == 0) if isoutput is None else np.asarray(isoutput, bool)
         self.noutput = int(self.isoutput.sum())
+        err_field = None
+        if obs_err_std is not None and np.ndim(obs_err_std) == 4:         # per-pixel error field (errvarname, src/data.jl:323-326)
+            err_field = np.asfortranarray(obs_err_std, np.float32)
+            if err_field.shape != (W, H, V, N):
+                raise ValueError("obs_err_std field must be (W,H,V,N)")
+            obs_err_std = None
         oes = np.ones(V, np.float32) if obs_err_std is None else np.ascontiguousarray(obs_err_std, np.float32)
         js = np.full(V, 0.05, np.float32) if jitter_std is None else np.ascontiguousarray(jitter_std, np.float32)
         iso = np.ascontiguousarray(self.isoutput, np.uint8)
@@ -428,9 +493,11 @@ class GriddedDataset:
         h = C.c_void_p()
         L.check(self._lib.dincae_gridded_create(ctx.handle, L.ptr(data_full), W, H, V, N, L.ptr(oes), L.ptr(js), L.ptr(iso),
                                                 int(remove_mean), L.ptr(md), L.ptr(lm), L.ptr(self.lon_scaled), L.ptr(self.lat_scaled),
-                                                L.ptr(tc), L.ptr(ts), ntime_win, L.HOST, C.byref(h)))
+                                                L.ptr(tc), L.ptr(ts), ntime_win, cube_loc, C.byref(h)))
         self.handle = h
         self.mask = mask
+        if err_field is not None:
+            L.check(self._lib.dincae_gridded_set_error(h, L.ptr(err_field), L.HOST))
 
     def __len__(self):
         return self.shape[3]
@@ -597,10 +664,10 @@ def _load_entry(d):
     from . import ncio
     lon, lat, time, data, err, _, mask = ncio.load_gridded_nc(d["filename"], d["varname"], d.get("errvarname"),
                                                               obs_err_std=d.get("obs_err_std", 1.0))
-    if d.get("errvarname") is not None:
-        raise L.DincaeError(L.EUNSUPPORTED, "per-pixel observation error fields (errvarname) are not supported: obs_err_std is one value per variable")
     out = dict(d)
     out.update(lon=lon, lat=lat, time=time, data=data, mask=mask)
+    if d.get("errvarname") is not None:
+        out["err"] = err                       # per-pixel error standard deviation (W,H,N), Inf where missing (src/data.jl:66-67)
     return out
 
 
@@ -629,19 +696,25 @@ def reconstruct(ctx, data_all, fnames_rec=None, *,
     if is3D or output_ndims != 1 or direction_obs is not None:
         raise L.DincaeError(L.EUNSUPPORTED, "is3D=true / output_ndims=2 / direction_obs are outside the hot path (SURVEY section 8f N4)")
 
-    def make(dlist, train, mean_data=None):
+    def make(dlist, train, mean_data=None, mask=None):
         dlist = [_load_entry(d) for d in dlist]                                          # {filename, varname} -> arrays (src/data.jl:88-110)
         d0 = dlist[0]
         data = np.stack([np.asarray(d["data"], np.float32) for d in dlist], axis=2)      # (W,H,V,N)
+        oes = [d.get("obs_err_std", 1.0) for d in dlist]
+        if any("err" in d for d in dlist):       # error_full of load_gridded_nc(data) (src/data.jl:88-110): a field for every variable
+            oes = np.stack([np.asarray(d["err"], np.float32) if "err" in d else np.full(data.shape[:2] + data.shape[3:], d.get("obs_err_std", 1.0), np.float32)
+                            for d in dlist], axis=2)
         return GriddedDataset(ctx, d0["lon"], d0["lat"], d0["time"], data, train=train,
-                              obs_err_std=[d.get("obs_err_std", 1.0) for d in dlist],
+                              obs_err_std=oes,
                               jitter_std=[d.get("jitter_std", 0.05) for d in dlist],
                               ntime_win=ntime_win, isoutput=[d.get("isoutput", i == 0) for i, d in enumerate(dlist)],
-                              remove_mean=remove_mean, mean_data=mean_data, mask=d0.get("mask"), cycle_periods=cycle_periods)
+                              remove_mean=remove_mean, mean_data=mean_data, mask=d0.get("mask") if mask is None else mask,
+                              cycle_periods=cycle_periods)
 
     train_data = make(data_all[0], True)
     train_mean = train_data.meandata
-    tests = [make(d, False, train_mean) for d in data_all[1:]]         # use common mean, src/model.jl:503-504
+    # use common mean (src/model.jl:503-504); savesample masks with the TRAINING data's mask (mask = train_data.mask, :641)
+    tests = [make(d, False, train_mean, mask=train_data.mask) for d in data_all[1:]]
     W, H, Cin = train_data.sizex()
     cfg = ModelConfig(W=W, H=H, ninput=Cin, noutput=train_data.noutput, enc_nfilter_internal=tuple(enc_nfilter_internal),
                       skipconnections=skipconnections, upsampling_method=str(upsampling_method).lstrip(":"),
@@ -662,6 +735,12 @@ def reconstruct(ctx, data_all, fnames_rec=None, *,
         if progress:
             progress("epoch: %5d loss %5.4f" % (e, losses[-1]))        # src/model.jl:596
         if e in save_epochs:
+            if modeldir is not None:                                   # model-checkpoint-%05d at every save epoch, src/model.jl:599-620
+                os.makedirs(modeldir, exist_ok=True)
+                model.save_checkpoint(os.path.join(modeldir, "model-checkpoint-%05d" % e), e=e, ntime_win=ntime_win, is3D=int(is3D),
+                                      cycle_periods=np.asarray(cycle_periods, np.float64), remove_mean=int(remove_mean),
+                                      train_mean_data=np.asarray(train_mean), noutput=train_data.noutput,
+                                      input_size=np.asarray([W, H, Cin]), output_ndims=output_ndims)
             for ds_, res in zip(tests, results):
                 res["count"] += 1                                      # ds.attrib["count"] += 1, src/data.jl:621-623
                 res["mean"], res["sigma"] = reconstruct_range(model, ds_, 0, len(ds_), res["count"], -9999.0, res["mean"], res["sigma"])
@@ -676,8 +755,16 @@ def reconstruct(ctx, data_all, fnames_rec=None, *,
                                           [res["mean"][:, :, :, i] for i in range(nv)], [res["sigma"][:, :, :, i] for i in range(nv)], res["count"])
             else:
                 np.savez(fn, **{k: v for k, v in res.items() if v is not None})
-    if paramfile is not None:
-        np.savez(paramfile, losses=np.asarray(losses), epochs=epochs, batch_size=batch_size)
+    if paramfile is not None:                                          # src/model.jl:655-676, attribute for attribute
+        from . import ncio
+        L_ = len(tuple(enc_nfilter_internal))
+        ncio.write_paramfile(paramfile, losses, dict(
+            epochs=epochs, batch_size=batch_size, truth_uncertain=bool(truth_uncertain), enc_nfilter_internal=list(enc_nfilter_internal),
+            skipconnections=list(range(2, L_ + 2) if skipconnections is None else skipconnections), clip_grad=float(clip_grad or 0.0),
+            regularization_L1_beta=float(regularization_L1_beta), regularization_L2_beta=float(regularization_L2_beta),
+            save_epochs=list(save_epochs), is3D=bool(is3D), upsampling_method=str(upsampling_method).lstrip(":"), ntime_win=ntime_win,
+            learning_rate=float(learning_rate), learning_rate_decay_epoch=float(learning_rate_decay_epoch), min_std_err=float(min_std_err),
+            loss_weights_refine=[float(x) for x in loss_weights_refine], cycle_periods=[float(x) for x in cycle_periods]))
     reconstruct.last_model = model
     return losses, results
 
@@ -770,19 +857,32 @@ def reconstruct_points(ctx, data, grid, fnames_rec=None, *,
                        skipconnections=None, clip_grad=5.0, regularization_L1_beta=0, regularization_L2_beta=0,
                        save_epochs=None, upsampling_method="nearest", probability_skip_for_training=0.2,
                        jitter_std_pos=(5.0, 5.0), ntime_win=9, learning_rate=0.001, learning_rate_decay_epoch=math.inf,
-                       min_std_err=0.006737946999085467, loss_weights_refine=(1.0,), auxdata=None, paramfile=None,
+                       min_std_err=0.006737946999085467, loss_weights_refine=(1.0,), auxdata_files=(), paramfile=None,
                        savesnapshot=False, laplacian_penalty=0, laplacian_error_penalty=None,
-                       seed=0, precision="tf32", init_params=None, progress=None):
+                       varname=None, auxdata=None, seed=0, precision="tf32", init_params=None, progress=None):
     """DINCAE.reconstruct_points (src/points.jl:509-696), keyword surface verbatim.
 
-    `data` = dict(lon, lat, values, id: lists of per-time-step vectors; dayofyear: (N,)) replaces the ragged
-    NetCDF file; `auxdata` (W,H,2*naux,N) replaces auxdata_files (already normalised)."""
+    `data` is the reference's `filename` (a CF contiguous-ragged NetCDF-3 file read by ncio.load_ragged_points, with
+    `varname`), or the same content in memory: dict(lon, lat, values, id: lists of per-time-step vectors; dayofyear: (N,)).
+    `auxdata_files` = [dict(filename, varname, errvarname)] as in the reference (src/points.jl:543, src/data.jl:124-146);
+    `auxdata` (W,H,2*naux,N) passes the already normalised array instead."""
     if save_epochs is None:
         save_epochs = range(min(epochs, 60), epochs + 1, 10)
     save_epochs = list(save_epochs)
     if len(save_epochs) == 0 or epochs < min(save_epochs):
         raise ValueError("No output will be saved. Consider to adjust save_epochs (currently %s) or epochs (currently %d)."
                          % (save_epochs, epochs))                     # src/points.jl:535-537
+    if isinstance(data, (str, bytes, os.PathLike)):
+        if varname is None:
+            raise ValueError("reconstruct_points: varname is required with a file name")
+        from . import ncio
+        values, (plon, plat), _dtime, pid, _dates, doy = ncio.load_ragged_points(os.fspath(data), varname)     # DINCAE.loaddata, src/points.jl:541
+        data = dict(lon=plon, lat=plat, values=values, id=pid, dayofyear=doy)
+    if len(auxdata_files) > 0:
+        if auxdata is not None:
+            raise ValueError("pass either auxdata_files or auxdata")
+        from . import ncio
+        auxdata = ncio.load_aux_data((len(grid[0]), len(grid[1]), len(data["values"])), list(auxdata_files))    # src/points.jl:545
     kw = dict(ntime_win=ntime_win, probability_skip_for_training=probability_skip_for_training,
               jitter_std_pos=jitter_std_pos, auxdata=auxdata)
     train = PointDataset(ctx, grid, data["lon"], data["lat"], data["values"], data["id"], data["dayofyear"], train=True, **kw)
@@ -835,7 +935,21 @@ def reconstruct_points(ctx, data, grid, fnames_rec=None, *,
                     result[name][:, :, idx] = np.where(np.isnan(v), np.float32(-9999.0), v)
     if fnames_rec is not None:
         np.savez(fnames_rec[0], **{k: v for k, v in result.items() if v is not None})
-    if paramfile is not None:
-        np.savez(paramfile, losses=np.asarray(losses), epochs=epochs, batch_size=batch_size)
+    if paramfile is not None:                                          # src/points.jl:658-692, attribute for attribute
+        from . import ncio
+        L_ = len(tuple(enc_nfilter_internal))
+        ncio.write_paramfile(paramfile, losses, dict(
+            epochs=epochs, batch_size=batch_size, truth_uncertain=bool(truth_uncertain), enc_nfilter_internal=list(enc_nfilter_internal),
+            skipconnections=list(range(2, L_ + 2) if skipconnections is None else skipconnections), clip_grad=float(clip_grad or 0.0),
+            regularization_L1_beta=float(regularization_L1_beta), regularization_L2_beta=float(regularization_L2_beta),
+            save_epochs=list(save_epochs), upsampling_method=str(upsampling_method).lstrip(":"),
+            probability_skip_for_training=float(probability_skip_for_training), jitter_std_pos=[float(x) for x in jitter_std_pos],
+            ntime_win=ntime_win, learning_rate=float(learning_rate), learning_rate_decay_epoch=float(learning_rate_decay_epoch),
+            min_std_err=float(min_std_err), loss_weights_refine=[float(x) for x in loss_weights_refine],
+            auxdata_filenames=[f["filename"] for f in auxdata_files] if len(auxdata_files) else "",
+            auxdata_varnames=[f["varname"] for f in auxdata_files] if len(auxdata_files) else "",
+            auxdata_errvarname=[str(f.get("errvarname")) for f in auxdata_files] if len(auxdata_files) else "",
+            savesnapshot=bool(savesnapshot), laplacian_penalty=float(laplacian_penalty),
+            laplacian_error_penalty=float(laplacian_penalty if laplacian_error_penalty is None else laplacian_error_penalty)))
     reconstruct_points.last_model = model
     return losses, result

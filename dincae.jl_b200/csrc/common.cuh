@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <string>
 #include <vector>
 #include "../../include/dincae_b200.h"
@@ -32,6 +33,12 @@ struct dincae_ctx {
     // reusable device scratch (grown on demand, never shrunk)
     void* scratch = nullptr;
     size_t scratch_bytes = 0;
+    // data-parallel gradient exchange (comm.cu): NCCL communicator of this rank, its stream and the fences against `stream`
+    void* comm = nullptr;
+    int comm_nranks = 1, comm_rank = 0;
+    cudaStream_t comm_stream = nullptr;
+    cudaEvent_t ev_comm_go = nullptr, ev_comm_done = nullptr;
+    int64_t collectives = 0;
     // pinned staging for small host<->device scalars
     void* pinned = nullptr;
     size_t pinned_bytes = 0;
@@ -116,6 +123,7 @@ void dc_prof_end(dincae_ctx* ctx);
     } while (0)
 
 int32_t dc_scratch(dincae_ctx* ctx, size_t bytes, void** out);       // grow-only device scratch
+int32_t dc_allreduce_on(dincae_ctx* ctx, float* buf, int64_t n, cudaStream_t stream);   // in-place NCCL SUM ordered on `stream`
 int32_t dc_pinned(dincae_ctx* ctx, size_t bytes, void** out);        // grow-only pinned host staging
 
 static inline int64_t dc_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

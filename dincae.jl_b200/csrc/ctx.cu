@@ -44,6 +44,7 @@ extern "C" int32_t dincae_ctx_destroy(dincae_ctx* c) {
     if (!c) return DINCAE_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    dincae_comm_destroy(c);
     if (c->scratch) cudaFree(c->scratch);
     if (c->pinned) cudaFreeHost(c->pinned);
     if (c->side) { cudaStreamSynchronize(c->side); cudaStreamDestroy(c->side); c->side = nullptr; }

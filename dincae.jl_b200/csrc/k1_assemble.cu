@@ -25,12 +25,14 @@ __global__ void subtract_mean_kernel(float* __restrict__ data, int64_t VHW, int6
         data[i] = data[i] - mean[i % VHW];      // data = data_full .- meandata, src/data.jl:299
 }
 
-__global__ void valid_count_kernel(const float* __restrict__ data, int64_t HW, int V, int v, unsigned long long* __restrict__ counts) {
-    // block n counts the non-NaN values of variable v at time step n
+__global__ void valid_count_kernel(const float* __restrict__ data, const float* __restrict__ err2, int64_t HW, int V, int v,
+                                   unsigned long long* __restrict__ counts) {
+    // block n counts the targets of variable v at time step n whose weight channel (1 - isnan) / err^2 is non-zero
     int64_t n = blockIdx.x;
     const float* p = data + (n * V + v) * HW;
+    const float* q = err2 ? err2 + (n * V + v) * HW : nullptr;
     unsigned int c = 0;
-    for (int64_t i = threadIdx.x; i < HW; i += blockDim.x) c += (p[i] == p[i]) ? 1u : 0u;
+    for (int64_t i = threadIdx.x; i < HW; i += blockDim.x) c += (p[i] == p[i] && (!q || 1.0f / q[i] != 0.f)) ? 1u : 0u;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&counts[n], (unsigned long long)c);
@@ -39,6 +41,7 @@ __global__ void valid_count_kernel(const float* __restrict__ data, int64_t HW, i
 constexpr int ASM_MAXB = 128;
 struct AsmArgs {
     const float* data;
+    const float* err2;       // per-pixel error variance cube or NULL (then params[v] applies to the whole variable)
     const float* lon;
     const float* lat;
     const float* tcos;
@@ -107,12 +110,13 @@ __global__ void __launch_bounds__(256) assemble_kernel(AsmArgs a) {
         for (int k = 0; k < a.T; k++) {
             int64_t n = ind - half + k;                       // nrange = clamp(ind-h:ind+h, 1, N), src/data.jl:405
             n = n < 0 ? 0 : (n > a.N - 1 ? a.N - 1 : n);
-            float d4[4], x1[4], x2[4];
+            float d4[4], x1[4], x2[4], e4[4] = {s2, s2, s2, s2};
             load(a.data + ((size_t)n * a.V + v) * HW + p0, d4);
+            if (a.err2) load(a.err2 + ((size_t)n * a.V + v) * HW + p0, e4);      // Inf where the error field is missing: both channels 0
             for (int e = 0; e < 4; e++) {
                 bool nan = d4[e] != d4[e];
-                x1[e] = (nan ? 0.f : d4[e]) / s2;
-                x2[e] = nan ? 0.f : 1.0f / s2;
+                x1[e] = (nan ? 0.f : d4[e]) / e4[e];
+                x2[e] = nan ? 0.f : 1.0f / e4[e];
             }
             if (perturb) {
                 if (k == centraln)
@@ -133,12 +137,13 @@ __global__ void __launch_bounds__(256) assemble_kernel(AsmArgs a) {
     for (int o = 0; o < a.nout; o++) {
         int v = a.outvars[o];
         const float s2 = a.params[v];
-        float d4[4], x1[4], x2[4];
+        float d4[4], x1[4], x2[4], e4[4] = {s2, s2, s2, s2};
         load(a.data + ((size_t)ind * a.V + v) * HW + p0, d4);
+        if (a.err2) load(a.err2 + ((size_t)ind * a.V + v) * HW + p0, e4);
         for (int e = 0; e < 4; e++) {
             bool nan = d4[e] != d4[e];
-            x1[e] = (nan ? 0.f : d4[e]) / s2;
-            x2[e] = nan ? 0.f : 1.0f / s2;
+            x1[e] = (nan ? 0.f : d4[e]) / e4[e];
+            x2[e] = nan ? 0.f : 1.0f / e4[e];
         }
         store(yo + (size_t)(2 * o) * HW, x1);
         store(yo + (size_t)(2 * o + 1) * HW, x2);
@@ -163,7 +168,7 @@ int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t
     for (int b0 = 0; b0 < B; b0 += ASM_MAXB) {
         int nb = B - b0 < ASM_MAXB ? B - b0 : ASM_MAXB;
         AsmArgs a;
-        a.data = ds->d_data; a.lon = ds->d_lon; a.lat = ds->d_lat; a.tcos = ds->d_tcos; a.tsin = ds->d_tsin;
+        a.data = ds->d_data; a.err2 = ds->d_err2; a.lon = ds->d_lon; a.lat = ds->d_lat; a.tcos = ds->d_tcos; a.tsin = ds->d_tsin;
         a.params = ds->d_params; a.outvars = ds->d_outvars;
         for (int b = 0; b < nb; b++) { a.tidx[b] = (int)h_time_idx[b0 + b]; a.imk[b] = h_imask ? (int)h_imask[b0 + b] : 0; }
         a.has_mask = h_imask != nullptr;
@@ -172,9 +177,31 @@ int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t
         a.xin = d_xin + (size_t)b0 * C * HW;
         a.xtrue = d_xtrue + (size_t)b0 * 2 * ds->nout * HW;
         int64_t groups = ((int64_t)HW + 3) / 4 * nb;
+        // algorithmic bytes per sample: T*V cube planes (+ the transplanted mask plane) read, C input + 2*nout target planes written
+        DC_WORK(ctx, 0.0, 4.0 * HW * nb * ((double)ds->T * ds->V + (h_imask ? 1 : 0) + C + 2 * ds->nout));
         DC_LAUNCH(ctx, assemble_kernel, (unsigned)dc_cdiv(groups, 256), 256, 0, a);
     }
     DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+// static per-step valid counts of every output variable (n_noncloud without a collective)
+static int32_t compute_valid_counts(dincae_gridded* ds) {
+    dincae_ctx* ctx = ds->ctx;
+    const int64_t HW = (int64_t)ds->W * ds->H, N = ds->N;
+    unsigned long long* d_counts = nullptr;
+    DC_CHECK_CUDA(cudaMalloc((void**)&d_counts, sizeof(unsigned long long) * N));
+    ds->valid_counts.resize(ds->nout);
+    std::vector<unsigned long long> hc(N);
+    for (int o = 0; o < ds->nout; o++) {
+        DC_CHECK_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(unsigned long long) * N, ctx->stream));
+        DC_LAUNCH(ctx, valid_count_kernel, (unsigned)N, 256, 0, ds->d_data, ds->d_err2, HW, ds->V, ds->outvars[o], d_counts);
+        DC_CHECK_LAUNCH();
+        DC_CHECK_CUDA(cudaMemcpyAsync(hc.data(), d_counts, sizeof(unsigned long long) * N, cudaMemcpyDeviceToHost, ctx->stream));
+        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+        ds->valid_counts[o].assign(hc.begin(), hc.end());
+    }
+    cudaFree(d_counts);
     return DINCAE_OK;
 }
 
@@ -239,20 +266,7 @@ extern "C" int32_t dincae_gridded_create(dincae_ctx* ctx, const float* data_full
     for (int o = 0; o < ds->nout; o++)
         DC_CHECK_CUDA(cudaMemcpyAsync(ds->d_mean_out + (size_t)o * HW, ds->d_mean + (size_t)ds->outvars[o] * HW, sizeof(float) * HW,
                                       cudaMemcpyDeviceToDevice, ctx->stream));
-    // static per-step valid counts of every output variable (n_noncloud without a collective)
-    unsigned long long* d_counts = nullptr;
-    DC_CHECK_CUDA(cudaMalloc((void**)&d_counts, sizeof(unsigned long long) * N));
-    ds->valid_counts.resize(ds->nout);
-    std::vector<unsigned long long> hc(N);
-    for (int o = 0; o < ds->nout; o++) {
-        DC_CHECK_CUDA(cudaMemsetAsync(d_counts, 0, sizeof(unsigned long long) * N, ctx->stream));
-        DC_LAUNCH(ctx, valid_count_kernel, (unsigned)N, 256, 0, ds->d_data, HW, V, ds->outvars[o], d_counts);
-        DC_CHECK_LAUNCH();
-        DC_CHECK_CUDA(cudaMemcpyAsync(hc.data(), d_counts, sizeof(unsigned long long) * N, cudaMemcpyDeviceToHost, ctx->stream));
-        DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
-        ds->valid_counts[o].assign(hc.begin(), hc.end());
-    }
-    cudaFree(d_counts);
+    DC_TRY(compute_valid_counts(ds));
     DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
     *out = ds;
     return DINCAE_OK;
@@ -262,12 +276,35 @@ extern "C" int32_t dincae_gridded_destroy(dincae_gridded* ds) {
     if (!ds) return DINCAE_OK;
     cudaSetDevice(ds->ctx->device);
     cudaStreamSynchronize(ds->ctx->stream);
-    void* ptrs[] = {ds->d_data, ds->d_mean, ds->d_mean_out, ds->d_lon, ds->d_lat, ds->d_tcos, ds->d_tsin, ds->d_landmask,
+    void* ptrs[] = {ds->d_data, ds->d_err2, ds->d_mean, ds->d_mean_out, ds->d_lon, ds->d_lat, ds->d_tcos, ds->d_tsin, ds->d_landmask,
                     ds->d_params, ds->d_outvars, ds->d_idx};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     delete ds;
     return DINCAE_OK;
+}
+
+namespace {
+__global__ void square_kernel(float* __restrict__ x, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] = x[i] * x[i];
+}
+}  // namespace
+
+extern "C" int32_t dincae_gridded_set_error(dincae_gridded* ds, const float* obs_err_std, int32_t loc) {
+    DC_REQUIRE(ds && obs_err_std, DINCAE_EINVAL, "dincae_gridded_set_error: NULL argument");
+    dincae_ctx* ctx = ds->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const int64_t total = (int64_t)ds->W * ds->H * ds->V * ds->N;
+    if (!ds->d_err2) {
+        cudaError_t e = cudaMalloc((void**)&ds->d_err2, sizeof(float) * total);
+        if (e != cudaSuccess) { dincae_set_error("dincae_gridded_set_error: cannot allocate %lld bytes: %s", (long long)total * 4, cudaGetErrorString(e)); ds->d_err2 = nullptr; return DINCAE_ENOMEM; }
+    }
+    DC_CHECK_CUDA(cudaMemcpyAsync(ds->d_err2, obs_err_std, sizeof(float) * total, loc == DINCAE_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, ctx->stream));
+    int nb = (int)(dc_cdiv(total, 256) < 65535 ? dc_cdiv(total, 256) : 65535);
+    DC_LAUNCH(ctx, square_kernel, nb, 256, 0, ds->d_err2, total);          // x ./= obs_err_std.^2, src/data.jl:324-325
+    DC_CHECK_LAUNCH();
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    return compute_valid_counts(ds);       // a target whose error is infinite carries no weight: it no longer counts
 }
 
 extern "C" int32_t dincae_gridded_get_mean(dincae_gridded* ds, float* host_mean) {

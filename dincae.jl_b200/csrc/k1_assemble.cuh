@@ -9,6 +9,7 @@ struct dincae_gridded {
     int W = 0, H = 0, V = 0, T = 0, nout = 0;
     int64_t N = 0;
     float* d_data = nullptr;        // [N][V][H][W]: data - mean, NaN = missing (ONE float per value)
+    float* d_err2 = nullptr;        // optional [N][V][H][W]: per-pixel observation error VARIANCE (errvarname, src/data.jl:66-67, :323-326)
     float* d_mean = nullptr;        // [V][H][W]
     float* d_mean_out = nullptr;    // [nout][H][W]: meandata[:,:,findall(isoutput)]
     float* d_lon = nullptr;         // [W] scaled to [-1,1]

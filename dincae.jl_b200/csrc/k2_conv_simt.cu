@@ -1017,6 +1017,7 @@ int32_t k2_pack(dincae_ctx* ctx, const float* src0, int C0, const float* src1, i
     DC_REQUIRE(!split || (ctx->tf32_acts && 2 * (C0 + C1) <= Cp), DINCAE_EINVAL, "k2_pack: split layout needs TF32 mode and Cp >= 2*C");
     int Cw = (int)dc_round_up((split ? 2 : 1) * (C0 + C1), 8);                  // whole 32-byte sectors; the rest of the row is never written (zero since allocation)
     if (Cw > Cp) Cw = Cp;
+    DC_WORK(ctx, 0.0, 4.0 * M * ((C0 + C1) + Cw));                 // real planes in, written channels out
     DC_LAUNCH_PDL(ctx, pack_planar_kernel, (unsigned)dc_cdiv(M, 256), 256, 0, src0, C0, src1, C1, B, H * W, dst, Cp, Cw, (int)ctx->tf32_acts, split);   // 8 warps x 32 pixels per block
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -1026,6 +1027,7 @@ int32_t k2_pool(dincae_ctx* ctx, const float* a, int B, int H, int W, int Cp, fl
     int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
     int64_t n = (int64_t)B * H2 * W2 * (Cp / 4);
     if (n == 0) return DINCAE_OK;
+    DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * H * W + (double)B * H2 * W2));
     DC_LAUNCH_PDL(ctx, pool_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * H2, n), 256, 0, a, B, H, W, Cp, H2, W2, x, (int)ctx->tf32_acts);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -1046,6 +1048,7 @@ int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, 
     if (n == 0) return DINCAE_OK;
     int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * Hs, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_upbwd: column partials not supported for %d channels", Cp);
+    DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * H * W + (double)B * Hs * Ws * ((r ? 1 : 0) + (G ? 1 : 0) + (gd ? 1 : 0))));   // gu in; r in, G and gd out at half resolution
     DC_LAUNCH_PDL(ctx, upbwd_kernel, nb, 256, 0, gu, B, H, W, Cp, Hs, Ws, r, slope, G, gd, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -1057,6 +1060,7 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     if (n == 0) return DINCAE_OK;
     int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * H, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd: column partials not supported for %d channels", Cp);
+    DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * H * W * 2 + (double)B * H2 * W2));       // a in, gc out, xg in at half resolution
     DC_LAUNCH_PDL(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -1075,6 +1079,7 @@ int32_t k2_up_nearest(dincae_ctx* ctx, const float* src0, const float* src1, int
     int64_t n = (int64_t)B * H * W * (Cp / 4);
     if (n == 0) return DINCAE_OK;
     DC_REQUIRE(!split || ctx->tf32_acts, DINCAE_EINVAL, "k2_up_nearest: split layout needs TF32 mode");
+    DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * Hs * Ws * (src1 ? 2 : 1) + (double)B * H * W * (split ? 2 : 1)));
     DC_LAUNCH_PDL(ctx, up_nearest_kernel, (unsigned)k2_row_blocks(ctx, (int64_t)B * Hs, n / 4), 256, 0, src0, src1, B, Hs, Ws, Cp, H, W, dst, (int)ctx->tf32_acts, split);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;

@@ -2374,6 +2374,9 @@ int32_t k2_reduce_batched(dincae_ctx* ctx, RedList& list) {
         blocks += (int)dc_cdiv(list.e[e].n / 4, list.e[e].n <= 512 ? 8 : 32);
     }
     list.blk_start[list.count] = blocks;
+    double rbytes = 0.0;
+    for (int e = 0; e < list.count; e++) rbytes += 4.0 * list.e[e].n * (list.e[e].splits + 1);      // every partial row read once, the sum written
+    DC_WORK(ctx, 0.0, rbytes);
     DC_LAUNCH(ctx, reduce_batched_kernel, blocks, 256, 0, list);
     DC_CHECK_LAUNCH();
     list.count = 0;

@@ -261,6 +261,7 @@ int32_t k3_count_valid(dincae_ctx* ctx, const float* xtrue, int B, int nout, int
 int32_t k3_head(dincae_ctx* ctx, const float* raw, int B, int nout, int64_t npix, float gamma, float* ms) {
     int64_t n = (int64_t)B * nout * npix;
     if (n == 0) return DINCAE_OK;
+    DC_WORK(ctx, 0.0, 16.0 * B * nout * npix);
     DC_LAUNCH(ctx, head_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, raw, (int64_t)B * nout, npix, gamma, ms);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
@@ -276,7 +277,10 @@ int32_t k3_loss_grid(dincae_ctx* ctx, const float* raw, const float* xtrue, cons
     double* part = (double*)scratch;
     int nb = red_blocks(ctx, n);
     bool lap = hp.lap != 0.f || hp.lap_err != 0.f;
+    // algorithmic bytes: raw (m, log 1/s2) + truth (2 channels) read, gradient (2 channels) written when training
+    const double lbytes = 4.0 * n * (4 + (graw ? 2 : 0));
     if (!lap) {
+        DC_WORK(ctx, 0.0, lbytes);
         DC_LAUNCH(ctx, loss_grid_kernel<true>, nb, RED_THREADS, 0, raw, xtrue, B, nout, npix, hp, inv_n, weight, part, graw);
         DC_CHECK_LAUNCH();
         DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
@@ -285,6 +289,7 @@ int32_t k3_loss_grid(dincae_ctx* ctx, const float* raw, const float* xtrue, cons
     }
     DC_REQUIRE(ms != nullptr, DINCAE_EINVAL, "k3_loss_grid: Laplacian penalty needs head(raw)");
     // (gm, gs) into graw's storage first, then the Laplacian + chain rule in place
+    DC_WORK(ctx, 0.0, lbytes);
     DC_LAUNCH(ctx, loss_grid_kernel<false>, nb, RED_THREADS, 0, raw, xtrue, B, nout, npix, hp, inv_n, weight, part, graw);
     DC_CHECK_LAUNCH();
     DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
@@ -313,6 +318,7 @@ int32_t k3_head_bwd(dincae_ctx* ctx, const float* raw, const float* ms, const fl
     double* part = (double*)scratch;
     int nb = red_blocks(ctx, n);
     // in-place use (g_ms == graw) is safe: each thread reads its own two elements before writing them
+    DC_WORK(ctx, 0.0, 4.0 * n * (2 + 2 + (g_ms ? 2 : 0) + (graw ? 2 : 0)));       // raw, ms (with stencil re-reads served by L2), g_ms in, graw out
     DC_LAUNCH(ctx, head_bwd_kernel, nb, RED_THREADS, 0, raw, ms, g_ms, B, nout, W, H, hp, weight, part, graw);
     DC_CHECK_LAUNCH();
     DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, loss_acc);
@@ -326,12 +332,33 @@ int32_t k3_adam(dincae_ctx* ctx, float* w, const float* g, float* m, float* v, i
     DC_REQUIRE(scratch_bytes >= k3_scratch_bytes(n), DINCAE_ESIZE, "k3_adam: scratch too small");
     double* part = (double*)scratch;
     int nb = red_blocks(ctx, n);
+    DC_WORK(ctx, 0.0, 28.0 * n);              // w, m, v read + written, g read
     DC_LAUNCH(ctx, adam_kernel<true>, nb, RED_THREADS, 0, w, g, m, v, n, p, part);
     DC_CHECK_LAUNCH();
     if (reg_acc && (p.l1 != 0.f || p.l2 != 0.f)) {
         DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, reg_acc);
         DC_CHECK_LAUNCH();
     }
+    return DINCAE_OK;
+}
+
+namespace {
+__global__ void __launch_bounds__(256) max_abs_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, unsigned int* __restrict__ out) {
+    float mx = 0.f;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float d = fabsf(a[i] - b[i]);
+        mx = (d > mx || d != d) ? (d != d ? __int_as_float(0x7f800000) : d) : mx;      // NaN counts as +inf
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_down_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(mx));
+}
+}  // namespace
+int32_t k3_max_abs_diff(dincae_ctx* ctx, const float* a, const float* b, int64_t n, float* out) {
+    DC_CHECK_CUDA(cudaMemsetAsync(out, 0, sizeof(float), ctx->stream));
+    if (n == 0) return DINCAE_OK;
+    DC_LAUNCH(ctx, max_abs_diff_kernel, 2 * ctx->num_sms, 256, 0, a, b, n, (unsigned int*)out);
+    DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
 
@@ -354,6 +381,7 @@ int32_t k3_savesample(dincae_ctx* ctx, const float* ms, int B, int nout, int64_t
                       const uint8_t* landmask, int count, float fill_value, float* m_out, float* sigma_out, int64_t var_stride) {
     int64_t n = (int64_t)B * nout * npix;
     if (n == 0) return DINCAE_OK;
+    DC_WORK(ctx, 0.0, (8.0 + (count > 1 ? 16.0 : 8.0)) * B * nout * npix);     // (m, s2) in; running mean read (count > 1) + written
     DC_LAUNCH(ctx, savesample_kernel, (unsigned)dc_cdiv(n, 256), 256, 0, ms, B, nout, npix, meandata_out, landmask, count, fill_value,
               m_out, sigma_out, var_stride);
     DC_CHECK_LAUNCH();

@@ -37,6 +37,8 @@ struct AdamParams {
 int32_t k3_adam(dincae_ctx* ctx, float* w, const float* g, float* m, float* v, int64_t n, const AdamParams& p,
                 double* reg_acc, void* scratch, size_t scratch_bytes);
 // reg_acc[0] += l1*sum|w| + l2*sum w^2 only (dincae_loss)
+// out[0] = max_i |a[i] - b[i]| (integer atomicMax on the bit pattern of non-negative floats: order-independent)
+int32_t k3_max_abs_diff(dincae_ctx* ctx, const float* a, const float* b, int64_t n, float* out);
 int32_t k3_reg(dincae_ctx* ctx, const float* w, int64_t n, float l1, float l2, double* reg_acc, void* scratch, size_t scratch_bytes);
 size_t k3_scratch_bytes(int64_t n_elems);
 // savesample arithmetic (src/data.jl:615-619,:653-675) fused: ms planar (W,H,2*nout,B) -> running mean into m_out/sigma_out

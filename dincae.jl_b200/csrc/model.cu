@@ -448,11 +448,34 @@ int32_t backward_all(dincae_model* M, int B) {
     DC_TRY(ensure_wT(M));
     M->wg_off = 0;
     M->red.count = 0;
-    for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
-    DC_TRY(k2_reduce_batched(M->ctx, M->red));
-    DC_TRY(k2_fold_split_grad(M->ctx, M->g_exp, M->g, M->split));
-    DC_LAUNCH(M->ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
-    DC_CHECK_LAUNCH();
+    dincae_ctx* ctx = M->ctx;
+    if (!M->dp_overlap) {
+        for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
+        DC_TRY(k2_reduce_batched(ctx, M->red));
+        DC_TRY(k2_fold_split_grad(ctx, M->g_exp, M->g, M->split));
+        DC_LAUNCH(ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
+        DC_CHECK_LAUNCH();
+        return DINCAE_OK;
+    }
+    // data-parallel step: the bucket of chain c (its parameter range; the last one also carries the loss slot) is finished and
+    // handed to NCCL on the communicator's stream as soon as chain c's backward pass ends; chains c-1 .. 0 keep computing
+    for (int c = M->nchains - 1; c >= 0; c--) {
+        DC_TRY(chain_backward(M, c, B));
+        DC_TRY(k2_reduce_batched(ctx, M->red));
+        DC_TRY(k2_fold_split_grad(ctx, M->g_exp, M->g, M->split_chain[c]));
+        int64_t n = M->chain_off[c + 1] - M->chain_off[c];
+        if (c == 0) {
+            DC_LAUNCH(ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
+            DC_CHECK_LAUNCH();
+            if (M->nchains == 1) n += 1;
+        }
+        DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_go, ctx->stream));
+        DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_comm_go, 0));
+        DC_TRY(dc_allreduce_on(ctx, M->g + M->chain_off[c], n, ctx->comm_stream));
+        if (c == 0 && M->nchains > 1) DC_TRY(dc_allreduce_on(ctx, M->g + M->n_int, 1, ctx->comm_stream));     // the loss slot sits behind the LAST chain's range
+    }
+    DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_done, ctx->comm_stream));
+    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_comm_done, 0));
     return DINCAE_OK;
 }
 
@@ -595,6 +618,15 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         const bool fused_head = tc_mode && cfg->upsampling == DINCAE_UP_NEAREST && k2_head_up_conv_eligible(decf[1], decf[0]);
         for (int l = L - 1; l >= 0; l--) fill(M->dec[c][l], decf[l + 1], decf[l], (l == 0 && !fused_head) ? 2 : 0);
     }
+    for (int c = 0; c < M->nchains; c++) {
+        M->chain_off[c] = M->enc[c][0].w_off;
+        M->split_chain[c].count = 0;
+        for (int i = 0; i < M->split.count; i++) {
+            const int64_t wo = M->split.d[i].w_off;
+            if (wo >= M->enc[c][0].w_off && (c + 1 == M->nchains || wo < M->enc[c + 1][0].w_off)) M->split_chain[c].d[M->split_chain[c].count++] = M->split.d[i];
+        }
+    }
+    M->chain_off[M->nchains] = off;
     M->n_int = off; M->n_flux = foff; M->n_wT = toff; M->n_wk = koff; M->n_wtk = tkoff; M->n_gexp = goff;
     // table for the transposed copies, in wT order; each entry copies 9*Cin_p*Cout_p values
     {
@@ -882,6 +914,47 @@ extern "C" int32_t dincae_train_step(dincae_model* M, const float* xin, const fl
     return dincae_apply_step(M, lr, loss);
 }
 
+extern "C" int32_t dincae_allreduce_grads(dincae_model* M) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_allreduce_grads: model is NULL");
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    return dc_allreduce_on(M->ctx, M->g, M->n_int + 1, M->ctx->stream);
+}
+
+extern "C" int32_t dincae_train_step_dp(dincae_model* M, const float* xin, const float* xtrue, int32_t B, const int64_t* n_valid_global,
+                                        float lr, int32_t loc, float* loss) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: model is NULL");
+    DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: no communicator (dincae_comm_init_rank)");
+    DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
+    M->dp_overlap = !M->ctx->prof;
+    int32_t st = dincae_grad_step(M, xin, xtrue, B, n_valid_global, loc);
+    const bool overlapped = M->dp_overlap;
+    M->dp_overlap = false;
+    DC_TRY(st);
+    if (!overlapped) DC_TRY(dincae_allreduce_grads(M));
+    return dincae_apply_step(M, lr, loss);
+}
+
+extern "C" int32_t dincae_replica_divergence(dincae_model* M, float* max_abs_diff) {
+    DC_REQUIRE(M && max_abs_diff, DINCAE_EINVAL, "dincae_replica_divergence: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_REQUIRE(ctx->comm != nullptr, DINCAE_EINVAL, "dincae_replica_divergence: no communicator");
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    DC_TRY(wgrad_join(M));
+    // the gradient workspace is free between steps: tmp = (rank == 0 ? w : 0), SUM over ranks = w_0, then max |w - w_0|
+    float* tmp = M->g;
+    if (ctx->comm_rank == 0) DC_CHECK_CUDA(cudaMemcpyAsync(tmp, M->w, sizeof(float) * M->n_int, cudaMemcpyDeviceToDevice, ctx->stream));
+    else DC_CHECK_CUDA(cudaMemsetAsync(tmp, 0, sizeof(float) * M->n_int, ctx->stream));
+    DC_TRY(dc_allreduce_on(ctx, tmp, M->n_int, ctx->stream));
+    DC_TRY(k3_max_abs_diff(ctx, M->w, tmp, M->n_int, (float*)M->d_inv_n));
+    DC_TRY(dc_allreduce_on(ctx, (float*)M->d_inv_n, 1, ctx->stream));       // SUM of non-negative per-rank maxima: 0 iff every rank is 0
+    void* pin = nullptr;
+    DC_TRY(dc_pinned(ctx, 64, &pin));
+    DC_CHECK_CUDA(cudaMemcpyAsync(pin, M->d_inv_n, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    *max_abs_diff = *(float*)pin;
+    return DINCAE_OK;
+}
+
 // ---- one-batch-ahead prefetch (PrefetchDataIter, src/data.jl:872-904) ------------------------------------------
 extern "C" int32_t dincae_batch_upload(dincae_model* M, int32_t slot, const float* xin_host, const float* xtrue_host, int32_t B) {
     DC_TRY(check_batch(M, B, "dincae_batch_upload"));
@@ -930,6 +1003,19 @@ extern "C" int32_t dincae_grad_step_slot(dincae_model* M, int32_t slot, int32_t 
     DC_CHECK_CUDA(cudaEventRecord(M->slot_free[slot], ctx->stream));
     M->slot_used[slot] = true;
     return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_train_step_dp_slot(dincae_model* M, int32_t slot, int32_t B, const int64_t* n_valid_global, float lr, float* loss) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: model is NULL");
+    DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: no communicator (dincae_comm_init_rank)");
+    DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: n_valid_global is NULL");
+    M->dp_overlap = !M->ctx->prof;
+    int32_t st = dincae_grad_step_slot(M, slot, B, n_valid_global);
+    const bool overlapped = M->dp_overlap;
+    M->dp_overlap = false;
+    DC_TRY(st);
+    if (!overlapped) DC_TRY(dincae_allreduce_grads(M));
+    return dincae_apply_step(M, lr, loss);
 }
 
 extern "C" int32_t dincae_loss_points(dincae_model* M, const float* xin, const float* pos, const float* x,

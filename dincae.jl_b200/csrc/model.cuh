@@ -32,6 +32,9 @@ struct ChainBufs {
 
 struct dincae_model {
     bool side_pending = false;   // weight gradients in flight on the context's side stream
+    bool dp_overlap = false;     // dincae_train_step_dp: all-reduce every chain's gradient bucket as soon as its backward pass ends
+    int64_t chain_off[DINCAE_MAX_CHAINS + 1];     // parameter range of chain c in the flat buffers: [chain_off[c], chain_off[c+1])
+    SplitTable split_chain[DINCAE_MAX_CHAINS];    // the split-operand layers of chain c
 
     dincae_ctx* ctx = nullptr;
     dincae_config cfg;

@@ -13,6 +13,7 @@ HOST, DEVICE, DEVICE_XIN = 0, 1, 2
 UP_NEAREST, UP_BILINEAR = 0, 1
 PREC_FP32, PREC_TF32, PREC_TF32X1 = 0, 1, 2
 MAX_LEVELS, MAX_CHAINS = 8, 4
+COMM_ID_BYTES = 128
 
 
 class Config(C.Structure):
@@ -69,9 +70,19 @@ SIGNATURES = {
     "dincae_grad_step_points": (i32, [vp, vp, vp, vp, vp, i32, i64, i32]),
     "dincae_grad_buffer": (i32, [vp, pp, C.POINTER(i64)]),
     "dincae_apply_step": (i32, [vp, f32, C.POINTER(f32)]),
+    "dincae_comm_unique_id": (i32, [vp]),
+    "dincae_comm_init_rank": (i32, [vp, i32, i32, vp]),
+    "dincae_comm_destroy": (i32, [vp]),
+    "dincae_comm_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "dincae_allreduce": (i32, [vp, vp, i64]),
+    "dincae_allreduce_grads": (i32, [vp]),
+    "dincae_train_step_dp": (i32, [vp, vp, vp, i32, vp, f32, i32, C.POINTER(f32)]),
+    "dincae_train_step_dp_slot": (i32, [vp, i32, i32, vp, f32, C.POINTER(f32)]),
+    "dincae_replica_divergence": (i32, [vp, C.POINTER(f32)]),
     "dincae_count_valid": (i32, [vp, vp, i32, i32, vp]),
     "dincae_gridded_create": (i32, [vp, vp, i32, i32, i32, i64, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, pp]),
     "dincae_gridded_destroy": (i32, [vp]),
+    "dincae_gridded_set_error": (i32, [vp, vp, i32]),
     "dincae_gridded_get_mean": (i32, [vp, vp]),
     "dincae_gridded_assemble": (i32, [vp, vp, vp, u64, u64, i32, vp, vp, i32]),
     "dincae_gridded_valid_counts": (i32, [vp, i32, vp]),

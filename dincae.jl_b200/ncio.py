@@ -148,3 +148,75 @@ def write_reconstruction(fname, varnames, lon, lat, meandata, mean, sigma, count
     finally:
         ds.close()
     return fname
+
+
+def load_ragged_points(fname, varname):
+    """DINCAE.loaddata (src/points.jl:429-446): a CF contiguous-ragged-array file (a count variable with the attribute
+    sample_dimension, here `size(time_instances)`; `varname`, lon, lat, dtime, id along the sample dimension; `dates` per
+    instance) -> values, (lon, lat), dtime, id as lists of per-instance vectors, dates as days since 1970 and the day of the
+    year of every instance (what PointCloud derives with Dates.dayofyear, src/points.jl:197-202)."""
+    ds = _open(fname)
+    try:
+        count = None
+        for name, v in ds.variables.items():
+            if hasattr(v, "sample_dimension"):
+                sd = v.sample_dimension
+                sd = sd.decode() if isinstance(sd, bytes) else sd
+                if ds.variables[varname].dimensions == (sd,):
+                    count = np.array(v[...], np.int64)
+        if count is None:
+            raise ValueError("%s: no count variable with sample_dimension = the dimension of %r" % (fname, varname))
+        ends = np.cumsum(count); starts = ends - count
+
+        def ragged(name, dtype, fill_nan):
+            var = ds.variables[name]
+            a = _masked(var, np.nan) if fill_nan else np.array(var[...])
+            a = a.astype(dtype)
+            return [a[s:e].copy() for s, e in zip(starts, ends)]
+        values = ragged(varname, np.float32, True)
+        lon = ragged("lon", np.float32, True); lat = ragged("lat", np.float32, True)
+        dv = ds.variables["dtime"]
+        du = dv.units.decode() if isinstance(dv.units, bytes) else dv.units
+        dt_all = _days_since_1970(np.array(dv[...], np.float64), du)
+        dtime = [dt_all[s:e].copy() for s, e in zip(starts, ends)]
+        ids = ragged("id", np.int64, False)
+        tv = ds.variables["dates"]
+        dates = _days_since_1970(np.array(tv[...], np.float64), tv.units.decode() if isinstance(tv.units, bytes) else tv.units)
+    finally:
+        ds.close()
+    epoch = _dt.datetime(1970, 1, 1)
+    doy = np.array([(epoch + _dt.timedelta(days=float(d))).timetuple().tm_yday for d in dates], np.float64)
+    return values, (lon, lat), dtime, ids, dates, doy
+
+
+def write_paramfile(fname, losses, attrs):
+    """The parameter file of reconstruct / reconstruct_points (src/model.jl:655-676, src/points.jl:658-692): variable
+    `losses(epochs)` plus one global attribute per keyword.  Booleans are written as Int, sequences as vectors, strings as text."""
+    if os.path.exists(fname):
+        os.remove(fname)
+    ds = netcdf_file(fname, "w", version=2)
+    try:
+        ds.createDimension("epochs", len(losses))
+        v = ds.createVariable("losses", "d", ("epochs",))
+        v[:] = np.asarray(losses, np.float64)
+        for k, val in attrs.items():
+            if isinstance(val, bool):
+                val = np.int32(val)
+            elif isinstance(val, str):
+                pass
+            elif isinstance(val, (list, tuple, range, np.ndarray)):
+                val = list(val)
+                if len(val) and all(isinstance(x, str) for x in val):
+                    val = ",".join(val)
+                elif all(float(x).is_integer() for x in val) and not any(isinstance(x, float) for x in val):
+                    val = np.asarray(val, np.int32)
+                else:
+                    val = np.asarray(val, np.float64)
+            elif isinstance(val, (int, np.integer)):
+                val = np.int32(val)
+            else:
+                val = np.float64(val)
+            setattr(ds, k, val)
+    finally:
+        ds.close()
+    return fname

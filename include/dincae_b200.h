@@ -8,10 +8,12 @@
  *   - external tensors keep the reference's memory order, Julia column-major WHCN
  *     (xin[i,j,c,b], i = lon fastest: src/data.jl:411-416), Float32; positions are
  *     interleaved (x,y) Float32 1-based fractional indices (src/points.jl:108-121).
- *   - `loc` says where caller buffers live: DINCAE_HOST pointers are borrowed for the call
- *     only (copied on the context's stream, result ready on return); DINCAE_DEVICE
- *     pointers must be valid on the context's device and the call is asynchronous on
- *     the context's stream unless a host scalar is returned.
+ *   - `loc` says where caller buffers live.  DINCAE_HOST pointers are borrowed and copied on the context's
+ *     stream: a call that returns a host scalar or host array is complete on return; a call that returns
+ *     nothing to the host (dincae_grad_step, dincae_apply_step with loss = NULL, dincae_batch_upload, ...)
+ *     may leave the copy in flight, so the buffer must stay untouched until dincae_sync (or the matching
+ *     *_slot call) returns.  DINCAE_DEVICE pointers must be valid on the context's device and the call is
+ *     asynchronous on the context's stream unless a host scalar is returned.
  *   - no CPU fallback exists anywhere behind this header.
  */
 #ifndef DINCAE_B200_H
@@ -151,6 +153,33 @@ int32_t dincae_grad_step_points(dincae_model* m, const float* xin, const float* 
                                 const int64_t* offsets, int32_t B, int64_t n_valid_global, int32_t loc);
 int32_t dincae_grad_buffer(dincae_model* m, float** dev_ptr, int64_t* n);
 int32_t dincae_apply_step(dincae_model* m, float lr, float* loss);
+/* ---- data-parallel gradient exchange (new capability: the reference trains on one device, src/flux.jl:23-40) -------------
+ * One process per GPU, one context per process.  The library owns an NCCL communicator per context (NCCL is bound with
+ * dlopen at the first call: an NCCL already loaded by the host process is shared, else libnccl.so.2, else $DINCAE_NCCL_LIB).
+ *   comm_unique_id : rank 0 creates the 128-byte rendezvous id (ncclGetUniqueId) and hands it to the other ranks by the
+ *                    host's own means (MPI.bcast, a file, torch.distributed ...).
+ *   comm_init_rank : collective over all ranks; binds the communicator to ctx's device.
+ *   allreduce      : in-place SUM of a device buffer over all ranks, asynchronous on the context's stream.
+ *   allreduce_grads: the same for the model's flat gradient buffer + loss slot (between grad_step* and apply_step).
+ *   train_step_dp  : grad_step + all-reduce + apply_step with the exchange OVERLAPPED with the backward pass: the
+ *                    gradients of refinement chain c are final once its backward pass ends (the chains run last to
+ *                    first), so their bucket crosses NVLink on the communicator's stream while the earlier chains'
+ *                    backward kernels still run.  n_valid_global as in grad_step (must not be NULL here).
+ *                    Bit-identical replicas: every rank applies the same update to the same sums.
+ *   train_step_dp_slot: the same on a mini-batch shard uploaded with dincae_batch_upload. */
+#define DINCAE_COMM_ID_BYTES 128
+int32_t dincae_comm_unique_id(void* id128);
+int32_t dincae_comm_init_rank(dincae_ctx* ctx, int32_t nranks, int32_t rank, const void* id128);
+int32_t dincae_comm_destroy(dincae_ctx* ctx);
+int32_t dincae_comm_info(dincae_ctx* ctx, int32_t* nranks, int32_t* rank, int32_t* nccl_version);
+int32_t dincae_allreduce(dincae_ctx* ctx, float* dev_buf, int64_t n);
+int32_t dincae_allreduce_grads(dincae_model* m);
+int32_t dincae_train_step_dp(dincae_model* m, const float* xin, const float* xtrue, int32_t B, const int64_t* n_valid_global,
+                             float lr, int32_t loc, float* loss);
+int32_t dincae_train_step_dp_slot(dincae_model* m, int32_t slot, int32_t B, const int64_t* n_valid_global, float lr, float* loss);
+/* max over all parameters of |w_rank - w_rank0| (replica drift check; 0 when the replicas are bit-identical); collective */
+int32_t dincae_replica_divergence(dincae_model* m, float* max_abs_diff);
+
 /* number of valid (xtrue[:,:,2v,:] != 0) targets per output variable in a batch (n_noncloud, src/model.jl:61) */
 int32_t dincae_count_valid(dincae_model* m, const float* xtrue, int32_t B, int32_t loc, int64_t* n_valid);
 
@@ -167,6 +196,9 @@ int32_t dincae_gridded_create(dincae_ctx* ctx, const float* data_full, int32_t W
                               const float* time_cos, const float* time_sin, int32_t ntime_win,
                               int32_t loc, dincae_gridded** out);
 int32_t dincae_gridded_destroy(dincae_gridded* ds);
+/* per-pixel observation error field (errvarname: src/data.jl:34,66-67 and the 4-D obs_err_std branch :323-326):
+ * obs_err_std (W,H,V,N) replaces the per-variable value, +Inf where the error field is missing (both channels become 0). */
+int32_t dincae_gridded_set_error(dincae_gridded* ds, const float* obs_err_std, int32_t loc);
 int32_t dincae_gridded_get_mean(dincae_gridded* ds, float* host_mean);   /* meandata (W,H,V) */
 /* time_idx[B] 0-based sample indices (perm[j]); imask[B] 0-based time index whose missing mask is
  * transplanted onto the centre step, NULL = no perturbation (train=false); jitter noise is

@@ -56,7 +56,10 @@ class NCData:
         data = (data_full - meandata[:, :, :, None]).astype(np.float32)   # :299
         nan = np.isnan(data)
         x = np.zeros((W, H, V, N, 2), np.float32, order="F")
-        s2 = (obs_err_std * obs_err_std).astype(np.float32)[None, None, :, None]
+        if obs_err_std.ndim == 1:                                         # :318-322 one value per variable
+            s2 = (obs_err_std * obs_err_std).astype(np.float32)[None, None, :, None]
+        else:                                                             # :323-326 per-pixel error field (errvarname), Inf = missing
+            s2 = (obs_err_std * obs_err_std).astype(np.float32)
         x[..., 0] = np.where(nan, np.float32(0), data) / s2               # :315,:321
         x[..., 1] = (1 - nan.astype(np.float32)) / s2                     # :316,:322
         self.x = x
