@@ -24,6 +24,15 @@ def _f32(a, order="F"):
     return np.asarray(a, dtype=np.float32, order=order)
 
 
+def _host_nccl_first():
+    """PyTorch bundles its own libnccl.so.2; the loader keeps one object per soname, so let torch load its copy before the
+    library dlopens NCCL (otherwise a later `import torch` would be handed the system copy and fail on missing symbols)."""
+    try:
+        import torch  # noqa: F401
+    except Exception:
+        pass
+
+
 class Context:
     """One GPU (replaces `_to_device(Atype)`, src/flux.jl:47-49)."""
 
@@ -49,6 +58,7 @@ class Context:
     @staticmethod
     def comm_unique_id() -> bytes:
         """Rank 0: the 128-byte NCCL rendezvous id, to be handed to every rank by the host's own means."""
+        _host_nccl_first()
         buf = C.create_string_buffer(L.COMM_ID_BYTES)
         L.check(L.load().dincae_comm_unique_id(buf))
         return buf.raw
@@ -56,6 +66,7 @@ class Context:
     def comm_init(self, nranks: int, rank: int, unique_id: bytes):
         if len(unique_id) != L.COMM_ID_BYTES:
             raise ValueError("unique_id must be %d bytes" % L.COMM_ID_BYTES)
+        _host_nccl_first()
         L.check(self._lib.dincae_comm_init_rank(self.handle, nranks, rank, C.c_char_p(unique_id)))
 
     def comm_info(self):
@@ -423,9 +434,10 @@ class Model:
         return out.value if want_loss else None
 
     def grad_step_points(self, xin, point_truth, n_valid_global=-1):
-        xin, B = self._batch(xin, None)
+        xin, B = self._batch(xin, len(point_truth))
         pos, x, offs = self._pack_points(point_truth)
-        L.check(self._lib.dincae_grad_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, int(n_valid_global), L.HOST))
+        loc = L.HOST if isinstance(xin, np.ndarray) else L.DEVICE_XIN
+        L.check(self._lib.dincae_grad_step_points(self.handle, L.ptr(xin), L.ptr(pos), L.ptr(x), L.ptr(offs), B, int(n_valid_global), loc))
 
     def close(self):
         if self.handle:

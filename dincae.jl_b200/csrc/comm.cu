@@ -4,7 +4,9 @@
 // summed over NVLink/NVSwitch before the identical L2 + ClipGrad + Adam update runs on every replica.
 //
 // NCCL is bound at run time (dlopen), not at link time: single-GPU users need no NCCL, and a host that already carries one
-// (PyTorch, CUDA.jl's NCCL.jl) shares its copy instead of loading a second one.
+// (PyTorch, CUDA.jl's NCCL.jl) shares its copy instead of loading a second one.  Order matters for such a host: the dynamic
+// loader keeps ONE object per soname, so a host that bundles its own libnccl.so.2 must have loaded it BEFORE the first
+// dincae_comm_* call (or point DINCAE_NCCL_LIB at it); otherwise the system copy found here is what the host gets later.
 #include "common.cuh"
 #include <dlfcn.h>
 #include <nccl.h>
@@ -30,10 +32,10 @@ int32_t nccl_api(NcclApi** out) {
     if (!g_nccl.handle) {
         const char* env = getenv("DINCAE_NCCL_LIB");
         void* h = nullptr;
-        if (env && *env) { h = dlopen(env, RTLD_NOW | RTLD_GLOBAL); g_nccl.path = env; }
+        if (env && *env) { h = dlopen(env, RTLD_NOW | RTLD_LOCAL); g_nccl.path = env; }
         if (!h) { h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD); g_nccl.path = "libnccl.so.2 (already loaded by the host process)"; }
-        if (!h) { h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL); g_nccl.path = "libnccl.so.2"; }
-        if (!h) { h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL); g_nccl.path = "libnccl.so"; }
+        if (!h) { h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL); g_nccl.path = "libnccl.so.2"; }
+        if (!h) { h = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL); g_nccl.path = "libnccl.so"; }
         DC_REQUIRE(h != nullptr, DINCAE_EUNSUPPORTED, "NCCL not found (%s); set DINCAE_NCCL_LIB to libnccl.so.2 for multi-GPU training", dlerror());
 #define NCCL_SYM(name)                                                                                       \
         g_nccl.name = (decltype(g_nccl.name))dlsym(h, "nccl" #name);                                          \

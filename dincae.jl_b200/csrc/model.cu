@@ -459,6 +459,8 @@ int32_t backward_all(dincae_model* M, int B) {
     }
     // data-parallel step: the bucket of chain c (its parameter range; the last one also carries the loss slot) is finished and
     // handed to NCCL on the communicator's stream as soon as chain c's backward pass ends; chains c-1 .. 0 keep computing
+    // (under the per-launch profile the same buckets go out on the main stream: every rank must issue the same collectives)
+    cudaStream_t cs = ctx->prof ? ctx->stream : ctx->comm_stream;
     for (int c = M->nchains - 1; c >= 0; c--) {
         DC_TRY(chain_backward(M, c, B));
         DC_TRY(k2_reduce_batched(ctx, M->red));
@@ -469,13 +471,17 @@ int32_t backward_all(dincae_model* M, int B) {
             DC_CHECK_LAUNCH();
             if (M->nchains == 1) n += 1;
         }
-        DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_go, ctx->stream));
-        DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->ev_comm_go, 0));
-        DC_TRY(dc_allreduce_on(ctx, M->g + M->chain_off[c], n, ctx->comm_stream));
-        if (c == 0 && M->nchains > 1) DC_TRY(dc_allreduce_on(ctx, M->g + M->n_int, 1, ctx->comm_stream));     // the loss slot sits behind the LAST chain's range
+        if (cs != ctx->stream) {
+            DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_go, ctx->stream));
+            DC_CHECK_CUDA(cudaStreamWaitEvent(cs, ctx->ev_comm_go, 0));
+        }
+        DC_TRY(dc_allreduce_on(ctx, M->g + M->chain_off[c], n, cs));
+        if (c == 0 && M->nchains > 1) DC_TRY(dc_allreduce_on(ctx, M->g + M->n_int, 1, cs));     // the loss slot sits behind the LAST chain's range
     }
-    DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_done, ctx->comm_stream));
-    DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_comm_done, 0));
+    if (cs != ctx->stream) {
+        DC_CHECK_CUDA(cudaEventRecord(ctx->ev_comm_done, cs));
+        DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_comm_done, 0));
+    }
     return DINCAE_OK;
 }
 
@@ -925,12 +931,10 @@ extern "C" int32_t dincae_train_step_dp(dincae_model* M, const float* xin, const
     DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: model is NULL");
     DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: no communicator (dincae_comm_init_rank)");
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
-    M->dp_overlap = !M->ctx->prof;
+    M->dp_overlap = true;
     int32_t st = dincae_grad_step(M, xin, xtrue, B, n_valid_global, loc);
-    const bool overlapped = M->dp_overlap;
     M->dp_overlap = false;
     DC_TRY(st);
-    if (!overlapped) DC_TRY(dincae_allreduce_grads(M));
     return dincae_apply_step(M, lr, loss);
 }
 
@@ -1009,12 +1013,10 @@ extern "C" int32_t dincae_train_step_dp_slot(dincae_model* M, int32_t slot, int3
     DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: model is NULL");
     DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: no communicator (dincae_comm_init_rank)");
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: n_valid_global is NULL");
-    M->dp_overlap = !M->ctx->prof;
+    M->dp_overlap = true;
     int32_t st = dincae_grad_step_slot(M, slot, B, n_valid_global);
-    const bool overlapped = M->dp_overlap;
     M->dp_overlap = false;
     DC_TRY(st);
-    if (!overlapped) DC_TRY(dincae_allreduce_grads(M));
     return dincae_apply_step(M, lr, loss);
 }
 
