@@ -3,7 +3,8 @@
   python scripts/ncu_summarize.py <launches.csv> <full.ncu-rep> <tag>
 writes profiles/<tag>_ncu_launches.csv (per-launch gpu__time_duration of one bench.py run), profiles/<tag>_ncu_step_share.txt
 (per-kernel totals and shares), profiles/<tag>_ncu_full_top_kernels.csv (selected --set full metrics per captured launch) and
-profiles/r01_ncu_traffic.json (dram read+write bytes per captured launch, keyed by the kernel names bench.py reports)."""
+profiles/<tag>_ncu_traffic.json (per kernel name as bench.py reports it: launches captured in ONE training step, mean DRAM
+read+write bytes per launch, mean duration) -- bench.py sets `roofline.traffic` from it."""
 import csv, collections, json, os, re, subprocess, sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -52,18 +53,19 @@ with open(os.path.join(prof, tag + "_ncu_full_top_kernels.csv"), "w") as f:
             vals.append(short(r[i]) if w == "Kernel Name" else r[i])
         f.write(",".join('"%s"' % v for v in vals) + "\n")
         name = short(r[hdr.index("Kernel Name")])
-        m = re.match(r"(\w+)<(?:\(int\))?(\d+)", name)
-        key = "%s_bn%s" % (m.group(1), m.group(2)) if m else name
-        if key.startswith("wgrad32_kernel"):
-            key = "wgrad32"
-        elif key.startswith("wgrad9_kernel_bn"):
-            key = "wgrad9_n" + key[len("wgrad9_kernel_bn"):]
-        elif key.startswith("wgradm_kernel"):
+        name = re.sub(r"\(int\)|\(bool\)", "", name)
+        m = re.match(r"(conv3x3_\w+)<(\d+)", name)
+        m9 = re.match(r"wgrad9_kernel<(\d+)", name)
+        key = "%s_bn%s" % (m.group(1), m.group(2)) if m else ("wgrad9_n" + m9.group(1) if m9 else name)
+        if key.startswith("wgradm_kernel"):
             key = "wgradm"
+        key = re.sub(r"<1>$", "<true>", re.sub(r"<0>$", "<false>", key)) if key.startswith(("loss_grid_kernel", "adam_kernel")) else key
         def num(col):
             i = hdr.index(col); v = float(r[i].replace(",", "")); u = units[i]
             return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
         traffic[key].append({"grid": r[hdr.index("Grid Size")], "dram_bytes": num("dram__bytes_read.sum") + num("dram__bytes_write.sum"),
                              "us": float(r[hdr.index("gpu__time_duration.sum")].replace(",", "")) * (1e-3 if units[hdr.index("gpu__time_duration.sum")] in ("ns", "nsecond") else 1)})
-json.dump(traffic, open(os.path.join(prof, "r01_ncu_traffic.json"), "w"), indent=1)
+summary = {k: {"launches_in_step": len(v), "dram_bytes_per_launch": sum(e["dram_bytes"] for e in v) / len(v),
+               "us_per_launch": sum(e["us"] for e in v) / len(v), "launches": v} for k, v in traffic.items()}
+json.dump(summary, open(os.path.join(prof, tag + "_ncu_traffic.json"), "w"), indent=1)
 print("kernels:", sorted(traffic))
