@@ -492,13 +492,14 @@ def main():
         roofs["tensor_source"] = "measured in this run: " + tf32["how"]
         traffic = {}
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "r02_ncu_traffic.json")))
+            import glob
+            traffic = json.load(open(sorted(glob.glob(os.path.join(ROOT, "profiles", "r02*_ncu_traffic.json")))[-1]))      # latest capture of this round
         except Exception:
             pass
         rooflines = [roofline_of(k, roofs, traffic) for k in kern_table if k["share"] >= 0.03]
         roof = dict(rooflines[0], peak_source=roofs["hbm_source"] if rooflines[0]["bound"] == "hbm" else roofs["tensor_source"],
                     note="dominant kernel of the per-launch CUDA-event profile (%d steps, kernels serialised); traffic = mean DRAM bytes per launch "
-                         "of the same kernel in profiles/r02_ncu_traffic.json (ncu --set full of the same command)" % nprof)
+                         "of the same kernel over one whole training step in profiles/r02*_ncu_traffic.json (ncu --set full of the same command)" % nprof)
         recon["frac_of_tf32_roof"] = recon["achieved_tflops"] / world / roofs["tf32_tflops"]
         if configs:
             bench_configs.finalize(configs, roofs, world)

@@ -3,7 +3,7 @@
 # 1. the bench command once without ncu (must exit 0), 2. launch list (gpu__time_duration per launch) of the same command,
 # 3. ncu --set full of ONE whole steady-state training step (every kernel of the step, so that per-kernel DRAM traffic and the
 #    algorithmic bytes bench.py reports refer to the same launches).  Raw outputs land in gpurun_out/; summarise them here with
-#    python scripts/ncu_summarize.py gpurun_out/<tag>_launches.csv gpurun_out/<tag>_full.ncu-rep <tag>
+#    python scripts/ncu_summarize.py gpurun_out/<tag>_launches.csv gpurun_out/<tag>_full_raw.csv <tag>
 set -u
 TAG=${1:-r02}
 OUT=gpurun_out
@@ -20,5 +20,9 @@ print(idx[3], idx[4] - idx[3])
 PY
 )
 echo "one step = launches [$SKIP, $SKIP+$COUNT)"
-ncu --set full --clock-control none --import-source on -s $SKIP -c $COUNT -o $OUT/${TAG}_full -f $CMD > $OUT/${TAG}_ncu2.log 2>&1
-ls -la $OUT/${TAG}_full.ncu-rep
+ncu --set full --clock-control none -s $SKIP -c $COUNT -o /tmp/${TAG}_full -f $CMD > $OUT/${TAG}_ncu2.log 2>&1
+# the report of a whole step is > 64 MiB (the limit of what gpurun brings back): export its raw page here, keep the report on the box
+ncu -i /tmp/${TAG}_full.ncu-rep --page raw --csv > $OUT/${TAG}_full_raw.csv
+# a small report WITH source correlation of the dominant kernel (two launches of conv3x3_persist<32>)
+ncu --set full --clock-control none --import-source on -k regex:conv3x3_persist -s 30 -c 2 -o $OUT/${TAG}_top -f $CMD > $OUT/${TAG}_ncu3.log 2>&1
+ls -la $OUT/${TAG}_full_raw.csv $OUT/${TAG}_top.ncu-rep

@@ -1,6 +1,6 @@
 """Turn the ncu outputs brought back in gpurun_out/ into the tracked summaries under profiles/.
 
-  python scripts/ncu_summarize.py <launches.csv> <full.ncu-rep> <tag>
+  python scripts/ncu_summarize.py <launches.csv> <full.ncu-rep | its --page raw --csv export> <tag>
 writes profiles/<tag>_ncu_launches.csv (per-launch gpu__time_duration of one bench.py run), profiles/<tag>_ncu_step_share.txt
 (per-kernel totals and shares), profiles/<tag>_ncu_full_top_kernels.csv (selected --set full metrics per captured launch) and
 profiles/<tag>_ncu_traffic.json (per kernel name as bench.py reports it: launches captured in ONE training step, mean DRAM
@@ -34,7 +34,7 @@ with open(os.path.join(prof, tag + "_ncu_step_share.txt"), "w") as f:
     for k, (c, v) in sorted(agg.items(), key=lambda x: -x[1][1]):
         f.write("%-44s %6d %12.1f %10.2f %6.1f%%\n" % (k[:44], c, v / 1e3, v / 1e3 / c, 100 * v / tot))
 
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+raw = open(rep).read() if rep.endswith(".csv") else subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rr = list(csv.reader(raw.splitlines()))
 hdr, data = rr[0], rr[2:]
 want = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",

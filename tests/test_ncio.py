@@ -92,3 +92,81 @@ def test_write_reconstruction_layout(tmp_path, ncio):
         assert np.allclose(ds.variables["lon"][...], lon) and np.allclose(ds.variables["lat"][...], lat)
     finally:
         ds.close()
+
+
+def _write_ragged(path, values, lon, lat, dtime, ids, dates1900, varname="sla"):
+    """CF contiguous ragged array file as documented in src/points.jl:478-501 (NetCDF-3: int instead of int64)."""
+    ds = netcdf_file(str(path), "w", version=2)
+    nobs = sum(len(v) for v in values)
+    ds.createDimension("time_instances", len(values)); ds.createDimension("obs", nobs)
+    v = ds.createVariable("size", "i", ("time_instances",)); v.sample_dimension = "obs"; v[:] = [len(x) for x in values]
+    v = ds.createVariable("dates", "d", ("time_instances",)); v.units = "days since 1900-01-01 00:00:00"; v[:] = dates1900
+    for name, arrs, t in ((varname, values, "f"), ("lon", lon, "f"), ("lat", lat, "f"), ("id", ids, "i"), ("dtime", dtime, "d")):
+        v = ds.createVariable(name, t, ("obs",))
+        if name == "dtime":
+            v.units = "days since 1900-01-01 00:00:00"
+        if name == varname:
+            v._FillValue = np.float32(-9999.0)
+        a = np.concatenate(arrs) if nobs else np.zeros(0)
+        if name == varname:
+            a = np.where(np.isnan(a), -9999.0, a)
+        v[:] = a
+    ds.close()
+
+
+def test_load_ragged_points(tmp_path, ncio):
+    # DINCAE.loaddata (src/points.jl:429-446): per-instance vectors out of the contiguous ragged representation, empty instance included
+    rng = np.random.default_rng(3)
+    counts = [4, 0, 7, 1]
+    values = [rng.standard_normal(c).astype(np.float32) for c in counts]
+    values[2][3] = np.nan
+    lon = [rng.uniform(-7, 37, c).astype(np.float32) for c in counts]
+    lat = [rng.uniform(29, 46, c).astype(np.float32) for c in counts]
+    ids = [rng.integers(1, 5, c).astype(np.int32) for c in counts]
+    dates = 36500.0 + 59 + np.arange(4)                       # 1999-12-08 + 59 ... day of year known below
+    dtime = [np.full(c, d) + rng.uniform(-0.5, 0.5, c) for c, d in zip(counts, dates)]
+    fn = tmp_path / "sla.nc"
+    _write_ragged(fn, values, lon, lat, dtime, ids, dates)
+    v2, (lo2, la2), dt2, id2, dates70, doy = ncio.load_ragged_points(str(fn), "sla")
+    assert [len(x) for x in v2] == counts
+    for a, b in zip(values, v2):
+        assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(a[~np.isnan(a)], b[~np.isnan(b)])
+    assert all(np.array_equal(a, b) for a, b in zip(lon, lo2)) and all(np.array_equal(a, b) for a, b in zip(lat, la2))
+    assert all(np.array_equal(a, b) for a, b in zip(ids, id2)) and id2[0].dtype == np.int64
+    assert np.allclose(dates70, dates - 25567.0) and all(np.allclose(a - 25567.0, b) for a, b in zip(dtime, dt2))
+    import datetime
+    d0 = datetime.date(1900, 1, 1) + datetime.timedelta(days=int(dates[0]))
+    assert doy[0] == d0.timetuple().tm_yday and np.all(np.diff(doy) == 1)
+
+
+def test_write_paramfile_attributes(tmp_path, ncio):
+    # src/model.jl:655-676: losses(epochs) + one global attribute per keyword
+    fn = tmp_path / "param.nc"
+    ncio.write_paramfile(str(fn), [3.0, 2.0, 1.5], dict(epochs=3, batch_size=50, truth_uncertain=False, enc_nfilter_internal=[16, 24, 36, 54],
+                                                       skipconnections=[2, 3, 4, 5], clip_grad=5.0, save_epochs=[2, 3], upsampling_method="nearest",
+                                                       learning_rate_decay_epoch=float("inf"), loss_weights_refine=[0.3, 0.7], is3D=False))
+    ds = netcdf_file(str(fn), "r", mmap=False)
+    try:
+        assert np.array_equal(ds.variables["losses"][...], [3.0, 2.0, 1.5]) and ds.dimensions["epochs"] == 3
+        assert int(ds.epochs) == 3 and int(ds.batch_size) == 50 and int(ds.truth_uncertain) == 0 and int(ds.is3D) == 0
+        assert list(ds.enc_nfilter_internal) == [16, 24, 36, 54] and list(ds.skipconnections) == [2, 3, 4, 5] and list(ds.save_epochs) == [2, 3]
+        assert float(ds.clip_grad) == 5.0 and np.isinf(ds.learning_rate_decay_epoch) and np.allclose(ds.loss_weights_refine, [0.3, 0.7])
+        assert ds.upsampling_method in (b"nearest", "nearest")
+    finally:
+        ds.close()
+
+
+def test_oracle_per_pixel_error_field():
+    # src/data.jl:323-326: a 4-D obs_err_std divides both channels pixel by pixel; Inf (missing error) zeroes them
+    from oracle import data as OD
+    rng = np.random.default_rng(5)
+    W, H, V, N = 6, 5, 2, 4
+    data = (rng.standard_normal((W, H, V, N)) + 10).astype(np.float32)
+    data[rng.random((W, H, V, N)) < 0.3] = np.nan
+    err = rng.uniform(0.5, 2.0, (W, H, V, N)).astype(np.float32)
+    err[0, 0, 0, :] = np.inf
+    od = OD.NCData(np.arange(W), np.arange(H), 11000.0 + np.arange(N), data, obs_err_std=err, ntime_win=3)
+    d = data - od.meandata[:, :, :, None]
+    ok = ~np.isnan(d)
+    assert np.allclose(od.x[..., 0][ok], (d / err ** 2)[ok]) and np.allclose(od.x[..., 1][ok], (1 / err ** 2)[ok])
+    assert np.all(od.x[0, 0, 0, :, :] == 0) and np.all(od.x[..., 1][~ok] == 0)
