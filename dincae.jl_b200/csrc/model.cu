@@ -24,13 +24,17 @@ __global__ void total_loss_kernel(const float* __restrict__ slot, const double* 
     if (out_f) out_f[0] = (float)t;
     if (out_d) out_d[0] = t;
 }
-__global__ void plane_of_kernel(const int64_t* __restrict__ offsets, int B, int64_t P, int32_t* __restrict__ plane_of) {
+// the per-sample point offsets travel BY VALUE (kernel parameter) like the valid counts: no staging copy of caller memory, hence
+// no stream synchronisation in the point-cloud step
+constexpr int PT_MAXB = 256;
+struct PtOffsets { int64_t v[PT_MAXB + 1]; };
+__global__ void plane_of_kernel(const __grid_constant__ PtOffsets offs, int B, int64_t P, int32_t* __restrict__ plane_of) {
     int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     if (p >= P) return;
     int lo = 0, hi = B;          // largest b with offsets[b] <= p
     while (hi - lo > 1) {
         int mid = (lo + hi) >> 1;
-        if (offsets[mid] <= p) lo = mid; else hi = mid;
+        if (offs.v[mid] <= p) lo = mid; else hi = mid;
     }
     plane_of[p] = lo;
 }
@@ -391,13 +395,13 @@ int32_t stage_points(dincae_model* M, const float* pos, const float* x, const in
     pt->pos = (const float*)pt->spos.ptr;
     pt->x = (const float*)pt->sx.ptr;
     pt->plane_of = (int32_t*)(M->pt_buf + 4 * M->pt_cap);
-    int64_t* d_off = (int64_t*)(M->pt_buf + 5 * M->pt_cap);
-    DC_CHECK_CUDA(cudaMemcpyAsync(d_off, offsets, sizeof(int64_t) * (B + 1), cudaMemcpyHostToDevice, ctx->stream));
+    DC_REQUIRE(B <= PT_MAXB, DINCAE_ESIZE, "point truth: at most %d samples per mini-batch", PT_MAXB);
     if (pt->P > 0) {
-        DC_LAUNCH(ctx, plane_of_kernel, (unsigned)dc_cdiv(pt->P, 256), 256, 0, d_off, B, pt->P, pt->plane_of);
+        PtOffsets po;
+        for (int b = 0; b <= B; b++) po.v[b] = offsets[b];
+        DC_LAUNCH(ctx, plane_of_kernel, (unsigned)dc_cdiv(pt->P, 256), 256, 0, po, B, pt->P, pt->plane_of);
         DC_CHECK_LAUNCH();
     }
-    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));    // offsets is caller memory (pageable)
     return DINCAE_OK;
 }
 
@@ -969,12 +973,24 @@ extern "C" int32_t dincae_batch_upload(dincae_model* M, int32_t slot, const floa
     const size_t npix = (size_t)M->cfg.W * M->cfg.H;
     const size_t nx = npix * M->cfg.ninput * M->maxB, ny = npix * 2 * M->O * M->maxB;
     if (!M->copy_stream) {
-        DC_CHECK_CUDA(cudaStreamCreateWithFlags(&M->copy_stream, cudaStreamNonBlocking));
-        for (int s = 0; s < 2; s++) {
-            DC_CHECK_CUDA(cudaMalloc((void**)&M->up_buf[s], sizeof(float) * (nx + ny)));
-            DC_CHECK_CUDA(cudaEventCreateWithFlags(&M->up_done[s], cudaEventDisableTiming));
-            DC_CHECK_CUDA(cudaEventCreateWithFlags(&M->slot_free[s], cudaEventDisableTiming));
+        // allocate into locals and publish only when everything succeeded: a failed allocation must not leave a half-built prefetch state
+        cudaStream_t cs = nullptr;
+        float* buf[2] = {nullptr, nullptr};
+        cudaEvent_t done[2] = {nullptr, nullptr}, fre[2] = {nullptr, nullptr};
+        cudaError_t e = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
+        for (int s = 0; s < 2 && e == cudaSuccess; s++) {
+            e = cudaMalloc((void**)&buf[s], sizeof(float) * (nx + ny));
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&done[s], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&fre[s], cudaEventDisableTiming);
         }
+        if (e != cudaSuccess) {
+            for (int s = 0; s < 2; s++) { if (buf[s]) cudaFree(buf[s]); if (done[s]) cudaEventDestroy(done[s]); if (fre[s]) cudaEventDestroy(fre[s]); }
+            if (cs) cudaStreamDestroy(cs);
+            dincae_set_error("dincae_batch_upload: cannot set up the prefetch slots: %s", cudaGetErrorString(e));
+            return e == cudaErrorMemoryAllocation ? DINCAE_ENOMEM : DINCAE_ECUDA;
+        }
+        M->copy_stream = cs;
+        for (int s = 0; s < 2; s++) { M->up_buf[s] = buf[s]; M->up_done[s] = done[s]; M->slot_free[s] = fre[s]; }
     }
     if (M->slot_used[slot]) DC_CHECK_CUDA(cudaStreamWaitEvent(M->copy_stream, M->slot_free[slot], 0));   // the step that read this slot has finished
     DC_CHECK_CUDA(cudaMemcpyAsync(M->up_buf[slot], xin_host, sizeof(float) * npix * M->cfg.ninput * B, cudaMemcpyHostToDevice, M->copy_stream));
@@ -1031,8 +1047,8 @@ extern "C" int32_t dincae_loss_points(dincae_model* M, const float* xin, const f
     PointTruth pt;
     DC_TRY(stage_points(M, pos, x, offsets, B, loc == DINCAE_DEVICE ? DINCAE_DEVICE : DINCAE_HOST, &pt));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
-    DC_TRY(model_forward(M, dx, B, false));
-    int32_t st = points_loss(M, pt, B, -1, false);
+    int32_t st = model_forward(M, dx, B, false);
+    if (st == DINCAE_OK) st = points_loss(M, pt, B, -1, false);
     dc_stage_free(ctx, &pt.spos);
     dc_stage_free(ctx, &pt.sx);
     DC_TRY(st);
@@ -1051,8 +1067,8 @@ extern "C" int32_t dincae_grad_step_points(dincae_model* M, const float* xin, co
     PointTruth pt;
     DC_TRY(stage_points(M, pos, x, offsets, B, loc == DINCAE_DEVICE ? DINCAE_DEVICE : DINCAE_HOST, &pt));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
-    DC_TRY(model_forward(M, dx, B, true));
-    int32_t st = points_loss(M, pt, B, n_valid_global, true);
+    int32_t st = model_forward(M, dx, B, true);
+    if (st == DINCAE_OK) st = points_loss(M, pt, B, n_valid_global, true);
     dc_stage_free(ctx, &pt.spos);
     dc_stage_free(ctx, &pt.sx);
     DC_TRY(st);

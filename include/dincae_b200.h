@@ -52,7 +52,8 @@ typedef struct dincae_config {
     int32_t nfilter[DINCAE_MAX_LEVELS]; /* enc_nfilter_internal */
     uint32_t skip_mask;              /* bit (l-1) set <=> level l in skipconnections (1-based, src/model.jl:277) */
     int32_t upsampling;              /* upsampling_method: DINCAE_UP_NEAREST | DINCAE_UP_BILINEAR */
-    int32_t nchains;                 /* length(loss_weights_refine) */
+    int32_t nchains;                 /* length(loss_weights_refine): 1, or 2 with the refinement stage (src/model.jl:322-340);
+                                        3 and 4 repeat the refinement wiring once more each (an extension, not in the reference) */
     float loss_weights[DINCAE_MAX_CHAINS]; /* loss_weights_refine */
     float gamma;                     /* log(min_std_err^-2), src/model.jl:318 */
     int32_t truth_uncertain;

@@ -53,3 +53,31 @@ def test_noalloc_rejects_oversize(pkg):
     with pytest.raises(pkg.lib.DincaeError) as e:
         pkg.api.interp_adjn_noalloc(d_pos, d_val, P, (8, 8), d_out, ctx)
     assert e.value.code == pkg.lib.ESIZE and "65536" in str(e.value)
+
+
+def test_noalloc_leaves_device_memory_untouched(pkg):
+    """The property the entry point exists for: after the one-time address lookup, calls take no device memory at all.
+    Two FRESH contexts (they have never run the allocating path, so no context scratch exists that a fallback could borrow)
+    call it while the free-memory reading of the device is watched; the second context also shows the cached address is reused."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(7)
+    W, H, P = 120, 90, 30000
+    pos, val = _case(rng, W, H, P)
+    ref = pkg.interp_adjn(pos, val, (W, H), pkg.Context(0))               # reference result from a separate context
+    d_pos = torch.from_numpy(pos).to(dev); d_val = torch.from_numpy(val).to(dev)
+    d_out = torch.empty((H, W), dtype=torch.float32, device=dev)
+    a, b = pkg.Context(0), pkg.Context(0)
+    pkg.api.interp_adjn_noalloc(d_pos, d_val, P, (W, H), d_out, a)        # warm-up: symbol address lookup / module load
+    a.sync()
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info(0)[0]
+    for ctx in (a, b, a, b):
+        d_out.fill_(5.0)
+        torch.cuda.synchronize()
+        pkg.api.interp_adjn_noalloc(d_pos, d_val, P, (W, H), d_out, ctx)
+        ctx.sync()
+        assert np.array_equal(d_out.cpu().numpy().T, ref)
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info(0)[0] == free0                          # nothing was allocated (or freed) on the device
