@@ -45,6 +45,8 @@ struct ConvArgs {
     int planar_fold;         // 1: planar channel k = accumulator column k + column (8 + k): the head conv's low-order weight
                              // columns (3xTF32 split, see k2_make_wK_split) are summed in the epilogue; needs planar_C <= 8
     float* pool_dst;         // optional: MeanPool((2,2)) of the output, only when k2_conv_fuses_pool(args) is true
+    uint32_t* mask_dst;      // pool-only mode (dst == NULL, pool_dst set): the activation itself is never written, only one bit per
+                             // element (output > 0 = what the backward pass needs of it), word [pixel][Cout_p / 32]
     double work_flops;    // algorithmic FLOPs (2*9*Cin*Cout*B*H*W with the REAL channel counts), for the profile
     double work_bytes;    // algorithmic HBM bytes (input + output + weights, REAL channel counts)
 };
@@ -131,6 +133,8 @@ int k2_colpart_blocks(dincae_ctx* ctx, int64_t n_elems4, int Cp);
 int32_t k2_upbwd(dincae_ctx* ctx, const float* gu, int B, int H, int W, int Cp, const float* r, float slope, float* G, float* gd, float* colpart = nullptr);
 // backward of mean-pool + activation mask: gc = 0.25 * xg[(y+oh)>>1,(x+ow)>>1] * act'(a)
 int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int H, int W, int Cp, float slope, float* gc, float* colpart = nullptr);
+// the same with the activation's sign bits (written by the pool-only conv epilogue) in place of the activation
+int32_t k2_poolbwd_mask(dincae_ctx* ctx, const float* xg, const uint32_t* mask, int B, int H, int W, int Cp, float slope, float* gc, float* colpart = nullptr);
 // bilinear (align_corners=true) upsample+crop of (src0 + src1) and its transpose
 // nearest upsample x2 + crop of (src0 + src1), materialised (TF32 mode: feeds the TMA kernels)
 // split != 0: dst has 2*Cp channels per pixel, [tf32(v) | tf32(v - tf32(v))] (input of the 3xTF32 head conv)

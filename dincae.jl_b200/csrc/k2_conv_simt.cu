@@ -486,7 +486,10 @@ __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu
     if (colpart) block_colpart(cacc, C4, Cp, colpart);
 }
 
-__global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, int B, int H, int W, int Cp,
+// act'(a) comes either from the stored activation `a` or, when the conv epilogue kept only its sign bits, from `mask`
+// (word [pixel][Cp / 32], bit c % 32 set <=> a[pixel][c] > 0)
+__global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, const uint32_t* __restrict__ mask,
+                                                      int B, int H, int W, int Cp,
                                                       int H2, int W2, float slope, float* __restrict__ gc, int rnd, float* __restrict__ colpart) {
     dc_pdl_launch_dependents();
     dc_pdl_wait();
@@ -503,9 +506,15 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ 
                 for (int x = rt.lane; x < W; x += rt.PL) {
                     float4 g = ldg4(rx + (size_t)((x + ow) >> 1) * Cp + c4 * 4);
                     const size_t off = ro + (size_t)x * Cp + c4 * 4;
-                    const float4 av = ldg4(a + off);
-                    g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
-                    g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+                    if (mask) {
+                        const uint32_t bits = __ldg(mask + ((size_t)row * W + x) * (Cp >> 5) + (c4 >> 3)) >> ((c4 & 7) * 4);
+                        g.x *= 0.25f * ((bits & 1u) ? 1.f : slope); g.y *= 0.25f * ((bits & 2u) ? 1.f : slope);
+                        g.z *= 0.25f * ((bits & 4u) ? 1.f : slope); g.w *= 0.25f * ((bits & 8u) ? 1.f : slope);
+                    } else {
+                        const float4 av = ldg4(a + off);
+                        g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
+                        g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+                    }
                     g = round_tf32(g, rnd);
                     *reinterpret_cast<float4*>(gc + off) = g;
                     cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
@@ -1061,7 +1070,20 @@ int32_t k2_poolbwd(dincae_ctx* ctx, const float* xg, const float* a, int B, int 
     int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * H, n);
     DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd: column partials not supported for %d channels", Cp);
     DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * H * W * 2 + (double)B * H2 * W2));       // a in, gc out, xg in at half resolution
-    DC_LAUNCH_PDL(ctx, poolbwd_kernel, nb, 256, 0, xg, a, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
+    DC_LAUNCH_PDL(ctx, poolbwd_kernel, nb, 256, 0, xg, a, (const uint32_t*)nullptr, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+int32_t k2_poolbwd_mask(dincae_ctx* ctx, const float* xg, const uint32_t* mask, int B, int H, int W, int Cp, float slope, float* gc, float* colpart) {
+    int H2 = H / 2 + H % 2, W2 = W / 2 + W % 2;
+    int64_t n = (int64_t)B * H * W * (Cp / 4);
+    if (n == 0) return DINCAE_OK;
+    DC_REQUIRE((Cp % 32) == 0, DINCAE_EINVAL, "k2_poolbwd_mask: %d channels are not whole mask words", Cp);
+    int nb = colpart ? k2_colpart_blocks(ctx, n, Cp) : k2_row_blocks(ctx, (int64_t)B * H, n);
+    DC_REQUIRE(nb > 0, DINCAE_EINVAL, "k2_poolbwd_mask: column partials not supported for %d channels", Cp);
+    DC_WORK(ctx, 0.0, 4.0 * Cp * ((double)B * H * W * (1.0 + 1.0 / 32) + (double)B * H2 * W2));     // gc out, sign bits + quarter-resolution xg in
+    DC_LAUNCH_PDL(ctx, poolbwd_kernel, nb, 256, 0, xg, (const float*)nullptr, mask, B, H, W, Cp, H2, W2, slope, gc, (int)ctx->tf32_acts, colpart);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

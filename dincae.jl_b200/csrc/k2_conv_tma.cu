@@ -28,6 +28,7 @@ struct TmaConvArgs {
     int planar_C, planar_accumulate, planar_fold;
     float* pool_dst;           // persistent kernel, even H and W: also writes MeanPool((2,2)) of the output, [B][H/2][W/2][Cout_p]
     int pool_rnd;              // round the pooled values to TF32 (they feed the next tensor-core conv)
+    uint32_t* mask_dst;        // pool-only mode (dst == NULL, pool_dst set): sign bits of the activation, word [pixel][Cout_p / 32]
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -512,9 +513,9 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, float4 v) {
 }
 // One 32-column slab of one accumulator row: bias, leaky ReLU as max(v, v * slope) (0 <= slope <= 1), optional addend, then
 // eight 16 B shared-memory stores at the 128B-swizzled chunk positions of this row.
-template <bool ADD, bool POOL>
+template <bool ADD, bool POOL, bool STORE = true>
 __device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* bs, float slope, const float* addp, uint32_t st_row, int sw,
-                                         float* poolp, int pool_rnd) {
+                                         float* poolp, int pool_rnd, uint32_t* maskw = nullptr) {
     float4 av[ADD ? 8 : 1];
     if (ADD) {
 #pragma unroll
@@ -533,8 +534,18 @@ __device__ __forceinline__ void epi_slab(const uint32_t (&r)[32], const float* b
         o[k].z = fmaxf(o[k].z, o[k].z * slope); o[k].w = fmaxf(o[k].w, o[k].w * slope);
         if (ADD) { o[k].x += av[k].x; o[k].y += av[k].y; o[k].z += av[k].z; o[k].w += av[k].w; }
     }
+    if (STORE) {
 #pragma unroll
-    for (int k = 0; k < 8; k++) st_shared_v4(st_row + (uint32_t)((k ^ sw) << 4), o[k]);
+        for (int k = 0; k < 8; k++) st_shared_v4(st_row + (uint32_t)((k ^ sw) << 4), o[k]);
+    } else {
+        // the full-resolution activation is not kept: only the sign of every element (what the backward pass needs of it)
+        uint32_t bits = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            bits |= (o[k].x > 0.f ? 1u : 0u) << (4 * k) | (o[k].y > 0.f ? 1u : 0u) << (4 * k + 1) | (o[k].z > 0.f ? 1u : 0u) << (4 * k + 2) |
+                    (o[k].w > 0.f ? 1u : 0u) << (4 * k + 3);
+        if (maskw) *maskw = bits;
+    }
     if (POOL) {
         // MeanPool((2,2)): tile row = h * 8 + w, so the 2 x 2 window of an even (h, w) is lanes {l, l^1, l^8, l^9} of this warp
 #pragma unroll
@@ -592,7 +603,28 @@ __device__ __forceinline__ void epi_tile(const TmaConvArgs& p, EpiCtx& e, uint32
             }
         }
     }
-    if (p.dst) {
+    if (!p.dst && p.pool_dst) {
+        // pool-only mode (encoder convs): MeanPool of the tile goes to pool_dst, the activation itself leaves only its sign bits
+        float* poolp = (pv && (e.lane & 9) == 0)
+                           ? p.pool_dst + ((((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * p.Cout_p + n0) : nullptr;
+        uint32_t* maskp = (p.mask_dst && pv) ? p.mask_dst + m * (size_t)(p.Cout_p >> 5) + (n0 >> 5) : nullptr;
+        uint32_t r[32];
+        tmem_ld16(lane_addr, *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+        tmem_ld16(lane_addr + 16u, *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+#pragma unroll 1
+        for (int sl = 0; sl < BN / 32; sl++) {
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            const int nl = sl * 32;
+            epi_slab<false, true, false>(r, &e.bias_s[n0 + nl], e.slope_eff, nullptr, 0u, 0, poolp ? poolp + nl : nullptr, p.pool_rnd,
+                                         maskp ? maskp + sl : nullptr);
+            if (sl + 1 < BN / 32) {
+                tmem_ld16(lane_addr + (uint32_t)(nl + 32), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                tmem_ld16(lane_addr + (uint32_t)(nl + 48), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        mbar_arrive(tempty);
+    } else if (p.dst) {
         const float* addp = (p.addend && pv) ? p.addend + m * p.Cout_p + n0 : nullptr;
         float* poolp = (p.pool_dst && pv && (e.lane & 9) == 0)
                            ? p.pool_dst + ((((size_t)b * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1)) * p.Cout_p + n0) : nullptr;
@@ -1071,8 +1103,9 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = a.planar_fold;
     DC_REQUIRE(!a.planar_fold || (a.planar_out && a.planar_C <= 8 && a.Cout_p >= 16), DINCAE_EINVAL, "conv3x3_persist: planar_fold needs a planar output of at most 8 channels");
-    p.pool_dst = a.pool_dst; p.pool_rnd = ctx->tf32_acts ? 1 : 0;
+    p.pool_dst = a.pool_dst; p.pool_rnd = ctx->tf32_acts ? 1 : 0; p.mask_dst = a.mask_dst;
     DC_REQUIRE(!a.pool_dst || k2_conv_fuses_pool(a), DINCAE_EINVAL, "conv3x3_persist: pool fusion needs even H, W, a leaky slope in [0,1) and no addend");
+    DC_REQUIRE(!a.mask_dst || (a.pool_dst && !a.dst && a.act == ACT_RELU), DINCAE_EINVAL, "conv3x3_persist: the sign mask belongs to the pool-only mode");
     int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
     static const int tune_bn = dc_env_int("DINCAE_TUNE_BN", 0), tune_bs = dc_env_int("DINCAE_TUNE_BSTAGES", 0),
                      tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
@@ -1196,7 +1229,7 @@ static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
     DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
-    p.pool_dst = nullptr; p.pool_rnd = 0;
+    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
     if (a.Cout_p % 256 == 0) HALO_LAUNCH(256, 2, 3);
@@ -1231,7 +1264,7 @@ static bool persist_selected(const ConvArgs& a) {
 // even H and W so that no window straddles the padding, activation in the max(v, v*slope) form, NHWC output present)
 bool k2_conv_fuses_pool(const ConvArgs& a) {
     static const int off = dc_env_int("DINCAE_NO_POOL_FUSION", 0);
-    return !off && k2_conv_tma_eligible(a) && persist_selected(a) && a.dst != nullptr && a.addend == nullptr && (a.H % 2) == 0 && (a.W % 2) == 0 &&
+    return !off && k2_conv_tma_eligible(a) && persist_selected(a) && a.planar_out == nullptr && a.addend == nullptr && (a.H % 2) == 0 && (a.W % 2) == 0 &&
            a.B * a.H * a.W > 0 && (a.act != ACT_RELU || (a.slope >= 0.f && a.slope < 1.f));
 }
 bool k2_conv_tma_eligible(const ConvArgs& a) {
@@ -1256,7 +1289,7 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
     DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
-    p.pool_dst = nullptr; p.pool_rnd = 0;
+    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
     if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
@@ -2353,7 +2386,7 @@ extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const f
     p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
     p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
     p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0; p.planar_fold = 0;
-    p.pool_dst = nullptr; p.pool_rnd = 0;
+    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
     alignas(64) CUtensorMap tmA, tmB;
     DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
     if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);

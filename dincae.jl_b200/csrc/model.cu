@@ -77,7 +77,7 @@ int32_t dec_source(dincae_model* M, int c, int l, int B, bool materialise, ConvS
     return DINCAE_OK;
 }
 
-int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
+int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B, bool train) {
     dincae_ctx* ctx = M->ctx;
     ChainBufs& cb = M->cb[c];
     const int L = M->L;
@@ -95,9 +95,17 @@ int32_t chain_forward(dincae_model* M, int c, const float* d_xin, int B) {
         a.in_real_C = e.split_mode == 1 ? 2 * e.Cin : e.Cin;                               // channels past this are zero padding
         a.act = ACT_RELU; a.slope = slope; a.addend = nullptr; a.dst = cb.A[l];
         a.work_flops = cflops(e, B, M->Hl[l], M->Wl[l]);
-        a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
-        const bool fuse_pool = k2_conv_fuses_pool(a);                             // even H, W on the tcgen05 path: the conv epilogue pools
-        a.pool_dst = fuse_pool ? cb.X[l + 1] : nullptr;
+        const bool fuse_pool = cb.MK[l] != nullptr;                               // even H, W on the tcgen05 path: the conv epilogue pools
+        if (fuse_pool) {
+            // relu(conv) itself is never written: the pooled tensor feeds the next level, the backward pass needs only its sign
+            // (one bit per element, and not even that for a pure forward pass)
+            a.pool_dst = cb.X[l + 1];
+            a.mask_dst = train ? cb.MK[l] : nullptr;
+            a.work_bytes = 4.0 * ((double)B * M->Hl[l] * M->Wl[l] * (e.Cin + (train ? e.Cout / 32.0 : 0.0)) + (double)B * M->Hl[l + 1] * M->Wl[l + 1] * e.Cout + 9.0 * e.Cin * e.Cout);
+            DC_REQUIRE(k2_conv_fuses_pool(a), DINCAE_EINVAL, "chain_forward: level %d was planned with a fused pool", l);
+        } else {
+            a.work_bytes = cbytes(e, B, M->Hl[l], M->Wl[l]);
+        }
         DC_TRY(k2_conv(ctx, a));                                                   // Conv(..., relu, pad=1), src/model.jl:267
         if (!fuse_pool) DC_TRY(k2_pool(ctx, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, cb.X[l + 1]));   // MeanPool, :268
     }
@@ -266,7 +274,8 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         const LayerInfo& e = M->enc[c][l];
         int ecolblocks = 0;
         float* ecolpart = colpart_alloc(M, (int64_t)B * M->Hl[l] * M->Wl[l] * (e.Cout_p / 4), e.Cout_p, &ecolblocks);
-        DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l], ecolpart));
+        if (cb.MK[l]) DC_TRY(k2_poolbwd_mask(ctx, xg, cb.MK[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l], ecolpart));
+        else DC_TRY(k2_poolbwd(ctx, xg, cb.A[l], B, M->Hl[l], M->Wl[l], e.Cout_p, slope, M->GC[l], ecolpart));
         WgradArgs wa{};
         wa.in = ConvSrc{cb.X[l], nullptr, SRC_DIRECT, M->Hl[l], M->Wl[l], e.Cin_pe};
         wa.B = B; wa.H = M->Hl[l]; wa.W = M->Wl[l]; wa.gout = M->GC[l]; wa.Cout_p = e.Cout_p;
@@ -558,10 +567,10 @@ int32_t download_internal(dincae_model* M, const float* src, float* flux) {
 
 }  // namespace
 
-int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool) {
+int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool train) {
     M->ctx->tf32_acts = M->wK != nullptr;
     if (M->wK) DC_TRY(ensure_wT(M));        // the tensor-core forward reads the K-major TF32 weight copy
-    for (int c = 0; c < M->nchains; c++) DC_TRY(chain_forward(M, c, d_xin, B));
+    for (int c = 0; c < M->nchains; c++) DC_TRY(chain_forward(M, c, d_xin, B, train));
     return DINCAE_OK;
 }
 
@@ -681,7 +690,11 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
         memset(&cb, 0, sizeof(cb));
         want((void**)&cb.X[0], act(0, M->enc[c][0].Cin_pe));
         for (int l = 0; l < L; l++) {
-            want((void**)&cb.A[l], act(l, M->enc[c][l].Cout_p));
+            // tensor-core modes, even level size, ReLU-type activation: the epilogue pools and keeps sign bits instead of A[l]
+            const bool pool_only = tc_mode && (M->Hl[l] % 2) == 0 && (M->Wl[l] % 2) == 0 && cfg->leaky_slope >= 0.f && cfg->leaky_slope < 1.f &&
+                                   dc_env_int("DINCAE_NO_POOL_FUSION", 0) == 0;
+            if (pool_only) want((void**)&cb.MK[l], sizeof(uint32_t) * Bm * M->Hl[l] * M->Wl[l] * (M->enc[c][l].Cout_p / 32));
+            else want((void**)&cb.A[l], act(l, M->enc[c][l].Cout_p));
             want((void**)&cb.X[l + 1], act(l + 1, M->enc[c][l].Cout_p));
             if (l >= 1) want((void**)&cb.R[l], act(l, M->dec[c][l].Cout_p));
             if (bil) want((void**)&cb.U[l], act(l, M->dec[c][l].Cin_pe));

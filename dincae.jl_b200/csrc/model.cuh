@@ -23,7 +23,8 @@ struct LayerInfo {
 
 struct ChainBufs {
     float* X[DINCAE_MAX_LEVELS + 1];   // X[l]: input of level l (X[0] = packed input), NHWC
-    float* A[DINCAE_MAX_LEVELS];       // relu(conv_enc_l)
+    float* A[DINCAE_MAX_LEVELS];       // relu(conv_enc_l); NULL where the conv epilogue pools and keeps only the sign bits MK[l]
+    uint32_t* MK[DINCAE_MAX_LEVELS];   // sign bits of relu(conv_enc_l), word [pixel][Cout_p / 32] (levels with the fused pool)
     float* R[DINCAE_MAX_LEVELS];       // relu(conv_dec_l), l >= 1
     float* U[DINCAE_MAX_LEVELS];       // bilinear only: materialised upsampled input of conv_dec_l
     float* RAW;                        // planar (W,H,2*nout,B): raw chain output
