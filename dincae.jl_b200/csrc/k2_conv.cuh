@@ -100,8 +100,6 @@ struct ConvSmallArgs {
 };
 
 int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a);        // dispatches to the tcgen05 kernel when eligible
-bool k2_conv_tc_eligible(const ConvArgs& a);
-int32_t k2_conv_tc(dincae_ctx* ctx, const ConvArgs& a);
 bool k2_conv_tma_eligible(const ConvArgs& a);
 bool k2_conv_fuses_pool(const ConvArgs& a);            // k2_conv(a) can also write MeanPool((2,2)) of its output to a.pool_dst
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a);

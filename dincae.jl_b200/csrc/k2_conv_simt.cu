@@ -1,7 +1,7 @@
 // K2 (FP32 CUDA-core path): implicit-GEMM 3x3 convolution, its weight gradient and the
 // element-wise level operators.  This is the exact-arithmetic path (DINCAE_PREC_FP32) and the
 // path for the HBM-bound edge convolutions (Cin <= 16 or Cout = 2*noutput); the tensor-core
-// (tcgen05) implicit GEMM for the wide middle layers lives in k2_conv_tc.cu.
+// (tcgen05) implicit GEMMs live in k2_conv_tma.cu.
 #include "k2_conv.cuh"
 
 namespace {
@@ -908,7 +908,6 @@ int32_t k2_conv(dincae_ctx* ctx, const ConvArgs& a) {
     if (Mtot == 0) return DINCAE_OK;
     if (k2_conv_tma_eligible(a)) return k2_conv_tma(ctx, a);
     DC_REQUIRE(a.planar_out == nullptr, DINCAE_EUNSUPPORTED, "k2_conv: planar output needs the TMA tensor-core kernel (driver without cuTensorMapEncodeTiled?)");
-    if (k2_conv_tc_eligible(a)) return k2_conv_tc(ctx, a);
     int Kpad = dc_round_up(9 * a.in.C, 16);
     int nchunks = Kpad / 16;
     DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)Mtot, a.work_bytes);

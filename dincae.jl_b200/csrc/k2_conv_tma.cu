@@ -112,127 +112,6 @@ __device__ __forceinline__ uint64_t make_desc_k_sw128(uint32_t saddr) {
 }
 __device__ __forceinline__ float act_apply(float v, int act, float slope) { return (act == ACT_RELU && v < 0.f) ? v * slope : v; }
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(128) conv3x3_tma(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int A_BYTES = TM_BM * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
-    __shared__ uint64_t bar_full[STAGES];
-    __shared__ uint64_t bar_empty[STAGES];
-    __shared__ uint64_t bar_done;
-    __shared__ uint32_t tmem_base_s;
-
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const uint32_t smem_base = smem_u32(smem);
-    const int t = threadIdx.x, warp = t >> 5;
-    const int n0 = blockIdx.y * BN;
-    const int patches = p.ptx * p.pty;
-    const int b = blockIdx.x / patches;
-    const int pr = blockIdx.x - b * patches;
-    const int y0 = (pr / p.ptx) * p.PH, x0 = (pr - (pr / p.ptx) * p.ptx) * p.PW;
-    const int nkc = p.Cin_p / TM_KC;
-    const int nchunks = 9 * nkc;
-
-    if (t == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
-#pragma unroll
-        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-        mbar_init(&bar_done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
-
-    if (t == 0) {
-        // ===== TMA producer =====
-        for (int i = 0; i < nchunks; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
-            const int tap = i / nkc, kc = i - tap * nkc;
-            const int ky = tap / 3, kx = tap - ky * 3;
-            uint8_t* sa = smem + (size_t)s * STAGE_BYTES;
-            mbar_expect_tx(&bar_full[s], (uint32_t)STAGE_BYTES);
-            tma_load_4d(sa, &tmA, &bar_full[s], kc * TM_KC, x0 + kx - 1, y0 + ky - 1, b);     // OOB -> zeros = conv padding
-            tma_load_2d(sa + A_BYTES, &tmB, &bar_full[s], tap * p.Cin_p + kc * TM_KC, n0);
-        }
-    } else if (t == 32) {
-        // ===== MMA issuer =====
-        for (int i = 0; i < nchunks; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint64_t da = make_desc_k_sw128(smem_base + (uint32_t)(s * STAGE_BYTES));
-            const uint64_t db = make_desc_k_sw128(smem_base + (uint32_t)(s * STAGE_BYTES + A_BYTES));
-#pragma unroll
-            for (int k = 0; k < TM_KC / 8; k++)
-                umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (i | k) != 0 ? 1u : 0u);
-            umma_commit(&bar_empty[s]);
-        }
-        umma_commit(&bar_done);
-    }
-    __syncwarp();
-    mbar_wait(&bar_done, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-
-    // ===== epilogue: thread t <-> TMEM lane t <-> patch pixel (t / PW, t % PW)
-    const int h = t / p.PW, w = t - h * p.PW;
-    const int y = y0 + h, x = x0 + w;
-    const bool pv = y < p.H && x < p.W;
-    const size_t m = ((size_t)b * p.H + y) * p.W + x;
-    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-    for (int cb = 0; cb < BN; cb += 16) {
-        uint32_t r[16];
-        tmem_ld16(lane_addr + (uint32_t)cb, r);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        const int n = n0 + cb;
-        if (pv && p.planar_out && n < p.planar_C) {
-            // planar (WHCN) output of the first planar_C channels: threads of a warp = consecutive x of one patch row -> coalesced
-#pragma unroll
-            for (int q = 0; q < 16; q++) {
-                const int co = n + q;
-                if (co < p.planar_C) {
-                    float v = __uint_as_float(r[q]) + (p.bias ? __ldg(p.bias + co) : 0.f);
-                    v = act_apply(v, p.act, p.slope);
-                    const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
-                    p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
-                }
-            }
-        }
-        if (pv && p.dst && n < p.Cout_p) {
-            const size_t off = m * p.Cout_p + n;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                float4 o;
-                o.x = __uint_as_float(r[4 * q + 0]); o.y = __uint_as_float(r[4 * q + 1]);
-                o.z = __uint_as_float(r[4 * q + 2]); o.w = __uint_as_float(r[4 * q + 3]);
-                if (p.bias) {
-                    float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * q));
-                    o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
-                }
-                o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
-                o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
-                if (p.addend) {
-                    float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * q));
-                    o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
-                }
-                *reinterpret_cast<float4*>(p.dst + off + 4 * q) = o;
-            }
-        }
-        if (!p.dst && n + 16 >= p.planar_C) break;       // planar-only output: the remaining accumulator columns are not needed
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
-}
-
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
@@ -292,8 +171,6 @@ int32_t make_tmap_w3(CUtensorMap* m, const float* ptr, int Cin_p, int rows, int 
     return DINCAE_OK;
 }
 
-template <int BN, int STAGES>
-constexpr int tm_smem_bytes() { return STAGES * (TM_BM * 128 + BN * 128) + 1024; }
 
 }  // namespace
 
@@ -319,137 +196,6 @@ __device__ __forceinline__ uint64_t make_desc_k_sw128_halo(uint32_t saddr, int u
     return d;
 }
 
-template <int BN, int ASTAGES, int BSTAGES>
-__global__ void __launch_bounds__(128) conv3x3_halo(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, TmaConvArgs p, int use_base_offset) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int B_BYTES = BN * 128;
-    __shared__ uint64_t bar_fullA[ASTAGES], bar_emptyA[ASTAGES], bar_fullB[BSTAGES], bar_emptyB[BSTAGES];
-    __shared__ uint64_t bar_done;
-    __shared__ uint32_t tmem_base_s;
-
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* smemB = smem + ASTAGES * HL_A_STRIDE;
-    const uint32_t smemA_u = smem_u32(smem), smemB_u = smem_u32(smemB);
-    const int t = threadIdx.x, warp = t >> 5;
-    const int n0 = blockIdx.y * BN;
-    const int patches = p.ptx * p.pty;
-    const int b = blockIdx.x / patches;
-    const int pr = blockIdx.x - b * patches;
-    const int y0 = (pr / p.ptx) * HL_PH, x0 = (pr - (pr / p.ptx) * p.ptx) * HL_PW;
-    const int nkc = p.Cin_p / TM_KC;
-
-    if (t == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
-#pragma unroll
-        for (int s = 0; s < ASTAGES; s++) { mbar_init(&bar_fullA[s], 1); mbar_init(&bar_emptyA[s], 1); }
-#pragma unroll
-        for (int s = 0; s < BSTAGES; s++) { mbar_init(&bar_fullB[s], 1); mbar_init(&bar_emptyB[s], 1); }
-        mbar_init(&bar_done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(TM_BM >> 4) << 24);
-
-    if (t == 0) {
-        // ===== TMA producer =====
-        int ib = 0;
-        for (int kc = 0; kc < nkc; kc++) {
-            const int sa = kc % ASTAGES, ua = kc / ASTAGES;
-            if (ua > 0) mbar_wait(&bar_emptyA[sa], (uint32_t)((ua - 1) & 1));
-            mbar_expect_tx(&bar_fullA[sa], (uint32_t)HL_A_BYTES);
-            tma_load_4d(smem + (size_t)sa * HL_A_STRIDE, &tmA, &bar_fullA[sa], kc * TM_KC, x0 - 1, y0 - 1, b);   // OOB -> zeros = conv padding
-            for (int tap = 0; tap < 9; tap++, ib++) {
-                const int sb = ib % BSTAGES, ub = ib / BSTAGES;
-                if (ub > 0) mbar_wait(&bar_emptyB[sb], (uint32_t)((ub - 1) & 1));
-                mbar_expect_tx(&bar_fullB[sb], (uint32_t)B_BYTES);
-                tma_load_2d(smemB + (size_t)sb * B_BYTES, &tmB, &bar_fullB[sb], tap * p.Cin_p + kc * TM_KC, n0);
-            }
-        }
-    } else if (t == 32) {
-        // ===== MMA issuer =====
-        int ib = 0;
-        for (int kc = 0; kc < nkc; kc++) {
-            const int sa = kc % ASTAGES, ua = kc / ASTAGES;
-            mbar_wait(&bar_fullA[sa], (uint32_t)(ua & 1));
-            for (int tap = 0; tap < 9; tap++, ib++) {
-                const int sb = ib % BSTAGES, ub = ib / BSTAGES;
-                mbar_wait(&bar_fullB[sb], (uint32_t)(ub & 1));
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const int dy = tap / 3, dx = tap - dy * 3;
-                const uint32_t a_addr = smemA_u + (uint32_t)(sa * HL_A_STRIDE + (dy * HL_HW + dx) * 128);
-                const uint64_t da = make_desc_k_sw128_halo(a_addr, use_base_offset);
-                const uint64_t db = make_desc_k_sw128(smemB_u + (uint32_t)(sb * B_BYTES));
-#pragma unroll
-                for (int k = 0; k < TM_KC / 8; k++)
-                    umma_tf32(tmem_d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), IDESC, (kc | tap | k) != 0 ? 1u : 0u);
-                umma_commit(&bar_emptyB[sb]);
-            }
-            umma_commit(&bar_emptyA[sa]);
-        }
-        umma_commit(&bar_done);
-    }
-    __syncwarp();
-    mbar_wait(&bar_done, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-
-    const int h = t / HL_PW, w = t - h * HL_PW;
-    const int y = y0 + h, x = x0 + w;
-    const bool pv = y < p.H && x < p.W;
-    const size_t m = ((size_t)b * p.H + y) * p.W + x;
-    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-    for (int cb = 0; cb < BN; cb += 16) {
-        uint32_t r[16];
-        tmem_ld16(lane_addr + (uint32_t)cb, r);
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        const int n = n0 + cb;
-        if (pv && p.planar_out && n < p.planar_C) {
-#pragma unroll
-            for (int q = 0; q < 16; q++) {
-                const int co = n + q;
-                if (co < p.planar_C) {
-                    float v = __uint_as_float(r[q]) + (p.bias ? __ldg(p.bias + co) : 0.f);
-                    v = act_apply(v, p.act, p.slope);
-                    const size_t po = (((size_t)b * p.planar_C + co) * p.H + y) * p.W + x;
-                    p.planar_out[po] = p.planar_accumulate ? p.planar_out[po] + v : v;
-                }
-            }
-        }
-        if (pv && p.dst && n < p.Cout_p) {
-            const size_t off = m * p.Cout_p + n;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                float4 o;
-                o.x = __uint_as_float(r[4 * q + 0]); o.y = __uint_as_float(r[4 * q + 1]);
-                o.z = __uint_as_float(r[4 * q + 2]); o.w = __uint_as_float(r[4 * q + 3]);
-                if (p.bias) {
-                    float4 bv = __ldg(reinterpret_cast<const float4*>(p.bias + n + 4 * q));
-                    o.x += bv.x; o.y += bv.y; o.z += bv.z; o.w += bv.w;
-                }
-                o.x = act_apply(o.x, p.act, p.slope); o.y = act_apply(o.y, p.act, p.slope);
-                o.z = act_apply(o.z, p.act, p.slope); o.w = act_apply(o.w, p.act, p.slope);
-                if (p.addend) {
-                    float4 av = __ldg(reinterpret_cast<const float4*>(p.addend + off + 4 * q));
-                    o.x += av.x; o.y += av.y; o.z += av.z; o.w += av.w;
-                }
-                *reinterpret_cast<float4*>(p.dst + off + 4 * q) = o;
-            }
-        }
-        if (!p.dst && n + 16 >= p.planar_C) break;
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
-}
-
 int32_t make_tmap_halo(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
     EncodeTiledFn enc = get_encode();
     DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
@@ -463,8 +209,6 @@ int32_t make_tmap_halo(CUtensorMap* m, const float* ptr, int C, int W, int H, in
     return DINCAE_OK;
 }
 
-template <int BN, int AS, int BS>
-constexpr int hl_smem_bytes() { return AS * HL_A_STRIDE + BS * BN * 128 + 1024; }
 
 }  // namespace
 
@@ -1107,11 +851,8 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     DC_REQUIRE(!a.pool_dst || k2_conv_fuses_pool(a), DINCAE_EINVAL, "conv3x3_persist: pool fusion needs even H, W, a leaky slope in [0,1) and no addend");
     DC_REQUIRE(!a.mask_dst || (a.pool_dst && !a.dst && a.act == ACT_RELU), DINCAE_EINVAL, "conv3x3_persist: the sign mask belongs to the pool-only mode");
     int bn = a.Cout_p % 256 == 0 ? 256 : (a.Cout_p % 128 == 0 ? 128 : (a.Cout_p % 64 == 0 ? 64 : 32));
-    static const int tune_bn = dc_env_int("DINCAE_TUNE_BN", 0), tune_bs = dc_env_int("DINCAE_TUNE_BSTAGES", 0),
-                     tune_as = dc_env_int("DINCAE_TUNE_ASTAGES", 0), tune_os = dc_env_int("DINCAE_TUNE_OSTAGES", 0);
     const int m_tiles = p.ptx * p.pty * a.B;
     while (bn > 64 && m_tiles * (a.Cout_p / bn) < ctx->num_sms) bn /= 2;     // few pixel tiles (deep levels): split N so every SM has work
-    if (tune_bn > 0 && tune_bn < bn) bn = tune_bn;
     const int nkc = a.in.C / TM_KC;
     PersistArgs q;
     q.ntiles_n = a.Cout_p / bn;
@@ -1125,13 +866,12 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     // one staging slab (the second CTA hides the bubbles between tiles).  Everything else: one CTA per SM with two epilogue
     // groups; resident weights if they fit beside two activation stages, else a ring of weight stages; whatever is left
     // deepens the activation ring (TMA latency is 2-3k cycles).
-    static const int tune_groups = dc_env_int("DINCAE_TUNE_GROUPS", 0), tune_tps = dc_env_int("DINCAE_TUNE_TPS", 0);
     q.tps = 1;
     const int static_smem = 5120;                     // barriers + bias (~3.2 KB) and the 1 KB alignment slack, rounded up
     const int small_plan = 2 * HL_A_STRIDE + resident_bytes + (a.dst ? 16384 : 0) + 1024;
-    const bool two_per_sm = q.ntiles_n == 1 && 2 * (small_plan + static_smem) <= 227 * 1024 && 4 * bn <= 512 && tune_groups != 2;
+    const bool two_per_sm = q.ntiles_n == 1 && 2 * (small_plan + static_smem) <= 227 * 1024 && 4 * bn <= 512;
     int smem, per_sm;
-    if (two_per_sm || tune_groups == 1) {
+    if (two_per_sm) {
         q.groups = 1; q.b_resident = 1; q.b_stages = 0; q.a_stages = 2; q.o_stages = a.dst ? 1 : 0;
         DC_REQUIRE(q.ntiles_n == 1 && small_plan + static_smem <= 227 * 1024, DINCAE_EUNSUPPORTED, "conv3x3_persist: one-group plan does not fit");
         smem = small_plan;
@@ -1140,39 +880,34 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
         q.groups = 2;
         const int budget = 227 * 1024 - static_smem - 1024;
         q.o_stages = a.dst ? 2 : 0;
-        if (tune_os > 0 && a.dst) q.o_stages = tune_os > PS_MAX_O ? PS_MAX_O : tune_os;
         int left = budget - 2 * q.o_stages * 16384;
         q.b_resident = (q.ntiles_n == 1 && resident_bytes + 2 * HL_A_STRIDE <= left) ? 1 : 0;
         if (q.b_resident) {
             q.b_stages = 0;
             left -= resident_bytes;
         } else {
-            q.tps = tune_tps > 0 ? tune_tps : 3;                 // one kernel row of taps per weight stage ...
+            q.tps = 3;                                           // one kernel row of taps per weight stage ...
             int bs = (left - 2 * HL_A_STRIDE) / (q.tps * bbytes);
             if (bs < 2) { q.tps = 1; bs = (left - 2 * HL_A_STRIDE) / bbytes; }      // ... unless two such stages do not fit
             if (bs > PS_MAX_B) bs = PS_MAX_B;
-            if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
             DC_REQUIRE(bs >= 2, DINCAE_EUNSUPPORTED, "conv3x3_persist: no room for two weight stages (BN=%d)", bn);
             q.b_stages = bs;
             left -= bs * q.tps * bbytes;
         }
         q.a_stages = left / HL_A_STRIDE;
         if (q.a_stages > PS_MAX_A) q.a_stages = PS_MAX_A;
-        if (tune_as > 0 && tune_as < q.a_stages) q.a_stages = tune_as;
         smem = q.a_stages * HL_A_STRIDE + (q.b_resident ? resident_bytes : q.b_stages * q.tps * bbytes) + 2 * q.o_stages * 16384 + 1024;
         per_sm = 1;
     }
     // paired tiles: streamed weights (deep levels), two pixel tiles per CTA share every weight stage
-    static const int tune_pair = dc_env_int("DINCAE_TUNE_PAIR", 1);
-    if (tune_pair && q.groups == 2 && !q.b_resident && bn <= 128 && m_tiles >= 2 && (tune_pair == 2 || (int)dc_cdiv(m_tiles, 2) * q.ntiles_n >= (ctx->num_sms * 3) / 4)) {
+    if (q.groups == 2 && !q.b_resident && bn <= 128 && m_tiles >= 2 && ((int)dc_cdiv(m_tiles, 2) * q.ntiles_n >= (ctx->num_sms * 3) / 4)) {
         const int budget = 227 * 1024 - static_smem - 1024;
-        q.o_stages = a.dst ? ((tune_os > 0) ? (tune_os > PS_MAX_O ? PS_MAX_O : tune_os) : 1) : 0;
+        q.o_stages = a.dst ? 1 : 0;
         int left = budget - 2 * q.o_stages * 16384 - 2 * (2 * HL_A_STRIDE);
-        q.tps = tune_tps > 0 ? tune_tps : 3;
+        q.tps = 3;
         int bs = left / (q.tps * bbytes);
         if (bs < 2) { q.tps = 1; bs = left / bbytes; }
         if (bs > PS_MAX_B) bs = PS_MAX_B;
-        if (tune_bs > 0 && tune_bs < bs) bs = tune_bs;
         if (bs >= 2) {
             q.b_stages = bs; q.a_stages = 2;
             left -= bs * q.tps * bbytes;
@@ -1203,99 +938,23 @@ static int32_t k2_conv_persist(dincae_ctx* ctx, const ConvArgs& a) {
     PERSIST_LAUNCH(32);
 }
 
-#define HALO_LAUNCH(BN_, AS_, BS_)                                                                                         \
-    do {                                                                                                                   \
-        auto conv3x3_halo_bn##BN_ = conv3x3_halo<BN_, AS_, BS_>;                                                           \
-        constexpr int smem = hl_smem_bytes<BN_, AS_, BS_>();                                                               \
-        static bool attr_set = false;                                                                                      \
-        if (!attr_set) {                                                                                                   \
-            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_halo_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));  \
-            attr_set = true;                                                                                               \
-        }                                                                                                                  \
-        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
-        dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
-        DC_LAUNCH(ctx, conv3x3_halo_bn##BN_, grid, 128, smem, tmA, tmB, p, halo_mode - 1);                                 \
-        DC_CHECK_LAUNCH();                                                                                                 \
-        return DINCAE_OK;                                                                                                  \
-    } while (0)
-
-static int32_t k2_conv_halo(dincae_ctx* ctx, const ConvArgs& a, int halo_mode) {
-    TmaConvArgs p;
-    p.B = a.B; p.H = a.H; p.W = a.W;
-    p.PW = HL_PW; p.PH = HL_PH;
-    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
-    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
-    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
-    DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
-    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
-    alignas(64) CUtensorMap tmA, tmB;
-    DC_TRY(make_tmap_halo(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B));
-    if (a.Cout_p % 256 == 0) HALO_LAUNCH(256, 2, 3);
-    if (a.Cout_p % 128 == 0) HALO_LAUNCH(128, 2, 4);
-    if (a.Cout_p % 64 == 0) HALO_LAUNCH(64, 2, 4);
-    HALO_LAUNCH(32, 2, 4);
-}
-
-#define TMA_LAUNCH(BN_, ST_)                                                                                               \
-    do {                                                                                                                   \
-        auto conv3x3_tma_bn##BN_ = conv3x3_tma<BN_, ST_>;                                                                  \
-        constexpr int smem = tm_smem_bytes<BN_, ST_>();                                                                    \
-        static bool attr_set = false;                                                                                      \
-        if (!attr_set) {                                                                                                   \
-            DC_CHECK_CUDA(cudaFuncSetAttribute(conv3x3_tma_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));   \
-            attr_set = true;                                                                                               \
-        }                                                                                                                  \
-        DC_TRY(make_tmap_w(&tmB, a.wgtK, a.ldk, a.Cout_p, BN_));                                                           \
-        dim3 grid((unsigned)(p.ptx * p.pty * a.B), (unsigned)(a.Cout_p / BN_));                                            \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
-        DC_LAUNCH(ctx, conv3x3_tma_bn##BN_, grid, 128, smem, tmA, tmB, p);                                                 \
-        DC_CHECK_LAUNCH();                                                                                                 \
-        return DINCAE_OK;                                                                                                  \
-    } while (0)
-
-static bool persist_selected(const ConvArgs& a) {
-    static int halo_mode = -1;
-    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
-    return halo_mode == 3 && (a.planar_out == nullptr || a.planar_C <= 16) && a.Cout_p <= 512;
-}
-// true when k2_conv() on these arguments can also emit MeanPool((2,2)) of its output into a.pool_dst (the persistent tcgen05 kernel,
-// even H and W so that no window straddles the padding, activation in the max(v, v*slope) form, NHWC output present)
+// true when k2_conv() on these arguments can also emit MeanPool((2,2)) of its output into a.pool_dst (even H and W so that no window
+// straddles the padding, activation in the max(v, v*slope) form, no residual add, NHWC or no full-resolution output)
 bool k2_conv_fuses_pool(const ConvArgs& a) {
     static const int off = dc_env_int("DINCAE_NO_POOL_FUSION", 0);
-    return !off && k2_conv_tma_eligible(a) && persist_selected(a) && a.planar_out == nullptr && a.addend == nullptr && (a.H % 2) == 0 && (a.W % 2) == 0 &&
+    return !off && k2_conv_tma_eligible(a) && a.planar_out == nullptr && a.addend == nullptr && (a.H % 2) == 0 && (a.W % 2) == 0 &&
            a.B * a.H * a.W > 0 && (a.act != ACT_RELU || (a.slope >= 0.f && a.slope < 1.f));
 }
+// the persistent tcgen05 kernel takes it; everything else (more than 512 output channels, a wide planar output, a fused
+// SIMT producer, no tensor-map encoder in the driver) goes to the FP32 CUDA-core kernel
 bool k2_conv_tma_eligible(const ConvArgs& a) {
     return a.wgtK != nullptr && a.in.mode == SRC_DIRECT && a.in.src1 == nullptr && (a.in.C % TM_KC) == 0 && (a.Cout_p % 32) == 0 &&
-           a.in_is_tf32 && get_encode() != nullptr;
+           a.in_is_tf32 && a.Cout_p <= PS_MAX_COUT && (a.planar_out == nullptr || a.planar_C <= 16) && get_encode() != nullptr;
 }
 
 int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
     if (a.B * a.H * a.W == 0) return DINCAE_OK;
-    // DINCAE_CONV_KERNEL: 0 = one activation box per tap; 1 = halo tile with shifted descriptors; 3 = persistent warp-specialised halo kernel (default)
-    static int halo_mode = -1;
-    if (halo_mode < 0) { const char* e = getenv("DINCAE_CONV_KERNEL"); halo_mode = e ? atoi(e) : 3; }
-    if (persist_selected(a)) return k2_conv_persist(ctx, a);
-    DC_REQUIRE(a.pool_dst == nullptr, DINCAE_EINVAL, "k2_conv_tma: pool fusion is only available in the persistent kernel");
-    if (halo_mode > 0) return k2_conv_halo(ctx, a, 1);
-    TmaConvArgs p;
-    p.B = a.B; p.H = a.H; p.W = a.W;
-    p.PW = a.W > 8 ? 16 : 8;
-    p.PH = TM_BM / p.PW;
-    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
-    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
-    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = a.planar_out; p.planar_C = a.planar_C; p.planar_accumulate = a.planar_accumulate; p.planar_fold = 0;
-    DC_REQUIRE(!a.planar_fold, DINCAE_EUNSUPPORTED, "planar_fold is only available in the persistent tcgen05 kernel");
-    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
-    alignas(64) CUtensorMap tmA, tmB;
-    DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
-    if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
-    if (a.Cout_p % 128 == 0) TMA_LAUNCH(128, 3);
-    if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
-    TMA_LAUNCH(32, 5);
+    return k2_conv_persist(ctx, a);
 }
 
 // =================================================================================================
@@ -1307,8 +966,6 @@ int32_t k2_conv_tma(dincae_ctx* ctx, const ConvArgs& a) {
 // pixels is split over CTAs and finished by a deterministic second-stage sum (no float atomics).
 namespace {
 
-constexpr int WG_KP = 32;             // pixels per stage (8 wide x 4 high)
-constexpr int WG_BLOCK = WG_KP * 128; // bytes of one 32-channel block of a stage
 
 struct WgradTmaArgs {
     int B, H, W;
@@ -1323,143 +980,7 @@ struct WgradTmaArgs {
 // MN-major TF32 operands must use the 128-byte swizzle with 32-byte atomicity (layout type SWIZZLE_128B_BASE32B,
 // Swizzle<2,5,2>: the 32-byte chunk index is XORed with the pixel-row index mod 4); its K atom is 4 rows (512 B), so one
 // K = 8 MMA spans two atoms SBO apart.  TMA writes the same pattern with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
-__device__ __forceinline__ uint64_t make_desc_mn_sw128(uint32_t saddr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
-    d |= (uint64_t)(WG_BLOCK >> 4) << 16;             // leading byte offset: next 32-channel block
-    d |= (uint64_t)(512 >> 4) << 32;                  // stride byte offset: next 4 pixel rows
-    d |= (uint64_t)1 << 46;
-    d |= (uint64_t)1 << 61;                           // SWIZZLE_128B_BASE32B
-    return d;
-}
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(128) wgrad_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int A_BYTES = 4 * WG_BLOCK, B_BYTES = (BN / 32) * WG_BLOCK, STAGE_BYTES = A_BYTES + B_BYTES;
-    __shared__ uint64_t bar_full[STAGES];
-    __shared__ uint64_t bar_empty[STAGES];
-    __shared__ uint64_t bar_done;
-    __shared__ uint32_t tmem_base_s;
-
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const uint32_t smem_base = smem_u32(smem);
-    const int t = threadIdx.x, warp = t >> 5;
-    const int split = blockIdx.x, m0 = blockIdx.y * 128;
-    const int ntiles = (p.n_ch + BN - 1) / BN;
-    const int tap = blockIdx.z / ntiles, n0 = (blockIdx.z - tap * ntiles) * BN;
-    const int ky = tap / 3, kx = tap - ky * 3;
-    const int64_t p_lo = (int64_t)split * p.patches_per_split;
-    int64_t p_hi = p_lo + p.patches_per_split;
-    if (p_hi > p.npatches) p_hi = p.npatches;
-    const int nst = (int)(p_hi - p_lo);
-    const int mblocks = min(4, (p.m_ch - m0) / 32), nblocks = min(BN / 32, (p.n_ch - n0) / 32);
-
-    // zero the channel blocks that no TMA box will ever fill (operand narrower than the MMA tile)
-    if (mblocks < 4 || nblocks < BN / 32) {
-        for (int s = 0; s < STAGES; s++) {
-            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-            for (int i = t; i < (4 - mblocks) * WG_BLOCK / 16; i += 128)
-                reinterpret_cast<float4*>(st + mblocks * WG_BLOCK)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int i = t; i < (BN / 32 - nblocks) * WG_BLOCK / 16; i += 128)
-                reinterpret_cast<float4*>(st + A_BYTES + nblocks * WG_BLOCK)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    if (t == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
-#pragma unroll
-        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-        mbar_init(&bar_done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)BN));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
-    // D = F32, A = B = TF32, both MN-major (bits 15, 16), N = BN, M = 128
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-
-    if (t == 0) {
-        // ===== TMA producer =====
-        const CUtensorMap* mapM = p.in_is_m ? &tmIn : &tmG;
-        const CUtensorMap* mapN = p.in_is_m ? &tmG : &tmIn;
-        const int sxM = p.in_is_m ? kx - 1 : 0, syM = p.in_is_m ? ky - 1 : 0;     // the tap shifts the `in` operand only
-        const int sxN = p.in_is_m ? 0 : kx - 1, syN = p.in_is_m ? 0 : ky - 1;
-        const int per_img = p.ptx * p.pty;
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
-            const int64_t pp = p_lo + i;
-            const int b = (int)(pp / per_img);
-            const int r = (int)(pp - (int64_t)b * per_img);
-            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
-            uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-            mbar_expect_tx(&bar_full[s], (uint32_t)((mblocks + nblocks) * WG_BLOCK));
-            for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * WG_BLOCK, mapM, &bar_full[s], m0 + j * 32, x0 + sxM, y0 + syM, b);
-            for (int j = 0; j < nblocks; j++) tma_load_4d(st + A_BYTES + j * WG_BLOCK, mapN, &bar_full[s], n0 + j * 32, x0 + sxN, y0 + syN, b);
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist) =====
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint64_t da = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES));
-            const uint64_t db = make_desc_mn_sw128(smem_base + (uint32_t)(s * STAGE_BYTES + A_BYTES));
-            if (elect_one_sync()) {
-                if (i == 0) umma_tf32(tmem_d, da, db, IDESC, 0u);
-                else umma_tf32_acc(tmem_d, da, db, IDESC);
-#pragma unroll
-                for (int k = 1; k < WG_KP / 8; k++)      // 8 pixel rows per MMA: advance by one 1024-byte atom
-                    umma_tf32_acc(tmem_d, da + (uint64_t)(64 * k), db + (uint64_t)(64 * k), IDESC);
-                umma_commit(&bar_empty[s]);
-                if (i == nst - 1) umma_commit(&bar_done);
-            }
-            __syncwarp();
-        }
-    }
-    __syncwarp();
-    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
-    const int mch = m0 + t;
-    if (nst > 0) {
-        mbar_wait(&bar_done, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    }
-    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-    for (int cb = 0; cb < BN; cb += 16) {
-        uint32_t r[16];
-        if (nst > 0) {
-            tmem_ld16(lane_addr + (uint32_t)cb, r);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        } else {
-#pragma unroll
-            for (int q = 0; q < 16; q++) r[q] = 0u;
-        }
-        if (mch < p.m_ch) {
-#pragma unroll
-            for (int q = 0; q < 16; q++) {
-                const int nch = n0 + cb + q;
-                if (nch < p.n_ch) {
-                    const int ci = p.in_is_m ? mch : nch, co = p.in_is_m ? nch : mch;
-                    out[((size_t)tap * p.Cin_p + ci) * p.Cout_p + co] = __uint_as_float(r[q]);
-                }
-            }
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)BN));
-}
-
-// dst[i] = sum over splits of partial[z][i].  Block = 32 consecutive outputs x 8 split groups: thread (c, zg) sums the splits
-// z = zg, zg+8, ... (4 loads in flight), the 8 group sums are combined in a fixed order -> deterministic second stage.
 __global__ void __launch_bounds__(256) reduce_splits_kernel(const float* __restrict__ partial, int splits, int64_t n, float* __restrict__ dst) {
     __shared__ float sh[8][32];
     const int c = threadIdx.x & 31, zg = threadIdx.x >> 5;
@@ -1561,20 +1082,10 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __rest
     }
 }
 // stage 2: one warp per column; lane l sums partials l, l+32, ... then a fixed-order shuffle tree
-__global__ void colsum_final_kernel(const float* __restrict__ part, int nblocks, int C, float* __restrict__ out) {
-    const int col = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (col >= C) return;
-    float s = 0.f;
-    for (int b = lane; b < nblocks; b += 32) s += part[(size_t)b * C + col];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
-    if (lane == 0) out[col] = s;
-}
 
 // Three taps per CTA (dx = -1, 0, +1 of one kernel row ky): the `in` operand is loaded once per patch as a (32 ch x 10 x 4)
 // box with a one-pixel halo in x; the three taps are three descriptor views of it (start shifted by dx pixel rows of 128 B,
 // the four 8-pixel k-steps one box row = 1280 B apart) feeding three TMEM accumulators, while the g box is shared.
-constexpr int WH_INBLK = 10 * 4 * 128;      // bytes of one 32-channel block of the `in` halo box
 __device__ __forceinline__ uint64_t make_desc_mn_sw128_lbo(uint32_t saddr, uint32_t lbo_bytes) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
@@ -1585,289 +1096,6 @@ __device__ __forceinline__ uint64_t make_desc_mn_sw128_lbo(uint32_t saddr, uint3
     return d;
 }
 
-template <int BN, int STAGES>
-__global__ void __launch_bounds__(128) wgrad_halo(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    constexpr int TCOLS = (3 * BN <= 128) ? 128 : (3 * BN <= 256 ? 256 : 512);
-    __shared__ uint64_t bar_full[STAGES];
-    __shared__ uint64_t bar_empty[STAGES];
-    __shared__ uint64_t bar_done;
-    __shared__ uint32_t tmem_base_s;
-
-    const int mblk_bytes = p.in_is_m ? WH_INBLK : WG_BLOCK, nblk_bytes = p.in_is_m ? WG_BLOCK : WH_INBLK;
-    const int a_bytes = 4 * mblk_bytes, stage_bytes = a_bytes + (BN / 32) * nblk_bytes;
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const uint32_t smem_base = smem_u32(smem);
-    const int t = threadIdx.x, warp = t >> 5;
-    const int split = blockIdx.x, m0 = blockIdx.y * 128;
-    const int ntiles = (p.n_ch + BN - 1) / BN;
-    const int ky = blockIdx.z / ntiles, n0 = (blockIdx.z - ky * ntiles) * BN;
-    const int64_t p_lo = (int64_t)split * p.patches_per_split;
-    int64_t p_hi = p_lo + p.patches_per_split;
-    if (p_hi > p.npatches) p_hi = p.npatches;
-    const int nst = (int)(p_hi - p_lo);
-    const int mblocks = min(4, (p.m_ch - m0) / 32), nblocks = min(BN / 32, (p.n_ch - n0) / 32);
-
-    if (mblocks < 4 || nblocks < BN / 32) {
-        for (int s = 0; s < STAGES; s++) {
-            uint8_t* st = smem + (size_t)s * stage_bytes;
-            for (int i = t; i < (4 - mblocks) * mblk_bytes / 16; i += 128)
-                reinterpret_cast<float4*>(st + mblocks * mblk_bytes)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int i = t; i < (BN / 32 - nblocks) * nblk_bytes / 16; i += 128)
-                reinterpret_cast<float4*>(st + a_bytes + nblocks * nblk_bytes)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    if (t == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
-#pragma unroll
-        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-        mbar_init(&bar_done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"((uint32_t)TCOLS));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-
-    if (t == 0) {
-        // ===== TMA producer =====
-        const int per_img = p.ptx * p.pty;
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
-            const int64_t pp = p_lo + i;
-            const int b = (int)(pp / per_img);
-            const int r = (int)(pp - (int64_t)b * per_img);
-            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
-            uint8_t* st = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&bar_full[s], (uint32_t)(mblocks * mblk_bytes + nblocks * nblk_bytes));
-            if (p.in_is_m) {
-                for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * mblk_bytes, &tmIn, &bar_full[s], m0 + j * 32, x0 - 1, y0 + ky - 1, b);
-                for (int j = 0; j < nblocks; j++) tma_load_4d(st + a_bytes + j * nblk_bytes, &tmG, &bar_full[s], n0 + j * 32, x0, y0, b);
-            } else {
-                for (int j = 0; j < mblocks; j++) tma_load_4d(st + j * mblk_bytes, &tmG, &bar_full[s], m0 + j * 32, x0, y0, b);
-                for (int j = 0; j < nblocks; j++) tma_load_4d(st + a_bytes + j * nblk_bytes, &tmIn, &bar_full[s], n0 + j * 32, x0 - 1, y0 + ky - 1, b);
-            }
-        }
-    } else if (warp == 1) {
-        // ===== MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist) =====
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t abase = smem_base + (uint32_t)(s * stage_bytes), bbase = abase + (uint32_t)a_bytes;
-            // descriptor bases once per stage; the 12 (dx, h) offsets are compile-time constants
-            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, (uint32_t)mblk_bytes), db0 = make_desc_mn_sw128_lbo(bbase, (uint32_t)nblk_bytes);
-            if (elect_one_sync()) {
-            if (p.in_is_m) {
-#pragma unroll
-                for (int dx = 0; dx < 3; dx++)
-#pragma unroll
-                    for (int h = 0; h < 4; h++) {       // one k-step = the 8 pixels of box row h
-                        const uint64_t da = da0 + (uint64_t)((dx * 128 + h * 1280) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
-                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, i != 0 ? 1u : 0u);
-                        else umma_tf32_acc(tmem_d + (uint32_t)(dx * BN), da, db, IDESC);
-                    }
-            } else {
-#pragma unroll
-                for (int dx = 0; dx < 3; dx++)
-#pragma unroll
-                    for (int h = 0; h < 4; h++) {
-                        const uint64_t da = da0 + (uint64_t)((h * 1024) >> 4), db = db0 + (uint64_t)((dx * 128 + h * 1280) >> 4);
-                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(dx * BN), da, db, IDESC, i != 0 ? 1u : 0u);
-                        else umma_tf32_acc(tmem_d + (uint32_t)(dx * BN), da, db, IDESC);
-                    }
-            }
-            umma_commit(&bar_empty[s]);
-            if (i == nst - 1) umma_commit(&bar_done);
-            }
-            __syncwarp();
-        }
-    }
-    __syncwarp();
-    float* out = p.partial + (size_t)split * 9 * p.Cin_p * p.Cout_p;
-    const int mch = m0 + t;
-    if (nst > 0) {
-        mbar_wait(&bar_done, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    }
-    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-    for (int dx = 0; dx < 3; dx++) {
-        const int tap = ky * 3 + dx;
-#pragma unroll 1
-        for (int cb = 0; cb < BN; cb += 16) {
-            uint32_t r[16];
-            if (nst > 0) {
-                tmem_ld16(lane_addr + (uint32_t)(dx * BN + cb), r);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            } else {
-#pragma unroll
-                for (int q = 0; q < 16; q++) r[q] = 0u;
-            }
-            if (mch < p.m_ch) {
-#pragma unroll
-                for (int q = 0; q < 16; q++) {
-                    const int nch = n0 + cb + q;
-                    if (nch < p.n_ch) {
-                        const int ci = p.in_is_m ? mch : nch, co = p.in_is_m ? nch : mch;
-                        out[((size_t)tap * p.Cin_p + ci) * p.Cout_p + co] = __uint_as_float(r[q]);
-                    }
-                }
-            }
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"((uint32_t)TCOLS));
-}
-
-int32_t make_tmap_inhalo(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
-    EncodeTiledFn enc = get_encode();
-    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
-    cuuint32_t box[4] = {32, 10, 4, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(in halo C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
-    return DINCAE_OK;
-}
-
-// Narrow layers (Cin_p = Cout_p = 32, the full-resolution edge convs): ALL nine taps in one CTA.  The `in` halo box
-// (32 ch x 10 x 6) of an 8x4 patch is loaded once; the three dx taps are stacked in the MMA M dimension by giving the
-// MN-major descriptor a leading-dimension offset of ONE pixel row (128 B): "channel block" j of the operand is simply the
-// same tile shifted by j pixels.  Three accumulators (one per ky) of 32 columns each; D lane = dx*32 + ci.
-constexpr int W32_IN_ROWS = 64;                   // 10*6 = 60 halo rows + 4 rows read (never used) by the 4th M block
-constexpr int W32_IN_BYTES = W32_IN_ROWS * 128, W32_STAGE = W32_IN_BYTES + WG_BLOCK;
-
-template <int STAGES>
-__global__ void __launch_bounds__(128) wgrad32_kernel(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmG, WgradTmaArgs p) {
-    extern __shared__ __align__(1024) uint8_t smem_raw[];
-    __shared__ uint64_t bar_full[STAGES];
-    __shared__ uint64_t bar_empty[STAGES];
-    __shared__ uint64_t bar_done;
-    __shared__ uint32_t tmem_base_s;
-    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    const uint32_t smem_base = smem_u32(smem);
-    const int t = threadIdx.x, warp = t >> 5;
-    const int split = blockIdx.x;
-    const int64_t p_lo = (int64_t)split * p.patches_per_split;
-    int64_t p_hi = p_lo + p.patches_per_split;
-    if (p_hi > p.npatches) p_hi = p.npatches;
-    const int nst = (int)(p_hi - p_lo);
-
-    // the 4 pad rows of every stage are read by the (discarded) 4th M block: keep them finite
-    for (int s = 0; s < STAGES; s++)
-        for (int i = t; i < 4 * 128 / 16; i += 128)
-            reinterpret_cast<float4*>(smem + (size_t)s * W32_STAGE + 60 * 128)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    if (t == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmIn)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmG)) : "memory");
-#pragma unroll
-        for (int s = 0; s < STAGES; s++) { mbar_init(&bar_full[s], 1); mbar_init(&bar_empty[s], 1); }
-        mbar_init(&bar_done, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(128u));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_d = tmem_base_s;
-    constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-
-    if (t == 0) {
-        const int per_img = p.ptx * p.pty;
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            if (u > 0) mbar_wait(&bar_empty[s], (uint32_t)((u - 1) & 1));
-            const int64_t pp = p_lo + i;
-            const int b = (int)(pp / per_img);
-            const int r = (int)(pp - (int64_t)b * per_img);
-            const int y0 = (r / p.ptx) * 4, x0 = (r - (r / p.ptx) * p.ptx) * 8;
-            uint8_t* st = smem + (size_t)s * W32_STAGE;
-            mbar_expect_tx(&bar_full[s], (uint32_t)(60 * 128 + WG_BLOCK));
-            tma_load_4d(st, &tmIn, &bar_full[s], 0, x0 - 1, y0 - 1, b);               // (32, 10, 6, 1) halo box
-            tma_load_4d(st + W32_IN_BYTES, &tmG, &bar_full[s], 0, x0, y0, b);         // (32, 8, 4, 1)
-        }
-    } else if (warp == 1) {
-        // MMA issuer: warp-uniform loop, one elected lane issues (see conv3x3_persist)
-        for (int i = 0; i < nst; i++) {
-            const int s = i % STAGES, u = i / STAGES;
-            mbar_wait(&bar_full[s], (uint32_t)(u & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t abase = smem_base + (uint32_t)(s * W32_STAGE);
-            const uint64_t da0 = make_desc_mn_sw128_lbo(abase, 128u);                 // M block j = the tile shifted by j pixel rows
-            const uint64_t db0 = make_desc_mn_sw128_lbo(abase + (uint32_t)W32_IN_BYTES, (uint32_t)WG_BLOCK);
-            if (elect_one_sync()) {
-#pragma unroll
-                for (int ky = 0; ky < 3; ky++)
-#pragma unroll
-                    for (int h = 0; h < 4; h++) {
-                        const uint64_t da = da0 + (uint64_t)(((ky + h) * 10 * 128) >> 4), db = db0 + (uint64_t)((h * 1024) >> 4);
-                        if (h == 0) umma_tf32(tmem_d + (uint32_t)(ky * 32), da, db, IDESC, i != 0 ? 1u : 0u);
-                        else umma_tf32_acc(tmem_d + (uint32_t)(ky * 32), da, db, IDESC);
-                    }
-                umma_commit(&bar_empty[s]);
-                if (i == nst - 1) umma_commit(&bar_done);
-            }
-            __syncwarp();
-        }
-    }
-    __syncwarp();
-    float* out = p.partial + (size_t)split * 9 * 32 * 32;
-    if (nst > 0) {
-        mbar_wait(&bar_done, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    }
-    const uint32_t lane_addr = tmem_d + ((uint32_t)(warp * 32) << 16);
-    const int dx = t >> 5, ci = t & 31;
-#pragma unroll 1
-    for (int cb = 0; cb < 96; cb += 16) {
-        uint32_t r[16];
-        if (nst > 0) {
-            tmem_ld16(lane_addr + (uint32_t)cb, r);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        } else {
-#pragma unroll
-            for (int k = 0; k < 16; k++) r[k] = 0u;
-        }
-        if (dx < 3) {
-            const int ky = cb >> 5, co0 = cb & 31;
-            float* o = out + ((size_t)(ky * 3 + dx) * 32 + ci) * 32 + co0;
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                *reinterpret_cast<float4*>(o + 4 * k) = make_float4(__uint_as_float(r[4 * k]), __uint_as_float(r[4 * k + 1]), __uint_as_float(r[4 * k + 2]), __uint_as_float(r[4 * k + 3]));
-        }
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(128u));
-}
-
-// Weight gradient with a 32-channel operand on one side and 32 or 64 channels on the other (the full- and half-resolution
-// layers): ALL nine taps come out of every MMA.  Per 8x4 pixel patch the 32-channel operand is loaded as a (10 x 4) box and the
-// three dx shifts are stacked in the MMA M dimension (MN-major descriptor with a leading-dimension offset of one pixel =
-// 128 B, 4th block = padding); the other operand is loaded as an (8 x 6) box per 32-channel block and the three dy shifts are
-// stacked in the N dimension the same way (leading-dimension offset of one box row = 1024 B).  So one M=128, N=96, K=8 MMA per
-// box row and channel block replaces nine N=32 MMAs: (128+96)*32 B instead of 9*(128+32)*32 B of shared-memory operand reads,
-// which is what bounds these small-N MMAs.
-//   in_is_m = 1:  M = in  (dx = block i),      N = g  (dy = 2 - block j)
-//   in_is_m = 0:  M = g   (dx = 2 - block i),  N = in (dy = block j)
-// Patches are 8 pixels wide and W9_PR rows high.  tcgen05.commit costs a pipeline drain (~250 cycles measured), so one commit
-// (= one stage) should cover many MMAs: 8 rows = 8 k-steps per stage.
 constexpr int W9_PR = 8;
 constexpr int W9_MBOX = 10 * W9_PR * 128;          // (10 x PR) box of the 32-channel operand
 constexpr int W9_MREGION = W9_MBOX + 1024;         // + zeroed overrun read by the (discarded) padding block
@@ -2139,64 +1367,30 @@ int32_t make_tmap_box(CUtensorMap* m, const float* ptr, int C, int W, int H, int
     return DINCAE_OK;
 }
 
-int32_t make_tmap_in32(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
-    EncodeTiledFn enc = get_encode();
-    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
-    cuuint32_t box[4] = {32, 10, 6, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(in32 C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
-    return DINCAE_OK;
-}
 
-int32_t make_tmap_patch(CUtensorMap* m, const float* ptr, int C, int W, int H, int B) {
-    EncodeTiledFn enc = get_encode();
-    DC_REQUIRE(enc != nullptr, DINCAE_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
-    cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
-    cuuint64_t gstr[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
-    cuuint32_t box[4] = {32, 8, 4, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)ptr, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                     CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    DC_REQUIRE(r == CUDA_SUCCESS, DINCAE_ECUDA, "cuTensorMapEncodeTiled(patch C=%d W=%d H=%d B=%d) failed: %d", C, W, H, B, (int)r);
-    return DINCAE_OK;
-}
 
-template <int BN, int STAGES>
-constexpr int wg_smem_bytes() { return STAGES * (4 * WG_BLOCK + (BN / 32) * WG_BLOCK) + 1024; }
 
-static bool wgradm_selected() {
-    static const int on = dc_env_int("DINCAE_WGRADM", 1);
-    return on != 0;
-}
+// wgrad9_kernel: a 32-channel side against 32 or 64 channels; wgradm_kernel: every other shape
 static bool wgrad9_selected(int Cin_p, int Cout_p) {
-    static const int on = dc_env_int("DINCAE_WGRAD9", 1);
-    return on && ((Cin_p == 32 && (Cout_p == 32 || Cout_p == 64)) || (Cin_p == 64 && Cout_p == 32));
+    return (Cin_p == 32 && (Cout_p == 32 || Cout_p == 64)) || (Cin_p == 64 && Cout_p == 32);
 }
-
-static int wgrad_patch_rows(int Cin_p, int Cout_p) { return (wgrad9_selected(Cin_p, Cout_p) || wgradm_selected()) ? 8 : 4; }
+constexpr int WGRAD_PATCH_ROWS = 8;
 
 void wgrad_tma_plan(int num_sms, const WgradArgs& a, int& bn, int& splits, int64_t& npatches, int64_t& pps, int& in_is_m) {
     const int Cin_p = a.in.C, Cout_p = a.Cout_p;
     in_is_m = Cin_p >= Cout_p;
     const int m_ch = in_is_m ? Cin_p : Cout_p, n_ch = in_is_m ? Cout_p : Cin_p;
     bn = n_ch % 256 == 0 ? 256 : (n_ch % 128 == 0 ? 128 : (n_ch % 64 == 0 ? 64 : 32));
-    const int mtiles = (m_ch + 127) / 128, ntiles = n_ch / bn;
-    npatches = (int64_t)a.B * dc_cdiv(a.H, wgrad_patch_rows(Cin_p, Cout_p)) * dc_cdiv(a.W, 8);
-    int tiles = mtiles * ntiles * (bn == 32 ? 3 : 9);     // three taps per CTA in the halo variant (narrow N only)
-    if (Cin_p == 32 && Cout_p == 32) tiles = 1;           // wgrad32_kernel: all nine taps in one CTA
-    const bool w9 = wgrad9_selected(Cin_p, Cout_p);
-    if (w9) { tiles = 1; in_is_m = Cin_p == 32; }          // wgrad9_kernel: all nine taps in every MMA; M = the 32-channel side
-    const bool wm = !w9 && wgradm_selected();
-    if (wm) {                                              // wgradm_kernel: one CTA per SM, (128-channel, 32-channel) blocks of all nine taps
-        tiles = mtiles * (n_ch / 32);
+    const int mtiles = (m_ch + 127) / 128;
+    npatches = (int64_t)a.B * dc_cdiv(a.H, WGRAD_PATCH_ROWS) * dc_cdiv(a.W, 8);
+    if (wgrad9_selected(Cin_p, Cout_p)) {                  // wgrad9_kernel: all nine taps in every MMA; M = the 32-channel side
+        in_is_m = Cin_p == 32;
+        splits = ((Cin_p == 32 && Cout_p == 32) ? 3 : 2) * num_sms;       // CTAs per SM the kernel fits (smem, TMEM)
+    } else {                                               // wgradm_kernel: one CTA per SM, (128-channel, 32-channel) blocks of all nine taps
+        const int tiles = mtiles * (n_ch / 32);
         splits = (num_sms + tiles - 1) / tiles;
-    } else
-    splits = (((bn == 32 && !w9) || (w9 && Cin_p == 32 && Cout_p == 32) ? 3 : 2) * num_sms + tiles - 1) / tiles;   // CTAs per SM the kernels fit (smem, TMEM)
-    int64_t maxs = dc_cdiv(npatches, wgrad_patch_rows(Cin_p, Cout_p) == 8 ? 2 : 4);
+    }
+    int64_t maxs = dc_cdiv(npatches, 2);
     if (splits > maxs) splits = (int)maxs;
     // the split partials are written and re-read once: keep them below ~16 MB per layer
     static const int cap_mb = dc_env_int("DINCAE_WGRAD_CAP_MB", 16);
@@ -2224,34 +1418,6 @@ size_t k2_wgrad_tma_scratch_bytes(int num_sms, int B, int H, int W, int Cin_p, i
     return ((size_t)splits * 9 * Cin_p * Cout_p + 1024 * (size_t)Cout_p) * sizeof(float);
 }
 
-#define WG_LAUNCH(BN_, ST_)                                                                                                \
-    do {                                                                                                                   \
-        auto wgrad_tma_bn##BN_ = wgrad_tma<BN_, ST_>;                                                                      \
-        constexpr int smem = wg_smem_bytes<BN_, ST_>();                                                                    \
-        static bool attr_set = false;                                                                                      \
-        if (!attr_set) {                                                                                                   \
-            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tma_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));     \
-            attr_set = true;                                                                                               \
-        }                                                                                                                  \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
-        DC_LAUNCH(ctx, wgrad_tma_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                  \
-        DC_CHECK_LAUNCH();                                                                                                 \
-    } while (0)
-
-#define WH_LAUNCH(BN_, ST_)                                                                                                \
-    do {                                                                                                                   \
-        auto wgrad_halo_bn##BN_ = wgrad_halo<BN_, ST_>;                                                                    \
-        constexpr int smem = ST_ * (4 * WH_INBLK + (BN_ / 32) * WH_INBLK) + 1024;                                          \
-        static bool attr_set = false;                                                                                      \
-        if (!attr_set) {                                                                                                   \
-            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad_halo_bn##BN_, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));    \
-            attr_set = true;                                                                                               \
-        }                                                                                                                  \
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * a.in.C * a.Cout_p * (double)a.B * a.H * a.W, a.work_bytes);        \
-        DC_LAUNCH(ctx, wgrad_halo_bn##BN_, grid, 128, smem, tmIn, tmG, p);                                                 \
-        DC_CHECK_LAUNCH();                                                                                                 \
-    } while (0)
-
 int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t scratch_bytes) {
     const int Cin_p = a.in.C, Cout_p = a.Cout_p;
     int bn, splits, in_is_m;
@@ -2262,13 +1428,10 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
     const int cs_blocks = (int)(M < (int64_t)4 * ctx->num_sms * 32 ? dc_cdiv(M, 32) : 4 * ctx->num_sms);
     DC_REQUIRE(scratch_bytes >= ((size_t)splits * nW + (size_t)cs_blocks * Cout_p) * sizeof(float), DINCAE_ESIZE, "k2_wgrad_tma: scratch too small");
     WgradTmaArgs p;
-    p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, wgrad_patch_rows(Cin_p, Cout_p));
+    p.B = a.B; p.H = a.H; p.W = a.W; p.ptx = (int)dc_cdiv(a.W, 8); p.pty = (int)dc_cdiv(a.H, WGRAD_PATCH_ROWS);
     p.Cin_p = Cin_p; p.Cout_p = Cout_p; p.in_is_m = in_is_m;
     p.m_ch = in_is_m ? Cin_p : Cout_p; p.n_ch = in_is_m ? Cout_p : Cin_p;
     p.npatches = np; p.patches_per_split = pps; p.partial = (float*)scratch;
-    alignas(64) CUtensorMap tmIn, tmG;
-    DC_TRY(make_tmap_patch(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
-    DC_TRY(make_tmap_patch(&tmG, a.gout, Cout_p, a.W, a.H, a.B));
     if (wgrad9_selected(Cin_p, Cout_p)) {
         alignas(64) CUtensorMap tmM, tmN;
         DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, 32, a.W, a.H, a.B, 10, W9_PR));
@@ -2288,7 +1451,7 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
             DC_LAUNCH(ctx, wgrad9_n64, (unsigned)splits, 128, smem, tmM, tmN, p);
         }
         DC_CHECK_LAUNCH();
-    } else if (wgradm_selected()) {
+    } else {
         alignas(64) CUtensorMap tmM, tmN;
         DC_TRY(make_tmap_box(&tmM, in_is_m ? a.in.src0 : a.gout, p.m_ch, a.W, a.H, a.B, 10, W9_PR));
         DC_TRY(make_tmap_box(&tmN, in_is_m ? a.gout : a.in.src0, p.n_ch, a.W, a.H, a.B, 8, W9_PR + 2));
@@ -2300,27 +1463,6 @@ int32_t k2_wgrad_tma(dincae_ctx* ctx, const WgradArgs& a, void* scratch, size_t 
         dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(p.n_ch / 32));
         DC_LAUNCH(ctx, wgradm, grid, 128, smem, tmM, tmN, p);
         DC_CHECK_LAUNCH();
-    } else if (Cin_p == 32 && Cout_p == 32) {
-        DC_TRY(make_tmap_in32(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
-        auto wgrad32 = wgrad32_kernel<6>;
-        constexpr int smem = 6 * W32_STAGE + 1024;
-        static bool attr_set = false;
-        if (!attr_set) {
-            DC_CHECK_CUDA(cudaFuncSetAttribute(wgrad32, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            attr_set = true;
-        }
-        DC_WORK(ctx, a.work_flops > 0 ? a.work_flops : 2.0 * 9 * 32 * 32 * (double)a.B * a.H * a.W, a.work_bytes);
-        DC_LAUNCH(ctx, wgrad32, (unsigned)splits, 128, smem, tmIn, tmG, p);
-        DC_CHECK_LAUNCH();
-    } else if (bn == 32) {
-        DC_TRY(make_tmap_inhalo(&tmIn, a.in.src0, Cin_p, a.W, a.H, a.B));
-        dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(3 * (p.n_ch / bn)));
-        WH_LAUNCH(32, 4);
-    } else {
-        dim3 grid((unsigned)splits, (unsigned)((p.m_ch + 127) / 128), (unsigned)(9 * (p.n_ch / bn)));
-        if (bn == 256) WG_LAUNCH(256, 2);
-        else if (bn == 128) WG_LAUNCH(128, 3);
-        else WG_LAUNCH(64, 4);
     }
     // second stages: split-K sum of dW and column-partial sum of the bias gradient (queued when a.defer is set)
     const float* cpart = a.colpart;
@@ -2362,37 +1504,20 @@ extern "C" int32_t dincae_debug_wgrad(dincae_ctx* ctx, const float* d_in, const 
 }
 
 // ---- test hook (not part of the public header): one 3x3 convolution through a chosen kernel family ----------------
-//   variant 0: FP32 CUDA-core kernel   1: tcgen05 with software-gather producer   2: TMA, one activation box per tap
-//           3: TMA halo tile + shifted descriptors   4: persistent warp-specialised halo kernel
+//   variant 0: FP32 CUDA-core kernel   4: persistent warp-specialised tcgen05 kernel (plain or paired tiles, as k2_conv picks)
 // d_w: [round_up(9*Cin_p,16)][Cout_p] forward layout; d_wK: K-major [Cout_p][9*Cin_p] copy (TF32-representable values).
 extern "C" int32_t dincae_debug_conv(dincae_ctx* ctx, const float* d_in, const float* d_w, const float* d_wK, const float* d_bias,
                                      int32_t B, int32_t H, int32_t W, int32_t Cin_p, int32_t Cout_p, int32_t relu, float* d_out, int32_t variant) {
     DC_REQUIRE(ctx && d_in && d_w && d_wK && d_out, DINCAE_EINVAL, "dincae_debug_conv: NULL argument");
+    DC_REQUIRE(variant == 0 || variant == 4, DINCAE_EUNSUPPORTED, "dincae_debug_conv: variant %d (0 = FP32 CUDA cores, 4 = persistent tcgen05)", variant);
     DC_CHECK_CUDA(cudaSetDevice(ctx->device));
     ConvArgs a{};
     a.in = ConvSrc{d_in, nullptr, SRC_DIRECT, H, W, Cin_p};
-    a.B = B; a.H = H; a.W = W; a.wgt = d_w; a.wgtK = variant == 0 ? nullptr : d_wK; a.ldk = 9 * Cin_p; a.in_is_tf32 = variant >= 2;
+    a.B = B; a.H = H; a.W = W; a.wgt = d_w; a.wgtK = variant == 0 ? nullptr : d_wK; a.ldk = 9 * Cin_p; a.in_is_tf32 = variant != 0;
     a.bias = d_bias; a.Cout_p = Cout_p; a.act = relu ? ACT_RELU : ACT_NONE; a.slope = 0.f; a.dst = d_out;
     if (variant == 0) return k2_conv(ctx, a);
-    if (variant == 1) { DC_REQUIRE(k2_conv_tc_eligible(a), DINCAE_EUNSUPPORTED, "dincae_debug_conv: shape not eligible"); return k2_conv_tc(ctx, a); }
-    DC_REQUIRE(k2_conv_tma_eligible(a), DINCAE_EUNSUPPORTED, "dincae_debug_conv: shape not eligible for the TMA kernels");
-    if (variant == 3) return k2_conv_halo(ctx, a, 1);
-    if (variant == 4) return k2_conv_persist(ctx, a);
-    // variant 2: the one-box-per-tap kernel
-    TmaConvArgs p;
-    p.B = a.B; p.H = a.H; p.W = a.W;
-    p.PW = a.W > 8 ? 16 : 8; p.PH = TM_BM / p.PW;
-    p.ptx = (int)dc_cdiv(a.W, p.PW); p.pty = (int)dc_cdiv(a.H, p.PH);
-    p.Cin_p = a.in.C; p.Cout_p = a.Cout_p;
-    p.bias = a.bias; p.act = a.act; p.slope = a.slope; p.addend = a.addend; p.dst = a.dst;
-    p.planar_out = nullptr; p.planar_C = 0; p.planar_accumulate = 0; p.planar_fold = 0;
-    p.pool_dst = nullptr; p.pool_rnd = 0; p.mask_dst = nullptr;
-    alignas(64) CUtensorMap tmA, tmB;
-    DC_TRY(make_tmap_act(&tmA, a.in.src0, a.in.C, a.W, a.H, a.B, p.PW, p.PH));
-    if (a.Cout_p % 256 == 0) TMA_LAUNCH(256, 2);
-    if (a.Cout_p % 128 == 0) TMA_LAUNCH(128, 3);
-    if (a.Cout_p % 64 == 0) TMA_LAUNCH(64, 4);
-    TMA_LAUNCH(32, 5);
+    DC_REQUIRE(k2_conv_tma_eligible(a), DINCAE_EUNSUPPORTED, "dincae_debug_conv: shape not eligible for the tcgen05 kernel");
+    return k2_conv_persist(ctx, a);
 }
 
 extern "C" int32_t dincae_debug_conv_trace(long long* d_trace) { g_persist_trace = d_trace; return DINCAE_OK; }

@@ -1,4 +1,4 @@
-"""Per-layer timing of the persistent tcgen05 conv on the cfg2 layer shapes (tuning aid; env DINCAE_TUNE_* overrides)."""
+"""Per-layer timing of the persistent tcgen05 conv on the cfg2 layer shapes (tuning aid)."""
 import sys, os, ctypes, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

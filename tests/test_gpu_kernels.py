@@ -1,7 +1,7 @@
-"""Kernel-level exactness of every tensor-core kernel family against the FP32 CUDA-core kernel.
-Operands are small integers (exactly representable in TF32, exact FP32 sums), so every variant -- software-gather tcgen05,
-TMA one-box-per-tap, TMA halo with shifted descriptors, persistent warp-specialised, and the three weight-gradient kernels --
-must agree BIT FOR BIT with the FP32 kernel: any swizzle / descriptor / tap-mapping error shows up as a hard mismatch."""
+"""Kernel-level exactness of the tensor-core kernels against the FP32 CUDA-core kernels.
+Operands are small integers (exactly representable in TF32, exact FP32 sums), so the persistent / paired-tile tcgen05 conv and the
+two weight-gradient kernels (wgrad9, wgradm) must agree BIT FOR BIT with the FP32 kernels and with torch: any swizzle /
+descriptor / tap-mapping error shows up as a hard mismatch."""
 import ctypes as C
 import numpy as np
 import pytest
@@ -39,7 +39,7 @@ def test_conv_kernel_families_bit_exact(env, B, H, W, Ci, Co):
     bias = torch.randint(-5, 6, (Co,), generator=g).float()
     w_fwd, w_k, bias = w_fwd.to(dev), w_k.to(dev), bias.to(dev)
     outs = []
-    for variant in range(5):
+    for variant in (0, 4):
         out = torch.full((B, H, W, Co), 7.0, device=dev)
         torch.cuda.synchronize()
         pkg.lib.check(lib.dincae_debug_conv(ctx.handle, x.data_ptr(), w_fwd.data_ptr(), w_k.data_ptr(), bias.data_ptr(),
@@ -49,8 +49,7 @@ def test_conv_kernel_families_bit_exact(env, B, H, W, Ci, Co):
     # independent check of the FP32 kernel itself against torch (cross-correlation, pad 1, ReLU)
     ref = torch.nn.functional.conv2d(x.cpu().permute(0, 3, 1, 2), w.reshape(3, 3, Ci, Co).permute(3, 2, 0, 1), bias.cpu(), padding=1).relu().permute(0, 2, 3, 1)
     assert torch.equal(outs[0], ref)
-    for variant in range(1, 5):
-        assert torch.equal(outs[variant], outs[0]), "conv variant %d differs" % variant
+    assert torch.equal(outs[1], outs[0]), "the tcgen05 conv differs from the FP32 kernel"
 
 
 WGRAD_SHAPES = [(1, 4, 8, 32, 32), (3, 9, 13, 32, 32), (2, 112, 112, 32, 32), (1, 4, 8, 128, 32), (2, 9, 13, 64, 32), (2, 9, 13, 32, 64),
