@@ -7,6 +7,5 @@ CUDA library; there is no CPU fallback: every call raises if the library or a GP
 """
 from . import lib            # noqa: F401  ctypes declarations of include/dincae_b200.h
 from . import api            # noqa: F401  reference-shaped host API
-from . import selftest       # noqa: F401
 from .api import (Context, Model, GriddedDataset, PointDataset, ModelConfig,
                   interpnd, interp_adjn, reconstruct, reconstruct_points)

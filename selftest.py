@@ -1,6 +1,7 @@
 """smoke(): one small invocation of the hot path on cuda:0, checked against the CPU oracle.
 
-The oracle (oracle/) is test infrastructure: it is imported here only as the checker."""
+Lives beside __graft_entry__.py, OUTSIDE the product package: the oracle (oracle/) is test infrastructure and nothing under
+dincae.jl_b200/ imports it; here it is the checker only."""
 import numpy as np
 
 
@@ -8,7 +9,8 @@ def smoke(verbose=True):
     import torch
     if not torch.cuda.is_available():
         raise RuntimeError("dincae_b200.smoke needs a CUDA device; the library has no CPU path")
-    from . import api
+    import __graft_entry__ as ge
+    api = ge.load_package().api
     from oracle import model as OM, data as OD, points as OP
 
     ctx = api.Context(0)

@@ -284,7 +284,8 @@ def test_error_paths(pkg, ctx):
 
 
 def test_smoke(pkg, ctx):
-    r = pkg.selftest.smoke(verbose=False)
+    import selftest
+    r = selftest.smoke(verbose=False)
     assert r["launches"] > 0
 
 
