@@ -356,8 +356,33 @@ __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restric
     const bool pv = m < total;
     const int b = pv ? (int)(m / HW) : 0, r = pv ? (int)(m - (int64_t)b * HW) : 0;
     const int Ct = C0 + C1;
+    // per-pixel base pointers: the channel loop only adds multiples of the plane size (no 64-bit multiplies per load)
+    const float* p0 = s0 + ((size_t)b * C0) * HW + r;
+    const float* p1 = s1 ? s1 + ((size_t)b * C1) * HW + r : nullptr;
+    const bool one_pass = split && 2 * Ct <= 32;            // [hi | lo] of every channel fits one 32-channel group: load each value once
     for (int cg = 0; cg < Cw; cg += 32) {                  // channels >= Cw are zero padding and stay as the buffer was created (zeros)
         const int nc = Cw - cg < 32 ? Cw - cg : 32;
+        if (one_pass) {
+            for (int c8 = 0; c8 < Ct; c8 += 8) {
+                float v[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int cc = c8 + k;
+                    v[k] = 0.f;
+                    if (pv && cc < Ct) v[k] = cc < C0 ? __ldg(p0 + (size_t)cc * HW) : __ldg(p1 + (size_t)(cc - C0) * HW);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int cc = c8 + k;
+                    if (cc < Ct) {
+                        const float hi = round_tf32(v[k]);
+                        tile[warp][lane][cc] = hi;
+                        tile[warp][lane][Ct + cc] = round_tf32(v[k] - hi);
+                    }
+                }
+            }
+            for (int cc = 2 * Ct; cc < nc; cc++) tile[warp][lane][cc] = 0.f;
+        } else
         for (int c8 = 0; c8 < nc; c8 += 8) {               // eight independent loads in flight per thread, then the shared stores
             float v[8];
 #pragma unroll
@@ -366,8 +391,8 @@ __global__ void __launch_bounds__(256) pack_planar_kernel(const float* __restric
                 if (split && cc >= Ct) cc = cc < 2 * Ct ? cc - Ct : Ct;         // [hi | lo | zero padding]
                 v[k] = 0.f;
                 if (pv) {
-                    if (cc < C0) v[k] = __ldg(s0 + ((size_t)b * C0 + cc) * HW + r);
-                    else if (cc < Ct) v[k] = __ldg(s1 + ((size_t)b * C1 + (cc - C0)) * HW + r);
+                    if (cc < C0) v[k] = __ldg(p0 + (size_t)cc * HW);
+                    else if (cc < Ct) v[k] = __ldg(p1 + (size_t)(cc - C0) * HW);
                 }
             }
 #pragma unroll
@@ -716,20 +741,26 @@ __global__ void __launch_bounds__(256) make_wT_tiled_kernel(const float* __restr
 // ---------------------------------------------------------------------------------------------
 // Head conv fused with its producer (src/model.jl:270-272 at l = 1 + src/flux.jl:4): raw = Conv3x3(crop(Upsample2x_nearest(s0 + s1)))
 // with NO = 2*noutput output channels, identity activation, planar (WHCN) output.  Exact FP32 on the CUDA cores in every
-// precision mode: the layer has 2*noutput columns (a 32-column MMA would be 94 % padding), is bound by its reads, and its
-// rounding error reaches (m, sigma) undamped, so this is where FP32 operands buy the most accuracy.
-// One thread = one LOW-resolution cell = the 2 x 2 output pixels above it: per input channel nine source values (its 3 x 3
-// low-resolution neighbourhood, shared-memory tile stored channel-major so a warp reads consecutive words) feed the 4 x 9 taps.
-// A tap that leaves the cropped image (odd H or W: output row 2i+1 == H) reads zero, as the conv padding does.
-constexpr int HU_TW = 32, HU_TH = 8;                        // low-resolution cells per block (x, y)
-constexpr int HU_SP = (HU_TW + 2) * (HU_TH + 2) + 1;        // channel stride of the tile (+1: conflict-free transposing fill)
-template <int NO>
-__global__ void __launch_bounds__(256) head_up_conv_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp, int Cin,
-                                                           const float* __restrict__ wgt, int Cin_p, int Cout_p, const float* __restrict__ bias,
-                                                           int H, int W, float* __restrict__ out) {
-    extern __shared__ float hu_smem[];
+// precision mode: the layer has 2*noutput columns (a 32-column MMA would be 94 % padding) and its rounding error reaches
+// (m, sigma) undamped, so this is where FP32 operands buy the most accuracy.
+// One thread = TWO neighbouring LOW-resolution cells = the 2 x 4 output pixels above them.  The (8+2) x (64+2) source tile
+// (s0 + s1) sits channel-major in shared memory; per input channel a thread reads its 3 x 4 source values as six 8-byte loads
+// and the weights as broadcast vector loads, so the inner loop is FMA-bound, not load-bound.
+//   PHASE = true (even H and W): an output pixel of phase (p, q) = (y & 1, x & 1) only sees 2 x 2 DISTINCT source cells, so the
+//     nine taps are pre-summed into 4 phases x 4 weights when the block stages them (2.25x fewer FMAs);
+//   PHASE = false (odd H or W): the nine taps are applied one by one and a tap that lands on the cropped row / column
+//     (output row 2*ys+1 == H) reads zero, as the conv padding does.
+constexpr int HU_TW = 64, HU_TH = 8;                        // low-resolution cells per block (x, y); 256 threads x 2 cells
+constexpr int HU_RS = HU_TW + 2;                            // row stride of the tile (even: 8-byte loads stay aligned)
+constexpr int HU_SP = HU_RS * (HU_TH + 2) + 2;              // channel stride (even)
+template <int NO, bool PHASE>
+__global__ void __launch_bounds__(256, 2) head_up_conv_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp, int Cin,
+                                                              const float* __restrict__ wgt, int Cin_p, int Cout_p, const float* __restrict__ bias,
+                                                              int H, int W, float* __restrict__ out) {
+    extern __shared__ __align__(16) float hu_smem[];
+    constexpr int NW = (PHASE ? 16 : 9) * NO;                // staged weights per input channel
     float* S = hu_smem;                                      // [Cin][HU_SP]
-    float* wS = hu_smem + (size_t)Cin * HU_SP;               // [Cin][9][NO]
+    float* wS = hu_smem + (((size_t)Cin * HU_SP + 3) & ~(size_t)3);      // [Cin][NW], 16-byte aligned
     dc_pdl_launch_dependents();
     dc_pdl_wait();
     const int tilesx = (Ws + HU_TW - 1) / HU_TW, tilesy = (Hs + HU_TH - 1) / HU_TH;
@@ -738,75 +769,137 @@ __global__ void __launch_bounds__(256) head_up_conv_kernel(const float* __restri
     bid -= b * tilesx * tilesy;
     const int ty0 = (bid / tilesx) * HU_TH, tx0 = (bid - (bid / tilesx) * tilesx) * HU_TW;
     const int t = threadIdx.x;
-    for (int i = t; i < Cin * 9 * NO; i += 256) {
-        const int o = i % NO, r = i / NO, tap = r % 9, ci = r / 9;
-        wS[i] = __ldg(wgt + ((size_t)tap * Cin_p + ci) * Cout_p + o);
+    for (int i = t; i < Cin * NW; i += 256) {
+        const int o = i % NO, r = i / NO, e = r % (PHASE ? 16 : 9), ci = r / (PHASE ? 16 : 9);
+        const float* wc = wgt + (size_t)ci * Cout_p + o;     // element (tap, ci, o) at wc[tap * Cin_p * Cout_p]
+        const size_t ts = (size_t)Cin_p * Cout_p;
+        float v;
+        if (PHASE) {
+            // e = ((p*2 + q)*2 + i)*2 + j: source cell (p + i, q + j) of the 3 x 3 neighbourhood; the taps dy that reach it from an
+            // output row of phase p are {0} / {1,2} for p = 0 and {0,1} / {2} for p = 1 (same for columns)
+            const int j = e & 1, ii = (e >> 1) & 1, q = (e >> 2) & 1, pp = e >> 3;
+            const int dy0 = pp == 0 ? (ii == 0 ? 0 : 1) : (ii == 0 ? 0 : 2), dy1 = pp == 0 ? (ii == 0 ? 0 : 2) : (ii == 0 ? 1 : 2);
+            const int dx0 = q == 0 ? (j == 0 ? 0 : 1) : (j == 0 ? 0 : 2), dx1 = q == 0 ? (j == 0 ? 0 : 2) : (j == 0 ? 1 : 2);
+            v = 0.f;
+            for (int dy = dy0; dy <= dy1; dy++)
+                for (int dx = dx0; dx <= dx1; dx++) v += __ldg(wc + (size_t)(dy * 3 + dx) * ts);
+        } else {
+            v = __ldg(wc + (size_t)e * ts);
+        }
+        wS[i] = v;
     }
-    {   // tile (with a one-cell halo, zero outside the source image), transposed to channel-major
+    {   // tile (with a one-cell halo, zero outside the source image), transposed to channel-major.  Eight (pairs of) 16-byte loads
+        // are in flight per thread before the first shared-memory store: one load per round trip would make the fill a chain of
+        // ~40 memory latencies per thread, which is longer than the arithmetic of the whole block
         const int C4 = (Cin + 3) >> 2;
-        constexpr int NP = (HU_TW + 2) * (HU_TH + 2);
-        for (int i = t; i < NP * C4; i += 256) {
-            const int c4 = i % C4, pix = i / C4, py = pix / (HU_TW + 2), px = pix - py * (HU_TW + 2);
-            const int ys = ty0 + py - 1, xs = tx0 + px - 1;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ys >= 0 && ys < Hs && xs >= 0 && xs < Ws) {
-                const size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + 4 * c4;
-                v = ldg4(s0 + off);
-                if (s1) { const float4 u = ldg4(s1 + off); v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w; }
+        constexpr int NP = HU_RS * (HU_TH + 2);
+        const int nitems = NP * C4;
+        for (int i0 = t; i0 < nitems; i0 += 8 * 256) {
+            float4 v[8], u[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const int i = i0 + k * 256;
+                v[k] = make_float4(0.f, 0.f, 0.f, 0.f); u[k] = v[k];
+                if (i < nitems) {
+                    const int c4 = i % C4, pix = i / C4, py = pix / HU_RS, px = pix - py * HU_RS;
+                    const int ys = ty0 + py - 1, xs = tx0 + px - 1;
+                    if (ys >= 0 && ys < Hs && xs >= 0 && xs < Ws) {
+                        const size_t off = (((size_t)b * Hs + ys) * Ws + xs) * Cp + 4 * c4;
+                        v[k] = ldg4(s0 + off);
+                        if (s1) u[k] = ldg4(s1 + off);
+                    }
+                }
             }
-            const int c = 4 * c4;
-            S[(size_t)c * HU_SP + pix] = v.x;
-            if (c + 1 < Cin) S[(size_t)(c + 1) * HU_SP + pix] = v.y;
-            if (c + 2 < Cin) S[(size_t)(c + 2) * HU_SP + pix] = v.z;
-            if (c + 3 < Cin) S[(size_t)(c + 3) * HU_SP + pix] = v.w;
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                const int i = i0 + k * 256;
+                if (i < nitems) {
+                    const int c4 = i % C4, pix = i / C4, c = 4 * c4;
+                    S[(size_t)c * HU_SP + pix] = v[k].x + u[k].x;
+                    if (c + 1 < Cin) S[(size_t)(c + 1) * HU_SP + pix] = v[k].y + u[k].y;
+                    if (c + 2 < Cin) S[(size_t)(c + 2) * HU_SP + pix] = v[k].z + u[k].z;
+                    if (c + 3 < Cin) S[(size_t)(c + 3) * HU_SP + pix] = v[k].w + u[k].w;
+                }
+            }
         }
     }
     __syncthreads();
     const int ly = t >> 5, lx = t & 31;
-    const int ys = ty0 + ly, xs = tx0 + lx;
-    const bool rowB = 2 * ys + 1 < H, colB = 2 * xs + 1 < W;         // output row 2*ys+1 / column 2*xs+1 exists (not cropped)
-    float acc[2][2][NO];
+    const int ys = ty0 + ly, xs = tx0 + 2 * lx;              // this thread's cells: (ys, xs) and (ys, xs + 1)
+    float acc[2][2][2][NO];                                  // [cell][p][q][o]
 #pragma unroll
-    for (int p = 0; p < 2; p++)
+    for (int n = 0; n < 2; n++)
 #pragma unroll
-        for (int q = 0; q < 2; q++)
+        for (int p = 0; p < 2; p++)
 #pragma unroll
-            for (int o = 0; o < NO; o++) acc[p][q][o] = 0.f;
-    const float* Sp = S + ly * (HU_TW + 2) + lx;
+            for (int q = 0; q < 2; q++)
+#pragma unroll
+                for (int o = 0; o < NO; o++) acc[n][p][q][o] = 0.f;
+    const float* Sp = S + ly * HU_RS + 2 * lx;
+    const bool rowB = 2 * ys + 1 < H;                        // output row 2*ys+1 exists (not cropped)
+    const bool colB0 = 2 * xs + 1 < W, colB1 = 2 * xs + 3 < W;
     for (int ci = 0; ci < Cin; ci++) {
-        // v[a][b]: a, b in {0,1,2} = source cell (ys-1+a, xs-1+b); index 3 = "this cell, seen from the output row/column that the
-        // crop removed" = zero padding
-        float v[4][4];
+        float v[3][4];                                       // source cells (ys-1+a, xs-1+c), c = 0..3 covers both cells
 #pragma unroll
-        for (int a = 0; a < 3; a++)
+        for (int a = 0; a < 3; a++) {
+            const float2 lo = *reinterpret_cast<const float2*>(Sp + (size_t)ci * HU_SP + a * HU_RS);
+            const float2 hi = *reinterpret_cast<const float2*>(Sp + (size_t)ci * HU_SP + a * HU_RS + 2);
+            v[a][0] = lo.x; v[a][1] = lo.y; v[a][2] = hi.x; v[a][3] = hi.y;
+        }
+        float w[NW];
+        if (NW % 4 == 0) {
 #pragma unroll
-            for (int c = 0; c < 3; c++) v[a][c] = Sp[(size_t)ci * HU_SP + a * (HU_TW + 2) + c];
+            for (int e = 0; e < NW / 4; e++) {
+                const float4 t4 = *reinterpret_cast<const float4*>(wS + (size_t)ci * NW + 4 * e);
+                w[4 * e] = t4.x; w[4 * e + 1] = t4.y; w[4 * e + 2] = t4.z; w[4 * e + 3] = t4.w;
+            }
+        } else {
 #pragma unroll
-        for (int c = 0; c < 3; c++) { v[3][c] = rowB ? v[1][c] : 0.f; v[c][3] = colB ? v[c][1] : 0.f; }
-        v[3][3] = (rowB && colB) ? v[1][1] : 0.f;
-        const float* wc = wS + ci * 9 * NO;
+            for (int e = 0; e < NW / 2; e++) {
+                const float2 t2 = *reinterpret_cast<const float2*>(wS + (size_t)ci * NW + 2 * e);
+                w[2 * e] = t2.x; w[2 * e + 1] = t2.y;
+            }
+        }
+        if (PHASE) {
 #pragma unroll
-        for (int dy = 0; dy < 3; dy++)
-#pragma unroll
-            for (int dx = 0; dx < 3; dx++) {
-                float w[NO];
-#pragma unroll
-                for (int o = 0; o < NO; o++) w[o] = wc[(dy * 3 + dx) * NO + o];
+            for (int n = 0; n < 2; n++)
 #pragma unroll
                 for (int p = 0; p < 2; p++)
 #pragma unroll
-                    for (int q = 0; q < 2; q++) {
-                        // output row 2*ys+p, tap dy-1 -> high-res row 2*ys+p+dy-1 -> source offset floor((p+dy-1)/2) in {-1,0,+1};
-                        // (p,dy) = (0,2) lands on row 2*ys+1, which may be cropped: slot 3
-                        const int a = (p == 0 && dy == 2) ? 3 : ((p + dy + 1) >> 1);
-                        const int c = (q == 0 && dx == 2) ? 3 : ((q + dx + 1) >> 1);
-                        const float x = v[a][c];
+                    for (int q = 0; q < 2; q++)
 #pragma unroll
-                        for (int o = 0; o < NO; o++) acc[p][q][o] = fmaf(x, w[o], acc[p][q][o]);
-                    }
+                        for (int i = 0; i < 2; i++)
+#pragma unroll
+                            for (int j = 0; j < 2; j++) {
+                                const float x = v[p + i][n + q + j];
+#pragma unroll
+                                for (int o = 0; o < NO; o++) acc[n][p][q][o] = fmaf(x, w[((((p * 2 + q) * 2 + i) * 2 + j)) * NO + o], acc[n][p][q][o]);
+                            }
+        } else {
+#pragma unroll
+            for (int n = 0; n < 2; n++) {
+                const bool colB = n == 0 ? colB0 : colB1;
+#pragma unroll
+                for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+                    for (int dx = 0; dx < 3; dx++)
+#pragma unroll
+                        for (int p = 0; p < 2; p++)
+#pragma unroll
+                            for (int q = 0; q < 2; q++) {
+                                // output row 2*ys+p, tap dy-1 -> high-res row 2*ys+p+dy-1 -> source offset floor((p+dy-1)/2) in {-1,0,+1};
+                                // (p,dy) = (0,2) lands on row 2*ys+1, which may be cropped (then it is padding: zero)
+                                const int a = (p + dy + 1) >> 1, c = (q + dx + 1) >> 1;
+                                float x = v[a][n + c];
+                                if (p == 0 && dy == 2 && !rowB) x = 0.f;
+                                if (q == 0 && dx == 2 && !colB) x = 0.f;
+#pragma unroll
+                                for (int o = 0; o < NO; o++) acc[n][p][q][o] = fmaf(x, w[(dy * 3 + dx) * NO + o], acc[n][p][q][o]);
+                            }
             }
+        }
     }
-    if (ys >= Hs || xs >= Ws) return;
+    if (ys >= Hs) return;
 #pragma unroll
     for (int o = 0; o < NO; o++) {
         const float bv = bias ? __ldg(bias + o) : 0.f;
@@ -815,8 +908,16 @@ __global__ void __launch_bounds__(256) head_up_conv_kernel(const float* __restri
             const int y = 2 * ys + p;
             if (y >= H) continue;
             float* dst = out + (((size_t)b * NO + o) * H + y) * W + 2 * xs;
-            dst[0] = acc[p][0][o] + bv;
-            if (colB) dst[1] = acc[p][1][o] + bv;
+#pragma unroll
+            for (int n = 0; n < 2; n++) {
+                if (xs + n >= Ws) continue;
+                if (PHASE) {                                  // even W: both columns exist, 8-byte aligned
+                    *reinterpret_cast<float2*>(dst + 2 * n) = make_float2(acc[n][p][0][o] + bv, acc[n][p][1][o] + bv);
+                } else {
+                    dst[2 * n] = acc[n][p][0][o] + bv;
+                    if (2 * (xs + n) + 1 < W) dst[2 * n + 1] = acc[n][p][1][o] + bv;
+                }
+            }
         }
     }
 }
@@ -875,8 +976,11 @@ int32_t k2_fold_split_grad(dincae_ctx* ctx, const float* gexp, float* g, const S
     return DINCAE_OK;
 }
 
+static size_t head_up_smem_bytes(int Cin, int nout2) {
+    return ((((size_t)Cin * HU_SP + 3) & ~(size_t)3) + (size_t)Cin * 16 * nout2) * sizeof(float);
+}
 bool k2_head_up_conv_eligible(int Cin, int nout2) {
-    return (nout2 == 2 || nout2 == 4 || nout2 == 6 || nout2 == 8) && (size_t)Cin * (HU_SP + 9 * nout2) * sizeof(float) <= 200 * 1024;
+    return (nout2 == 2 || nout2 == 4 || nout2 == 6 || nout2 == 8) && head_up_smem_bytes(Cin, nout2) <= 200 * 1024;
 }
 int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int Cin,
                         const float* wgt, int Cin_p, int Cout_p, const float* bias, int nout2, int H, int W, float* out,
@@ -884,19 +988,23 @@ int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, i
     if ((int64_t)B * H * W == 0) return DINCAE_OK;
     DC_REQUIRE(k2_head_up_conv_eligible(Cin, nout2), DINCAE_EUNSUPPORTED, "k2_head_up_conv: %d input / %d output channels not supported", Cin, nout2);
     DC_REQUIRE(Hs == H / 2 + H % 2 && Ws == W / 2 + W % 2, DINCAE_EINVAL, "k2_head_up_conv: source is not the half-resolution level");
-    const int smem = (int)((size_t)Cin * (HU_SP + 9 * nout2) * sizeof(float));
+    const int smem = (int)head_up_smem_bytes(Cin, nout2);
     const unsigned grid = (unsigned)(B * ((Ws + HU_TW - 1) / HU_TW) * ((Hs + HU_TH - 1) / HU_TH));
+    const bool phase = (H % 2) == 0 && (W % 2) == 0;
     DC_WORK(ctx, work_flops, work_bytes);
-#define HU_LAUNCH(NO_)                                                                                                      \
+#define HU_LAUNCH(NO_, PH_)                                                                                                 \
     do {                                                                                                                    \
         static int attr = 0;                                                                                                \
-        if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_up_conv_kernel<NO_>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
-        DC_LAUNCH_PDL(ctx, head_up_conv_kernel<NO_>, grid, 256, smem, src0, src1, B, Hs, Ws, Cp, Cin, wgt, Cin_p, Cout_p, bias, H, W, out); \
+        auto head_up_conv = head_up_conv_kernel<NO_, PH_>;                                                                  \
+        if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_up_conv, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
+        DC_LAUNCH_PDL(ctx, head_up_conv, grid, 256, smem, src0, src1, B, Hs, Ws, Cp, Cin, wgt, Cin_p, Cout_p, bias, H, W, out); \
     } while (0)
-    if (nout2 == 2) HU_LAUNCH(2);
-    else if (nout2 == 4) HU_LAUNCH(4);
-    else if (nout2 == 6) HU_LAUNCH(6);
-    else HU_LAUNCH(8);
+#define HU_PICK(NO_) do { if (phase) HU_LAUNCH(NO_, true); else HU_LAUNCH(NO_, false); } while (0)
+    if (nout2 == 2) HU_PICK(2);
+    else if (nout2 == 4) HU_PICK(4);
+    else if (nout2 == 6) HU_PICK(6);
+    else HU_PICK(8);
+#undef HU_PICK
 #undef HU_LAUNCH
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
