@@ -148,15 +148,19 @@ def points_config(pkg, ctx, timer, torch, dev, rank, world, precision, cpu):
     xbuf = torch.empty(Wd * Hd * C * B, dtype=torch.float32, device=dev)
     k = [0]
 
+    nvalid_step = np.array([int((x[:, 1] != 0).sum()) for x in ds.x], np.int64)      # valid observations per time step (static)
+
     def step():
-        idx = rng.integers(0, N, B * world)
-        keep = [ds.draw_track_keep(int(i), rng) for i in idx]                 # integer work on the host, identical on all ranks
+        idx = rng.integers(0, N, B * world)                                      # the same draw on every rank
         lo = rank * B
-        xin, truth = ds.assemble(idx[lo:lo + B], seed=3, sample_ctr0=k[0] * B * world + lo, keep=keep[lo:lo + B], xin=xbuf)
+        # track dropout of this rank's own samples (integer work on the host); one generator per (step, sample) so that no rank
+        # has to draw for the others
+        keep = [ds.draw_track_keep(int(i), np.random.default_rng([17, k[0], lo + j])) for j, i in enumerate(idx[lo:lo + B])]
+        xin, truth = ds.assemble(idx[lo:lo + B], seed=3, sample_ctr0=k[0] * B * world + lo, keep=keep, xin=xbuf)
         k[0] += 1
         if world == 1:
             return model.train_step_points(xin, truth, 1e-3, want_loss=False)
-        nglob = int(sum(int((ds.x[i][:, 1] != 0).sum()) for i in idx))       # valid observations of the GLOBAL batch
+        nglob = int(nvalid_step[idx].sum())                                      # valid observations of the GLOBAL batch
         model.grad_step_points(xin, truth, n_valid_global=nglob)
         model.allreduce_grads()
         return model.apply_step(1e-3, want_loss=False)
