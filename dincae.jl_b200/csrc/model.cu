@@ -178,6 +178,14 @@ float* colpart_alloc(dincae_model* M, int64_t n_elems4, int Cp, int* nblocks) {
 // The weight gradients hang off the backward chain (nothing downstream reads them before the final reduction), so in TF32 mode
 // they are issued on the context's side stream: each one forks after its g tensor has been produced and runs beside the
 // data-gradient / level kernels of the main stream; wgrad_join() makes the main stream wait before buffers are reused.
+// DINCAE_DP_OVERLAP=1: per-chain gradient buckets all-reduced on the communicator's stream behind the backward pass instead of one
+// all-reduce after it.  Off by default because it measured SLOWER (2 GPUs: 1.387 against 1.377 ms per step; with NCCL held to 2 CTAs
+// 1.69 ms): the persistent conv kernels are launched with exactly one CTA (pair) per SM, so every SM that a concurrent NCCL kernel
+// occupies leaves a CTA waiting for a whole kernel duration.
+static bool dp_overlap_on() {
+    static const int on = dc_env_int("DINCAE_DP_OVERLAP", 0);
+    return on != 0;
+}
 static bool side_stream_on() {
     static const int on = dc_env_int("DINCAE_SIDE_STREAM", 1);
     return on != 0;
@@ -948,10 +956,12 @@ extern "C" int32_t dincae_train_step_dp(dincae_model* M, const float* xin, const
     DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: model is NULL");
     DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: no communicator (dincae_comm_init_rank)");
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
-    M->dp_overlap = true;
+    M->dp_overlap = dp_overlap_on();
     int32_t st = dincae_grad_step(M, xin, xtrue, B, n_valid_global, loc);
+    const bool bucketed = M->dp_overlap;
     M->dp_overlap = false;
     DC_TRY(st);
+    if (!bucketed) DC_TRY(dincae_allreduce_grads(M));
     return dincae_apply_step(M, lr, loss);
 }
 
@@ -1042,10 +1052,12 @@ extern "C" int32_t dincae_train_step_dp_slot(dincae_model* M, int32_t slot, int3
     DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: model is NULL");
     DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: no communicator (dincae_comm_init_rank)");
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_slot: n_valid_global is NULL");
-    M->dp_overlap = true;
+    M->dp_overlap = dp_overlap_on();
     int32_t st = dincae_grad_step_slot(M, slot, B, n_valid_global);
+    const bool bucketed = M->dp_overlap;
     M->dp_overlap = false;
     DC_TRY(st);
+    if (!bucketed) DC_TRY(dincae_allreduce_grads(M));
     return dincae_apply_step(M, lr, loss);
 }
 
