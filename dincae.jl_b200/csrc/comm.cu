@@ -20,6 +20,7 @@ struct NcclApi {
     decltype(&ncclCommInitRank) CommInitRank = nullptr;
     decltype(&ncclCommDestroy) CommDestroy = nullptr;
     decltype(&ncclAllReduce) AllReduce = nullptr;
+    decltype(&ncclAllGather) AllGather = nullptr;
     decltype(&ncclGetErrorString) GetErrorString = nullptr;
     decltype(&ncclGetVersion) GetVersion = nullptr;
     std::string path;
@@ -40,7 +41,7 @@ int32_t nccl_api(NcclApi** out) {
 #define NCCL_SYM(name)                                                                                       \
         g_nccl.name = (decltype(g_nccl.name))dlsym(h, "nccl" #name);                                          \
         DC_REQUIRE(g_nccl.name != nullptr, DINCAE_EUNSUPPORTED, "NCCL library %s lacks nccl" #name, g_nccl.path.c_str());
-        NCCL_SYM(GetUniqueId) NCCL_SYM(CommInitRank) NCCL_SYM(CommDestroy) NCCL_SYM(AllReduce) NCCL_SYM(GetErrorString) NCCL_SYM(GetVersion)
+        NCCL_SYM(GetUniqueId) NCCL_SYM(CommInitRank) NCCL_SYM(CommDestroy) NCCL_SYM(AllReduce) NCCL_SYM(AllGather) NCCL_SYM(GetErrorString) NCCL_SYM(GetVersion)
 #undef NCCL_SYM
         g_nccl.handle = h;
     }
@@ -127,6 +128,22 @@ int32_t dc_allreduce_on(dincae_ctx* ctx, float* buf, int64_t n, cudaStream_t str
     DC_TRY(nccl_api(&api));
     DC_CHECK_NCCL(api, api->AllReduce(buf, buf, (size_t)n, ncclFloat, ncclSum, (ncclComm_t)ctx->comm, stream));
     ctx->collectives++;
+    return DINCAE_OK;
+}
+
+// set-up helpers of the peer-memory all-reduce (p2p.cu): exchange of a few bytes per rank and agreement on a flag
+int32_t dc_comm_allgather_bytes(dincae_ctx* ctx, const void* d_send, void* d_recv, size_t bytes_per_rank) {
+    DC_REQUIRE(ctx->comm != nullptr, DINCAE_EINVAL, "no communicator");
+    NcclApi* api;
+    DC_TRY(nccl_api(&api));
+    DC_CHECK_NCCL(api, api->AllGather(d_send, d_recv, bytes_per_rank, ncclChar, (ncclComm_t)ctx->comm, ctx->stream));
+    return DINCAE_OK;
+}
+int32_t dc_comm_allreduce_min_i32(dincae_ctx* ctx, int32_t* d_val) {
+    DC_REQUIRE(ctx->comm != nullptr, DINCAE_EINVAL, "no communicator");
+    NcclApi* api;
+    DC_TRY(nccl_api(&api));
+    DC_CHECK_NCCL(api, api->AllReduce(d_val, d_val, 1, ncclInt32, ncclMin, (ncclComm_t)ctx->comm, ctx->stream));
     return DINCAE_OK;
 }
 

@@ -124,6 +124,8 @@ void dc_prof_end(dincae_ctx* ctx);
 
 int32_t dc_scratch(dincae_ctx* ctx, size_t bytes, void** out);       // grow-only device scratch
 int32_t dc_allreduce_on(dincae_ctx* ctx, float* buf, int64_t n, cudaStream_t stream);   // in-place NCCL SUM ordered on `stream`
+int32_t dc_comm_allgather_bytes(dincae_ctx* ctx, const void* d_send, void* d_recv, size_t bytes_per_rank);
+int32_t dc_comm_allreduce_min_i32(dincae_ctx* ctx, int32_t* d_val);
 int32_t dc_pinned(dincae_ctx* ctx, size_t bytes, void** out);        // grow-only pinned host staging
 
 static inline int64_t dc_cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -518,7 +518,7 @@ int32_t read_loss(dincae_model* M, bool from_slot, float* out_f, double* out_d) 
     DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
     if (out_f) *out_f = *(float*)pin;
     if (out_d) *out_d = *(double*)((char*)pin + 8);
-    return DINCAE_OK;
+    return model_p2p_check(M);
 }
 
 // Flux order <-> internal padded layout (host side)
@@ -728,6 +728,8 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     }
     want((void**)&M->MS, planar_out);
     want((void**)&M->GMS, planar_out);
+    want((void**)&M->p2p_flags, 256);
+    want((void**)&M->p2p_stage, sizeof(float) * (M->n_int + 4 + 4 * 16));       // N slots of ceil(n / N) float4 each
     want((void**)&M->d_loss, sizeof(double) * 8);
     want((void**)&M->d_inv_n, sizeof(float) * 16);
     want((void**)&M->d_nvalid, sizeof(unsigned long long) * 16);
@@ -773,6 +775,7 @@ extern "C" int32_t dincae_model_destroy(dincae_model* M) {
     if (!M) return DINCAE_OK;
     cudaSetDevice(M->ctx->device);
     cudaStreamSynchronize(M->ctx->stream);
+    model_p2p_release(M);        // collective when the peers' workspaces are mapped (data-parallel training over peer memory)
     if (M->all_mem) cudaFree(M->all_mem);
     if (M->pt_buf) cudaFree(M->pt_buf);
     if (M->copy_stream) {
@@ -948,7 +951,7 @@ extern "C" int32_t dincae_train_step(dincae_model* M, const float* xin, const fl
 extern "C" int32_t dincae_allreduce_grads(dincae_model* M) {
     DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_allreduce_grads: model is NULL");
     DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
-    return dc_allreduce_on(M->ctx, M->g, M->n_int + 1, M->ctx->stream);
+    return model_allreduce_grads(M);
 }
 
 extern "C" int32_t dincae_train_step_dp(dincae_model* M, const float* xin, const float* xtrue, int32_t B, const int64_t* n_valid_global,

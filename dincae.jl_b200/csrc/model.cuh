@@ -33,6 +33,12 @@ struct ChainBufs {
 
 struct dincae_model {
     bool side_pending = false;   // weight gradients in flight on the context's side stream
+    // peer-memory all-reduce of the gradient buffer (p2p.cu): the other ranks' workspaces mapped through CUDA IPC
+    int p2p_state = 0;                 // 0 = not tried, 1 = ready, -1 = unavailable (NCCL is used)
+    void* p2p_peer_base[16] = {};      // peer rank -> its all_mem mapped here (own rank: all_mem)
+    uint32_t* p2p_flags = nullptr;     // this rank's flag words (inside all_mem, zero at creation)
+    float* p2p_stage = nullptr;        // this rank's staging area: the peers push their parts of this rank's slice here
+    uint32_t p2p_epoch = 0;
     bool dp_overlap = false;     // dincae_train_step_dp: all-reduce every chain's gradient bucket as soon as its backward pass ends
     int64_t chain_off[DINCAE_MAX_CHAINS + 1];     // parameter range of chain c in the flat buffers: [chain_off[c], chain_off[c+1])
     SplitTable split_chain[DINCAE_MAX_CHAINS];    // the split-operand layers of chain c
@@ -81,4 +87,9 @@ struct dincae_model {
 };
 
 int32_t model_forward(dincae_model* M, const float* d_xin, int B, bool train);
-int32_t model_head_last(dincae_model* M, int B, float* d_out);    // (m, sigma2) of the last chain into d_out (planar)
+int32_t model_head_last(dincae_model* M, int B, float* d_out);
+// SUM of M->g[0, n) over all ranks, in place, on the context's stream: two-shot all-reduce over NVLink peer memory when the ranks'
+// workspaces could be mapped (one process per GPU, CUDA IPC), else ncclAllReduce
+int32_t model_allreduce_grads(dincae_model* M);
+void model_p2p_release(dincae_model* M);
+int32_t model_p2p_check(dincae_model* M);    // (m, sigma2) of the last chain into d_out (planar)

@@ -162,11 +162,14 @@ int32_t dincae_apply_step(dincae_model* m, float lr, float* loss);
  *   comm_init_rank : collective over all ranks; binds the communicator to ctx's device.
  *   allreduce      : in-place SUM of a device buffer over all ranks, asynchronous on the context's stream.
  *   allreduce_grads: the same for the model's flat gradient buffer + loss slot (between grad_step* and apply_step).
- *   train_step_dp  : grad_step + all-reduce + apply_step with the exchange OVERLAPPED with the backward pass: the
- *                    gradients of refinement chain c are final once its backward pass ends (the chains run last to
- *                    first), so their bucket crosses NVLink on the communicator's stream while the earlier chains'
- *                    backward kernels still run.  n_valid_global as in grad_step (must not be NULL here).
- *                    Bit-identical replicas: every rank applies the same update to the same sums.
+ *   train_step_dp  : grad_step + all-reduce + apply_step in one call.  n_valid_global as in grad_step (must not be NULL here).
+ *                    From 4 ranks on the all-reduce is the library's own kernel over NVLink peer memory (the ranks'
+ *                    workspaces are mapped into each other with CUDA IPC at the first step: one process per GPU; reduce-
+ *                    scatter and all-gather as posted stores, two flag rounds; DINCAE_P2P=0/1 forces NCCL / this kernel);
+ *                    it falls back to ncclAllReduce when the mapping is not possible.  Every element is summed by one rank
+ *                    in rank order, so the replicas stay bit-identical.  While the mapping exists dincae_model_destroy is
+ *                    collective (every rank must call it).  DINCAE_DP_OVERLAP=1 selects per-chain NCCL buckets behind the
+ *                    backward pass instead (measured slower: the persistent kernels own every SM).
  *   train_step_dp_slot: the same on a mini-batch shard uploaded with dincae_batch_upload. */
 #define DINCAE_COMM_ID_BYTES 128
 int32_t dincae_comm_unique_id(void* id128);
