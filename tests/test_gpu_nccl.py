@@ -1,5 +1,6 @@
-"""Data-parallel training through the library's own NCCL collective on >= 2 GPUs (skipped on a one-GPU box): shards + the
-overlapped per-chain all-reduce reproduce single-GPU training on the whole mini-batch, and the replicas stay bit-identical."""
+"""Data-parallel training through the library's own collective on >= 2 GPUs (skipped on a one-GPU box): shards + the gradient
+all-reduce (NCCL, and the peer-memory kernel) reproduce single-GPU training on the whole mini-batch, and the replicas stay
+bit-identical."""
 import json
 import os
 import subprocess
@@ -11,14 +12,16 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 @pytest.mark.gpu
-def test_train_step_dp_equals_full_batch_and_replicas_identical():
+@pytest.mark.parametrize("p2p", ["0", "1"])          # ncclAllReduce / the library's all-reduce kernel over NVLink peer memory
+def test_train_step_dp_equals_full_batch_and_replicas_identical(p2p):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
     world = 2
     with tempfile.TemporaryDirectory() as d:
         procs = [subprocess.Popen([sys.executable, os.path.join(ROOT, "tests", "_nccl_worker.py"), str(r), str(world), d],
-                                  stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(world)]
+                                  stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=dict(os.environ, DINCAE_P2P=p2p))
+                 for r in range(world)]
         outs = [p.communicate(timeout=600)[0] for p in procs]
         assert all(p.returncode == 0 for p in procs), "\n".join(o[-3000:] for o in outs)
         res = [json.load(open(os.path.join(d, "rank%d.json" % r))) for r in range(world)]
