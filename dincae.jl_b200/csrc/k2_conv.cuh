@@ -118,6 +118,16 @@ bool k2_head_up_conv_eligible(int Cin, int nout2);
 int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, int B, int Hs, int Ws, int Cp, int Cin,
                         const float* wgt, int Cin_p, int Cout_p, const float* bias, int nout2, int H, int W, float* out,
                         double work_flops, double work_bytes);
+// Backward of the fused head, exact FP32 from the planar gradient g = d loss / d raw (nout2 channels at (H, W)):
+//   k2_head_bwd_data : G = up^T(conv^T(g)) at (Hs, Ws) with Cp channels, GD = G * act'(R) (TF32-rounded; R, G or GD may be NULL)
+//   k2_head_wgrad    : dW (padded layout, padding zeroed) and db of the head conv from the half-resolution source src0 (+ src1);
+//                      scratch holds the per-block partials (k2_head_bwd_scratch_bytes), summed in block order
+bool k2_head_bwd_eligible(int Cin, int nout2);
+size_t k2_head_bwd_scratch_bytes(int B, int Hs, int Ws, int Cin, int nout2);
+int32_t k2_head_bwd_data(dincae_ctx* ctx, const float* g, int B, int H, int W, int Hs, int Ws, const float* wgt, int Cin, int Cin_p, int Cout_p,
+                         int nout2, const float* R, float slope, int Cp, float* G, float* GD);
+int32_t k2_head_wgrad(dincae_ctx* ctx, const float* src0, const float* src1, const float* g, int B, int H, int W, int Hs, int Ws, int Cp, int Cin,
+                      int nout2, int Cin_p, int Cout_p, float* dW, float* db, void* scratch, size_t scratch_bytes);
 // planar (Julia WHCN) -> NHWC padded; channels [0,C0) from src0, [C0,C0+C1) from src1 (cat(xout,xin,dims=3), src/model.jl:186)
 // split != 0 (tensor-core mode, first conv of a chain): the C = C0 + C1 real channels are written twice as
 // [tf32(a) | tf32(a - tf32(a))], so that the conv multiplies the unrounded activation (a_hi + a_lo) * tf32(w); the matching

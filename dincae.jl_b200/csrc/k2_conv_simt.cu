@@ -922,6 +922,244 @@ __global__ void __launch_bounds__(256, 2) head_up_conv_kernel(const float* __res
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Backward of the fused head (adjoint of head_up_conv_kernel), exact FP32 on the CUDA cores, straight from the planar gradient
+// g = d loss / d raw (NO channels at full resolution):
+//
+// head_bwd_data_kernel: G[i,j,ci] = sum over the (up to) 2 x 2 output pixels (y,x) above low-resolution cell (i,j) and the nine
+//   taps of g[y-(dy-1), x-(dx-1), co] * w[tap][ci][co]  = data gradient of the conv followed by the adjoint of nearest up-sampling
+//   + crop; GD = G * act'(R) (rounded to TF32: it feeds the tensor-core convs of level 1).  One thread = one cell: it holds the
+//   4 x 4 x NO window of g that reaches the cell in registers and accumulates 32 input channels at a time against weights staged
+//   in shared memory ([combination][ci], 16-byte broadcast loads).  Replaces: pack(g) + data-gradient conv at full resolution +
+//   the 51 MB tensor between them + up-sampling backward.
+//   PHASE = true (even H, W): the taps that pair a window pixel with the cell are pre-summed (16 x NO weights per ci);
+//   PHASE = false: pixel by pixel with bounds (the cropped row / column of an odd size does not exist).
+template <int NO, bool PHASE>
+__global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restrict__ g, int B, int H, int W, int Hs, int Ws,
+                                                            const float* __restrict__ wgt, int Cin, int Cin_p, int Cout_p,
+                                                            const float* __restrict__ R, float slope, int Cp,
+                                                            float* __restrict__ G, float* __restrict__ GD, int rnd) {
+    extern __shared__ __align__(16) float hb_smem[];
+    constexpr int NC = (PHASE ? 16 : 9) * NO;                // weight rows (combinations) per input channel
+    const int Cr = (Cin + 31) & ~31;                         // row length: whole 32-channel chunks (zero padded)
+    dc_pdl_launch_dependents();
+    dc_pdl_wait();
+    const int t = threadIdx.x;
+    for (int i = t; i < NC * Cr; i += 256) {
+        const int ci = i % Cr, e = i / Cr, co = e % NO, k = e / NO;
+        float v = 0.f;
+        if (ci < Cin) {
+            const float* wc = wgt + (size_t)ci * Cout_p + co;
+            const size_t ts = (size_t)Cin_p * Cout_p;
+            if (PHASE) {
+                // window pixel (a, b) (row 2i-1+a, column 2j-1+b) reaches output pixel (2i+p, 2j+q) through tap dy = p - a + 2
+                const int a = k >> 2, b = k & 3;
+                for (int pp = 0; pp < 2; pp++)
+                    for (int q = 0; q < 2; q++) {
+                        const int dy = pp - a + 2, dx = q - b + 2;
+                        if (dy >= 0 && dy < 3 && dx >= 0 && dx < 3) v += __ldg(wc + (size_t)(dy * 3 + dx) * ts);
+                    }
+            } else {
+                v = __ldg(wc + (size_t)k * ts);
+            }
+        }
+        hb_smem[i] = v;
+    }
+    __syncthreads();
+    const int tilesx = (Ws + 31) / 32, tilesy = (Hs + 7) / 8;
+    int bid = blockIdx.x;
+    const int b = bid / (tilesx * tilesy);
+    bid -= b * tilesx * tilesy;
+    const int ci_ = (bid / tilesx) * 8 + (t >> 5), cj = (bid - (bid / tilesx) * tilesx) * 32 + (t & 31);
+    if (ci_ >= Hs || cj >= Ws) return;
+    float gw[4][4][NO];
+#pragma unroll
+    for (int a = 0; a < 4; a++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const int y = 2 * ci_ - 1 + a, x = 2 * cj - 1 + c;
+            const bool in = y >= 0 && y < H && x >= 0 && x < W;
+#pragma unroll
+            for (int o = 0; o < NO; o++) gw[a][c][o] = in ? __ldg(g + (((size_t)b * NO + o) * H + y) * W + x) : 0.f;
+        }
+    const bool rowB = 2 * ci_ + 1 < H, colB = 2 * cj + 1 < W;
+    const size_t cell = ((size_t)b * Hs + ci_) * Ws + cj;
+    for (int c0 = 0; c0 < Cp; c0 += 32) {
+        float acc[32];
+#pragma unroll
+        for (int k = 0; k < 32; k++) acc[k] = 0.f;
+        if (c0 < Cr) {
+            if (PHASE) {
+#pragma unroll
+                for (int a = 0; a < 4; a++)
+#pragma unroll
+                    for (int c = 0; c < 4; c++)
+#pragma unroll
+                        for (int o = 0; o < NO; o++) {
+                            const float x = gw[a][c][o];
+                            const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((a * 4 + c) * NO + o) * Cr + c0);
+#pragma unroll
+                            for (int k = 0; k < 8; k++) {
+                                const float4 w4 = wr[k];
+                                acc[4 * k] = fmaf(x, w4.x, acc[4 * k]); acc[4 * k + 1] = fmaf(x, w4.y, acc[4 * k + 1]);
+                                acc[4 * k + 2] = fmaf(x, w4.z, acc[4 * k + 2]); acc[4 * k + 3] = fmaf(x, w4.w, acc[4 * k + 3]);
+                            }
+                        }
+            } else {
+#pragma unroll
+                for (int pp = 0; pp < 2; pp++)
+#pragma unroll
+                    for (int q = 0; q < 2; q++) {
+                        if ((pp == 1 && !rowB) || (q == 1 && !colB)) continue;      // that output pixel was cropped
+#pragma unroll
+                        for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+                            for (int dx = 0; dx < 3; dx++)
+#pragma unroll
+                                for (int o = 0; o < NO; o++) {
+                                    const float x = gw[pp - dy + 2][q - dx + 2][o];
+                                    const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((dy * 3 + dx) * NO + o) * Cr + c0);
+#pragma unroll
+                                    for (int k = 0; k < 8; k++) {
+                                        const float4 w4 = wr[k];
+                                        acc[4 * k] = fmaf(x, w4.x, acc[4 * k]); acc[4 * k + 1] = fmaf(x, w4.y, acc[4 * k + 1]);
+                                        acc[4 * k + 2] = fmaf(x, w4.z, acc[4 * k + 2]); acc[4 * k + 3] = fmaf(x, w4.w, acc[4 * k + 3]);
+                                    }
+                                }
+                    }
+            }
+        }
+        const size_t off = cell * Cp + c0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            float4 v = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+            if (G) *reinterpret_cast<float4*>(G + off + 4 * k) = v;
+            if (GD) {
+                if (R) {
+                    const float4 rv = ldg4(R + off + 4 * k);
+                    v.x *= act_grad(rv.x, slope); v.y *= act_grad(rv.y, slope); v.z *= act_grad(rv.z, slope); v.w *= act_grad(rv.w, slope);
+                }
+                *reinterpret_cast<float4*>(GD + off + 4 * k) = round_tf32(v, rnd);
+            }
+        }
+    }
+}
+
+// head_wgrad_kernel: dW[tap][ci][co] = sum over pixels of U[y+dy-1, x+dx-1, ci] * g[y, x, co] with U = crop(upsample(s0 + s1)) never
+//   materialised: for a low-resolution cell the source value multiplies Gsum[tap][co] = the sum of g over the (up to four) pixels
+//   whose tap lands in that cell, so dW = sum over cells of S[cell][ci] x Gsum[cell][tap][co] -- an outer-product reduction with 4x
+//   fewer products than the pixel form.  One block = 8 x 32 cells: thread t < 256 prepares Gsum (and the bias partials) of cell t,
+//   the tile of S is staged pixel-major (no transposition), then thread (ci, tap) of each 32-channel chunk walks the 256 cells.
+//   Block partials [block][9*Cin*NO + NO] are summed in block order by head_wgrad_reduce_kernel: deterministic.
+template <int NO>
+__global__ void __launch_bounds__(288) head_wgrad_kernel(const float* __restrict__ s0, const float* __restrict__ s1, const float* __restrict__ g,
+                                                          int B, int H, int W, int Hs, int Ws, int Cp, int Cin, float* __restrict__ part) {
+    extern __shared__ __align__(16) float hw_smem[];
+    constexpr int NG = 9 * NO, NGP = (NG + 3) & ~3;          // Gsum row (padded to 16 bytes)
+    const int Cr = (Cin + 31) & ~31;
+    float* S = hw_smem;                                      // [256 cells][Cr]
+    float* Gs = hw_smem + 256 * Cr;                          // [256 cells][NGP]
+    float* bs = Gs + 256 * NGP;                              // [256 cells][NO] bias partials
+    const int t = threadIdx.x;
+    const int tilesx = (Ws + 31) / 32, tilesy = (Hs + 7) / 8;
+    int bid = blockIdx.x;
+    const int b = bid / (tilesx * tilesy);
+    bid -= b * tilesx * tilesy;
+    const int i0 = (bid / tilesx) * 8, j0 = (bid - (bid / tilesx) * tilesx) * 32;
+    // ---- S tile: 256 cells x Cr channels, float4 along channels
+    {
+        const int C4 = Cr >> 2;
+        for (int i = t; i < 256 * C4; i += 288) {
+            const int c4 = i % C4, cl = i / C4, ci_ = i0 + (cl >> 5), cj = j0 + (cl & 31);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ci_ < Hs && cj < Ws && 4 * c4 < Cp) {
+                const size_t off = (((size_t)b * Hs + ci_) * Ws + cj) * Cp + 4 * c4;
+                v = ldg4(s0 + off);
+                if (s1) { const float4 u = ldg4(s1 + off); v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w; }
+            }
+            *reinterpret_cast<float4*>(S + (size_t)cl * Cr + 4 * c4) = v;
+        }
+    }
+    // ---- Gsum and bias partials of every cell
+    if (t < 256) {
+        const int ci_ = i0 + (t >> 5), cj = j0 + (t & 31);
+        float gw[4][4][NO];
+#pragma unroll
+        for (int a = 0; a < 4; a++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int y = 2 * ci_ - 1 + a, x = 2 * cj - 1 + c;
+                const bool in = ci_ < Hs && cj < Ws && y >= 0 && y < H && x >= 0 && x < W;
+#pragma unroll
+                for (int o = 0; o < NO; o++) gw[a][c][o] = in ? __ldg(g + (((size_t)b * NO + o) * H + y) * W + x) : 0.f;
+            }
+        // pixel (y, x) = window (a, c) meets this cell through tap dy iff Y = y + dy - 1 is an existing row of U with Y >> 1 == cell row:
+        // Y in {2i, 2i+1} (2i+1 only if it is < H)  =>  a = Y - (dy - 1) - (2i - 1) = (Y - 2i) - dy + 2
+#pragma unroll
+        for (int dy = 0; dy < 3; dy++)
+#pragma unroll
+            for (int dx = 0; dx < 3; dx++)
+#pragma unroll
+                for (int o = 0; o < NO; o++) {
+                    float sum = 0.f;
+#pragma unroll
+                    for (int pp = 0; pp < 2; pp++)
+#pragma unroll
+                        for (int q = 0; q < 2; q++) {
+                            const bool ok = (pp == 0 || 2 * ci_ + 1 < H) && (q == 0 || 2 * cj + 1 < W);
+                            sum += ok ? gw[pp - dy + 2][q - dx + 2][o] : 0.f;
+                        }
+                    Gs[(size_t)t * NGP + (dy * 3 + dx) * NO + o] = sum;
+                }
+#pragma unroll
+        for (int o = 0; o < NO; o++) bs[t * NO + o] = gw[1][1][o] + gw[1][2][o] + gw[2][1][o] + gw[2][2][o];     // the cell's own pixels (zero where outside)
+    }
+    __syncthreads();
+    float* pb = part + (size_t)blockIdx.x * (9 * Cin * NO + NO);
+    const int lane_c = t & 31, tap = t >> 5;                 // 288 threads = 32 channels x 9 taps
+    for (int c0 = 0; c0 < Cr; c0 += 32) {
+        float acc[NO];
+#pragma unroll
+        for (int o = 0; o < NO; o++) acc[o] = 0.f;
+#pragma unroll 4
+        for (int cl = 0; cl < 256; cl++) {
+            const float sv = S[(size_t)cl * Cr + c0 + lane_c];
+#pragma unroll
+            for (int o = 0; o < NO; o++) acc[o] = fmaf(sv, Gs[(size_t)cl * NGP + tap * NO + o], acc[o]);
+        }
+        if (c0 + lane_c < Cin) {
+#pragma unroll
+            for (int o = 0; o < NO; o++) pb[((size_t)tap * Cin + c0 + lane_c) * NO + o] = acc[o];
+        }
+    }
+    if (t < NO) {
+        float sum = 0.f;
+        for (int cl = 0; cl < 256; cl++) sum += bs[cl * NO + t];
+        pb[9 * Cin * NO + t] = sum;
+    }
+}
+
+// second stage: one warp per gradient value sums its column of the block partials (lane k takes blocks k, k+32, ... in order, then a
+// fixed shuffle tree: deterministic) and writes it at its place in the padded layout [9*Cin_p][Cout_p] / db (zeroed beforehand)
+__global__ void __launch_bounds__(256) head_wgrad_reduce_kernel(const float* __restrict__ part, int nblocks, int Cin, int NO, int Cin_p, int Cout_p,
+                                                                float* __restrict__ dW, float* __restrict__ db) {
+    const int rowlen = 9 * Cin * NO + NO;
+    const int v = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (v >= rowlen) return;
+    float s = 0.f;
+    for (int k = lane; k < nblocks; k += 32) s += part[(size_t)k * rowlen + v];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+        if (v < 9 * Cin * NO) {
+            const int co = v % NO, r = v / NO, ci = r % Cin, tap = r / Cin;
+            dW[((size_t)tap * Cin_p + ci) * Cout_p + co] = s;
+        } else {
+            db[v - 9 * Cin * NO] = s;
+        }
+    }
+}
+
 // expanded K-major forward weights of the 3xTF32 layers (layout: SplitLayerDesc in k2_conv.cuh); one layer per blockIdx.y
 __global__ void __launch_bounds__(256) make_wK_split_kernel(const float* __restrict__ w, float* __restrict__ wK, const __grid_constant__ SplitTable tab) {
     const SplitLayerDesc L = tab.d[blockIdx.y];
@@ -1006,6 +1244,64 @@ int32_t k2_head_up_conv(dincae_ctx* ctx, const float* src0, const float* src1, i
     else HU_PICK(8);
 #undef HU_PICK
 #undef HU_LAUNCH
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+size_t k2_head_bwd_scratch_bytes(int B, int Hs, int Ws, int Cin, int nout2) {
+    const size_t nblocks = (size_t)B * ((Ws + 31) / 32) * ((Hs + 7) / 8);
+    return nblocks * (size_t)(9 * Cin * nout2 + nout2) * sizeof(float);
+}
+bool k2_head_bwd_eligible(int Cin, int nout2) {
+    const int Cr = (Cin + 31) & ~31;
+    return (nout2 == 2 || nout2 == 4) && (size_t)16 * nout2 * Cr * sizeof(float) <= 96 * 1024 &&
+           (size_t)(256 * Cr + 256 * ((9 * nout2 + 3) & ~3) + 256 * nout2) * sizeof(float) <= 200 * 1024;
+}
+int32_t k2_head_bwd_data(dincae_ctx* ctx, const float* g, int B, int H, int W, int Hs, int Ws, const float* wgt, int Cin, int Cin_p, int Cout_p,
+                         int nout2, const float* R, float slope, int Cp, float* G, float* GD) {
+    if ((int64_t)B * Hs * Ws == 0) return DINCAE_OK;
+    DC_REQUIRE(k2_head_bwd_eligible(Cin, nout2), DINCAE_EUNSUPPORTED, "k2_head_bwd_data: %d input / %d output channels not supported", Cin, nout2);
+    DC_REQUIRE((Cp % 32) == 0, DINCAE_EINVAL, "k2_head_bwd_data: %d channels are not whole 32-channel chunks", Cp);
+    const bool phase = (H % 2) == 0 && (W % 2) == 0;
+    const int Cr = (Cin + 31) & ~31;
+    const int smem = (int)((size_t)(phase ? 16 : 9) * nout2 * Cr * sizeof(float));
+    const unsigned grid = (unsigned)(B * ((Ws + 31) / 32) * ((Hs + 7) / 8));
+    DC_WORK(ctx, 2.0 * 9 * Cin * nout2 * (double)B * H * W, 4.0 * ((double)nout2 * B * H * W + (double)Cp * B * Hs * Ws * ((G ? 1 : 0) + (GD ? 1 : 0) + (R ? 1 : 0))));
+#define HB_LAUNCH(NO_, PH_)                                                                                                  \
+    do {                                                                                                                     \
+        static int attr = 0;                                                                                                 \
+        auto head_bwd_data = head_bwd_data_kernel<NO_, PH_>;                                                                 \
+        if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_bwd_data, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
+        DC_LAUNCH_PDL(ctx, head_bwd_data, grid, 256, smem, g, B, H, W, Hs, Ws, wgt, Cin, Cin_p, Cout_p, R, slope, Cp, G, GD, (int)ctx->tf32_acts); \
+    } while (0)
+    if (nout2 == 2) { if (phase) HB_LAUNCH(2, true); else HB_LAUNCH(2, false); }
+    else { if (phase) HB_LAUNCH(4, true); else HB_LAUNCH(4, false); }
+#undef HB_LAUNCH
+    DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+int32_t k2_head_wgrad(dincae_ctx* ctx, const float* src0, const float* src1, const float* g, int B, int H, int W, int Hs, int Ws, int Cp, int Cin,
+                      int nout2, int Cin_p, int Cout_p, float* dW, float* db, void* scratch, size_t scratch_bytes) {
+    if ((int64_t)B * Hs * Ws == 0) return DINCAE_OK;
+    DC_REQUIRE(k2_head_bwd_eligible(Cin, nout2), DINCAE_EUNSUPPORTED, "k2_head_wgrad: %d input / %d output channels not supported", Cin, nout2);
+    DC_REQUIRE(scratch_bytes >= k2_head_bwd_scratch_bytes(B, Hs, Ws, Cin, nout2), DINCAE_ESIZE, "k2_head_wgrad: scratch too small");
+    const int Cr = (Cin + 31) & ~31;
+    const int smem = (int)((size_t)(256 * Cr + 256 * ((9 * nout2 + 3) & ~3) + 256 * nout2) * sizeof(float));
+    const unsigned grid = (unsigned)(B * ((Ws + 31) / 32) * ((Hs + 7) / 8));
+    DC_WORK(ctx, 2.0 * 9 * Cin * nout2 * (double)B * H * W, 4.0 * ((double)nout2 * B * H * W + (double)Cin * B * Hs * Ws * (src1 ? 2 : 1)));
+#define HW_LAUNCH(NO_)                                                                                                       \
+    do {                                                                                                                     \
+        static int attr = 0;                                                                                                 \
+        auto head_wgrad = head_wgrad_kernel<NO_>;                                                                            \
+        if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
+        DC_LAUNCH(ctx, head_wgrad, grid, 288, smem, src0, src1, g, B, H, W, Hs, Ws, Cp, Cin, (float*)scratch);               \
+    } while (0)
+    if (nout2 == 2) HW_LAUNCH(2); else HW_LAUNCH(4);
+#undef HW_LAUNCH
+    DC_CHECK_LAUNCH();
+    DC_CHECK_CUDA(cudaMemsetAsync(dW, 0, sizeof(float) * 9 * (size_t)Cin_p * Cout_p, ctx->stream));        // the padding entries stay exactly zero
+    DC_CHECK_CUDA(cudaMemsetAsync(db, 0, sizeof(float) * Cout_p, ctx->stream));
+    DC_LAUNCH(ctx, head_wgrad_reduce_kernel, (unsigned)dc_cdiv(9 * Cin * nout2 + nout2, 8), 256, 0, (const float*)scratch, (int)grid, Cin, nout2, Cin_p, Cout_p, dW, db);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }

@@ -56,6 +56,10 @@ inline bool head_fused(const dincae_model* M) {
     return M->wK != nullptr && M->cfg.upsampling == DINCAE_UP_NEAREST && k2_head_up_conv_eligible(M->dec[0][0].Cin, 2 * M->O);
 }
 
+// ... and so does its backward pass: data gradient + up-sampling backward in one FP32 kernel straight from the planar loss
+// gradient, weight gradient from the half-resolution source (U[0], GD0 and GU[0] are never written)
+inline bool head_bwd_fused(const dincae_model* M) { return head_fused(M) && k2_head_bwd_eligible(M->dec[0][0].Cin, 2 * M->O); }
+
 // the producer of conv_dec_l: upsample(+crop) of y_{l+1} = R[l+1] (+ X[l+1] when level l+1 has a skip) or X[L]
 int32_t dec_source(dincae_model* M, int c, int l, int B, bool materialise, ConvSrc* s) {
     ChainBufs& cb = M->cb[c];
@@ -236,13 +240,37 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
     const float slope = M->cfg.leaky_slope;
     const bool nearest = M->cfg.upsampling == DINCAE_UP_NEAREST;
     // ---- decoder, top (l = 0) to bottom
-    DC_TRY(k2_pack(ctx, cb.GRAW, 2 * M->O, nullptr, 0, B, M->Hl[0], M->Wl[0], M->GD0, M->nco));
-    for (int l = 0; l < L; l++) {
+    const bool hbf = head_bwd_fused(M);
+    if (hbf) {
+        // head layer: weight gradient on the side stream, data gradient + up^T (+ relu' of level 1) on the main stream
+        const LayerInfo& d = M->dec[c][0];
+        const float* src0 = (L == 1) ? cb.X[1] : cb.R[1];
+        const float* src1 = has_skip(M, 1) ? cb.X[1] : nullptr;
+        const size_t need = (k2_head_bwd_scratch_bytes(B, M->Hl[1], M->Wl[1], d.Cin, 2 * M->O) + 255) / 256 * 256;
+        DC_REQUIRE(M->wg_off + need <= M->wg_scratch_bytes, DINCAE_ESIZE, "weight-gradient scratch arena exhausted");
+        const bool side = side_stream_on() && !ctx->prof;
+        cudaStream_t main_stream = ctx->stream;
+        if (side) {
+            DC_TRY(wgrad_fork(ctx));
+            ctx->stream = ctx->side;
+            M->side_pending = true;
+        }
+        int32_t st = k2_head_wgrad(ctx, src0, src1, cb.GRAW, B, M->Hl[0], M->Wl[0], M->Hl[1], M->Wl[1], d.Cin_p, d.Cin, 2 * M->O, d.Cin_p, d.Cout_p,
+                                   M->g + d.w_off, M->g + d.b_off, (char*)M->wg_scratch + M->wg_off, need);
+        ctx->stream = main_stream;
+        M->wg_off += need;
+        DC_TRY(st);
+        DC_TRY(k2_head_bwd_data(ctx, cb.GRAW, B, M->Hl[0], M->Wl[0], M->Hl[1], M->Wl[1], M->w + d.w_off, d.Cin, d.Cin_p, d.Cout_p, 2 * M->O,
+                                L == 1 ? nullptr : cb.R[1], slope, d.Cin_p, M->G[1], L == 1 ? nullptr : M->GD[1]));
+    } else {
+        DC_TRY(k2_pack(ctx, cb.GRAW, 2 * M->O, nullptr, 0, B, M->Hl[0], M->Wl[0], M->GD0, M->nco));
+    }
+    for (int l = hbf ? 1 : 0; l < L; l++) {
         const LayerInfo& d = M->dec[c][l];
         const float* gd = (l == 0) ? M->GD0 : M->GD[l];
         float* colpart = nullptr;
         int colblocks = 0;
-        if (l > 0) {
+        if (l > 0 && !(hbf && l == 1)) {
             // G[l] = up^T(GU[l-1]); GD[l] = G[l] * relu'(R[l])  (+ per-block column sums of GD[l] = first stage of the bias gradient)
             if (nearest) {
                 colpart = colpart_alloc(M, (int64_t)B * M->Hl[l] * M->Wl[l] * (d.Cout_p / 4), d.Cout_p, &colblocks);
@@ -271,7 +299,7 @@ int32_t chain_backward(dincae_model* M, int c, int B) {
         a.work_bytes = cbytes(d, B, M->Hl[l], M->Wl[l]);
         DC_TRY(k2_conv(ctx, a));
     }
-    {   // G[L] = gradient w.r.t. X[L] (the innermost level is the identity, src/model.jl:263-264)
+    if (!(hbf && L == 1)) {   // G[L] = gradient w.r.t. X[L] (the innermost level is the identity, src/model.jl:263-264)
         const LayerInfo& d = M->dec[c][L - 1];
         if (nearest) DC_TRY(k2_upbwd(ctx, M->GU[L - 1], B, M->Hl[L - 1], M->Wl[L - 1], d.Cin_p, nullptr, slope, M->G[L], nullptr));
         else DC_TRY(k2_up_bilinear_bwd(ctx, M->GU[L - 1], B, M->Hl[L - 1], M->Wl[L - 1], d.Cin_p, M->Hl[L], M->Wl[L], nullptr, slope, M->G[L], nullptr));
@@ -746,6 +774,7 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
             size_t tb = k2_wgrad_tma_scratch_bytes(ctx->num_sms, M->maxB, M->Hl[l], M->Wl[l], M->dec[c][l].Cin_pe, M->dec[c][l].Cout_p);
             wg_sum += ((ta + 255) / 256 * 256) + ((tb + 255) / 256 * 256);
             wg_sum += 2 * (((size_t)8 * ctx->num_sms * 512 * sizeof(float) + 255) / 256 * 256);      // bias column partials of both layers
+            if (l == 0) wg_sum += (k2_head_bwd_scratch_bytes(M->maxB, M->Hl[1], M->Wl[1], M->dec[c][0].Cin, 2 * M->O) + 255) / 256 * 256;   // fused head
         }
     if (tc_mode && wg_sum > wgb) wgb = wg_sum;    // TF32 mode: one slice per layer (second stages are batched)
     M->wg_scratch_bytes = wgb;
