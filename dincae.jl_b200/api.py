@@ -330,6 +330,13 @@ class Model:
                                             C.byref(out) if want_loss else None))
         return out.value if want_loss else None
 
+    def step_graph(self, enable=None):
+        """Switch the CUDA-graph replay of the gridded gradient step on/off for this model (None: only query);
+        returns the number of captured graphs (dincae_model_step_graph)."""
+        n = C.c_int32()
+        L.check(self._lib.dincae_model_step_graph(self.handle, -1 if enable is None else int(bool(enable)), C.byref(n)))
+        return n.value
+
     def upload(self, slot, xin, xtrue):
         """Start the host->device copy of a mini-batch into prefetch slot 0/1 (PrefetchDataIter, src/data.jl:872-904)."""
         xin = _f32(xin); xtrue = _f32(xtrue)

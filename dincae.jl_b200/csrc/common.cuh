@@ -71,10 +71,31 @@ void dincae_set_error(const char* fmt, ...);
 
 static inline int dc_env_int_early(const char* name, int dflt) { const char* e = getenv(name); return e ? atoi(e) : dflt; }
 // every kernel launch of the library goes through this so that gpu_launches is a count, not a guess
+// Measurement builds only (-DDINCAE_ABLATE, scripts/ablate.py): DINCAE_ABLATE=name[,name] drops the launches whose kernel expression
+// contains one of the names, so that the step-time difference gives the cost a kernel really has inside the overlapped step
+// (results are garbage).  The shipped library is built without the flag and has no such switch.
+#ifdef DINCAE_ABLATE
+static inline bool dc_ablated(const char* name) {
+    const char* e = getenv("DINCAE_ABLATE");
+    if (!e || !*e) return false;
+    std::string list(e);
+    size_t pos = 0;
+    while (pos <= list.size()) {
+        size_t c = list.find(',', pos);
+        if (c == std::string::npos) c = list.size();
+        if (c > pos && strstr(name, list.substr(pos, c - pos).c_str())) return true;
+        pos = c + 1;
+    }
+    return false;
+}
+#define DC_ABLATED(kernel) ([] { static const bool s = dc_ablated(#kernel); return s; }())
+#else
+#define DC_ABLATED(kernel) false
+#endif
 #define DC_LAUNCH(ctx, kernel, grid, block, smem, ...)                        \
     do {                                                                      \
         if ((ctx)->prof) dc_prof_begin((ctx), #kernel);                       \
-        kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);      \
+        if (!DC_ABLATED(kernel)) kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);      \
         if ((ctx)->prof) dc_prof_end((ctx));                                  \
         (ctx)->cur_flops = 0.0;                                               \
         (ctx)->cur_bytes = 0.0;                                               \
@@ -94,7 +115,7 @@ static inline bool dc_pdl_on() { static const int on = dc_env_int_early("DINCAE_
         _at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                            \
         _at[0].val.programmaticStreamSerializationAllowed = 1;                                     \
         _cfg.attrs = _at; _cfg.numAttrs = (dc_pdl_on() && !(ctx)->prof) ? 1 : 0;                   \
-        cudaLaunchKernelEx(&_cfg, kernel, __VA_ARGS__);                                            \
+        if (!DC_ABLATED(kernel)) cudaLaunchKernelEx(&_cfg, kernel, __VA_ARGS__);                   \
         if ((ctx)->prof) dc_prof_end((ctx));                                                       \
         (ctx)->cur_flops = 0.0;                                                                    \
         (ctx)->cur_bytes = 0.0;                                                                    \

@@ -469,8 +469,10 @@ __device__ __forceinline__ void block_colpart(float4 acc, int C4, int Cp, float*
     }
 }
 
+constexpr int LV_U = 1;      // cells per thread and iteration of the 4-load adjoint kernel
+constexpr int LV_V = 1;      // ... of the 1- and 2-load kernels
 // gu at (H,W); outputs at (Hs,Ws) = (H/2 + H%2, W/2 + W%2)
-__global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
+__global__ void __launch_bounds__(256, 8) upbwd_kernel(const float* __restrict__ gu, int B, int H, int W, int Cp, int Hs, int Ws,
                                                     const float* __restrict__ r, float slope, float* __restrict__ G, float* __restrict__ gd, int rnd,
                                                     float* __restrict__ colpart) {
     dc_pdl_launch_dependents();
@@ -485,25 +487,43 @@ __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu
             const float* ra = gu + ((size_t)b * H + ya) * W * Cp;
             const float* rb = gu + ((size_t)b * H + (yb < H ? yb : ya)) * W * Cp;
             const size_t ro = (size_t)row * Ws * Cp;
+            // LV_U cells per thread and iteration, every load issued before the first use: these kernels are bound by the number
+            // of memory round trips a thread makes one after the other, not by bandwidth
             for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
-                for (int xs = rt.lane; xs < Ws; xs += rt.PL) {
-                    const int xa = 2 * xs, xb = xa + 1;
-                    float4 s = ldg4(ra + (size_t)xa * Cp + c4 * 4);
-                    if (xb < W) { float4 v = ldg4(ra + (size_t)xb * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
-                    if (yb < H) {
-                        float4 v = ldg4(rb + (size_t)xa * Cp + c4 * 4); s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-                        if (xb < W) { float4 u = ldg4(rb + (size_t)xb * Cp + c4 * 4); s.x += u.x; s.y += u.y; s.z += u.z; s.w += u.w; }
+                for (int x0 = rt.lane; x0 < Ws; x0 += LV_U * rt.PL) {
+                    float4 va[LV_U], vb[LV_U], vc[LV_U], vd[LV_U], rv[LV_U];
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int k = 0; k < LV_U; k++) {
+                        const int xs = x0 + k * rt.PL, xa = 2 * xs, xb = xa + 1;
+                        const bool in = xs < Ws;
+                        va[k] = in ? ldg4(ra + (size_t)xa * Cp + c4 * 4) : z4;
+                        vb[k] = in && xb < W ? ldg4(ra + (size_t)xb * Cp + c4 * 4) : z4;
+                        vc[k] = in && yb < H ? ldg4(rb + (size_t)xa * Cp + c4 * 4) : z4;
+                        vd[k] = in && yb < H && xb < W ? ldg4(rb + (size_t)xb * Cp + c4 * 4) : z4;
+                        rv[k] = in && gd && r ? ldg4(r + ro + (size_t)xs * Cp + c4 * 4) : z4;
                     }
-                    const size_t off = ro + (size_t)xs * Cp + c4 * 4;
-                    if (G) *reinterpret_cast<float4*>(G + off) = s;
-                    if (gd) {
-                        if (r) {
-                            float4 rv = ldg4(r + off);
-                            s.x *= act_grad(rv.x, slope); s.y *= act_grad(rv.y, slope); s.z *= act_grad(rv.z, slope); s.w *= act_grad(rv.w, slope);
+#pragma unroll
+                    for (int k = 0; k < LV_U; k++) {
+                        const int xs = x0 + k * rt.PL, xb = 2 * xs + 1;
+                        if (xs >= Ws) break;
+                        float4 s = va[k];
+                        if (xb < W) { s.x += vb[k].x; s.y += vb[k].y; s.z += vb[k].z; s.w += vb[k].w; }
+                        if (yb < H) {
+                            s.x += vc[k].x; s.y += vc[k].y; s.z += vc[k].z; s.w += vc[k].w;
+                            if (xb < W) { s.x += vd[k].x; s.y += vd[k].y; s.z += vd[k].z; s.w += vd[k].w; }
                         }
-                        s = round_tf32(s, rnd);
-                        *reinterpret_cast<float4*>(gd + off) = s;
-                        cacc.x += s.x; cacc.y += s.y; cacc.z += s.z; cacc.w += s.w;
+                        const size_t off = ro + (size_t)xs * Cp + c4 * 4;
+                        if (G) *reinterpret_cast<float4*>(G + off) = s;
+                        if (gd) {
+                            if (r) {
+                                s.x *= act_grad(rv[k].x, slope); s.y *= act_grad(rv[k].y, slope);
+                                s.z *= act_grad(rv[k].z, slope); s.w *= act_grad(rv[k].w, slope);
+                            }
+                            s = round_tf32(s, rnd);
+                            *reinterpret_cast<float4*>(gd + off) = s;
+                            cacc.x += s.x; cacc.y += s.y; cacc.z += s.z; cacc.w += s.w;
+                        }
                     }
                 }
         }
@@ -513,7 +533,7 @@ __global__ void __launch_bounds__(256) upbwd_kernel(const float* __restrict__ gu
 
 // act'(a) comes either from the stored activation `a` or, when the conv epilogue kept only its sign bits, from `mask`
 // (word [pixel][Cp / 32], bit c % 32 set <=> a[pixel][c] > 0)
-__global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, const uint32_t* __restrict__ mask,
+__global__ void __launch_bounds__(256, 8) poolbwd_kernel(const float* __restrict__ xg, const float* __restrict__ a, const uint32_t* __restrict__ mask,
                                                       int B, int H, int W, int Cp,
                                                       int H2, int W2, float slope, float* __restrict__ gc, int rnd, float* __restrict__ colpart) {
     dc_pdl_launch_dependents();
@@ -528,21 +548,34 @@ __global__ void __launch_bounds__(256) poolbwd_kernel(const float* __restrict__ 
             const float* rx = xg + ((size_t)b * H2 + ((y + oh) >> 1)) * W2 * Cp;
             const size_t ro = (size_t)row * W * Cp;
             for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
-                for (int x = rt.lane; x < W; x += rt.PL) {
-                    float4 g = ldg4(rx + (size_t)((x + ow) >> 1) * Cp + c4 * 4);
-                    const size_t off = ro + (size_t)x * Cp + c4 * 4;
-                    if (mask) {
-                        const uint32_t bits = __ldg(mask + ((size_t)row * W + x) * (Cp >> 5) + (c4 >> 3)) >> ((c4 & 7) * 4);
-                        g.x *= 0.25f * ((bits & 1u) ? 1.f : slope); g.y *= 0.25f * ((bits & 2u) ? 1.f : slope);
-                        g.z *= 0.25f * ((bits & 4u) ? 1.f : slope); g.w *= 0.25f * ((bits & 8u) ? 1.f : slope);
-                    } else {
-                        const float4 av = ldg4(a + off);
-                        g.x *= 0.25f * act_grad(av.x, slope); g.y *= 0.25f * act_grad(av.y, slope);
-                        g.z *= 0.25f * act_grad(av.z, slope); g.w *= 0.25f * act_grad(av.w, slope);
+                for (int x0 = rt.lane; x0 < W; x0 += LV_V * rt.PL) {
+                    float4 gv[LV_V], av[LV_V];
+                    uint32_t bits[LV_V];
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int k = 0; k < LV_V; k++) {                       // all loads of LV_V cells first (see upbwd_kernel)
+                        const int x = x0 + k * rt.PL;
+                        const bool in = x < W;
+                        gv[k] = in ? ldg4(rx + (size_t)((x + ow) >> 1) * Cp + c4 * 4) : z4;
+                        if (mask) bits[k] = in ? __ldg(mask + ((size_t)row * W + x) * (Cp >> 5) + (c4 >> 3)) >> ((c4 & 7) * 4) : 0u;
+                        else av[k] = in ? ldg4(a + ro + (size_t)x * Cp + c4 * 4) : z4;
                     }
-                    g = round_tf32(g, rnd);
-                    *reinterpret_cast<float4*>(gc + off) = g;
-                    cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
+#pragma unroll
+                    for (int k = 0; k < LV_V; k++) {
+                        const int x = x0 + k * rt.PL;
+                        if (x >= W) break;
+                        float4 g = gv[k];
+                        if (mask) {
+                            g.x *= 0.25f * ((bits[k] & 1u) ? 1.f : slope); g.y *= 0.25f * ((bits[k] & 2u) ? 1.f : slope);
+                            g.z *= 0.25f * ((bits[k] & 4u) ? 1.f : slope); g.w *= 0.25f * ((bits[k] & 8u) ? 1.f : slope);
+                        } else {
+                            g.x *= 0.25f * act_grad(av[k].x, slope); g.y *= 0.25f * act_grad(av[k].y, slope);
+                            g.z *= 0.25f * act_grad(av[k].z, slope); g.w *= 0.25f * act_grad(av[k].w, slope);
+                        }
+                        g = round_tf32(g, rnd);
+                        *reinterpret_cast<float4*>(gc + ro + (size_t)x * Cp + c4 * 4) = g;
+                        cacc.x += g.x; cacc.y += g.y; cacc.z += g.z; cacc.w += g.w;
+                    }
                 }
         }
     }
@@ -596,7 +629,7 @@ __global__ void up_bilinear_kernel(const float* __restrict__ s0, const float* __
     }
 }
 // one thread per SOURCE cell: the (optionally summed) value is read once and written to its 2 x 2 (cropped) destination cells
-__global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
+__global__ void __launch_bounds__(256, 8) up_nearest_kernel(const float* __restrict__ s0, const float* __restrict__ s1, int B, int Hs, int Ws, int Cp,
                                                          int H, int W, float* __restrict__ dst, int rnd, int split) {
     dc_pdl_launch_dependents();
     dc_pdl_wait();
@@ -612,12 +645,23 @@ __global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict
         float* da = dst + ((size_t)b * H + ya) * W * Cd;
         float* db = yb < H ? dst + ((size_t)b * H + yb) * W * Cd : nullptr;
         for (int c4 = rt.c4; c4 < C4; c4 += rt.CW)
-            for (int xs = rt.lane; xs < Ws; xs += rt.PL) {
+          for (int x0 = rt.lane; x0 < Ws; x0 += LV_V * rt.PL) {
+            float4 v0[LV_V], v1[LV_V];
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < LV_V; k++) {                               // all loads of LV_V cells first (see upbwd_kernel)
+                const int xs = x0 + k * rt.PL;
+                const bool in = xs < Ws && 2 * xs < W;
+                v0[k] = in ? ldg4(s0 + rs + (size_t)xs * Cp + c4 * 4) : z4;
+                v1[k] = in && s1 ? ldg4(s1 + rs + (size_t)xs * Cp + c4 * 4) : z4;
+            }
+#pragma unroll
+            for (int k = 0; k < LV_V; k++) {
+                const int xs = x0 + k * rt.PL;
                 const int xa = 2 * xs, xb = xa + 1;
-                if (xa >= W) continue;
-                const size_t off = rs + (size_t)xs * Cp + c4 * 4;
-                float4 v = ldg4(s0 + off);
-                if (s1) { float4 w = ldg4(s1 + off); v.x += w.x; v.y += w.y; v.z += w.z; v.w += w.w; }
+                if (xs >= Ws || xa >= W) break;
+                float4 v = v0[k];
+                if (s1) { v.x += v1[k].x; v.y += v1[k].y; v.z += v1[k].z; v.w += v1[k].w; }
                 const float4 full = v;
                 v = round_tf32(v, rnd);
                 *reinterpret_cast<float4*>(da + (size_t)xa * Cd + c4 * 4) = v;
@@ -636,6 +680,7 @@ __global__ void __launch_bounds__(256) up_nearest_kernel(const float* __restrict
                     }
                 }
             }
+          }
     }
 }
 // transpose: each low-res cell gathers from the high-res cells whose stencil touches it (deterministic)
@@ -928,24 +973,28 @@ __global__ void __launch_bounds__(256, 2) head_up_conv_kernel(const float* __res
 //
 // head_bwd_data_kernel: G[i,j,ci] = sum over the (up to) 2 x 2 output pixels (y,x) above low-resolution cell (i,j) and the nine
 //   taps of g[y-(dy-1), x-(dx-1), co] * w[tap][ci][co]  = data gradient of the conv followed by the adjoint of nearest up-sampling
-//   + crop; GD = G * act'(R) (rounded to TF32: it feeds the tensor-core convs of level 1).  One thread = one cell: it holds the
-//   4 x 4 x NO window of g that reaches the cell in registers and accumulates 32 input channels at a time against weights staged
+//   + crop; GD = G * act'(R) (rounded to TF32: it feeds the tensor-core convs of level 1).  HB_LPC lanes share one cell: each holds the
+//   4 x 4 x NO window of g that reaches the cell in registers and accumulates its 32 / HB_LPC channels of a chunk against weights staged
 //   in shared memory ([combination][ci], 16-byte broadcast loads).  Replaces: pack(g) + data-gradient conv at full resolution +
 //   the 51 MB tensor between them + up-sampling backward.
 //   PHASE = true (even H, W): the taps that pair a window pixel with the cell are pre-summed (16 x NO weights per ci);
 //   PHASE = false: pixel by pixel with bounds (the cropped row / column of an odd size does not exist).
+constexpr int HB_LPC = 1;                                    // lanes that share one cell (each owns 32 / HB_LPC channels of a chunk)
+constexpr int HB_THREADS = 128;
+constexpr int HB_ROWS = HB_THREADS / HB_LPC / 32;            // block tile: HB_ROWS x 32 cells
 template <int NO, bool PHASE>
-__global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restrict__ g, int B, int H, int W, int Hs, int Ws,
-                                                            const float* __restrict__ wgt, int Cin, int Cin_p, int Cout_p,
-                                                            const float* __restrict__ R, float slope, int Cp,
-                                                            float* __restrict__ G, float* __restrict__ GD, int rnd) {
+__global__ void __launch_bounds__(HB_THREADS, 768 / HB_THREADS) head_bwd_data_kernel(const float* __restrict__ g, int B, int H, int W, int Hs, int Ws,
+                                                                       const float* __restrict__ wgt, int Cin, int Cin_p, int Cout_p,
+                                                                       const float* __restrict__ R, float slope, int Cp,
+                                                                       float* __restrict__ G, float* __restrict__ GD, int rnd) {
     extern __shared__ __align__(16) float hb_smem[];
     constexpr int NC = (PHASE ? 16 : 9) * NO;                // weight rows (combinations) per input channel
+    constexpr int NQ = 8 / HB_LPC;                           // 16-byte channel groups per lane and chunk: groups sub, sub + HB_LPC, ...
     const int Cr = (Cin + 31) & ~31;                         // row length: whole 32-channel chunks (zero padded)
     dc_pdl_launch_dependents();
     dc_pdl_wait();
     const int t = threadIdx.x;
-    for (int i = t; i < NC * Cr; i += 256) {
+    for (int i = t; i < NC * Cr; i += HB_THREADS) {
         const int ci = i % Cr, e = i / Cr, co = e % NO, k = e / NO;
         float v = 0.f;
         if (ci < Cin) {
@@ -966,11 +1015,14 @@ __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restr
         hb_smem[i] = v;
     }
     __syncthreads();
-    const int tilesx = (Ws + 31) / 32, tilesy = (Hs + 7) / 8;
+    // HB_LPC neighbouring lanes share a cell: together they store whole 64-byte runs of G / GD, and the grid holds HB_LPC times the
+    // threads of a thread-per-cell layout (the kernel is bound by memory latency, not by arithmetic)
+    const int tilesx = (Ws + 31) / 32, tilesy = (Hs + HB_ROWS - 1) / HB_ROWS;
     int bid = blockIdx.x;
     const int b = bid / (tilesx * tilesy);
     bid -= b * tilesx * tilesy;
-    const int ci_ = (bid / tilesx) * 8 + (t >> 5), cj = (bid - (bid / tilesx) * tilesx) * 32 + (t & 31);
+    const int sub = t % HB_LPC, ct = t / HB_LPC;
+    const int ci_ = (bid / tilesx) * HB_ROWS + (ct >> 5), cj = (bid - (bid / tilesx) * tilesx) * 32 + (ct & 31);
     if (ci_ >= Hs || cj >= Ws) return;
     float gw[4][4][NO];
 #pragma unroll
@@ -985,9 +1037,21 @@ __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restr
     const bool rowB = 2 * ci_ + 1 < H, colB = 2 * cj + 1 < W;
     const size_t cell = ((size_t)b * Hs + ci_) * Ws + cj;
     for (int c0 = 0; c0 < Cp; c0 += 32) {
-        float acc[32];
+        const size_t off = cell * Cp + c0 + 4 * sub;
+        // act'(R) of this lane's channels as sign bits, fetched BEFORE the arithmetic so that the latency hides behind it
+        uint32_t rbits = 0xffffffffu;
+        if (GD && R) {
+            rbits = 0u;
 #pragma unroll
-        for (int k = 0; k < 32; k++) acc[k] = 0.f;
+            for (int k = 0; k < NQ; k++) {
+                const float4 rv = ldg4(R + off + 4 * HB_LPC * k);
+                rbits |= (rv.x > 0.f ? 1u : 0u) << (4 * k) | (rv.y > 0.f ? 1u : 0u) << (4 * k + 1) | (rv.z > 0.f ? 1u : 0u) << (4 * k + 2) |
+                         (rv.w > 0.f ? 1u : 0u) << (4 * k + 3);
+            }
+        }
+        float acc[4 * NQ];
+#pragma unroll
+        for (int k = 0; k < 4 * NQ; k++) acc[k] = 0.f;
         if (c0 < Cr) {
             if (PHASE) {
 #pragma unroll
@@ -997,10 +1061,10 @@ __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restr
 #pragma unroll
                         for (int o = 0; o < NO; o++) {
                             const float x = gw[a][c][o];
-                            const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((a * 4 + c) * NO + o) * Cr + c0);
+                            const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((a * 4 + c) * NO + o) * Cr + c0) + sub;
 #pragma unroll
-                            for (int k = 0; k < 8; k++) {
-                                const float4 w4 = wr[k];
+                            for (int k = 0; k < NQ; k++) {
+                                const float4 w4 = wr[HB_LPC * k];
                                 acc[4 * k] = fmaf(x, w4.x, acc[4 * k]); acc[4 * k + 1] = fmaf(x, w4.y, acc[4 * k + 1]);
                                 acc[4 * k + 2] = fmaf(x, w4.z, acc[4 * k + 2]); acc[4 * k + 3] = fmaf(x, w4.w, acc[4 * k + 3]);
                             }
@@ -1018,10 +1082,10 @@ __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restr
 #pragma unroll
                                 for (int o = 0; o < NO; o++) {
                                     const float x = gw[pp - dy + 2][q - dx + 2][o];
-                                    const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((dy * 3 + dx) * NO + o) * Cr + c0);
+                                    const float4* wr = reinterpret_cast<const float4*>(hb_smem + (size_t)((dy * 3 + dx) * NO + o) * Cr + c0) + sub;
 #pragma unroll
-                                    for (int k = 0; k < 8; k++) {
-                                        const float4 w4 = wr[k];
+                                    for (int k = 0; k < NQ; k++) {
+                                        const float4 w4 = wr[HB_LPC * k];
                                         acc[4 * k] = fmaf(x, w4.x, acc[4 * k]); acc[4 * k + 1] = fmaf(x, w4.y, acc[4 * k + 1]);
                                         acc[4 * k + 2] = fmaf(x, w4.z, acc[4 * k + 2]); acc[4 * k + 3] = fmaf(x, w4.w, acc[4 * k + 3]);
                                     }
@@ -1029,17 +1093,14 @@ __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restr
                     }
             }
         }
-        const size_t off = cell * Cp + c0;
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
+        for (int k = 0; k < NQ; k++) {
             float4 v = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
-            if (G) *reinterpret_cast<float4*>(G + off + 4 * k) = v;
+            if (G) *reinterpret_cast<float4*>(G + off + 4 * HB_LPC * k) = v;
             if (GD) {
-                if (R) {
-                    const float4 rv = ldg4(R + off + 4 * k);
-                    v.x *= act_grad(rv.x, slope); v.y *= act_grad(rv.y, slope); v.z *= act_grad(rv.z, slope); v.w *= act_grad(rv.w, slope);
-                }
-                *reinterpret_cast<float4*>(GD + off + 4 * k) = round_tf32(v, rnd);
+                const uint32_t m = rbits >> (4 * k);
+                v.x *= (m & 1u) ? 1.f : slope; v.y *= (m & 2u) ? 1.f : slope; v.z *= (m & 4u) ? 1.f : slope; v.w *= (m & 8u) ? 1.f : slope;
+                *reinterpret_cast<float4*>(GD + off + 4 * HB_LPC * k) = round_tf32(v, rnd);
             }
         }
     }
@@ -1265,14 +1326,14 @@ int32_t k2_head_bwd_data(dincae_ctx* ctx, const float* g, int B, int H, int W, i
     const bool phase = (H % 2) == 0 && (W % 2) == 0;
     const int Cr = (Cin + 31) & ~31;
     const int smem = (int)((size_t)(phase ? 16 : 9) * nout2 * Cr * sizeof(float));
-    const unsigned grid = (unsigned)(B * ((Ws + 31) / 32) * ((Hs + 7) / 8));
+    const unsigned grid = (unsigned)(B * ((Ws + 31) / 32) * ((Hs + HB_ROWS - 1) / HB_ROWS));
     DC_WORK(ctx, 2.0 * 9 * Cin * nout2 * (double)B * H * W, 4.0 * ((double)nout2 * B * H * W + (double)Cp * B * Hs * Ws * ((G ? 1 : 0) + (GD ? 1 : 0) + (R ? 1 : 0))));
 #define HB_LAUNCH(NO_, PH_)                                                                                                  \
     do {                                                                                                                     \
         static int attr = 0;                                                                                                 \
         auto head_bwd_data = head_bwd_data_kernel<NO_, PH_>;                                                                 \
         if (smem > attr) { DC_CHECK_CUDA(cudaFuncSetAttribute(head_bwd_data, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = smem; } \
-        DC_LAUNCH_PDL(ctx, head_bwd_data, grid, 256, smem, g, B, H, W, Hs, Ws, wgt, Cin, Cin_p, Cout_p, R, slope, Cp, G, GD, (int)ctx->tf32_acts); \
+        DC_LAUNCH_PDL(ctx, head_bwd_data, grid, HB_THREADS, smem, g, B, H, W, Hs, Ws, wgt, Cin, Cin_p, Cout_p, R, slope, Cp, G, GD, (int)ctx->tf32_acts); \
     } while (0)
     if (nout2 == 2) { if (phase) HB_LAUNCH(2, true); else HB_LAUNCH(2, false); }
     else { if (phase) HB_LAUNCH(4, true); else HB_LAUNCH(4, false); }

@@ -382,7 +382,8 @@ int32_t stage_batch(dincae_model* M, const float* src, int C, int B, int32_t loc
 }
 
 // gridded loss of all chains (+ gradients w.r.t. the raw chain outputs when train)
-int32_t gridded_loss(dincae_model* M, const float* d_xtrue, int B, const int64_t* n_valid_global, bool train) {
+// 1 / n_valid per output variable (the global count in a data-parallel step, else counted from this batch)
+int32_t gridded_counts(dincae_model* M, const float* d_xtrue, int B, const int64_t* n_valid_global) {
     dincae_ctx* ctx = M->ctx;
     const int64_t npix = (int64_t)M->cfg.W * M->cfg.H;
     if (n_valid_global) {
@@ -396,6 +397,11 @@ int32_t gridded_loss(dincae_model* M, const float* d_xtrue, int B, const int64_t
     }
     DC_LAUNCH(ctx, inv_n_kernel, 1, 32, 0, M->d_nvalid, M->O, M->d_inv_n);
     DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+int32_t gridded_chain_losses(dincae_model* M, const float* d_xtrue, int B, bool train) {
+    dincae_ctx* ctx = M->ctx;
+    const int64_t npix = (int64_t)M->cfg.W * M->cfg.H;
     HeadParams hp = head_params(M);
     const bool lap = hp.lap != 0.f || hp.lap_err != 0.f;
     for (int c = 0; c < M->nchains; c++) {
@@ -490,6 +496,11 @@ int32_t points_loss(dincae_model* M, PointTruth& pt, int B, int64_t n_valid_glob
                            M->red_scratch, M->red_scratch_bytes));
     }
     return DINCAE_OK;
+}
+
+int32_t gridded_loss(dincae_model* M, const float* d_xtrue, int B, const int64_t* n_valid_global, bool train) {
+    DC_TRY(gridded_counts(M, d_xtrue, B, n_valid_global));
+    return gridded_chain_losses(M, d_xtrue, B, train);
 }
 
 int32_t backward_all(dincae_model* M, int B) {
@@ -800,10 +811,12 @@ extern "C" int32_t dincae_model_create(dincae_ctx* ctx, const dincae_config* cfg
     return DINCAE_OK;
 }
 
+static void step_graphs_release(dincae_model* M);
 extern "C" int32_t dincae_model_destroy(dincae_model* M) {
     if (!M) return DINCAE_OK;
     cudaSetDevice(M->ctx->device);
     cudaStreamSynchronize(M->ctx->stream);
+    step_graphs_release(M);
     model_p2p_release(M);        // collective when the peers' workspaces are mapped (data-parallel training over peer memory)
     if (M->all_mem) cudaFree(M->all_mem);
     if (M->pt_buf) cudaFree(M->pt_buf);
@@ -930,6 +943,95 @@ extern "C" int32_t dincae_loss(dincae_model* M, const float* xin, const float* x
     return read_loss(M, false, nullptr, loss);
 }
 
+// forward + loss + backward of a gridded step on device buffers
+static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B) {
+    DC_TRY(model_forward(M, dx, B, true));
+    DC_TRY(gridded_chain_losses(M, dy, B, true));
+    return backward_all(M, B);
+}
+static bool step_graph_on() {
+    static const int on = dc_env_int("DINCAE_GRAPH", 1);
+    return on != 0;
+}
+static void step_graphs_release(dincae_model* M) {
+    for (StepGraph& g : M->step_graph) {
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+        g = StepGraph();
+    }
+}
+// Replays the step as a CUDA graph once its key (buffers, batch size) has been seen twice: the first step with a key runs launch by
+// launch (and does every lazy set-up: shared-memory attributes, tensor maps, the side stream), the second is captured -- both
+// streams, the programmatic-dependent-launch edges included -- and replayed from then on.  The derived weight copies are refreshed
+// INSIDE the graph on every replay (after an optimiser step they are always stale; refreshing them when they are not is harmless).
+// Not used under the per-launch profile, with bucketed overlap (NCCL calls between the chains), or after a failed capture.
+static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B) {
+    dincae_ctx* ctx = M->ctx;
+    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off) return grad_step_body(M, dx, dy, B);
+    StepGraph* g = nullptr;
+    StepGraph* lru = &M->step_graph[0];
+    for (StepGraph& c : M->step_graph) {
+        if (c.B == B && c.dx == dx && c.dy == dy) { g = &c; break; }
+        if (c.last_use < lru->last_use) lru = &c;
+    }
+    M->graph_tick++;
+    if (g && g->exec) {
+        g->last_use = M->graph_tick;
+        DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
+        ctx->launches += g->launches;
+        M->wT_dirty = false;
+        return DINCAE_OK;
+    }
+    if (!g) {                                  // first time: remember the key, run launch by launch
+        if (lru->exec) cudaGraphExecDestroy(lru->exec);
+        *lru = StepGraph();
+        lru->dx = dx; lru->dy = dy; lru->B = B; lru->last_use = M->graph_tick;
+        return grad_step_body(M, dx, dy, B);
+    }
+    g->last_use = M->graph_tick;
+    const int64_t launches0 = ctx->launches;
+    M->wT_dirty = true;
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
+    int32_t st = DINCAE_OK;
+    if (e == cudaSuccess) {
+        st = grad_step_body(M, dx, dy, B);
+        e = cudaStreamEndCapture(ctx->stream, &graph);
+    }
+    const int64_t captured = ctx->launches - launches0;
+    ctx->launches = launches0;
+    if (e == cudaSuccess && st == DINCAE_OK && graph) e = cudaGraphInstantiate(&g->exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (e != cudaSuccess || st != DINCAE_OK || !g->exec) {
+        cudaGetLastError();
+        g->exec = nullptr;
+        M->graph_off = true;
+        M->side_pending = false;
+        M->wT_dirty = true;
+        return grad_step_body(M, dx, dy, B);
+    }
+    g->launches = captured;
+    DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->launches;
+    M->wT_dirty = false;
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_model_step_graph(dincae_model* M, int32_t enable, int32_t* captured) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_model_step_graph: model is NULL");
+    DC_REQUIRE(enable >= -1 && enable <= 1, DINCAE_EINVAL, "dincae_model_step_graph: enable must be -1 (query), 0 or 1");
+    if (enable >= 0) {
+        DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+        DC_CHECK_CUDA(cudaStreamSynchronize(M->ctx->stream));
+        if (!enable) step_graphs_release(M);
+        M->graph_off = !enable;
+    }
+    if (captured) {
+        *captured = 0;
+        for (const StepGraph& g : M->step_graph) *captured += g.exec != nullptr;
+    }
+    return DINCAE_OK;
+}
+
 extern "C" int32_t dincae_grad_step(dincae_model* M, const float* xin, const float* xtrue, int32_t B,
                                     const int64_t* n_valid_global, int32_t loc) {
     DC_TRY(check_batch(M, B, "dincae_grad_step"));
@@ -940,9 +1042,8 @@ extern "C" int32_t dincae_grad_step(dincae_model* M, const float* xin, const flo
     DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
     DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
-    DC_TRY(model_forward(M, dx, B, true));
-    DC_TRY(gridded_loss(M, dy, B, n_valid_global, true));
-    return backward_all(M, B);
+    DC_TRY(gridded_counts(M, dy, B, n_valid_global));          // per-step values: stays outside the captured part
+    return grad_step_body_or_graph(M, dx, dy, B);
 }
 
 extern "C" int32_t dincae_grad_buffer(dincae_model* M, float** dev_ptr, int64_t* n) {

@@ -31,7 +31,23 @@ struct ChainBufs {
     float* GRAW;                       // planar gradient w.r.t. RAW
 };
 
+// One captured gradient step (forward + loss + backward of every chain, both streams): the ~80 launches of a step are replayed as
+// one CUDA graph, which takes the per-kernel boundary from 2-4 us (stream launches, with or without programmatic dependent launch)
+// to about 1.2 us (measured: scripts/microbench/launch_floor.cu).  Keyed on what the launches were recorded with.
+struct StepGraph {
+    const float* dx = nullptr;       // device input / truth the step reads
+    const float* dy = nullptr;
+    int B = 0;
+    cudaGraphExec_t exec = nullptr;  // nullptr: the key has been seen once (that step ran launch by launch, which also did every lazy setup)
+    int64_t launches = 0;            // kernels one replay launches
+    uint64_t last_use = 0;
+};
+constexpr int DC_STEP_GRAPHS = 4;
+
 struct dincae_model {
+    StepGraph step_graph[DC_STEP_GRAPHS];
+    uint64_t graph_tick = 0;
+    bool graph_off = false;      // capture failed once: launch by launch from then on
     bool side_pending = false;   // weight gradients in flight on the context's side stream
     // peer-memory all-reduce of the gradient buffer (p2p.cu): the other ranks' workspaces mapped through CUDA IPC
     int p2p_state = 0;                 // 0 = not tried, 1 = ready, -1 = unavailable (NCCL is used)

@@ -127,6 +127,13 @@ int32_t dincae_loss(dincae_model* m, const float* xin, const float* xtrue, int32
 /* one mini-batch of train_epoch! (src/flux.jl:28-36): withgradient + ClipGrad + Adam; lr per call (src/flux.jl:25) */
 int32_t dincae_train_step(dincae_model* m, const float* xin, const float* xtrue, int32_t B, float lr,
                           int32_t loc, float* loss);
+/* The gridded gradient step (dincae_train_step / _slot / _dp / dincae_grad_step) replays its ~80 kernel launches as one CUDA graph
+ * once the same (device input, device truth, B) has been seen twice: first step launch by launch, second step captured, then replay
+ * (up to four keys are kept, least recently used replaced; DINCAE_GRAPH=0 in the environment disables it for the process).  Same
+ * kernels, same order, same results; no counterpart in the reference (Flux launches kernel by kernel, src/flux.jl:28-36).
+ * enable = 0 / 1 switches it for this model (0 also drops the captured graphs), -1 only queries; captured (may be NULL) <- number
+ * of instantiated graphs. */
+int32_t dincae_model_step_graph(dincae_model* m, int32_t enable, int32_t* captured);
 /* one-batch-ahead prefetch (PrefetchDataIter, src/data.jl:872-904): upload mini-batch i+1 into the other slot (0/1) on a copy
  * stream while mini-batch i trains; host buffers (pinned for a truly asynchronous copy) must stay valid until the matching
  * dincae_train_step_slot returns. */
