@@ -966,7 +966,8 @@ static void step_graphs_release(dincae_model* M) {
 // Not used under the per-launch profile, with bucketed overlap (NCCL calls between the chains), or after a failed capture.
 static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B) {
     dincae_ctx* ctx = M->ctx;
-    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off) return grad_step_body(M, dx, dy, B);
+    const bool capturable = ctx->stream != nullptr && ctx->stream != cudaStreamLegacy && ctx->stream != cudaStreamPerThread;
+    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B);
     StepGraph* g = nullptr;
     StepGraph* lru = &M->step_graph[0];
     for (StepGraph& c : M->step_graph) {
