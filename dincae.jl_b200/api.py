@@ -126,6 +126,26 @@ def interp_adjn(pos, values, sz, ctx: Optional[Context] = None):
     return out
 
 
+def vector2_costfun(xrec, xtrue, truth_uncertain, directionobs, ctx: Optional[Context] = None, with_grad=False):
+    """vector2_costfun(xrec, xtrue, truth_uncertain, directionobs) (src/vector2.jl:53-100): xrec (W,H,5,B), xtrue (W,H,2*nsites,B),
+    directionobs (W,H,nsites) or (W,H,nsites,B) in degrees -> cost, or (cost, d cost / d xrec) with with_grad=True."""
+    ctx = ctx or default_context()
+    xrec = np.asfortranarray(xrec, np.float32); xtrue = np.asfortranarray(xtrue, np.float32)
+    directionobs = np.asfortranarray(directionobs, np.float32)
+    W, H, five, B = xrec.shape
+    nsites = directionobs.shape[2]
+    if five != 5 or xtrue.shape != (W, H, 2 * nsites, B) or directionobs.shape[:2] != (W, H) or directionobs.ndim not in (3, 4):
+        raise ValueError("vector2_costfun: xrec %s, xtrue %s, directionobs %s do not fit together" % (xrec.shape, xtrue.shape, directionobs.shape))
+    if directionobs.ndim == 4 and directionobs.shape[3] != B:
+        raise ValueError("vector2_costfun: directionobs has %d samples, xrec %d" % (directionobs.shape[3], B))
+    cost = C.c_double()
+    grad = np.zeros(xrec.shape, np.float32, order="F") if with_grad else None
+    L.check(ctx._lib.dincae_vector2_loss(ctx.handle, L.ptr(xrec), L.ptr(xtrue), L.ptr(directionobs), W, H, nsites, B,
+                                         int(directionobs.ndim == 4), int(bool(truth_uncertain)), L.HOST, C.byref(cost),
+                                         L.ptr(grad) if with_grad else None))
+    return (cost.value, grad) if with_grad else cost.value
+
+
 def interp_adjn_noalloc(pos_dev, values_dev, P, sz, out_dev, ctx: Optional[Context] = None):
     """interp_adjn for callers that may not allocate GPU memory (their device memory belongs to another
     pool, as under CUDA.jl's allocator around a ccall).  All three buffers are device memory the caller

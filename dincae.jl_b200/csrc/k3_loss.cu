@@ -387,3 +387,130 @@ int32_t k3_savesample(dincae_ctx* ctx, const float* ms, int B, int nout, int64_t
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
+
+
+// ---- 2-D vector (HF-radar radial currents) cost, src/vector2.jl:13-100 ------------------------------------------------
+namespace {
+// xrec (W,H,5,B) = (u', v', L11, L21, L22): P = L L^T is the error covariance of (u, v) = P (u', v')  (vector2_covariance / _mean,
+// :13-51); every site s sees the projection on its bearing (:27-44) m = sin(t) u + cos(t) v, s2 = max(p' P p, 1e-4) (:78) and
+// is scored against xtrue (W,H,2*nsites,B) = (m_true / s2_true, 1 / s2_true) per site with costfun_single (src/model.jl:54-100).
+// One thread = one pixel of one sample: the five inputs are read once, the nsites terms and their gradient summed in site order.
+__global__ void __launch_bounds__(RED_THREADS) vector2_count_kernel(const float* __restrict__ xtrue, int64_t npix, int nsites, int B,
+                                                                    unsigned long long* __restrict__ n_valid) {
+    const int64_t total = (int64_t)B * nsites * npix;
+    unsigned int c = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t sb = i / npix, p = i - sb * npix;          // sb = b * nsites + s
+        c += (xtrue[(2 * sb + 1) * npix + p] != 0.f) ? 1u : 0u;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_down_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(n_valid, (unsigned long long)c);   // integer atomics: exact, order-free
+}
+
+__global__ void __launch_bounds__(RED_THREADS) vector2_loss_kernel(const float* __restrict__ xrec, const float* __restrict__ xtrue,
+                                                                   const float* __restrict__ dir, int64_t npix, int nsites, int B,
+                                                                   int dir_has_batch, int truth_uncertain,
+                                                                   const unsigned long long* __restrict__ n_valid, double* __restrict__ part,
+                                                                   float* __restrict__ grad) {
+    const int64_t total = (int64_t)B * npix;
+    const float inv_n = 1.0f / (float)n_valid[0];
+    double acc = 0.0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / npix, p = i - b * npix;
+        const float* xr = xrec + (b * 5) * npix + p;
+        const float x1 = xr[0], x2 = xr[npix], l11 = xr[2 * npix], l21 = xr[3 * npix], l22 = xr[4 * npix];
+        const float p11 = l11 * l11, p12 = l11 * l21, p22 = l21 * l21 + l22 * l22;                  // :19-21
+        const float u = x1 * p11 + x2 * p12, v = x1 * p12 + x2 * p22;                                // :47-48
+        float gx1 = 0.f, gx2 = 0.f, gp11 = 0.f, gp12 = 0.f, gp22 = 0.f;
+        for (int s = 0; s < nsites; s++) {
+            const float d = dir[((dir_has_batch ? b * nsites : 0) + s) * npix + p];
+            const float t = d * 3.14159274f / 180.f;                                                  // directionobs * pi / 180 in Float32, :28
+            const float sn = sinf(t), cs = cosf(t);
+            const float m = sn * u + cs * v;                                                          // :36-37
+            const float s2raw = sn * sn * p11 + 2.f * sn * cs * p12 + cs * cs * p22;                  // :39-41
+            const float s2 = fmaxf(s2raw, 1e-4f);                                                     // :78
+            const float* xt = xtrue + ((b * nsites + s) * 2) * npix + p;
+            const float inv_true = xt[npix];
+            if (inv_true == 0.f) continue;                                                            // mask_noncloud, :90
+            const float s2t = 1.0f / fmaxf(inv_true, 1e-3f);                                          // sinv, src/model.jl:7-10
+            const float mt = xt[0] * s2t;                                                             // :86
+            const float df = m - mt;
+            float term, num;
+            if (truth_uncertain) { term = logf(s2 / s2t) + (df * df + s2t) / s2; num = df * df + s2t; }   // src/model.jl:80-88
+            else { term = logf(s2) + df * df / s2; num = df * df; }                                       // :90-94
+            acc += (double)term;
+            if (grad) {
+                const float gm = 2.f * df / s2;
+                const float gs = s2raw > 1e-4f ? (1.f / s2 - num / (s2 * s2)) : 0.f;
+                // m = sn u + cs v with u, v linear in (x1, x2) and in P
+                gx1 += gm * (sn * p11 + cs * p12);
+                gx2 += gm * (sn * p12 + cs * p22);
+                gp11 += gm * sn * x1 + gs * sn * sn;
+                gp12 += gm * (sn * x2 + cs * x1) + gs * 2.f * sn * cs;
+                gp22 += gm * cs * x2 + gs * cs * cs;
+            }
+        }
+        if (grad) {
+            float* g = grad + (b * 5) * npix + p;
+            g[0] = gx1 * inv_n;
+            g[npix] = gx2 * inv_n;
+            g[2 * npix] = (2.f * l11 * gp11 + l21 * gp12) * inv_n;         // P11 = L11^2, P12 = L11 L21
+            g[3 * npix] = (l11 * gp12 + 2.f * l21 * gp22) * inv_n;         // P12, P22 = L21^2 + L22^2
+            g[4 * npix] = (2.f * l22 * gp22) * inv_n;
+        }
+    }
+    const double sblk = block_sum(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = sblk;
+}
+__global__ void vector2_finish_kernel(const double* __restrict__ sum, const unsigned long long* __restrict__ n_valid, double* __restrict__ out) {
+    out[0] = sum[0] / (double)n_valid[0];
+}
+}  // namespace
+
+extern "C" int32_t dincae_vector2_loss(dincae_ctx* ctx, const float* xrec, const float* xtrue, const float* directionobs, int32_t W, int32_t H,
+                                       int32_t nsites, int32_t B, int32_t dir_has_batch, int32_t truth_uncertain, int32_t loc, double* loss,
+                                       float* grad) {
+    DC_REQUIRE(ctx && xrec && xtrue && directionobs && loss, DINCAE_EINVAL, "dincae_vector2_loss: NULL argument");
+    DC_REQUIRE(W >= 1 && H >= 1 && nsites >= 1 && B >= 1, DINCAE_EINVAL, "dincae_vector2_loss: bad sizes W=%d H=%d nsites=%d B=%d", W, H, nsites, B);
+    DC_REQUIRE(loc == DINCAE_HOST || loc == DINCAE_DEVICE, DINCAE_EINVAL, "dincae_vector2_loss: loc must be DINCAE_HOST or DINCAE_DEVICE");
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const int64_t npix = (int64_t)W * H;
+    const size_t nrec = sizeof(float) * 5 * npix * B, ntrue = sizeof(float) * 2 * nsites * npix * B;
+    const size_t ndir = sizeof(float) * nsites * npix * (dir_has_batch ? B : 1);
+    DevIn drec, dtrue, ddir;
+    DC_TRY(dc_stage_in(ctx, xrec, nrec, loc, &drec));
+    DC_TRY(dc_stage_in(ctx, xtrue, ntrue, loc, &dtrue));
+    DC_TRY(dc_stage_in(ctx, directionobs, ndir, loc, &ddir));
+    // scratch: block partials, [sum, cost] doubles, the valid count; + the gradient when it goes back to the host
+    const size_t head = (RED_MAX_BLOCKS + 4) * sizeof(double);
+    void* sc = nullptr;
+    DC_TRY(dc_scratch(ctx, head + ((grad && loc == DINCAE_HOST) ? nrec : 0), &sc));
+    double* part = (double*)sc;
+    double* sums = part + RED_MAX_BLOCKS;                                   // [0] = sum of terms, [1] = cost
+    unsigned long long* nv = (unsigned long long*)(sums + 2);
+    float* dgrad = grad ? (loc == DINCAE_HOST ? (float*)((char*)sc + head) : grad) : nullptr;
+    DC_CHECK_CUDA(cudaMemsetAsync(sums, 0, 4 * sizeof(double), ctx->stream));
+    const int nb = red_blocks(ctx, (int64_t)B * npix);
+    DC_LAUNCH(ctx, vector2_count_kernel, red_blocks(ctx, (int64_t)B * nsites * npix), RED_THREADS, 0, (const float*)dtrue.ptr, npix, nsites, B, nv);
+    DC_CHECK_LAUNCH();
+    DC_WORK(ctx, 0.0, (double)nrec * (grad ? 2 : 1) + ntrue + (double)sizeof(float) * nsites * npix * B);
+    DC_LAUNCH(ctx, vector2_loss_kernel, nb, RED_THREADS, 0, (const float*)drec.ptr, (const float*)dtrue.ptr, (const float*)ddir.ptr, npix, nsites, B,
+              dir_has_batch ? 1 : 0, truth_uncertain ? 1 : 0, nv, part, dgrad);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, final_sum_kernel, 1, 256, 0, part, nb, sums);
+    DC_CHECK_LAUNCH();
+    DC_LAUNCH(ctx, vector2_finish_kernel, 1, 1, 0, sums, nv, sums + 1);
+    DC_CHECK_LAUNCH();
+    void* pin = nullptr;
+    DC_TRY(dc_pinned(ctx, 64, &pin));
+    DC_CHECK_CUDA(cudaMemcpyAsync(pin, sums + 1, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (grad && loc == DINCAE_HOST) DC_CHECK_CUDA(cudaMemcpyAsync(grad, dgrad, nrec, cudaMemcpyDeviceToHost, ctx->stream));
+    DC_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    dc_stage_free(ctx, &drec);
+    dc_stage_free(ctx, &dtrue);
+    dc_stage_free(ctx, &ddir);
+    *loss = *(double*)pin;
+    DC_REQUIRE(*loss == *loss, DINCAE_EINVAL, "cost function value is NaN");     // src/vector2.jl:95-97
+    return DINCAE_OK;
+}

@@ -62,6 +62,7 @@ SIGNATURES = {
     "dincae_loss": (i32, [vp, vp, vp, i32, i32, C.POINTER(C.c_double)]),
     "dincae_train_step": (i32, [vp, vp, vp, i32, f32, i32, C.POINTER(f32)]),
     "dincae_model_step_graph": (i32, [vp, i32, C.POINTER(i32)]),
+    "dincae_vector2_loss": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, C.POINTER(C.c_double), vp]),
     "dincae_batch_upload": (i32, [vp, i32, vp, vp, i32]),
     "dincae_train_step_slot": (i32, [vp, i32, i32, f32, C.POINTER(f32)]),
     "dincae_grad_step_slot": (i32, [vp, i32, i32, vp]),

@@ -148,6 +148,16 @@ int32_t dincae_loss_points(dincae_model* m, const float* xin, const float* pos, 
 int32_t dincae_train_step_points(dincae_model* m, const float* xin, const float* pos, const float* x,
                                  const int64_t* offsets, int32_t B, float lr, int32_t loc, float* loss);
 
+/* vector2_costfun(xrec, xtrue, truth_uncertain, directionobs) (src/vector2.jl:53-100, the cost behind output_ndims = 2): a 2-D vector
+ * field observed as radial components at nsites sites.  xrec (W,H,5,B) = (u', v', L11, L21, L22) is the raw model output (the
+ * vector model has no final transform, src/model.jl:352-362), xtrue (W,H,2*nsites,B) = (m / sigma2, 1 / sigma2) per site,
+ * directionobs (W,H,nsites) or, with dir_has_batch != 0, (W,H,nsites,B): bearings in degrees.  loss <- the cost (host double);
+ * grad (may be NULL; same shape and place as xrec) <- d cost / d xrec.  A NaN cost is an error, as in the reference (:95-97).
+ * loc = DINCAE_HOST or DINCAE_DEVICE for all four arrays. */
+int32_t dincae_vector2_loss(dincae_ctx* ctx, const float* xrec, const float* xtrue, const float* directionobs, int32_t W, int32_t H,
+                            int32_t nsites, int32_t B, int32_t dir_has_batch, int32_t truth_uncertain, int32_t loc, double* loss,
+                            float* grad);
+
 /* Data-parallel split of train_step (new capability; the reference is single-device):
  *   grad_step   : forward + backward of the local shard; gradients are normalised by n_valid_global
  *                 (per output variable; NULL = count this shard's own) so a SUM over ranks gives the

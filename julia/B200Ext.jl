@@ -324,6 +324,23 @@ function interp_adjn!(pos::AbstractVector{NTuple{2,Float32}}, values::B200Array{
     return nothing
 end
 
+"""vector2_costfun(xrec, xtrue, truth_uncertain, directionobs) (src/vector2.jl:53-100) on B200Arrays: the cost of the 2-D vector
+model (output_ndims = 2) and, for its pullback, the gradient w.r.t. xrec from the same call."""
+function vector2_costfun_and_grad(xrec::B200Array{Float32,4}, xtrue::B200Array{Float32,4}, truth_uncertain::Bool, directionobs)
+    W, H, five, B = size(xrec)
+    nsites = size(directionobs, 3)
+    (five == 5 && size(xtrue) == (W, H, 2nsites, B)) || error("vector2_costfun: sizes do not fit")
+    cost = Ref{Float64}(0)
+    grad = Array{Float32}(undef, W, H, 5, B)
+    d = directionobs isa B200Array ? directionobs.data : Array{Float32}(directionobs)
+    check(ccall((:dincae_vector2_loss, lib), Int32,
+                (Ptr{Cvoid}, Ptr{Float32}, Ptr{Float32}, Ptr{Float32}, Int32, Int32, Int32, Int32, Int32, Int32, Int32, Ref{Float64}, Ptr{Float32}),
+                ctx().h, xrec.data, xtrue.data, d, W, H, nsites, B, ndims(directionobs) == 4, truth_uncertain, HOST, cost, grad))
+    return Float32(cost[]), grad
+end
+DINCAE.vector2_costfun(xrec::B200Array{Float32,4}, xtrue::B200Array{Float32,4}, truth_uncertain, directionobs) =
+    vector2_costfun_and_grad(xrec, xtrue, truth_uncertain, directionobs)[1]
+
 # ---- reconstruct_points: mini-batch gridding on the device ---------------------------------------------------------------
 # Base.iterate(::PointCloud) (src/points.jl:317-340) grids 2*ntime_win scatters per sample with the CPU loop of interp_adjn!.
 # For Atype <: B200Array the same mini-batch comes from dincae_points_assemble: the dataset (positions after posindices!
