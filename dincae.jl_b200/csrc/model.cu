@@ -399,16 +399,17 @@ int32_t gridded_counts(dincae_model* M, const float* d_xtrue, int B, const int64
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
 }
-int32_t gridded_chain_losses(dincae_model* M, const float* d_xtrue, int B, bool train) {
+int32_t gridded_chain_loss(dincae_model* M, int c, const float* d_xtrue, int B, bool train) {
     dincae_ctx* ctx = M->ctx;
     const int64_t npix = (int64_t)M->cfg.W * M->cfg.H;
     HeadParams hp = head_params(M);
     const bool lap = hp.lap != 0.f || hp.lap_err != 0.f;
-    for (int c = 0; c < M->nchains; c++) {
-        if (lap) DC_TRY(k3_head(ctx, M->cb[c].RAW, B, M->O, npix, hp.gamma, M->MS));
-        DC_TRY(k3_loss_grid(ctx, M->cb[c].RAW, d_xtrue, lap ? M->MS : nullptr, B, M->O, M->cfg.W, M->cfg.H, hp, M->d_inv_n,
-                            M->cfg.loss_weights[c], M->d_loss, train ? M->cb[c].GRAW : nullptr, M->red_scratch, M->red_scratch_bytes));
-    }
+    if (lap) DC_TRY(k3_head(ctx, M->cb[c].RAW, B, M->O, npix, hp.gamma, M->MS));
+    return k3_loss_grid(ctx, M->cb[c].RAW, d_xtrue, lap ? M->MS : nullptr, B, M->O, M->cfg.W, M->cfg.H, hp, M->d_inv_n,
+                        M->cfg.loss_weights[c], M->d_loss, train ? M->cb[c].GRAW : nullptr, M->red_scratch, M->red_scratch_bytes);
+}
+int32_t gridded_chain_losses(dincae_model* M, const float* d_xtrue, int B, bool train) {
+    for (int c = 0; c < M->nchains; c++) DC_TRY(gridded_chain_loss(M, c, d_xtrue, B, train));
     return DINCAE_OK;
 }
 
@@ -943,10 +944,34 @@ extern "C" int32_t dincae_loss(dincae_model* M, const float* xin, const float* x
     return read_loss(M, false, nullptr, loss);
 }
 
-// forward + loss + backward of a gridded step on device buffers
-static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B) {
-    DC_TRY(model_forward(M, dx, B, true));
-    DC_TRY(gridded_chain_losses(M, dy, B, true));
+// forward + loss + backward of a gridded step on device buffers.  Two things hang off the main chain on the side stream: the valid
+// counts of the truth (count_here: the single-GPU step counts them itself; needed only by the first loss) and the loss of every
+// chain but the last, which runs beside the next chain's forward pass (the loss kernels use no shared memory, so they fit on the SMs
+// next to the conv CTAs).  The chains' terms are still added to the loss in chain order: results do not change.
+static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B, bool count_here) {
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
+    HeadParams hp = head_params(M);
+    const bool branch = side_stream_on() && !ctx->prof && hp.lap == 0.f && hp.lap_err == 0.f;
+    cudaStream_t main_stream = ctx->stream;
+    auto on_side = [&](auto&& fn) -> int32_t {
+        if (!branch) return fn();
+        DC_TRY(wgrad_fork(ctx));
+        ctx->stream = ctx->side;
+        M->side_pending = true;
+        int32_t st = fn();
+        ctx->stream = main_stream;
+        return st;
+    };
+    if (count_here) DC_TRY(on_side([&] { return gridded_counts(M, dy, B, nullptr); }));
+    ctx->tf32_acts = M->wK != nullptr;
+    if (M->wK) DC_TRY(ensure_wT(M));        // the tensor-core forward reads the K-major TF32 weight copy
+    for (int c = 0; c < M->nchains; c++) {
+        DC_TRY(chain_forward(M, c, dx, B, true));
+        if (c + 1 < M->nchains) DC_TRY(on_side([&] { return gridded_chain_loss(M, c, dy, B, true); }));
+    }
+    DC_TRY(wgrad_join(M));
+    DC_TRY(gridded_chain_loss(M, M->nchains - 1, dy, B, true));
     return backward_all(M, B);
 }
 static bool step_graph_on() {
@@ -961,17 +986,17 @@ static void step_graphs_release(dincae_model* M) {
 }
 // Replays the step as a CUDA graph once its key (buffers, batch size) has been seen twice: the first step with a key runs launch by
 // launch (and does every lazy set-up: shared-memory attributes, tensor maps, the side stream), the second is captured -- both
-// streams, the programmatic-dependent-launch edges included -- and replayed from then on.  The derived weight copies are refreshed
+// streams, with plain edges instead of programmatic-dependent-launch ones -- and replayed from then on.  The derived weight copies are refreshed
 // INSIDE the graph on every replay (after an optimiser step they are always stale; refreshing them when they are not is harmless).
 // Not used under the per-launch profile, with bucketed overlap (NCCL calls between the chains), or after a failed capture.
-static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B) {
+static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B, bool count_here) {
     dincae_ctx* ctx = M->ctx;
     const bool capturable = ctx->stream != nullptr && ctx->stream != cudaStreamLegacy && ctx->stream != cudaStreamPerThread;
-    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B);
+    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B, count_here);
     StepGraph* g = nullptr;
     StepGraph* lru = &M->step_graph[0];
     for (StepGraph& c : M->step_graph) {
-        if (c.B == B && c.dx == dx && c.dy == dy) { g = &c; break; }
+        if (c.B == B && c.dx == dx && c.dy == dy && c.count_here == count_here) { g = &c; break; }
         if (c.last_use < lru->last_use) lru = &c;
     }
     M->graph_tick++;
@@ -985,8 +1010,8 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
     if (!g) {                                  // first time: remember the key, run launch by launch
         if (lru->exec) cudaGraphExecDestroy(lru->exec);
         *lru = StepGraph();
-        lru->dx = dx; lru->dy = dy; lru->B = B; lru->last_use = M->graph_tick;
-        return grad_step_body(M, dx, dy, B);
+        lru->dx = dx; lru->dy = dy; lru->B = B; lru->count_here = count_here; lru->last_use = M->graph_tick;
+        return grad_step_body(M, dx, dy, B, count_here);
     }
     g->last_use = M->graph_tick;
     const int64_t launches0 = ctx->launches;
@@ -995,7 +1020,9 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
     cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
     int32_t st = DINCAE_OK;
     if (e == cudaSuccess) {
-        st = grad_step_body(M, dx, dy, B);
+        ctx->capturing = true;
+        st = grad_step_body(M, dx, dy, B, count_here);
+        ctx->capturing = false;
         e = cudaStreamEndCapture(ctx->stream, &graph);
     }
     const int64_t captured = ctx->launches - launches0;
@@ -1008,7 +1035,7 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
         M->graph_off = true;
         M->side_pending = false;
         M->wT_dirty = true;
-        return grad_step_body(M, dx, dy, B);
+        return grad_step_body(M, dx, dy, B, count_here);
     }
     g->launches = captured;
     DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
@@ -1042,9 +1069,8 @@ extern "C" int32_t dincae_grad_step(dincae_model* M, const float* xin, const flo
     const float *dx, *dy;
     DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
     DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
-    DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
-    DC_TRY(gridded_counts(M, dy, B, n_valid_global));          // per-step values: stays outside the captured part
-    return grad_step_body_or_graph(M, dx, dy, B);
+    if (n_valid_global) DC_TRY(gridded_counts(M, dy, B, n_valid_global));      // per-step host values: stay outside the captured part
+    return grad_step_body_or_graph(M, dx, dy, B, n_valid_global == nullptr);
 }
 
 extern "C" int32_t dincae_grad_buffer(dincae_model* M, float** dev_ptr, int64_t* n) {

@@ -38,6 +38,7 @@ struct StepGraph {
     const float* dx = nullptr;       // device input / truth the step reads
     const float* dy = nullptr;
     int B = 0;
+    bool count_here = false;         // the step counts the valid targets itself (no global count handed in)
     cudaGraphExec_t exec = nullptr;  // nullptr: the key has been seen once (that step ran launch by launch, which also did every lazy setup)
     int64_t launches = 0;            // kernels one replay launches
     uint64_t last_use = 0;
