@@ -342,6 +342,38 @@ int32_t k3_adam(dincae_ctx* ctx, float* w, const float* g, float* m, float* v, i
     return DINCAE_OK;
 }
 
+// ---- CUDA-graph support: the optimiser kernel's AdamParams argument (learning rate, bias corrections) changes every step ------
+cudaGraphNode_t k3_find_adam_node(cudaGraph_t graph) {
+    size_t n = 0;
+    if (cudaGraphGetNodes(graph, nullptr, &n) != cudaSuccess || n == 0) return nullptr;
+    std::vector<cudaGraphNode_t> nodes(n);
+    if (cudaGraphGetNodes(graph, nodes.data(), &n) != cudaSuccess) return nullptr;
+    cudaGraphNode_t found = nullptr;
+    for (size_t i = 0; i < n; i++) {
+        cudaGraphNodeType ty;
+        if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+        cudaKernelNodeParams kp;
+        if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess) continue;
+        if (kp.func == (void*)adam_kernel<true>) {
+            if (found) return nullptr;               // more than one: not a step graph this code knows
+            found = nodes[i];
+        }
+    }
+    return found;
+}
+int32_t k3_update_adam_node(cudaGraphExec_t exec, cudaGraphNode_t node, const AdamParams& p) {
+    cudaKernelNodeParams kp;
+    DC_CHECK_CUDA(cudaGraphKernelNodeGetParams(node, &kp));
+    void* args[7];
+    for (int i = 0; i < 7; i++) args[i] = kp.kernelParams[i];     // (w, g, m, v, n, p, part): everything but p stays as captured
+    AdamParams copy = p;
+    args[5] = &copy;
+    kp.kernelParams = args;
+    kp.extra = nullptr;
+    DC_CHECK_CUDA(cudaGraphExecKernelNodeSetParams(exec, node, &kp));
+    return DINCAE_OK;
+}
+
 namespace {
 __global__ void __launch_bounds__(256) max_abs_diff_kernel(const float* __restrict__ a, const float* __restrict__ b, int64_t n, unsigned int* __restrict__ out) {
     float mx = 0.f;

@@ -36,6 +36,9 @@ struct AdamParams {
 // fused: g += 2*l2*w + l1*sign(w); clamp; Adam; also reg_acc[0] += l1*sum|w| + l2*sum w^2 (pre-update weights)
 int32_t k3_adam(dincae_ctx* ctx, float* w, const float* g, float* m, float* v, int64_t n, const AdamParams& p,
                 double* reg_acc, void* scratch, size_t scratch_bytes);
+// CUDA-graph support: the (single) node of the optimiser kernel in a captured step, and the per-step update of its AdamParams
+cudaGraphNode_t k3_find_adam_node(cudaGraph_t graph);
+int32_t k3_update_adam_node(cudaGraphExec_t exec, cudaGraphNode_t node, const AdamParams& p);
 // reg_acc[0] += l1*sum|w| + l2*sum w^2 only (dincae_loss)
 // out[0] = max_i |a[i] - b[i]| (integer atomicMax on the bit pattern of non-negative floats: order-independent)
 int32_t k3_max_abs_diff(dincae_ctx* ctx, const float* a, const float* b, int64_t n, float* out);

@@ -511,7 +511,21 @@ int32_t backward_all(dincae_model* M, int B) {
     M->red.count = 0;
     dincae_ctx* ctx = M->ctx;
     if (!M->dp_overlap) {
-        for (int c = M->nchains - 1; c >= 0; c--) DC_TRY(chain_backward(M, c, B));
+        const bool branch = side_stream_on() && !ctx->prof && M->wK != nullptr;
+        for (int c = M->nchains - 1; c >= 0; c--) {
+            DC_TRY(chain_backward(M, c, B));
+            if (c > 0 && branch && M->red.count > 0) {
+                // the split-K sums of chain c (an HBM-bound kernel without shared memory) run on the side stream beside the backward
+                // pass of chain c-1; that chain's weight gradients queue behind them, its final join covers both
+                cudaStream_t main_stream = ctx->stream;
+                DC_TRY(wgrad_fork(ctx));
+                ctx->stream = ctx->side;
+                M->side_pending = true;
+                int32_t st = k2_reduce_batched(ctx, M->red);
+                ctx->stream = main_stream;
+                DC_TRY(st);
+            }
+        }
         DC_TRY(k2_reduce_batched(ctx, M->red));
         DC_TRY(k2_fold_split_grad(ctx, M->g_exp, M->g, M->split));
         DC_LAUNCH(ctx, store_loss_kernel, 1, 1, 0, M->d_loss, M->g + M->n_int);
@@ -948,7 +962,7 @@ extern "C" int32_t dincae_loss(dincae_model* M, const float* xin, const float* x
 // counts of the truth (count_here: the single-GPU step counts them itself; needed only by the first loss) and the loss of every
 // chain but the last, which runs beside the next chain's forward pass (the loss kernels use no shared memory, so they fit on the SMs
 // next to the conv CTAs).  The chains' terms are still added to the loss in chain order: results do not change.
-static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B, bool count_here) {
+static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap) {
     dincae_ctx* ctx = M->ctx;
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
     HeadParams hp = head_params(M);
@@ -972,46 +986,54 @@ static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy,
     }
     DC_TRY(wgrad_join(M));
     DC_TRY(gridded_chain_loss(M, M->nchains - 1, dy, B, true));
-    return backward_all(M, B);
+    DC_TRY(backward_all(M, B));
+    if (ap) {                                  // L1/L2 + ClipGrad + Adam of the same step (single-GPU training)
+        DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss + 1, 0, sizeof(double), ctx->stream));
+        DC_TRY(k3_adam(ctx, M->w, M->g, M->m, M->v, M->n_int, *ap, M->d_loss + 1, M->red_scratch, M->red_scratch_bytes));
+    }
+    return DINCAE_OK;
 }
 static bool step_graph_on() {
     static const int on = dc_env_int("DINCAE_GRAPH", 1);
     return on != 0;
 }
+static void step_graph_drop(StepGraph& g) {
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (g.graph) cudaGraphDestroy(g.graph);
+    g = StepGraph();
+}
 static void step_graphs_release(dincae_model* M) {
-    for (StepGraph& g : M->step_graph) {
-        if (g.exec) cudaGraphExecDestroy(g.exec);
-        g = StepGraph();
-    }
+    for (StepGraph& g : M->step_graph) step_graph_drop(g);
 }
 // Replays the step as a CUDA graph once its key (buffers, batch size) has been seen twice: the first step with a key runs launch by
 // launch (and does every lazy set-up: shared-memory attributes, tensor maps, the side stream), the second is captured -- both
 // streams, with plain edges instead of programmatic-dependent-launch ones -- and replayed from then on.  The derived weight copies are refreshed
 // INSIDE the graph on every replay (after an optimiser step they are always stale; refreshing them when they are not is harmless).
 // Not used under the per-launch profile, with bucketed overlap (NCCL calls between the chains), or after a failed capture.
-static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B, bool count_here) {
+static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap) {
     dincae_ctx* ctx = M->ctx;
     const bool capturable = ctx->stream != nullptr && ctx->stream != cudaStreamLegacy && ctx->stream != cudaStreamPerThread;
-    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B, count_here);
+    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B, count_here, ap);
+    const bool apply = ap != nullptr;
     StepGraph* g = nullptr;
     StepGraph* lru = &M->step_graph[0];
     for (StepGraph& c : M->step_graph) {
-        if (c.B == B && c.dx == dx && c.dy == dy && c.count_here == count_here) { g = &c; break; }
+        if (c.B == B && c.dx == dx && c.dy == dy && c.count_here == count_here && c.apply == apply) { g = &c; break; }
         if (c.last_use < lru->last_use) lru = &c;
     }
     M->graph_tick++;
     if (g && g->exec) {
         g->last_use = M->graph_tick;
+        if (apply) DC_TRY(k3_update_adam_node(g->exec, g->adam_node, *ap));      // this step's learning rate and bias corrections
         DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
         ctx->launches += g->launches;
         M->wT_dirty = false;
         return DINCAE_OK;
     }
     if (!g) {                                  // first time: remember the key, run launch by launch
-        if (lru->exec) cudaGraphExecDestroy(lru->exec);
-        *lru = StepGraph();
-        lru->dx = dx; lru->dy = dy; lru->B = B; lru->count_here = count_here; lru->last_use = M->graph_tick;
-        return grad_step_body(M, dx, dy, B, count_here);
+        step_graph_drop(*lru);
+        lru->dx = dx; lru->dy = dy; lru->B = B; lru->count_here = count_here; lru->apply = apply; lru->last_use = M->graph_tick;
+        return grad_step_body(M, dx, dy, B, count_here, ap);
     }
     g->last_use = M->graph_tick;
     const int64_t launches0 = ctx->launches;
@@ -1021,21 +1043,27 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
     int32_t st = DINCAE_OK;
     if (e == cudaSuccess) {
         ctx->capturing = true;
-        st = grad_step_body(M, dx, dy, B, count_here);
+        st = grad_step_body(M, dx, dy, B, count_here, ap);
         ctx->capturing = false;
         e = cudaStreamEndCapture(ctx->stream, &graph);
     }
     const int64_t captured = ctx->launches - launches0;
     ctx->launches = launches0;
     if (e == cudaSuccess && st == DINCAE_OK && graph) e = cudaGraphInstantiate(&g->exec, graph, 0);
-    if (graph) cudaGraphDestroy(graph);
+    g->graph = graph;
+    if (e == cudaSuccess && g->exec && apply) {
+        g->adam_node = k3_find_adam_node(graph);
+        if (!g->adam_node) st = DINCAE_ECUDA;
+    }
     if (e != cudaSuccess || st != DINCAE_OK || !g->exec) {
         cudaGetLastError();
-        g->exec = nullptr;
+        if (g->exec) cudaGraphExecDestroy(g->exec);
+        if (g->graph) cudaGraphDestroy(g->graph);
+        g->exec = nullptr; g->graph = nullptr; g->adam_node = nullptr;
         M->graph_off = true;
         M->side_pending = false;
         M->wT_dirty = true;
-        return grad_step_body(M, dx, dy, B, count_here);
+        return grad_step_body(M, dx, dy, B, count_here, ap);
     }
     g->launches = captured;
     DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
@@ -1070,7 +1098,7 @@ extern "C" int32_t dincae_grad_step(dincae_model* M, const float* xin, const flo
     DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
     DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
     if (n_valid_global) DC_TRY(gridded_counts(M, dy, B, n_valid_global));      // per-step host values: stay outside the captured part
-    return grad_step_body_or_graph(M, dx, dy, B, n_valid_global == nullptr);
+    return grad_step_body_or_graph(M, dx, dy, B, n_valid_global == nullptr, nullptr);
 }
 
 extern "C" int32_t dincae_grad_buffer(dincae_model* M, float** dev_ptr, int64_t* n) {
@@ -1080,10 +1108,8 @@ extern "C" int32_t dincae_grad_buffer(dincae_model* M, float** dev_ptr, int64_t*
     return DINCAE_OK;
 }
 
-extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
-    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_apply_step: model is NULL");
-    dincae_ctx* ctx = M->ctx;
-    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+// optimiser step t+1: advances the step count and the running beta powers
+static AdamParams adam_params_next(dincae_model* M, float lr) {
     M->t_step += 1;
     M->bt1 *= (double)M->cfg.adam_beta1;
     M->bt2 *= (double)M->cfg.adam_beta2;
@@ -1092,6 +1118,21 @@ extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
     p.clip = M->cfg.clip_grad; p.l1 = M->cfg.l1_beta; p.l2 = M->cfg.l2_beta;
     p.inv_bc1 = (float)(1.0 / (1.0 - M->bt1));
     p.inv_bc2 = (float)(1.0 / (1.0 - M->bt2));
+    return p;
+}
+// single-GPU training step on device buffers: gradient step and optimiser update as ONE captured graph
+static int32_t train_step_device(dincae_model* M, const float* dx, const float* dy, int B, float lr) {
+    const AdamParams p = adam_params_next(M, lr);
+    int32_t st = grad_step_body_or_graph(M, dx, dy, B, true, &p);
+    M->wT_dirty = true;
+    return st;
+}
+
+extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
+    DC_REQUIRE(M != nullptr, DINCAE_EINVAL, "dincae_apply_step: model is NULL");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const AdamParams p = adam_params_next(M, lr);
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss + 1, 0, sizeof(double), ctx->stream));
     DC_TRY(k3_adam(ctx, M->w, M->g, M->m, M->v, M->n_int, p, M->d_loss + 1, M->red_scratch, M->red_scratch_bytes));
     M->wT_dirty = true;
@@ -1101,8 +1142,16 @@ extern "C" int32_t dincae_apply_step(dincae_model* M, float lr, float* loss) {
 
 extern "C" int32_t dincae_train_step(dincae_model* M, const float* xin, const float* xtrue, int32_t B, float lr,
                                      int32_t loc, float* loss) {
-    DC_TRY(dincae_grad_step(M, xin, xtrue, B, nullptr, loc));
-    return dincae_apply_step(M, lr, loss);
+    DC_TRY(check_batch(M, B, "dincae_train_step"));
+    DC_REQUIRE(xin && xtrue, DINCAE_EINVAL, "dincae_train_step: NULL argument");
+    dincae_ctx* ctx = M->ctx;
+    DC_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const float *dx, *dy;
+    DC_TRY(stage_batch(M, xin, M->cfg.ninput, B, loc, M->in_xin, &dx));
+    DC_TRY(stage_batch(M, xtrue, 2 * M->O, B, loc, M->in_xtrue, &dy));
+    DC_TRY(train_step_device(M, dx, dy, B, lr));
+    if (loss) return read_loss(M, true, loss, nullptr);
+    return DINCAE_OK;
 }
 
 extern "C" int32_t dincae_allreduce_grads(dincae_model* M) {
@@ -1189,10 +1238,11 @@ extern "C" int32_t dincae_train_step_slot(dincae_model* M, int32_t slot, int32_t
     DC_CHECK_CUDA(cudaSetDevice(ctx->device));
     const size_t nx = (size_t)M->cfg.W * M->cfg.H * M->cfg.ninput * M->maxB;
     DC_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, M->up_done[slot], 0));
-    DC_TRY(dincae_grad_step(M, M->up_buf[slot], M->up_buf[slot] + nx, B, nullptr, DINCAE_DEVICE));
+    DC_TRY(train_step_device(M, M->up_buf[slot], M->up_buf[slot] + nx, B, lr));
     DC_CHECK_CUDA(cudaEventRecord(M->slot_free[slot], ctx->stream));
     M->slot_used[slot] = true;
-    return dincae_apply_step(M, lr, loss);
+    if (loss) return read_loss(M, true, loss, nullptr);
+    return DINCAE_OK;
 }
 
 extern "C" int32_t dincae_grad_step_slot(dincae_model* M, int32_t slot, int32_t B, const int64_t* n_valid_global) {

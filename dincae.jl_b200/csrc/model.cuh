@@ -39,6 +39,9 @@ struct StepGraph {
     const float* dy = nullptr;
     int B = 0;
     bool count_here = false;         // the step counts the valid targets itself (no global count handed in)
+    bool apply = false;              // the optimiser update is part of the step (dincae_train_step / _slot)
+    cudaGraph_t graph = nullptr;     // kept for the optimiser node, whose arguments are updated before every replay
+    cudaGraphNode_t adam_node = nullptr;
     cudaGraphExec_t exec = nullptr;  // nullptr: the key has been seen once (that step ran launch by launch, which also did every lazy setup)
     int64_t launches = 0;            // kernels one replay launches
     uint64_t last_use = 0;

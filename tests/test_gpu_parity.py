@@ -490,7 +490,8 @@ def test_step_graph_replay_is_bit_identical(pkg):
     for graph in (False, True):
         m = pkg.Model(ctx, cfg, seed=3)
         m.step_graph(graph)
-        losses = [m.train_step(d_xin, d_xt, 1e-3, B=B, want_loss=True) for _ in range(6)]
+        # a different learning rate every step: the replay must pick up this step's optimiser arguments, not the captured ones
+        losses = [m.train_step(d_xin, d_xt, 1e-3 * 0.8 ** k, B=B, want_loss=True) for k in range(6)]
         ncap = m.step_graph()
         assert ncap == (1 if graph else 0)
         out.append((np.array(losses), m.get_params().copy()))
