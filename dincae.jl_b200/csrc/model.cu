@@ -1004,6 +1004,62 @@ static void step_graph_drop(StepGraph& g) {
 }
 static void step_graphs_release(dincae_model* M) {
     for (StepGraph& g : M->step_graph) step_graph_drop(g);
+    for (FwdGraph& g : M->fwd_graph) {
+        if (g.exec) cudaGraphExecDestroy(g.exec);
+        g = FwdGraph();
+    }
+}
+// model(M->in_xin) -> (m, sigma2) in M->MS for reconstruction: the same first-eager / second-captured / then-replayed scheme as the
+// training step, keyed on the batch size alone (both buffers belong to the model).  The weights do not change between the batches
+// of a reconstruction, so their derived copies are refreshed, if stale, BEFORE the graph.
+static int32_t forward_infer_or_graph(dincae_model* M, int B) {
+    dincae_ctx* ctx = M->ctx;
+    auto body = [&]() -> int32_t {
+        DC_TRY(model_forward(M, M->in_xin, B, false));
+        return model_head_last(M, B, M->MS);
+    };
+    const bool capturable = ctx->stream != nullptr && ctx->stream != cudaStreamLegacy && ctx->stream != cudaStreamPerThread;
+    if (!step_graph_on() || ctx->prof || M->graph_off || !capturable) return body();
+    if (M->wK) DC_TRY(ensure_wT(M));
+    FwdGraph* g = nullptr;
+    for (FwdGraph& c : M->fwd_graph)
+        if (c.B == B) g = &c;
+    if (g && g->exec) {
+        DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
+        ctx->launches += g->launches;
+        return DINCAE_OK;
+    }
+    if (!g) {
+        FwdGraph* slot = &M->fwd_graph[B == M->maxB ? 0 : 1];
+        if (slot->exec) cudaGraphExecDestroy(slot->exec);
+        *slot = FwdGraph();
+        slot->B = B;
+        return body();
+    }
+    const int64_t launches0 = ctx->launches;
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal);
+    int32_t st = DINCAE_OK;
+    if (e == cudaSuccess) {
+        ctx->capturing = true;
+        st = body();
+        ctx->capturing = false;
+        e = cudaStreamEndCapture(ctx->stream, &graph);
+    }
+    const int64_t captured = ctx->launches - launches0;
+    ctx->launches = launches0;
+    if (e == cudaSuccess && st == DINCAE_OK && graph) e = cudaGraphInstantiate(&g->exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (e != cudaSuccess || st != DINCAE_OK || !g->exec) {
+        cudaGetLastError();
+        g->exec = nullptr;
+        M->graph_off = true;
+        return body();
+    }
+    g->launches = captured;
+    DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
+    ctx->launches += g->launches;
+    return DINCAE_OK;
 }
 // Replays the step as a CUDA graph once its key (buffers, batch size) has been seen twice: the first step with a key runs launch by
 // launch (and does every lazy set-up: shared-memory attributes, tensor maps, the side stream), the second is captured -- both
@@ -1342,8 +1398,7 @@ extern "C" int32_t dincae_reconstruct_range(dincae_model* M, dincae_gridded* ds,
         int B = (int)(nsteps - s < M->maxB ? nsteps - s : M->maxB);
         for (int b = 0; b < B; b++) idx[b] = t0 + s + b;          // DataBatches(train=false): sequential, no perturbation
         DC_TRY(k1_assemble(ds, idx.data(), nullptr, 0, 0, B, M->in_xin, M->in_xtrue));
-        DC_TRY(model_forward(M, M->in_xin, B, false));
-        DC_TRY(model_head_last(M, B, M->MS));
+        DC_TRY(forward_infer_or_graph(M, B));
         DC_TRY(k3_savesample(ctx, M->MS, B, M->O, npix, ds->d_mean_out, ds->d_landmask, count, fill_value,
                              dm + (size_t)s * npix, dsg + (size_t)s * npix, npix * nsteps));
     }

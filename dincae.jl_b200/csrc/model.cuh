@@ -47,9 +47,16 @@ struct StepGraph {
     uint64_t last_use = 0;
 };
 constexpr int DC_STEP_GRAPHS = 4;
+// the forward pass of reconstruction (staging buffer in, (m, sigma2) buffer out) for one batch size
+struct FwdGraph {
+    int B = 0;                       // 0 = free
+    cudaGraphExec_t exec = nullptr;  // nullptr: seen once
+    int64_t launches = 0;
+};
 
 struct dincae_model {
     StepGraph step_graph[DC_STEP_GRAPHS];
+    FwdGraph fwd_graph[2];           // full batches and the last partial one
     uint64_t graph_tick = 0;
     bool graph_off = false;      // capture failed once: launch by launch from then on
     bool side_pending = false;   // weight gradients in flight on the context's side stream

@@ -497,3 +497,28 @@ def test_step_graph_replay_is_bit_identical(pkg):
         out.append((np.array(losses), m.get_params().copy()))
     assert np.array_equal(out[0][0], out[1][0])
     assert np.array_equal(out[0][1], out[1][1])
+
+
+def test_reconstruction_graph_replay_is_bit_identical(pkg, ctx):
+    """The forward pass of reconstruct_range is replayed as a CUDA graph from the third batch of a size on: same fields as launch by
+    launch, also after the weights changed (the derived TF32 copies are refreshed before the replay)."""
+    rng = np.random.default_rng(8)
+    W, H, V, N, T = 24, 20, 1, 23, 3
+    data = _cube(rng, W, H, V, N)
+    mask = rng.random((W, H)) > 0.15
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, train=False, ntime_win=T, mask=mask)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=10, enc_nfilter_internal=(16, 32), loss_weights_refine=(0.3, 0.7), max_batch=4, precision="tf32")
+    out = []
+    for graph in (False, True):
+        model = pkg.Model(ctx, cfg, seed=4)
+        model.step_graph(graph)
+        a = pkg.api.reconstruct_range(model, ds, 0, N)              # 5 full batches + one of 3
+        b = pkg.api.reconstruct_range(model, ds, 0, N)              # every batch replayed (graph) / launched (no graph)
+        model.set_params(model.get_params() * np.float32(1.02))
+        c = pkg.api.reconstruct_range(model, ds, 2, N)
+        out.append([x.copy() for pair in (a, b, c) for x in pair])
+        assert np.array_equal(out[-1][0], out[-1][2]) and np.array_equal(out[-1][1], out[-1][3])
+        assert not np.array_equal(out[-1][0][:, :, 2:], out[-1][4])
+    for x, y in zip(*out):
+        assert np.array_equal(x, y)
