@@ -394,12 +394,14 @@ def main():
         """device-resident step: assemble this rank's shard on the GPU, train, (all-reduce overlapped with backward), Adam."""
         idx, imask = draw()
         lo = rank * B
-        ds.assemble(idx[lo:lo + B], imask[lo:lo + B], seed=7, sample_ctr0=step_no[0] * B * world + lo, xin=xin_d, xtrue=xt_d)
+        ctr0 = step_no[0] * B * world + lo
         step_no[0] += 1
+        # assembly (getxy! of this rank's samples) + training step in one library call = one CUDA graph per step
         if world == 1:
-            return model.train_step(xin_d, xt_d, wl["lr"], B=B, want_loss=want_loss)
+            return model.train_step_gridded(ds, idx[lo:lo + B], imask[lo:lo + B], wl["lr"], seed=7, sample_ctr0=ctr0, want_loss=want_loss)
         nglob = np.array([counts[idx].sum()], np.int64)       # n_noncloud of the GLOBAL batch from static per-step counts: no collective
-        return model.train_step_dp(xin_d, xt_d, wl["lr"], nglob, B=B, want_loss=want_loss)
+        return model.train_step_gridded(ds, idx[lo:lo + B], imask[lo:lo + B], wl["lr"], seed=7, sample_ctr0=ctr0, n_valid_global=nglob,
+                                        want_loss=want_loss)
 
     # ---- device-resident arm -------------------------------------------------------------
     for _ in range(args.warmup):

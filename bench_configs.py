@@ -56,19 +56,16 @@ def gridded_config(pkg, ctx, timer, torch, dev, rank, world, precision, *, name,
     model = pkg.Model(ctx, cfg, seed=1)
     counts = ds.valid_counts(0)
     npix = W * H
-    xin_d = torch.empty(B * cin * npix, dtype=torch.float32, device=dev)
-    xt_d = torch.empty(B * 2 * npix, dtype=torch.float32, device=dev)
     rng = np.random.default_rng(99)
     k = [0]
 
     def step():
         idx = rng.integers(0, ncube, B * world); imask = rng.integers(0, ncube, B * world)
         lo = rank * B
-        ds.assemble(idx[lo:lo + B], imask[lo:lo + B], seed=7, sample_ctr0=k[0] * B * world + lo, xin=xin_d, xtrue=xt_d)
+        ctr0 = k[0] * B * world + lo
         k[0] += 1
-        if world == 1:
-            return model.train_step(xin_d, xt_d, 1e-3, B=B, want_loss=False)
-        return model.train_step_dp(xin_d, xt_d, 1e-3, np.array([counts[idx].sum()], np.int64), B=B, want_loss=False)
+        nglob = None if world == 1 else np.array([counts[idx].sum()], np.int64)
+        return model.train_step_gridded(ds, idx[lo:lo + B], imask[lo:lo + B], 1e-3, seed=7, sample_ctr0=ctr0, n_valid_global=nglob, want_loss=False)
     for _ in range(2):
         step()
     ms_step, blocks = _median_block(timer, step, steps, repeats)
@@ -90,7 +87,6 @@ def gridded_config(pkg, ctx, timer, torch, dev, rank, world, precision, *, name,
         per = recon_fields // world
         if recon_seed_per_rank:                   # a big record: every rank generates just its own shard on the device
             ds.close()
-            del xin_d, xt_d
             torch.cuda.empty_cache()
             lon, lat, days, cube, sea = bench.synth_cube_device(W, H, V, per, dev, seed=100 + rank, chunk=64)
             ds = pkg.GriddedDataset(ctx, lon, lat, days, cube, train=False, ntime_win=T, mask=sea, isoutput=isoutput)

@@ -350,6 +350,22 @@ class Model:
                                             C.byref(out) if want_loss else None))
         return out.value if want_loss else None
 
+    def train_step_gridded(self, ds, time_idx, imask, lr, seed=0, sample_ctr0=0, n_valid_global=None, want_loss=True):
+        """One mini-batch of train_epoch! straight from the device-resident dataset `ds`: batch assembly (getxy!) + training step as
+        one call (dincae_train_step_gridded); with n_valid_global the data-parallel form on this rank's shard."""
+        time_idx = np.ascontiguousarray(time_idx, np.int64)
+        im = None if imask is None else np.ascontiguousarray(imask, np.int64)
+        out = C.c_float()
+        po = C.byref(out) if want_loss else None
+        if n_valid_global is None:
+            L.check(self._lib.dincae_train_step_gridded(self.handle, ds.handle, L.ptr(time_idx), L.ptr(im), seed, sample_ctr0,
+                                                        len(time_idx), lr, po))
+        else:
+            nv = np.ascontiguousarray(n_valid_global, np.int64)
+            L.check(self._lib.dincae_train_step_dp_gridded(self.handle, ds.handle, L.ptr(time_idx), L.ptr(im), seed, sample_ctr0,
+                                                           len(time_idx), L.ptr(nv), lr, po))
+        return out.value if want_loss else None
+
     def step_graph(self, enable=None):
         """Switch the CUDA-graph replay of the gridded gradient step on/off for this model (None: only query);
         returns the number of captured graphs (dincae_model_step_graph)."""

@@ -152,11 +152,10 @@ __global__ void __launch_bounds__(256) assemble_kernel(AsmArgs a) {
 
 }  // namespace
 
-int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
-                    int B, float* d_xin, float* d_xtrue) {
-    dincae_ctx* ctx = ds->ctx;
-    if (B == 0) return DINCAE_OK;
-    for (int b = 0; b < B; b++) {
+// validates the indices of samples [b0, b0 + nb) and fills the kernel arguments of their launch
+static int32_t asm_fill(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
+                        int b0, int nb, float* d_xin, float* d_xtrue, AsmArgs& a) {
+    for (int b = b0; b < b0 + nb; b++) {
         DC_REQUIRE(h_time_idx[b] >= 0 && h_time_idx[b] < ds->N, DINCAE_EINVAL, "assemble: time_idx[%d]=%lld out of [0,%lld)", b,
                    (long long)h_time_idx[b], (long long)ds->N);
         if (h_imask)
@@ -165,23 +164,67 @@ int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t
     DC_REQUIRE(ds->N < 0x7FFFFFFF, DINCAE_ESIZE, "assemble: more than 2^31 time steps");
     const size_t HW = (size_t)ds->W * ds->H;
     const int C = 4 + 2 * ds->T * ds->V;
+    a.data = ds->d_data; a.err2 = ds->d_err2; a.lon = ds->d_lon; a.lat = ds->d_lat; a.tcos = ds->d_tcos; a.tsin = ds->d_tsin;
+    a.params = ds->d_params; a.outvars = ds->d_outvars;
+    for (int b = 0; b < nb; b++) { a.tidx[b] = (int)h_time_idx[b0 + b]; a.imk[b] = h_imask ? (int)h_imask[b0 + b] : 0; }
+    a.has_mask = h_imask != nullptr;
+    a.W = ds->W; a.H = ds->H; a.V = ds->V; a.T = ds->T; a.nout = ds->nout; a.B = nb; a.N = ds->N;
+    a.seed = seed; a.ctr0 = ctr0 + (uint64_t)b0;
+    a.xin = d_xin + (size_t)b0 * C * HW;
+    a.xtrue = d_xtrue + (size_t)b0 * 2 * ds->nout * HW;
+    return DINCAE_OK;
+}
+
+int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
+                    int B, float* d_xin, float* d_xtrue) {
+    dincae_ctx* ctx = ds->ctx;
+    if (B == 0) return DINCAE_OK;
+    const size_t HW = (size_t)ds->W * ds->H;
+    const int C = 4 + 2 * ds->T * ds->V;
     for (int b0 = 0; b0 < B; b0 += ASM_MAXB) {
         int nb = B - b0 < ASM_MAXB ? B - b0 : ASM_MAXB;
         AsmArgs a;
-        a.data = ds->d_data; a.err2 = ds->d_err2; a.lon = ds->d_lon; a.lat = ds->d_lat; a.tcos = ds->d_tcos; a.tsin = ds->d_tsin;
-        a.params = ds->d_params; a.outvars = ds->d_outvars;
-        for (int b = 0; b < nb; b++) { a.tidx[b] = (int)h_time_idx[b0 + b]; a.imk[b] = h_imask ? (int)h_imask[b0 + b] : 0; }
-        a.has_mask = h_imask != nullptr;
-        a.W = ds->W; a.H = ds->H; a.V = ds->V; a.T = ds->T; a.nout = ds->nout; a.B = nb; a.N = ds->N;
-        a.seed = seed; a.ctr0 = ctr0 + (uint64_t)b0;
-        a.xin = d_xin + (size_t)b0 * C * HW;
-        a.xtrue = d_xtrue + (size_t)b0 * 2 * ds->nout * HW;
+        DC_TRY(asm_fill(ds, h_time_idx, h_imask, seed, ctr0, b0, nb, d_xin, d_xtrue, a));
         int64_t groups = ((int64_t)HW + 3) / 4 * nb;
         // algorithmic bytes per sample: T*V cube planes (+ the transplanted mask plane) read, C input + 2*nout target planes written
         DC_WORK(ctx, 0.0, 4.0 * HW * nb * ((double)ds->T * ds->V + (h_imask ? 1 : 0) + C + 2 * ds->nout));
         DC_LAUNCH(ctx, assemble_kernel, (unsigned)dc_cdiv(groups, 256), 256, 0, a);
     }
     DC_CHECK_LAUNCH();
+    return DINCAE_OK;
+}
+
+// ---- CUDA-graph support (dincae_train_step_gridded): the sample indices of the assembly launch change every step ---------------
+int k1_assemble_max_single_launch() { return ASM_MAXB; }
+cudaGraphNode_t k1_find_assemble_node(cudaGraph_t graph) {
+    size_t n = 0;
+    if (cudaGraphGetNodes(graph, nullptr, &n) != cudaSuccess || n == 0) return nullptr;
+    std::vector<cudaGraphNode_t> nodes(n);
+    if (cudaGraphGetNodes(graph, nodes.data(), &n) != cudaSuccess) return nullptr;
+    cudaGraphNode_t found = nullptr;
+    for (size_t i = 0; i < n; i++) {
+        cudaGraphNodeType ty;
+        if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+        cudaKernelNodeParams kp;
+        if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess) continue;
+        if (kp.func == (void*)assemble_kernel) {
+            if (found) return nullptr;
+            found = nodes[i];
+        }
+    }
+    return found;
+}
+int32_t k1_update_assemble_node(cudaGraphExec_t exec, cudaGraphNode_t node, dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask,
+                                uint64_t seed, uint64_t ctr0, int B, float* d_xin, float* d_xtrue) {
+    DC_REQUIRE(B >= 1 && B <= ASM_MAXB, DINCAE_ESIZE, "assemble node: batch %d outside [1,%d]", B, ASM_MAXB);
+    AsmArgs a;
+    DC_TRY(asm_fill(ds, h_time_idx, h_imask, seed, ctr0, 0, B, d_xin, d_xtrue, a));
+    cudaKernelNodeParams kp;
+    DC_CHECK_CUDA(cudaGraphKernelNodeGetParams(node, &kp));      // grid and block stay as captured (same B, same grid size)
+    void* args[1] = {&a};
+    kp.kernelParams = args;
+    kp.extra = nullptr;
+    DC_CHECK_CUDA(cudaGraphExecKernelNodeSetParams(exec, node, &kp));
     return DINCAE_OK;
 }
 

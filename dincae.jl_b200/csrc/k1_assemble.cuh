@@ -25,6 +25,11 @@ struct dincae_gridded {
     std::vector<std::vector<int64_t>> valid_counts;   // [nout][N]
 };
 
+// CUDA-graph support: the (single) assembly node of a captured step and the per-step update of its sample indices
+int k1_assemble_max_single_launch();
+cudaGraphNode_t k1_find_assemble_node(cudaGraph_t graph);
+int32_t k1_update_assemble_node(cudaGraphExec_t exec, cudaGraphNode_t node, dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask,
+                                uint64_t seed, uint64_t ctr0, int B, float* d_xin, float* d_xtrue);
 // device-pointer core used by dincae_gridded_assemble and dincae_reconstruct_range
 int32_t k1_assemble(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
                     int B, float* d_xin, float* d_xtrue);

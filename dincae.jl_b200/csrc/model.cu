@@ -962,8 +962,17 @@ extern "C" int32_t dincae_loss(dincae_model* M, const float* xin, const float* x
 // counts of the truth (count_here: the single-GPU step counts them itself; needed only by the first loss) and the loss of every
 // chain but the last, which runs beside the next chain's forward pass (the loss kernels use no shared memory, so they fit on the SMs
 // next to the conv CTAs).  The chains' terms are still added to the loss in chain order: results do not change.
-static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap) {
+// the mini-batch a step assembles for itself from a device-resident dataset (getxy!, src/data.jl:391-517)
+struct AsmCall {
+    dincae_gridded* ds;
+    const int64_t* time_idx;
+    const int64_t* imask;
+    uint64_t seed, ctr0;
+};
+static int32_t grad_step_body(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap,
+                              const AsmCall* ac = nullptr) {
     dincae_ctx* ctx = M->ctx;
+    if (ac) DC_TRY(k1_assemble(ac->ds, ac->time_idx, ac->imask, ac->seed, ac->ctr0, B, const_cast<float*>(dx), const_cast<float*>(dy)));
     DC_CHECK_CUDA(cudaMemsetAsync(M->d_loss, 0, sizeof(double) * 8, ctx->stream));
     HeadParams hp = head_params(M);
     const bool branch = side_stream_on() && !ctx->prof && hp.lap == 0.f && hp.lap_err == 0.f;
@@ -1066,21 +1075,26 @@ static int32_t forward_infer_or_graph(dincae_model* M, int B) {
 // streams, with plain edges instead of programmatic-dependent-launch ones -- and replayed from then on.  The derived weight copies are refreshed
 // INSIDE the graph on every replay (after an optimiser step they are always stale; refreshing them when they are not is harmless).
 // Not used under the per-launch profile, with bucketed overlap (NCCL calls between the chains), or after a failed capture.
-static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap) {
+static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const float* dy, int B, bool count_here, const AdamParams* ap,
+                                       const AsmCall* ac = nullptr) {
     dincae_ctx* ctx = M->ctx;
     const bool capturable = ctx->stream != nullptr && ctx->stream != cudaStreamLegacy && ctx->stream != cudaStreamPerThread;
-    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable) return grad_step_body(M, dx, dy, B, count_here, ap);
+    if (!step_graph_on() || ctx->prof || M->dp_overlap || M->graph_off || !capturable || (ac && B > k1_assemble_max_single_launch()))
+        return grad_step_body(M, dx, dy, B, count_here, ap, ac);
     const bool apply = ap != nullptr;
+    const void* ds = ac ? (const void*)ac->ds : nullptr;
     StepGraph* g = nullptr;
     StepGraph* lru = &M->step_graph[0];
     for (StepGraph& c : M->step_graph) {
-        if (c.B == B && c.dx == dx && c.dy == dy && c.count_here == count_here && c.apply == apply) { g = &c; break; }
+        if (c.B == B && c.dx == dx && c.dy == dy && c.count_here == count_here && c.apply == apply && c.ds == ds) { g = &c; break; }
         if (c.last_use < lru->last_use) lru = &c;
     }
     M->graph_tick++;
     if (g && g->exec) {
         g->last_use = M->graph_tick;
         if (apply) DC_TRY(k3_update_adam_node(g->exec, g->adam_node, *ap));      // this step's learning rate and bias corrections
+        if (ac) DC_TRY(k1_update_assemble_node(g->exec, g->asm_node, ac->ds, ac->time_idx, ac->imask, ac->seed, ac->ctr0, B,
+                                               const_cast<float*>(dx), const_cast<float*>(dy)));     // ... and sample indices
         DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
         ctx->launches += g->launches;
         M->wT_dirty = false;
@@ -1088,8 +1102,8 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
     }
     if (!g) {                                  // first time: remember the key, run launch by launch
         step_graph_drop(*lru);
-        lru->dx = dx; lru->dy = dy; lru->B = B; lru->count_here = count_here; lru->apply = apply; lru->last_use = M->graph_tick;
-        return grad_step_body(M, dx, dy, B, count_here, ap);
+        lru->dx = dx; lru->dy = dy; lru->B = B; lru->count_here = count_here; lru->apply = apply; lru->ds = ds; lru->last_use = M->graph_tick;
+        return grad_step_body(M, dx, dy, B, count_here, ap, ac);
     }
     g->last_use = M->graph_tick;
     const int64_t launches0 = ctx->launches;
@@ -1099,7 +1113,7 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
     int32_t st = DINCAE_OK;
     if (e == cudaSuccess) {
         ctx->capturing = true;
-        st = grad_step_body(M, dx, dy, B, count_here, ap);
+        st = grad_step_body(M, dx, dy, B, count_here, ap, ac);
         ctx->capturing = false;
         e = cudaStreamEndCapture(ctx->stream, &graph);
     }
@@ -1111,15 +1125,19 @@ static int32_t grad_step_body_or_graph(dincae_model* M, const float* dx, const f
         g->adam_node = k3_find_adam_node(graph);
         if (!g->adam_node) st = DINCAE_ECUDA;
     }
+    if (e == cudaSuccess && g->exec && ac) {
+        g->asm_node = k1_find_assemble_node(graph);
+        if (!g->asm_node) st = DINCAE_ECUDA;
+    }
     if (e != cudaSuccess || st != DINCAE_OK || !g->exec) {
         cudaGetLastError();
         if (g->exec) cudaGraphExecDestroy(g->exec);
         if (g->graph) cudaGraphDestroy(g->graph);
-        g->exec = nullptr; g->graph = nullptr; g->adam_node = nullptr;
+        g->exec = nullptr; g->graph = nullptr; g->adam_node = nullptr; g->asm_node = nullptr;
         M->graph_off = true;
         M->side_pending = false;
         M->wT_dirty = true;
-        return grad_step_body(M, dx, dy, B, count_here, ap);
+        return grad_step_body(M, dx, dy, B, count_here, ap, ac);
     }
     g->launches = captured;
     DC_CHECK_CUDA(cudaGraphLaunch(g->exec, ctx->stream));
@@ -1223,6 +1241,49 @@ extern "C" int32_t dincae_train_step_dp(dincae_model* M, const float* xin, const
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
     M->dp_overlap = dp_overlap_on();
     int32_t st = dincae_grad_step(M, xin, xtrue, B, n_valid_global, loc);
+    const bool bucketed = M->dp_overlap;
+    M->dp_overlap = false;
+    DC_TRY(st);
+    if (!bucketed) DC_TRY(dincae_allreduce_grads(M));
+    return dincae_apply_step(M, lr, loss);
+}
+
+static int32_t check_dataset(const dincae_model* M, const dincae_gridded* ds, const char* who) {
+    DC_REQUIRE(ds != nullptr, DINCAE_EINVAL, "%s: dataset is NULL", who);
+    DC_REQUIRE(ds->ctx == M->ctx, DINCAE_EINVAL, "%s: dataset and model belong to different contexts", who);
+    DC_REQUIRE(ds->W == M->cfg.W && ds->H == M->cfg.H && 4 + 2 * ds->T * ds->V == M->cfg.ninput && ds->nout == M->O, DINCAE_EINVAL,
+               "%s: dataset (W=%d,H=%d,channels=%d,nout=%d) does not match the model", who, ds->W, ds->H, 4 + 2 * ds->T * ds->V, ds->nout);
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_train_step_gridded(dincae_model* M, dincae_gridded* ds, const int64_t* time_idx, const int64_t* imask, uint64_t seed,
+                                             uint64_t sample_ctr0, int32_t B, float lr, float* loss) {
+    DC_TRY(check_batch(M, B, "dincae_train_step_gridded"));
+    DC_TRY(check_dataset(M, ds, "dincae_train_step_gridded"));
+    DC_REQUIRE(time_idx != nullptr, DINCAE_EINVAL, "dincae_train_step_gridded: time_idx is NULL");
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    const AsmCall ac{ds, time_idx, imask, seed, sample_ctr0};
+    const int64_t t0 = M->t_step; const double b1 = M->bt1, b2 = M->bt2;
+    const AdamParams p = adam_params_next(M, lr);
+    int32_t st = grad_step_body_or_graph(M, M->in_xin, M->in_xtrue, B, true, &p, &ac);
+    if (st != DINCAE_OK) { M->t_step = t0; M->bt1 = b1; M->bt2 = b2; return st; }     // e.g. an index out of range: nothing was updated
+    M->wT_dirty = true;
+    if (loss) return read_loss(M, true, loss, nullptr);
+    return DINCAE_OK;
+}
+
+extern "C" int32_t dincae_train_step_dp_gridded(dincae_model* M, dincae_gridded* ds, const int64_t* time_idx, const int64_t* imask, uint64_t seed,
+                                                uint64_t sample_ctr0, int32_t B, const int64_t* n_valid_global, float lr, float* loss) {
+    DC_TRY(check_batch(M, B, "dincae_train_step_dp_gridded"));
+    DC_TRY(check_dataset(M, ds, "dincae_train_step_dp_gridded"));
+    DC_REQUIRE(time_idx != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: time_idx is NULL");
+    DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: no communicator (dincae_comm_init_rank)");
+    DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
+    DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
+    const AsmCall ac{ds, time_idx, imask, seed, sample_ctr0};
+    M->dp_overlap = dp_overlap_on();
+    int32_t st = gridded_counts(M, M->in_xtrue, B, n_valid_global);
+    if (st == DINCAE_OK) st = grad_step_body_or_graph(M, M->in_xin, M->in_xtrue, B, false, nullptr, &ac);
     const bool bucketed = M->dp_overlap;
     M->dp_overlap = false;
     DC_TRY(st);

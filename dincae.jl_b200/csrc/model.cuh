@@ -40,6 +40,8 @@ struct StepGraph {
     int B = 0;
     bool count_here = false;         // the step counts the valid targets itself (no global count handed in)
     bool apply = false;              // the optimiser update is part of the step (dincae_train_step / _slot)
+    const void* ds = nullptr;        // the step starts with the batch assembly from this dataset (dincae_train_step_gridded)
+    cudaGraphNode_t asm_node = nullptr;
     cudaGraph_t graph = nullptr;     // kept for the optimiser node, whose arguments are updated before every replay
     cudaGraphNode_t adam_node = nullptr;
     cudaGraphExec_t exec = nullptr;  // nullptr: the key has been seen once (that step ran launch by launch, which also did every lazy setup)

@@ -87,6 +87,8 @@ SIGNATURES = {
     "dincae_gridded_set_error": (i32, [vp, vp, i32]),
     "dincae_gridded_get_mean": (i32, [vp, vp]),
     "dincae_gridded_assemble": (i32, [vp, vp, vp, u64, u64, i32, vp, vp, i32]),
+    "dincae_train_step_gridded": (i32, [vp, vp, vp, vp, u64, u64, i32, f32, C.POINTER(f32)]),
+    "dincae_train_step_dp_gridded": (i32, [vp, vp, vp, vp, u64, u64, i32, vp, f32, C.POINTER(f32)]),
     "dincae_gridded_valid_counts": (i32, [vp, i32, vp]),
     "dincae_reconstruct_range": (i32, [vp, vp, i64, i64, i32, f32, vp, vp, i32]),
     "dincae_points_create": (i32, [vp, i32, i32, i64, vp, vp, vp, vp, i32, vp, vp, vp, vp, i32, f32, f32, pp]),

@@ -227,6 +227,15 @@ int32_t dincae_gridded_get_mean(dincae_gridded* ds, float* host_mean);   /* mean
 int32_t dincae_gridded_assemble(dincae_gridded* ds, const int64_t* time_idx, const int64_t* imask,
                                 uint64_t seed, uint64_t sample_ctr0, int32_t B,
                                 float* xin, float* xtrue, int32_t loc);
+/* One mini-batch of train_epoch! over DataBatches straight from the device-resident dataset (iterate, src/data.jl:831-868, then
+ * src/flux.jl:28-36): getxy! of the samples time_idx / imask (arguments as in dincae_gridded_assemble) into the model's own batch
+ * buffers, then dincae_train_step on them -- one captured CUDA graph whose sample indices, learning rate and Adam step are patched per
+ * call, so consecutive steps run back to back on the GPU.  Same results as dincae_gridded_assemble + dincae_train_step.
+ * The data-parallel form takes this rank's shard and the GLOBAL valid counts (dincae_train_step_dp). */
+int32_t dincae_train_step_gridded(dincae_model* m, dincae_gridded* ds, const int64_t* time_idx, const int64_t* imask, uint64_t seed,
+                                  uint64_t sample_ctr0, int32_t B, float lr, float* loss);
+int32_t dincae_train_step_dp_gridded(dincae_model* m, dincae_gridded* ds, const int64_t* time_idx, const int64_t* imask, uint64_t seed,
+                                     uint64_t sample_ctr0, int32_t B, const int64_t* n_valid_global, float lr, float* loss);
 /* valid-target count of every time step for output variable v (static; lets data-parallel ranks
  * know n_noncloud of the global batch without a collective) */
 int32_t dincae_gridded_valid_counts(dincae_gridded* ds, int32_t v, int64_t* host_counts);

@@ -522,3 +522,39 @@ def test_reconstruction_graph_replay_is_bit_identical(pkg, ctx):
         assert not np.array_equal(out[-1][0][:, :, 2:], out[-1][4])
     for x, y in zip(*out):
         assert np.array_equal(x, y)
+
+
+def test_train_step_gridded_equals_assemble_plus_train_step(pkg, ctx):
+    """dincae_train_step_gridded (assembly + step as one patched CUDA graph) == dincae_gridded_assemble + dincae_train_step, bit for
+    bit over eight steps with different samples, masks, jitter counters and learning rates; a bad index leaves the model untouched."""
+    import torch
+    rng = np.random.default_rng(21)
+    W, H, V, N, T, B = 28, 24, 1, 40, 3, 4
+    data = _cube(rng, W, H, V, N)
+    lon, lat, days = np.linspace(-7, -1, W), np.linspace(34, 38, H), 11000.0 + np.arange(N)
+    ds = pkg.GriddedDataset(ctx, lon, lat, days, data, train=True, ntime_win=T)
+    cfg = pkg.ModelConfig(W=W, H=H, ninput=10, enc_nfilter_internal=(16, 32), loss_weights_refine=(0.3, 0.7), regularization_L2_beta=1e-3,
+                          max_batch=B, precision="tf32")
+    dev = torch.device("cuda", ctx.device)
+    xin_d = torch.empty(B * 10 * W * H, dtype=torch.float32, device=dev); xt_d = torch.empty(B * 2 * W * H, dtype=torch.float32, device=dev)
+    draws = [(rng.integers(0, N, B), rng.integers(0, N, B)) for _ in range(8)]
+    a = pkg.Model(ctx, cfg, seed=3); b = pkg.Model(ctx, cfg, seed=3)
+    la, lb = [], []
+    for k, (idx, im) in enumerate(draws):
+        lr = 1e-3 * 0.9 ** k
+        ds.assemble(idx, im, seed=7, sample_ctr0=k * B, xin=xin_d, xtrue=xt_d)
+        la.append(a.train_step(xin_d, xt_d, lr, B=B, want_loss=True))
+        lb.append(b.train_step_gridded(ds, idx, im, lr, seed=7, sample_ctr0=k * B, want_loss=True))
+    assert b.step_graph() >= 1
+    assert np.array_equal(np.array(la), np.array(lb))
+    assert np.array_equal(a.get_params(), b.get_params())
+    w = b.get_params().copy()
+    with pytest.raises(pkg.lib.DincaeError):
+        b.train_step_gridded(ds, np.array([0, 1, N, 2]), None, 1e-3)
+    assert np.array_equal(b.get_params(), w)
+    # the step count was not advanced by the failed call: one more good step on both still agrees
+    idx, im = draws[0]
+    ds.assemble(idx, im, seed=7, sample_ctr0=99, xin=xin_d, xtrue=xt_d)
+    l1 = a.train_step(xin_d, xt_d, 1e-3, B=B, want_loss=True)
+    l2 = b.train_step_gridded(ds, idx, im, 1e-3, seed=7, sample_ctr0=99, want_loss=True)
+    assert l1 == l2 and np.array_equal(a.get_params(), b.get_params())
