@@ -11,8 +11,12 @@ namespace {
 // valid-pixel counts handed over BY VALUE (kernel parameter): no host->device copy of a stack variable, hence no stream
 // synchronisation in the data-parallel step
 struct NValidArg { unsigned long long v[16]; };
-__global__ void set_nvalid_kernel(NValidArg a, int nout, unsigned long long* __restrict__ n) {
-    if ((int)threadIdx.x < nout) n[threadIdx.x] = a.v[threadIdx.x];
+// the count handed in by the host and, when inv_n is given, its reciprocal in the same launch (see inv_n_kernel)
+__global__ void set_nvalid_kernel(NValidArg a, int nout, unsigned long long* __restrict__ n, float* __restrict__ inv_n = nullptr) {
+    if ((int)threadIdx.x < nout) {
+        n[threadIdx.x] = a.v[threadIdx.x];
+        if (inv_n) inv_n[threadIdx.x] = 1.0f / (float)a.v[threadIdx.x];
+    }
 }
 __global__ void inv_n_kernel(const unsigned long long* __restrict__ n, int nout, float* __restrict__ inv_n) {
     int v = threadIdx.x;
@@ -390,11 +394,11 @@ int32_t gridded_counts(dincae_model* M, const float* d_xtrue, int B, const int64
         NValidArg nv{};
         DC_REQUIRE(M->O <= 16, DINCAE_EUNSUPPORTED, "at most 16 output variables");
         for (int v = 0; v < M->O; v++) nv.v[v] = (unsigned long long)n_valid_global[v];
-        DC_LAUNCH(ctx, set_nvalid_kernel, 1, 32, 0, nv, M->O, M->d_nvalid);
+        DC_LAUNCH(ctx, set_nvalid_kernel, 1, 32, 0, nv, M->O, M->d_nvalid, M->d_inv_n);
         DC_CHECK_LAUNCH();
-    } else {
-        DC_TRY(k3_count_valid(ctx, d_xtrue, B, M->O, npix, M->d_nvalid));
+        return DINCAE_OK;
     }
+    DC_TRY(k3_count_valid(ctx, d_xtrue, B, M->O, npix, M->d_nvalid));
     DC_LAUNCH(ctx, inv_n_kernel, 1, 32, 0, M->d_nvalid, M->O, M->d_inv_n);
     DC_CHECK_LAUNCH();
     return DINCAE_OK;
