@@ -152,16 +152,21 @@ __global__ void __launch_bounds__(256) assemble_kernel(AsmArgs a) {
 
 }  // namespace
 
-// validates the indices of samples [b0, b0 + nb) and fills the kernel arguments of their launch
-static int32_t asm_fill(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
-                        int b0, int nb, float* d_xin, float* d_xtrue, AsmArgs& a) {
-    for (int b = b0; b < b0 + nb; b++) {
+int32_t k1_check_indices(const dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, int B) {
+    for (int b = 0; b < B; b++) {
         DC_REQUIRE(h_time_idx[b] >= 0 && h_time_idx[b] < ds->N, DINCAE_EINVAL, "assemble: time_idx[%d]=%lld out of [0,%lld)", b,
                    (long long)h_time_idx[b], (long long)ds->N);
         if (h_imask)
             DC_REQUIRE(h_imask[b] >= 0 && h_imask[b] < ds->N, DINCAE_EINVAL, "assemble: imask[%d]=%lld out of range", b, (long long)h_imask[b]);
     }
     DC_REQUIRE(ds->N < 0x7FFFFFFF, DINCAE_ESIZE, "assemble: more than 2^31 time steps");
+    return DINCAE_OK;
+}
+
+// validates the indices of samples [b0, b0 + nb) and fills the kernel arguments of their launch
+static int32_t asm_fill(dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, uint64_t seed, uint64_t ctr0,
+                        int b0, int nb, float* d_xin, float* d_xtrue, AsmArgs& a) {
+    DC_TRY(k1_check_indices(ds, h_time_idx + b0, h_imask ? h_imask + b0 : nullptr, nb));
     const size_t HW = (size_t)ds->W * ds->H;
     const int C = 4 + 2 * ds->T * ds->V;
     a.data = ds->d_data; a.err2 = ds->d_err2; a.lon = ds->d_lon; a.lat = ds->d_lat; a.tcos = ds->d_tcos; a.tsin = ds->d_tsin;

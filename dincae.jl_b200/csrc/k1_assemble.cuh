@@ -26,6 +26,7 @@ struct dincae_gridded {
 };
 
 // CUDA-graph support: the (single) assembly node of a captured step and the per-step update of its sample indices
+int32_t k1_check_indices(const dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask, int B);
 int k1_assemble_max_single_launch();
 cudaGraphNode_t k1_find_assemble_node(cudaGraph_t graph);
 int32_t k1_update_assemble_node(cudaGraphExec_t exec, cudaGraphNode_t node, dincae_gridded* ds, const int64_t* h_time_idx, const int64_t* h_imask,

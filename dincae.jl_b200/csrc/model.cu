@@ -1265,6 +1265,7 @@ extern "C" int32_t dincae_train_step_gridded(dincae_model* M, dincae_gridded* ds
     DC_TRY(check_batch(M, B, "dincae_train_step_gridded"));
     DC_TRY(check_dataset(M, ds, "dincae_train_step_gridded"));
     DC_REQUIRE(time_idx != nullptr, DINCAE_EINVAL, "dincae_train_step_gridded: time_idx is NULL");
+    DC_TRY(k1_check_indices(ds, time_idx, imask, B));        // a caller's bad index must not look like a failed capture
     DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
     const AsmCall ac{ds, time_idx, imask, seed, sample_ctr0};
     const int64_t t0 = M->t_step; const double b1 = M->bt1, b2 = M->bt2;
@@ -1283,6 +1284,7 @@ extern "C" int32_t dincae_train_step_dp_gridded(dincae_model* M, dincae_gridded*
     DC_REQUIRE(time_idx != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: time_idx is NULL");
     DC_REQUIRE(M->ctx->comm != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: no communicator (dincae_comm_init_rank)");
     DC_REQUIRE(n_valid_global != nullptr, DINCAE_EINVAL, "dincae_train_step_dp_gridded: n_valid_global is NULL (the gradient sums must be normalised by the GLOBAL count)");
+    DC_TRY(k1_check_indices(ds, time_idx, imask, B));
     DC_CHECK_CUDA(cudaSetDevice(M->ctx->device));
     const AsmCall ac{ds, time_idx, imask, seed, sample_ctr0};
     M->dp_overlap = dp_overlap_on();
