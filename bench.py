@@ -7,7 +7,8 @@
 Headline workload (BASELINE.json configs[1]): tutorial SST gap-filling model, 112x112 grid, ntime_win=3 (10 input channels),
 enc_nfilter_internal=32*2^(0:3), refinement stage loss_weights_refine=(0.3,0.7), regularization_L2_beta=1e-3,
 batch 32 per GPU, synthetic cloud-masked SST cube resident in HBM.  One "step" = one training mini-batch:
-batch assembly (K1) -> forward (K2) -> head+loss (K3) -> backward (K2) -> [all-reduce, inside the library] -> L2+clip+Adam (K3).
+batch assembly (K1) -> forward (K2) -> head+loss (K3) -> backward (K2) -> [all-reduce, inside the library] -> L2+clip+Adam (K3),
+issued as ONE library call (dincae_train_step_gridded / _dp_gridded) that replays the step as a CUDA graph.
 metric = training samples/s (whole job); `value` = median of REPEATS timed blocks of exactly K steps each.
 Beside the headline the line carries: `e2e` (host buffers through the C-ABI), `rooflines` (every kernel >= 3 % of the step
 against the measured HBM / TF32 tensor roofs), `recon` (Mpixel/s), `configs` (short runs of the other BASELINE configs:
