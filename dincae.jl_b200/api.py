@@ -664,6 +664,13 @@ def learning_rate(lr0, epoch, decay_epoch):
 def train_epoch(model: Model, batches, lr):
     """train_epoch! (src/flux.jl:24-40): mean of the per-batch losses, partial batch included (T17)."""
     loss_sum, n = 0.0, 0
+    if isinstance(batches, DataBatches) and batches.device_buffers is not None and batches.world_size == 1 and batches.ds.ctx is model.ctx:
+        # device-resident dataset: assembly + step of every mini-batch in one library call (one CUDA graph per step);
+        # bit-identical to assembling into the device buffers and calling train_step on them
+        for idx, imask, ctr in batches.batches():
+            loss_sum += model.train_step_gridded(batches.ds, idx, imask, lr, seed=batches.seed, sample_ctr0=ctr)
+            n += 1
+        return loss_sum / n
     for xin, xtrue, B in batches:
         loss_sum += model.train_step(xin, xtrue, lr, B=B)
         n += 1
